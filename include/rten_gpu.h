@@ -1,0 +1,188 @@
+/* rten_gpu.h — C ABI of librten_gpu.so, the B200 (sm_100a) replacement for RTen's dense-compute hot path.
+ *
+ * This is exactly the surface a Rust `rten-gpu-sys` FFI crate would bind.  Every entry point
+ * cites the reference interface it replaces as  path:line  relative to the RTen 0.12.0 tree.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ / torch types cross this boundary.
+ *   - every function returns rtg_status.  0 = ok; 1..6 mirror the six OpError variants of the reference
+ *     (src/ops/mod.rs:665-705) and rtg_last_error() returns the same static message string the reference uses;
+ *     RTG_ERR_PANIC marks conditions where the reference panics (src/gemm.rs:743-750,773).
+ *   - tensors are (pointer, dtype, shape, element strides) views like the reference's `Input` views
+ *     (src/ops/mod.rs:177-180); `device` says where `data` lives: RTG_HOST (-1) or a CUDA device ordinal.  Host
+ *     tensors are staged through pinned memory inside the call; device tensors are used in place.
+ *   - there is NO CPU fallback: a call fails with RTG_ERR_CUDA if no sm_100 device is usable.
+ */
+#ifndef RTEN_GPU_H_
+#define RTEN_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t rtg_status;
+enum {
+  RTG_OK = 0,
+  RTG_ERR_INCORRECT_INPUT_TYPE = 1,      /* OpError::IncorrectInputType      src/ops/mod.rs:667 */
+  RTG_ERR_INCORRECT_OUTPUT_TYPE = 2,     /* OpError::IncorrectOutputType     src/ops/mod.rs:671 */
+  RTG_ERR_INCOMPATIBLE_INPUT_SHAPES = 3, /* OpError::IncompatibleInputShapes src/ops/mod.rs:675 */
+  RTG_ERR_MISSING_INPUTS = 4,            /* OpError::MissingInputs           src/ops/mod.rs:678 */
+  RTG_ERR_INVALID_VALUE = 5,             /* OpError::InvalidValue            src/ops/mod.rs:682 */
+  RTG_ERR_UNSUPPORTED_VALUE = 6,         /* OpError::UnsupportedValue        src/ops/mod.rs:685 */
+  RTG_ERR_PANIC = 50,                    /* the reference would panic (assert!) here */
+  RTG_ERR_CUDA = 100,
+  RTG_ERR_NCCL = 101,
+  RTG_ERR_INTERNAL = 102,
+  RTG_ERR_FORMAT = 103                   /* malformed .rten file: ModelLoadError, src/model.rs:60-110 */
+};
+
+/* Thread-local message of the last failing call on this thread (never NULL). */
+const char* rtg_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------ tensors */
+enum { RTG_F32 = 0, RTG_I32 = 1 };       /* the reference's only two element types, src/ops/mod.rs:168-180 */
+enum { RTG_HOST = -1 };
+#define RTG_MAX_DIMS 8
+
+typedef struct rtg_tensor {
+  void* data;
+  int32_t dtype;
+  int32_t ndim;
+  int64_t shape[RTG_MAX_DIMS];
+  int64_t strides[RTG_MAX_DIMS]; /* in elements; may describe transposed / NHWC views */
+  int32_t device;                /* RTG_HOST or CUDA ordinal */
+} rtg_tensor;
+
+/* ------------------------------------------------------------------------------------------------ context */
+/* One context per (GPU, host thread): owns a stream, the device TensorPool (src/tensor_pool.rs:103-199) and the
+ * cache of device-resident, pre-arranged weights (the role of prepack_a/prepack_b, src/gemm.rs:337-438). */
+typedef struct rtg_ctx rtg_ctx;
+
+enum { RTG_MATH_TF32 = 0, RTG_MATH_3XTF32 = 1 };
+
+rtg_status rtg_ctx_create(int32_t device, rtg_ctx** out);
+rtg_status rtg_ctx_destroy(rtg_ctx* ctx);
+/* Use an externally owned cudaStream_t (e.g. torch's current stream) instead of the context's own. */
+rtg_status rtg_ctx_set_stream(rtg_ctx* ctx, void* cuda_stream);
+/* RTG_MATH_3XTF32 (default): results within rtol 1e-5 of the reference.  RTG_MATH_TF32: rtol 2e-3. */
+rtg_status rtg_ctx_set_math(rtg_ctx* ctx, int32_t mode);
+rtg_status rtg_ctx_get_math(rtg_ctx* ctx, int32_t* mode);
+rtg_status rtg_ctx_sync(rtg_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+rtg_status rtg_ctx_launch_count(rtg_ctx* ctx, uint64_t* count);
+/* Name of the GEMM kernel variant chosen by the last contraction call (diagnostics / tests). */
+const char* rtg_ctx_last_kernel(rtg_ctx* ctx);
+
+/* TensorPool::alloc / add / alloc_count / hit_count / len      src/tensor_pool.rs:129-192 */
+rtg_status rtg_pool_alloc(rtg_ctx* ctx, size_t bytes, void** dptr);
+rtg_status rtg_pool_free(rtg_ctx* ctx, void* dptr);
+rtg_status rtg_pool_stats(rtg_ctx* ctx, uint64_t* alloc_count, uint64_t* hit_count, uint64_t* len);
+rtg_status rtg_upload(rtg_ctx* ctx, void* dst_device, const void* src_host, size_t bytes);
+rtg_status rtg_download(rtg_ctx* ctx, void* dst_host, const void* src_device, size_t bytes);
+
+/* ------------------------------------------------------------------------------------------------ GemmExecutor */
+/* GemmExecutor::gemm / gemm_bias / gemm_uninit_bias                src/gemm.rs:448-542
+ *   out[m*out_row_stride + n] = alpha * sum_k a[m,k]*b[k,n] + beta * out[..] + bias[m]
+ * a is [m,k] with element strides (a_rs, a_cs); b is [k,n] with (b_rs, b_cs).  bias has length m or is NULL.
+ * beta == 0 never reads `out` (it may hold NaN; src/gemm.rs:1349-1387).  k == 0 gives out = beta*out (:757-765).
+ * `device` is RTG_HOST or the ordinal all pointers live on.  out_len is the length of `out` in elements; a short
+ * output is RTG_ERR_PANIC "Output buffer should be large enough" (src/gemm.rs:1167-1183). */
+rtg_status rtg_gemm(rtg_ctx* ctx, int32_t device, float* out, size_t out_len, size_t out_row_stride, const float* a,
+                    size_t m, size_t k, ptrdiff_t a_rs, ptrdiff_t a_cs, const float* b, size_t b_rows, size_t n,
+                    ptrdiff_t b_rs, ptrdiff_t b_cs, float alpha, float beta, const float* bias, size_t bias_len);
+
+/* ------------------------------------------------------------------------------------------------ operators */
+enum { RTG_PAD_FIXED = 0, RTG_PAD_SAME = 1 }; /* Padding::{Fixed,Same}  src/ops/mod.rs:127-166 */
+enum {
+  RTG_ACT_NONE = 0, RTG_ACT_RELU = 1, RTG_ACT_CLIP = 2, RTG_ACT_GELU = 3, RTG_ACT_SIGMOID = 4, RTG_ACT_SILU = 5,
+  RTG_ACT_ERF = 6
+};
+
+typedef struct rtg_conv_attrs {   /* struct Conv {groups, dilations, padding, strides}  src/ops/conv.rs:282-293 */
+  int32_t groups;
+  int32_t pad_mode;               /* RTG_PAD_FIXED | RTG_PAD_SAME */
+  int64_t pads[4];                /* [top, left, bottom, right]  (1-D conv: [left, right]) */
+  int32_t n_pads;
+  int64_t strides[2];
+  int32_t n_strides;
+  int64_t dilations[2];
+  int32_t n_dilations;
+} rtg_conv_attrs;
+
+/* calc_output_size_and_padding + conv() shape checks             src/ops/pooling.rs:27-89, src/ops/conv.rs:86-197
+ * Writes the output shape ([N,O,Oh,Ow], or [N,O,Ow] for 3-D input). */
+rtg_status rtg_conv_out_shape(const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias_or_null,
+                              const rtg_conv_attrs* attrs, int64_t* out_shape, int32_t* out_ndim);
+/* Conv::run / conv()                                             src/ops/conv.rs:86-311
+ * input NCHW (any strides; NHWC-strided views are consumed without a copy), weight [O, C/groups, Kh, Kw], bias [O].
+ * `residual` (same shape as output, or NULL) and `act` are the fused epilogue: out = act(conv + bias + residual).
+ * With residual == NULL and act == RTG_ACT_NONE this is exactly the reference operator. */
+rtg_status rtg_conv(rtg_ctx* ctx, const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias_or_null,
+                    const rtg_conv_attrs* attrs, const rtg_tensor* residual_or_null, int32_t act, float act_lo,
+                    float act_hi, rtg_tensor* output);
+
+/* matmul() / MatMul::run                                          src/ops/matmul.rs:119-254 */
+rtg_status rtg_matmul_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* out_shape, int32_t* out_ndim);
+rtg_status rtg_matmul(rtg_ctx* ctx, const rtg_tensor* a, const rtg_tensor* b, rtg_tensor* output);
+/* gemm_op() / Gemm::run  (ONNX Gemm: alpha*A'B' + beta*C)          src/ops/matmul.rs:27-81 */
+rtg_status rtg_gemm_op(rtg_ctx* ctx, const rtg_tensor* a, const rtg_tensor* b, const rtg_tensor* c_or_null,
+                       float alpha, float beta, int32_t transpose_a, int32_t transpose_b, rtg_tensor* output);
+
+/* UnaryFloatOp::{run,run_in_place} for Relu/Clip/Gelu/Sigmoid/Silu/Erf   src/ops/unary_elementwise.rs:22-63
+ * In place when output->data == input->data. */
+rtg_status rtg_unary(rtg_ctx* ctx, int32_t act, const rtg_tensor* input, float lo, float hi, rtg_tensor* output);
+enum { RTG_BIN_ADD = 0, RTG_BIN_SUB = 1, RTG_BIN_MUL = 2, RTG_BIN_DIV = 3 };
+/* binary_op / binary_op_in_place with numpy broadcasting          src/ops/binary_elementwise.rs:65-157,261-322 */
+rtg_status rtg_binary_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* out_shape, int32_t* out_ndim);
+rtg_status rtg_binary(rtg_ctx* ctx, int32_t op, const rtg_tensor* a, const rtg_tensor* b, rtg_tensor* output);
+
+/* MaxPool / AveragePool / GlobalAveragePool                        src/ops/pooling.rs:91-420 */
+typedef struct rtg_pool_attrs {
+  int64_t kernel[2];
+  int64_t strides[2];
+  int32_t pad_mode;
+  int64_t pads[4];
+  int32_t count_include_pad;
+} rtg_pool_attrs;
+enum { RTG_POOL_MAX = 0, RTG_POOL_AVG = 1 };
+rtg_status rtg_pool2d_out_shape(const rtg_tensor* input, const rtg_pool_attrs* attrs, int64_t* out_shape);
+rtg_status rtg_pool2d(rtg_ctx* ctx, int32_t kind, const rtg_tensor* input, const rtg_pool_attrs* attrs,
+                      rtg_tensor* output);
+rtg_status rtg_global_average_pool(rtg_ctx* ctx, const rtg_tensor* input, rtg_tensor* output);
+
+/* ------------------------------------------------------------------------------------------------ Model / Graph */
+/* Model::load / load_file, Model::run, Graph::run                  src/model.rs:214-309,580-646; src/graph.rs:733-1073
+ * A `.rten` file (V1 or V2 container, src/header.rs:60-80, src/schema.fbs) is parsed by a hand-written FlatBuffers
+ * reader; operators are instantiated through the op registry (src/op_registry.rs:36-62) and executed on the GPU. */
+typedef struct rtg_model rtg_model;
+rtg_status rtg_model_load_file(rtg_ctx* ctx, const char* path, int32_t optimize, rtg_model** out);
+rtg_status rtg_model_load(rtg_ctx* ctx, const void* data, size_t len, int32_t optimize, rtg_model** out);
+rtg_status rtg_model_free(rtg_model* model);
+rtg_status rtg_model_num_inputs(const rtg_model* model, int32_t* n);
+rtg_status rtg_model_num_outputs(const rtg_model* model, int32_t* n);
+/* Name and (possibly symbolic: -1) shape of the i-th graph input / output:  Model::input_ids / node_info */
+rtg_status rtg_model_input_info(const rtg_model* model, int32_t i, const char** name, int64_t* shape, int32_t* ndim,
+                                int32_t* dtype);
+rtg_status rtg_model_output_info(const rtg_model* model, int32_t i, const char** name, int64_t* shape, int32_t* ndim,
+                                 int32_t* dtype);
+rtg_status rtg_model_num_ops(const rtg_model* model, int32_t* n);
+
+/* Run handle: the outputs of one Model::run.  Shapes are known after the run; copy out with rtg_run_output_copy. */
+typedef struct rtg_run rtg_run;
+rtg_status rtg_model_run(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_run** out);
+rtg_status rtg_run_num_outputs(const rtg_run* run, int32_t* n);
+rtg_status rtg_run_output_info(const rtg_run* run, int32_t i, int64_t* shape, int32_t* ndim, int32_t* dtype);
+/* Copies output i (contiguous, reference layout) to `dst` on `device` (RTG_HOST or ordinal). */
+rtg_status rtg_run_output_copy(rtg_run* run, int32_t i, void* dst, size_t dst_bytes, int32_t device);
+rtg_status rtg_run_free(rtg_run* run);
+/* RunOptions{timing}: per-operator device time of the last run as text   src/graph.rs:467-483, src/timing.rs */
+rtg_status rtg_model_set_timing(rtg_model* model, int32_t enabled);
+const char* rtg_model_timing_report(rtg_model* model);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTEN_GPU_H_ */

@@ -1,0 +1,8 @@
+"""rten_fork_b200 — B200 (sm_100a) implementation of RTen's dense-compute hot path behind the reference's operator API.
+
+The compute lives in ``librten_gpu.so`` (hand-written CUDA, C ABI in ``include/rten_gpu.h``); this package is the
+host-side mirror of the reference interface for that path.  There is no CPU fallback.
+"""
+from ._native import MATH_3XTF32, MATH_TF32, RtgError  # noqa: F401
+from .context import Context, default_context  # noqa: F401
+from .gemm import GemmExecutor, gemm  # noqa: F401

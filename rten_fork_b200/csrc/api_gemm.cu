@@ -1,0 +1,85 @@
+// C ABI: rtg_gemm — the GemmExecutor entry point (reference: src/gemm.rs:448-542, 733-765).
+#include "gemm_host.h"
+
+using namespace rtg;
+
+namespace rtg {
+
+// Elements spanned by a [rows, cols] view with the given strides.
+static size_t span_elems(size_t rows, size_t cols, ptrdiff_t rs, ptrdiff_t cs) {
+  if (rows == 0 || cols == 0) return 0;
+  return (rows - 1) * static_cast<size_t>(rs) + (cols - 1) * static_cast<size_t>(cs) + 1;
+}
+
+}  // namespace rtg
+
+extern "C" rtg_status rtg_gemm(rtg_ctx* ctx_, int32_t device, float* out, size_t out_len, size_t out_row_stride,
+                               const float* a, size_t m, size_t k, ptrdiff_t a_rs, ptrdiff_t a_cs, const float* b,
+                               size_t b_rows, size_t n, ptrdiff_t b_rs, ptrdiff_t b_cs, float alpha, float beta,
+                               const float* bias, size_t bias_len) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
+  // The reference asserts these (src/gemm.rs:743-750); a panic becomes a status code.
+  if (k != b_rows) return set_error(RTG_ERR_PANIC, "Columns of matrix `a` must match rows of matrix `b`");
+  if (bias && bias_len != m) return set_error(RTG_ERR_PANIC, "Bias vector length must match rows of matrix `a`");
+  if (a_rs < 0 || a_cs < 0 || b_rs < 0 || b_cs < 0) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "negative strides");
+  if (m == 0 || n == 0) return RTG_OK;  // src/gemm.rs:753-755
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  const bool host = device == RTG_HOST;
+  if (!host && device != ctx->device) return set_error(RTG_ERR_INVALID_VALUE, "tensor device does not match context");
+
+  if (k == 0) {
+    // src/gemm.rs:757-765: the whole output slice becomes beta * out (0 when beta == 0); bias is not applied.
+    if (host) {
+      for (size_t i = 0; i < out_len; ++i) out[i] = beta == 0.f ? 0.f : beta * out[i];
+      return RTG_OK;
+    }
+    return scale_buffer(ctx, out, out_len, beta);
+  }
+  if (out_row_stride < n || (m - 1) * out_row_stride + n > out_len)
+    return set_error(RTG_ERR_PANIC, "Output buffer should be large enough");
+
+  Scratch da, db, dout, dbias;
+  const float *pa = a, *pb = b, *pbias = bias;
+  float* pout = out;
+  const size_t out_span = (m - 1) * out_row_stride + n;
+  if (host) {
+    const size_t na = span_elems(m, k, a_rs, a_cs), nb = span_elems(k, n, b_rs, b_cs);
+    RTG_TRY(da.alloc(ctx, na * 4));
+    RTG_TRY(db.alloc(ctx, nb * 4));
+    RTG_TRY(dout.alloc(ctx, out_span * 4));
+    RTG_CUDA(cudaMemcpyAsync(da.p, a, na * 4, cudaMemcpyHostToDevice, ctx->stream));
+    RTG_CUDA(cudaMemcpyAsync(db.p, b, nb * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (beta != 0.f) RTG_CUDA(cudaMemcpyAsync(dout.p, out, out_span * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (bias) {
+      RTG_TRY(dbias.alloc(ctx, m * 4));
+      RTG_CUDA(cudaMemcpyAsync(dbias.p, bias, m * 4, cudaMemcpyHostToDevice, ctx->stream));
+      pbias = dbias.f32();
+    }
+    pa = da.f32();
+    pb = db.f32();
+    pout = dout.f32();
+  }
+
+  Epilogue ep;
+  ep.alpha = alpha;
+  ep.beta = beta;
+  ep.bias = pbias;
+  ep.bias_mode = BIAS_ROW;
+  ep.R = beta != 0.f ? pout : nullptr;
+  OutMap om = {static_cast<int64_t>(out_row_stride), 0, 0, 0};
+  ep.rmap = om;
+  RTG_TRY(gemm_device(ctx, MatView{pa, (int64_t)m, (int64_t)k, a_rs, a_cs}, MatView{pb, (int64_t)k, (int64_t)n, b_rs, b_cs},
+                      pout, om, ep));
+  if (host) {
+    if (out_row_stride == n) {
+      RTG_CUDA(cudaMemcpyAsync(out, pout, out_span * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+      // only the [m, n] window belongs to the result; the gaps between rows stay untouched
+      RTG_CUDA(cudaMemcpy2DAsync(out, out_row_stride * 4, pout, out_row_stride * 4, n * 4, m, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+    }
+    RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
+  return RTG_OK;
+}

@@ -1,0 +1,44 @@
+// Internal (device-pointer) entry points of the contraction engine.
+#pragma once
+#include "gemm_sm100.cuh"
+#include "runtime.h"
+
+namespace rtg {
+
+struct MatView {      // [rows, cols] f32 matrix view on the device, element strides
+  const float* p;
+  int64_t rows, cols, rs, cs;
+};
+
+struct Epilogue {
+  float alpha = 1.f, beta = 0.f;
+  const float* bias = nullptr;
+  int bias_mode = BIAS_NONE;
+  const float* R = nullptr;   // residual / beta source
+  OutMap rmap = {0, 0, 0, 0};
+  int act = ACT_NONE;
+  float act_lo = 0.f, act_hi = 0.f;
+};
+
+// D = epilogue(A[M,K] . B[K,N]).  A and B may have any strides; operands that TMA cannot address directly (neither
+// dimension contiguous, unaligned base or pitch) are first gathered into pool scratch by a copy kernel.
+rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap, const Epilogue& ep);
+
+// Implicit-GEMM convolution over an NHWC activation tensor using TMA im2col loads.
+struct ConvGeom {
+  int n, h, w, c_total;        // input tensor [n, h, w, c_total] NHWC dense
+  int c_off, cg;               // channel slice of this group
+  int kh, kw, oh, ow;
+  int stride_h, stride_w, pad_t, pad_l, pad_b, pad_r, dil_h, dil_w;
+};
+// wmat: [Og][kh*kw*c_blocks*32] K-major weight matrix for this group (zero padded per tap), Og output channels.
+rtg_status conv_gemm_device(Context* ctx, const float* x_nhwc, const ConvGeom& g, const float* wmat, int og,
+                            float* D, OutMap dmap, const Epilogue& ep);
+bool conv_im2col_supported(const ConvGeom& g);
+
+// dst[r*dst_ld + c] = src[r*rs + c*cs]
+rtg_status copy_strided_2d(Context* ctx, float* dst, int64_t dst_ld, const float* src, int64_t rows, int64_t cols,
+                           int64_t rs, int64_t cs);
+rtg_status scale_buffer(Context* ctx, float* p, size_t n, float beta);
+
+}  // namespace rtg

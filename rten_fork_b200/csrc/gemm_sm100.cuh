@@ -1,0 +1,418 @@
+// Warp-specialised, persistent, TMA-fed tcgen05 GEMM for sm_100a.
+//
+//   D[M,N] = act( alpha * A[M,K] . B[K,N]  + beta * R[M,N] + bias )
+//
+// Replaces the reference's BLIS-style loop nest + SIMD micro-kernel
+// (reference: src/gemm.rs:733-1050 gemm_impl/gemm_block, src/gemm/kernels.rs:206-316 simd_gemm).  The A/B packing
+// step of the reference (src/gemm/packing.rs:20-186) has no equivalent here: TMA writes 128B-swizzled K-major (or
+// MN-major) tiles straight into shared memory in the layout the tensor core's matrix descriptors read.
+//
+// Roles (one CTA per SM, 128 x BN output tile per step, BK = 32 floats = one 128-byte swizzle row):
+//   warps 0..E-1  epilogue       (tcgen05.ld -> alpha/beta/bias/activation -> global stores; warp w may only read
+//                                 TMEM lanes 32(w%4)..+31, so these are the first warps; E = 4, or 8 in MODE 1
+//                                 where warps 4-7 take the upper half of the tile's columns)
+//   warp E        TMA producer   (tiled 2-D loads, or im2col-mode loads over an NHWC activation tensor)
+//   warp E+1      MMA issuer     (one thread: tcgen05.mma.kind::tf32, accumulators in TMEM, double-buffered)
+//                                 + TMEM allocation
+//   warps E+2..   3xTF32 split   (MODE 1 only, 6 warps: write lo = x - tf32(x) planes next to the raw tiles)
+//
+// MODE 0 (TF32):   one MMA per k-step on the raw fp32 bits (the tensor core keeps the top 19 bits).
+// MODE 1 (3xTF32): hi = raw (the tensor core truncates to the top 19 bits itself; verified on B200),
+//                  lo = rna_tf32(x - trunc19(x));
+//                  acc += lo_A*hi_B + hi_A*lo_B + hi_A*hi_B.
+//   The tensor core adds into the TMEM accumulator with truncation, which for long K drifts past the reference's
+//   1e-5 tolerance (measured 2.3e-5 at K=1024).  MODE 1 therefore accumulates in TMEM only over chunks of
+//   kChunkKb k-blocks; the epilogue warps drain each chunk and keep the running sum in registers with
+//   round-to-nearest adds (the same two-level scheme the reference gets from its kc=256 depth blocks, src/gemm.rs:546).
+#pragma once
+#include "sm100_ptx.cuh"
+#include "vecmath.cuh"
+
+namespace rtg {
+
+enum BiasMode : int { BIAS_NONE = 0, BIAS_ROW = 1, BIAS_COL = 2 };
+
+// Where output element (m, n) lives:  base(m) + n * col_stride, with
+//   row-major   : base = m * ld,                                             col_stride = 1
+//   NCHW pixels : base = ((m / hw) * chan_total + chan_off) * hw + (m % hw),  col_stride = hw   (m = image*hw + pixel)
+struct OutMap {
+  int64_t ld;          // row stride (row-major mode)
+  int32_t hw;          // 0 => row-major, >0 => NCHW with hw pixels per image
+  int32_t chan_total;  // NCHW: channels of the destination tensor (>= N when writing a group slice)
+  int32_t chan_off;    // NCHW / NHWC: first channel (column) written by this launch
+};
+
+struct Im2colArgs {  // A operand produced by TMA im2col over NHWC input (A_KIND 1)
+  int32_t ow, oh;    // output spatial size
+  int32_t stride_w, stride_h;
+  int32_t pad_l, pad_t;
+  int32_t dil_w, dil_h;
+  int32_t kw, kh;
+  int32_t c_blocks;  // ceil(C / 32): k-blocks per filter tap
+  int32_t c_off;     // first channel of this group
+};
+
+struct GemmArgs {
+  int32_t M, N, K;
+  int32_t num_kb;  // k-blocks of 32
+  float alpha, beta;
+  const float* bias;
+  int32_t bias_mode;
+  const float* R;  // residual / beta source, addressed through `rmap`
+  float* D;
+  OutMap dmap, rmap;
+  int32_t act;
+  float act_lo, act_hi;
+  int32_t flags;   // bit 0: (debug) MODE 1 also overwrites the raw operand tile with its hi part
+  Im2colArgs ic;
+};
+
+constexpr int kBM = 128;
+constexpr int kBK = 32;  // floats per k-block (128 bytes)
+constexpr int kABytes = kBM * kBK * 4;
+constexpr int kChunkKb = 4;  // MODE 1: k-blocks accumulated in TMEM before the epilogue folds them (K = 128)
+
+template <int BN, int MODE>
+struct GemmCfg {
+  static_assert(MODE == 0 || BN <= 128, "3xTF32 keeps BN/2 running sums per epilogue thread in registers");
+  static constexpr int kBBytes = BN * kBK * 4;
+  static constexpr int kRawBytes = kABytes + kBBytes;
+  static constexpr int kStageBytes = kRawBytes * (MODE ? 2 : 1);
+  static constexpr int kMaxSmem = 227 * 1024 - 2048;  // barriers + alignment slack
+  static constexpr int kStagesRaw = kMaxSmem / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 512 /*barriers*/;
+  // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
+  // and 6 split warps so that the operand split keeps up with the tensor core.
+  static constexpr int kEpiWarps = MODE ? 8 : 4;
+  static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
+  static constexpr int kXfThreads = MODE ? 192 : 0;
+  static constexpr int kThreads = (kEpiWarps + 2) * 32 + kXfThreads;
+  static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+};
+
+__device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& base, int64_t& cs) {
+  if (om.hw > 0) {
+    const int img = m / om.hw;
+    base = (static_cast<int64_t>(img) * om.chan_total + om.chan_off) * om.hw + (m - img * om.hw);
+    cs = om.hw;
+  } else {
+    base = static_cast<int64_t>(m) * om.ld + om.chan_off;
+    cs = 1;
+  }
+}
+
+template <int BN, int MODE, int A_KIND, int B_MAJOR>
+__global__ void __launch_bounds__(GemmCfg<BN, MODE>::kThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmArgs args) {
+  using Cfg = GemmCfg<BN, MODE>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr bool kChunked = MODE == 1;
+  constexpr int kTmaWarp = Cfg::kEpiWarps, kMmaWarp = Cfg::kEpiWarps + 1;
+  extern __shared__ uint8_t smem_raw[];
+  // 128B swizzle atoms need 1024-byte aligned tiles.
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto xf_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (3 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (3 * kStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (3 * kStages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_tiles = (args.M + kBM - 1) / kBM;
+  const int n_tiles = (args.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int num_kb = args.num_kb;
+  const int chunk_kb = kChunked ? kChunkKb : num_kb;  // k-blocks per TMEM accumulation chunk
+
+  if (warp == kTmaWarp && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), 1);
+      ptx::mbar_init(xf_bar(s), Cfg::kXfThreads);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(tfull_bar(a), 1);
+      ptx::mbar_init(tempty_bar(a), Cfg::kEpiWarps * 32);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == kMmaWarp) {
+    ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == kTmaWarp) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_tiles) * kBM;
+        const int n0 = (tile % n_tiles) * BN;
+        int pix_w = 0, pix_h = 0, pix_n = 0;
+        if (A_KIND == 1) {
+          const int ohw = args.ic.oh * args.ic.ow;
+          pix_n = m0 / ohw;
+          const int r = m0 - pix_n * ohw;
+          const int oy = r / args.ic.ow;
+          const int ox = r - oy * args.ic.ow;
+          pix_w = ox * args.ic.stride_w - args.ic.pad_l;
+          pix_h = oy * args.ic.stride_h - args.ic.pad_t;
+        }
+        int tap_x = 0, tap_y = 0, cb = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+          const uint32_t a_dst = smem_base + s * Cfg::kStageBytes;
+          const uint32_t b_dst = a_dst + kABytes;
+          ptx::mbar_expect_tx(full_bar(s), Cfg::kRawBytes);
+          if (A_KIND == 0) {
+            ptx::tma_load_2d(a_dst, &tmA, full_bar(s), kb * kBK, m0);
+          } else {
+            ptx::tma_load_im2col_4d(a_dst, &tmA, full_bar(s), args.ic.c_off + cb * kBK, pix_w, pix_h, pix_n,
+                                    static_cast<uint16_t>(tap_x * args.ic.dil_w),
+                                    static_cast<uint16_t>(tap_y * args.ic.dil_h));
+            if (++cb == args.ic.c_blocks) {
+              cb = 0;
+              if (++tap_x == args.ic.kw) {
+                tap_x = 0;
+                ++tap_y;
+              }
+            }
+          }
+          if (B_MAJOR == 0) {
+            // B stored [N][K] (K contiguous): one box of BN rows x 128 bytes
+            ptx::tma_load_2d(b_dst, &tmB, full_bar(s), kb * kBK, n0);
+          } else {
+            // B stored [K][N] (N contiguous): BN/32 boxes of 32 k-rows x 128 bytes, 4 KB apart
+#pragma unroll
+            for (int c = 0; c < BN / 32; ++c)
+              ptx::tma_load_2d(b_dst + c * 4096, &tmB, full_bar(s), n0 + c * 32, kb * kBK);
+          }
+          if (++s == kStages) {
+            s = 0;
+            ph ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == kMmaWarp) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_tf32(kBM, BN, 0, B_MAJOR);
+      // K-major operands: 128B swizzle, 8-row groups 1024 B apart.  MN-major fp32 operands must use the
+      // 128B-swizzle-with-32B-atoms layout: 4 k-rows (512 B) per atom, 32-column chunks 4096 B apart.
+      constexpr uint32_t b_layout = B_MAJOR ? ptx::kSwizzle128Base32 : ptx::kSwizzle128;
+      constexpr uint32_t b_lbo = B_MAJOR ? 4096 : 16;
+      constexpr uint32_t b_sbo = B_MAJOR ? 512 : 1024;
+      int s = 0;
+      uint32_t ph = 0;
+      int as = 0;
+      uint32_t aph = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
+          ptx::mbar_wait(tempty_bar(as), aph ^ 1u);
+          ptx::tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * BN;
+          const int kb1 = min(num_kb, kb0 + chunk_kb);
+          for (int kb = kb0; kb < kb1; ++kb) {
+            ptx::mbar_wait(MODE ? xf_bar(s) : full_bar(s), ph);
+            ptx::tc_fence_after();
+            const uint32_t a_raw = smem_base + s * Cfg::kStageBytes;
+            const uint32_t b_raw = a_raw + kABytes;
+            const uint32_t a_lo = a_raw + Cfg::kRawBytes;
+            const uint32_t b_lo = b_raw + Cfg::kRawBytes;
+#pragma unroll
+            for (int k = 0; k < kBK / 8; ++k) {
+              // K-major: 8 floats = 32 bytes further along the swizzled 128-byte row.
+              // MN-major: 8 k-rows = 1024 bytes further.
+              const uint32_t a_off = k * 32;
+              const uint32_t b_off = B_MAJOR ? k * 1024 : k * 32;
+              const uint64_t da = ptx::make_smem_desc(a_raw + a_off, 16, 1024);
+              const uint64_t db = ptx::make_smem_desc(b_raw + b_off, b_lbo, b_sbo, b_layout);
+              const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
+              if (MODE == 0) {
+                ptx::mma_tf32_ss(d_tmem, da, db, idesc, acc);
+              } else {
+                const uint64_t dal = ptx::make_smem_desc(a_lo + a_off, 16, 1024);
+                const uint64_t dbl = ptx::make_smem_desc(b_lo + b_off, b_lbo, b_sbo, b_layout);
+                ptx::mma_tf32_ss(d_tmem, dal, db, idesc, acc);
+                ptx::mma_tf32_ss(d_tmem, da, dbl, idesc, 1);
+                ptx::mma_tf32_ss(d_tmem, da, db, idesc, 1);
+              }
+            }
+            ptx::mma_commit(empty_bar(s));
+            if (++s == kStages) {
+              s = 0;
+              ph ^= 1u;
+            }
+          }
+          ptx::mma_commit(tfull_bar(as));
+          if (++as == 2) {
+            as = 0;
+            aph ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp < Cfg::kEpiWarps) {
+    // ===================================================== epilogue
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    constexpr int kCols = Cfg::kColsPerThread;
+    const int col0 = (warp >> 2) * kCols;  // first tile column this warp handles
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / n_tiles) * kBM;
+      const int n0 = (tile % n_tiles) * BN;
+      const int m = m0 + q * 32 + lane;
+      const bool row_ok = m < args.M;
+      int64_t d_base, r_base, d_cs, r_cs;
+      out_row_base(args.dmap, m, d_base, d_cs);
+      out_row_base(args.rmap, m, r_base, r_cs);
+      const float row_bias = (args.bias_mode == BIAS_ROW && row_ok) ? args.bias[m] : 0.f;
+      const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+
+      // alpha / beta / bias / activation on 32 consecutive columns starting at n0 + c0, then store
+      auto finish = [&](float (&v)[32], int c0) {
+        if (!row_ok) return;
+        const int ncols = min(32, args.N - (n0 + c0));
+        const bool vec_ok = (d_cs == 1) && (ncols == 32) && (((d_base + n0 + c0) & 3) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(args.D) & 15) == 0);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = n0 + c0 + j;
+          float x = args.alpha * v[j];
+          if (args.R != nullptr && j < ncols) x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
+          if (args.bias_mode == BIAS_ROW) x += row_bias;
+          if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
+          v[j] = apply_act(x, args.act, args.act_lo, args.act_hi);
+        }
+        if (vec_ok) {
+          float4* dst = reinterpret_cast<float4*>(args.D + d_base + n0 + c0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
+        }
+      };
+
+      if (!kChunked) {
+        ptx::mbar_wait(tfull_bar(as), aph);
+        ptx::tc_fence_after();
+#pragma unroll 1
+        for (int c0 = col0; c0 < col0 + kCols; c0 += 32) {
+          if (n0 + c0 >= args.N) break;
+          float v[32];
+          ptx::tmem_ld_32x32(lane_addr + as * BN + c0, v);
+          ptx::tmem_ld_wait();
+          finish(v, c0);
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(tempty_bar(as));
+        if (++as == 2) {
+          as = 0;
+          aph ^= 1u;
+        }
+      } else {
+        // running sums in registers, one per output column of this thread's row
+        float acc[kCols];
+        for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
+          ptx::mbar_wait(tfull_bar(as), aph);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < kCols; c0 += 32) {
+            float v[32];
+            ptx::tmem_ld_32x32(lane_addr + as * BN + col0 + c0, v);
+            ptx::tmem_ld_wait();
+            if (kb0 == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[c0 + j] = v[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[c0 + j] = __fadd_rn(acc[c0 + j], v[j]);
+            }
+          }
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(tempty_bar(as));
+          if (++as == 2) {
+            as = 0;
+            aph ^= 1u;
+          }
+        }
+#pragma unroll
+        for (int c0 = 0; c0 < kCols; c0 += 32) {
+          if (n0 + col0 + c0 < args.N) {
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = acc[c0 + j];
+            finish(v, col0 + c0);
+          }
+        }
+      }
+    }
+  } else if (MODE == 1 && warp > kMmaWarp) {
+    // ===================================================== 3xTF32 operand split
+    const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
+    const bool store_hi = (args.flags & 1) != 0;  // debug: the tensor core truncates raw bits to the same hi
+    int s = 0;
+    uint32_t ph = 0;
+    constexpr int kVecs = Cfg::kRawBytes / 16;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(full_bar(s), ph);
+        uint8_t* raw = smem_raw + (smem_base - ptx::smem_u32(smem_raw)) + s * Cfg::kStageBytes;
+        float4* rawv = reinterpret_cast<float4*>(raw);
+        float4* lov = reinterpret_cast<float4*>(raw + Cfg::kRawBytes);
+#pragma unroll 4
+        for (int i = t; i < kVecs; i += Cfg::kXfThreads) {
+          const float4 x = rawv[i];
+          float4 hi;
+          hi.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+          hi.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+          hi.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
+          hi.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
+          uint32_t l0, l1, l2, l3;
+          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l0) : "f"(x.x - hi.x));
+          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l1) : "f"(x.y - hi.y));
+          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l2) : "f"(x.z - hi.z));
+          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l3) : "f"(x.w - hi.w));
+          if (store_hi) rawv[i] = hi;
+          lov[i] = make_float4(__uint_as_float(l0), __uint_as_float(l1), __uint_as_float(l2), __uint_as_float(l3));
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::mbar_arrive(xf_bar(s));
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+}  // namespace rtg
