@@ -1,0 +1,329 @@
+// Conv operator on the device (reference: src/ops/conv.rs:86-311 conv(), conv_2d_pointwise :24-68,
+// src/ops/conv/depthwise.rs:127-203, src/ops/conv/im2col.rs).  Dense and grouped convolutions run as implicit GEMM on
+// the tcgen05 kernel with TMA im2col loads over NHWC activations (pixels are GEMM rows, output channels GEMM columns,
+// batch folded into M); depthwise runs as a direct CUDA-core kernel.
+#include "conv_kernels.cuh"
+#include "ops.h"
+
+namespace rtg {
+
+// ---------------------------------------------------------------- shape / attribute checks
+rtg_status conv_plan(const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias,
+                     const rtg_conv_attrs* a, ConvPlan* p) {
+  if (!input || !weight) return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
+  if (input->dtype != RTG_F32 || weight->dtype != RTG_F32 || (bias && bias->dtype != RTG_F32))
+    return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  int64_t pads[4] = {0, 0, 0, 0};
+  int64_t strides[2], dils[2];
+  if (input->ndim == 3) {
+    // 1-D convolution is lifted to 2-D (src/ops/conv.rs:98-139)
+    if (weight->ndim != 3) return set_error(RTG_ERR_INVALID_VALUE, "kernel must have 3 dims (OCW)");
+    p->is_1d = true;
+    p->n = input->shape[0], p->c = input->shape[1], p->h = 1, p->w = input->shape[2];
+    p->o = weight->shape[0], p->cg = weight->shape[1], p->kh = 1, p->kw = weight->shape[2];
+    if (a->pad_mode == RTG_PAD_FIXED) {
+      if (a->n_pads != 2) return set_error(RTG_ERR_INVALID_VALUE, "expected 2 pad values");
+      pads[1] = a->pads[0], pads[3] = a->pads[1];
+    }
+    if (a->n_strides != 1) return set_error(RTG_ERR_INVALID_VALUE, "expected 1 stride value");
+    if (a->n_dilations != 1) return set_error(RTG_ERR_INVALID_VALUE, "expected 1 dilation value");
+    strides[0] = 1, strides[1] = a->strides[0];
+    dils[0] = 1, dils[1] = a->dilations[0];
+  } else {
+    if (input->ndim != 4) return set_error(RTG_ERR_INVALID_VALUE, "input must have 4 dims (NCHW)");
+    if (weight->ndim != 4) return set_error(RTG_ERR_INVALID_VALUE, "kernel must have 4 dims (OCHW)");
+    p->is_1d = false;
+    p->n = input->shape[0], p->c = input->shape[1], p->h = input->shape[2], p->w = input->shape[3];
+    p->o = weight->shape[0], p->cg = weight->shape[1], p->kh = weight->shape[2], p->kw = weight->shape[3];
+    if (a->n_strides != 2) return set_error(RTG_ERR_INVALID_VALUE, "expected 2 stride values");
+    if (a->n_dilations != 2) return set_error(RTG_ERR_INVALID_VALUE, "expected 2 dilation values");
+    strides[0] = a->strides[0], strides[1] = a->strides[1];
+    dils[0] = a->dilations[0], dils[1] = a->dilations[1];
+    if (a->pad_mode == RTG_PAD_FIXED) {
+      if (a->n_pads != 4) return set_error(RTG_ERR_INVALID_VALUE, "Expected 4 padding values");
+      for (int i = 0; i < 4; ++i) pads[i] = a->pads[i];
+    }
+  }
+  if (bias && bias->ndim != 1) return set_error(RTG_ERR_INVALID_VALUE, "bias must have 1 dims");
+
+  // calc_output_size_and_padding (src/ops/pooling.rs:27-89)
+  if (dils[0] <= 0 || dils[1] <= 0) return set_error(RTG_ERR_INVALID_VALUE, "Dilations must be > 0");
+  if (strides[0] <= 0 || strides[1] <= 0) return set_error(RTG_ERR_INVALID_VALUE, "Strides must be > 0");
+  if (p->kh <= 0 || p->kw <= 0) return set_error(RTG_ERR_PANIC, "kernel size must be > 0");
+  if (a->pad_mode == RTG_PAD_SAME) {
+    p->oh = div_ceil(p->h, strides[0]);
+    p->ow = div_ceil(p->w, strides[1]);
+    if (p->oh == 0 || p->ow == 0) return set_error(RTG_ERR_PANIC, "attempt to subtract with overflow");
+    const int64_t th = std::max<int64_t>(0, (p->oh - 1) * strides[0] + (p->kh - 1) * dils[0] + 1 - p->h);
+    const int64_t tw = std::max<int64_t>(0, (p->ow - 1) * strides[1] + (p->kw - 1) * dils[1] + 1 - p->w);
+    pads[0] = th / 2, pads[1] = tw / 2, pads[2] = div_ceil(th, 2), pads[3] = div_ceil(tw, 2);  // SAME_UPPER
+  } else {
+    for (int i = 0; i < 4; ++i)
+      if (pads[i] < 0) return set_error(RTG_ERR_INVALID_VALUE, "padding must be >= 0");
+    const int64_t ph = p->h + pads[0] + pads[2], pw = p->w + pads[1] + pads[3];
+    const int64_t dkh = p->kh + (p->kh - 1) * (dils[0] - 1), dkw = p->kw + (p->kw - 1) * (dils[1] - 1);
+    if (ph < dkh || pw < dkw) return set_error(RTG_ERR_INVALID_VALUE, "Input too small for kernel size");
+    p->oh = (ph - dils[0] * (p->kh - 1) - 1) / strides[0] + 1;
+    p->ow = (pw - dils[1] * (p->kw - 1) - 1) / strides[1] + 1;
+  }
+  for (int i = 0; i < 4; ++i) p->pads[i] = pads[i];
+  p->stride_h = strides[0], p->stride_w = strides[1], p->dil_h = dils[0], p->dil_w = dils[1];
+  p->groups = a->groups;
+
+  const bool has_padding = pads[0] > 0 || pads[1] > 0 || pads[2] > 0 || pads[3] > 0;
+  p->pointwise = p->kh == 1 && p->kw == 1 && !has_padding && p->groups == 1 && strides[0] == 1 && strides[1] == 1 &&
+                 dils[0] == 1 && dils[1] == 1;
+  p->depthwise = false;
+  if (p->pointwise) {
+    // The reference goes straight to the GEMM here, whose assert fires on a channel mismatch (src/gemm.rs:743).
+    if (p->cg != p->c) return set_error(RTG_ERR_PANIC, "Columns of matrix `a` must match rows of matrix `b`");
+  } else {
+    if (p->groups == 0) return set_error(RTG_ERR_PANIC, "attempt to divide by zero");
+    if (p->c / p->groups != p->cg)
+      return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES,
+                       "Input channels (per group) does not match kernel input channels");
+    if (p->c % p->groups != 0 || p->o % p->groups != 0)
+      return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES,
+                       "Input channels and output channels must be divisible by group count");
+    p->depthwise = p->c == p->o && p->groups == p->c;
+  }
+  if (bias && bias->shape[0] != p->o) return set_error(RTG_ERR_PANIC, "Bias vector length must match rows of matrix `a`");
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- weights
+rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out) {
+  out->wmat = nullptr;
+  out->direct = false;
+  const int khw = static_cast<int>(p.kh * p.kw);
+  if (p.o == 0 || p.cg == 0) return RTG_OK;
+  if (p.depthwise) {
+    void* d = nullptr;
+    RTG_TRY(ctx->pool.alloc(static_cast<size_t>(p.c) * khw * 4, &d));
+    const int total = static_cast<int>(p.c) * khw;
+    transpose_dw_weights_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(static_cast<float*>(d), w_dev,
+                                                                            static_cast<int>(p.c), khw);
+    ctx->launches++;
+    RTG_CUDA(cudaGetLastError());
+    out->wmat = static_cast<float*>(d);
+    out->kpt = 0;
+    return RTG_OK;
+  }
+  if (p.pointwise && p.c % 4 == 0 && (reinterpret_cast<uintptr_t>(w_dev) & 15) == 0) {
+    out->wmat = const_cast<float*>(w_dev);  // [O][C] is already the K-major B operand
+    out->direct = true;
+    out->kpt = static_cast<int>(p.c);
+    return RTG_OK;
+  }
+  const int kpt = static_cast<int>(div_ceil(p.cg, kBK) * kBK);
+  const int64_t total = p.o * khw * kpt;
+  void* d = nullptr;
+  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(total) * 4, &d));
+  const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), 148 * 16));
+  arrange_conv_weights_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(d), w_dev, static_cast<int>(p.o),
+                                                               static_cast<int>(p.cg), khw, kpt);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  out->wmat = static_cast<float*>(d);
+  out->kpt = kpt;
+  return RTG_OK;
+}
+
+void conv_release_weights(Context* ctx, ConvWeights* w) {
+  if (w->wmat && !w->direct) ctx->pool.free(w->wmat);
+  w->wmat = nullptr;
+}
+
+// ---------------------------------------------------------------- forward
+namespace {
+
+// Is the (H, W) plane of a 4-D view addressable as one dimension of H*W elements with a single stride?
+bool plane_collapsible(const rtg_tensor& t) { return t.shape[2] == 1 || t.strides[2] == t.shape[3] * t.strides[3]; }
+int64_t plane_stride(const rtg_tensor& t) { return t.shape[3] == 1 && t.shape[2] > 1 ? t.strides[2] : t.strides[3]; }
+
+// Gather channels [c_off, c_off+c) of x into a dense NHWC buffer with channel pitch cp (zero padded).
+rtg_status to_nhwc(Context* ctx, const rtg_tensor& x, int c_off, int c, int cp, float* dst) {
+  const int n = static_cast<int>(x.shape[0]);
+  const int hw = static_cast<int>(x.shape[2] * x.shape[3]);
+  if (n == 0 || hw == 0 || cp == 0) return RTG_OK;
+  dim3 grid(static_cast<unsigned>(div_ceil(hw, 32)), static_cast<unsigned>(div_ceil(cp, 32)), n);
+  if (grid.y > 65535 || grid.z > 65535) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "conv: batch or channels too large");
+  nchw_to_nhwc_kernel<<<grid, dim3(32, 8), 0, ctx->stream>>>(dst, static_cast<const float*>(x.data), c, hw, cp,
+                                                            x.strides[0], x.strides[1], plane_stride(x), c_off);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+rtg_status from_nhwc(Context* ctx, const float* src, int c, int cp, const rtg_tensor& out, int c_off) {
+  const int n = static_cast<int>(out.shape[0]);
+  const int hw = static_cast<int>(out.shape[2] * out.shape[3]);
+  if (n == 0 || hw == 0 || c == 0) return RTG_OK;
+  dim3 grid(static_cast<unsigned>(div_ceil(hw, 32)), static_cast<unsigned>(div_ceil(c, 32)), n);
+  nhwc_to_nchw_kernel<<<grid, dim3(32, 8), 0, ctx->stream>>>(static_cast<float*>(out.data), src, c, hw, cp,
+                                                            out.strides[0], out.strides[1], plane_stride(out), c_off);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+}  // namespace
+
+rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in, const ConvWeights& w,
+                        const float* bias, const rtg_tensor* residual_in, int act, float act_lo, float act_hi,
+                        const rtg_tensor& out_in) {
+  if (p.n == 0 || p.o == 0 || p.oh == 0 || p.ow == 0) return RTG_OK;
+  if (p.n > INT32_MAX || p.c > INT32_MAX || p.h > INT32_MAX || p.w > INT32_MAX || p.o > INT32_MAX)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "conv dims exceed i32");
+  // 4-D views of input / output (1-D convolutions carry H = 1)
+  rtg_tensor x = x_in, out = out_in;
+  rtg_tensor res_store;
+  const rtg_tensor* residual = residual_in;
+  auto lift = [&](rtg_tensor& t) {
+    if (t.ndim == 3) {
+      t.ndim = 4;
+      t.shape[3] = t.shape[2], t.strides[3] = t.strides[2];
+      t.shape[2] = 1, t.strides[2] = t.shape[3] * t.strides[3];
+    }
+  };
+  lift(x);
+  lift(out);
+  if (residual) {
+    res_store = *residual;
+    lift(res_store);
+    residual = &res_store;
+  }
+
+  // ---- output layout: NHWC-dense and NCHW-dense are written directly by the kernels
+  Scratch out_tmp, res_tmp;
+  rtg_tensor out_final = out;
+  const bool need_out_tmp = !is_nhwc_dense(out) && !is_contiguous(out);
+  if (need_out_tmp) {
+    RTG_TRY(out_tmp.alloc(ctx, static_cast<size_t>(numel(out)) * 4));
+    out.data = out_tmp.p;
+    set_contiguous_strides(out);
+  }
+  const bool out_nhwc = is_nhwc_dense(out);
+  if (residual) {
+    bool same = true;
+    for (int i = 0; i < 4; ++i) same = same && (residual->shape[i] == out.shape[i]);
+    if (!same) return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES, "residual shape must match the convolution output");
+    bool same_strides = true;
+    for (int i = 0; i < 4; ++i) same_strides = same_strides && (out.shape[i] == 1 || residual->strides[i] == out.strides[i]);
+    if (!same_strides) {
+      RTG_TRY(res_tmp.alloc(ctx, static_cast<size_t>(numel(out)) * 4));
+      rtg_tensor r2 = out;
+      r2.data = res_tmp.p;
+      RTG_TRY(copy_view(ctx, r2, *residual));
+      res_store = r2;
+      residual = &res_store;
+    }
+  }
+
+  const int N = static_cast<int>(p.n), C = static_cast<int>(p.c), H = static_cast<int>(p.h), W = static_cast<int>(p.w);
+  const int O = static_cast<int>(p.o), OH = static_cast<int>(p.oh), OW = static_cast<int>(p.ow);
+  const int G = static_cast<int>(p.groups), CG = static_cast<int>(p.cg), OG = O / std::max(G, 1);
+
+  // ---- input as dense NHWC.  Sources that are neither NHWC-dense nor plane-collapsible are made contiguous first.
+  Scratch x_cont, x_nhwc;
+  if (!is_nhwc_dense(x) && !plane_collapsible(x)) {
+    RTG_TRY(x_cont.alloc(ctx, static_cast<size_t>(numel(x)) * 4));
+    rtg_tensor xc = x;
+    xc.data = x_cont.p;
+    set_contiguous_strides(xc);
+    RTG_TRY(copy_view(ctx, xc, x));
+    x = xc;
+  }
+
+  if (p.depthwise) {
+    if (residual) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "fused residual is not supported for depthwise convolution");
+    const float* xp = static_cast<const float*>(x.data);
+    int cp_in = C;
+    if (!is_nhwc_dense(x)) {
+      RTG_TRY(x_nhwc.alloc(ctx, static_cast<size_t>(N) * H * W * C * 4));
+      RTG_TRY(to_nhwc(ctx, x, 0, C, C, x_nhwc.f32()));
+      xp = x_nhwc.f32();
+    }
+    Scratch o_nhwc;
+    float* op = static_cast<float*>(out.data);
+    if (!out_nhwc) {
+      RTG_TRY(o_nhwc.alloc(ctx, static_cast<size_t>(N) * OH * OW * C * 4));
+      op = o_nhwc.f32();
+    }
+    DwGeom g = {N, H, W, C, cp_in, C, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
+                static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.pads[0]),
+                static_cast<int>(p.pads[1]), static_cast<int>(p.dil_h), static_cast<int>(p.dil_w), act, act_lo, act_hi};
+    const bool vec4 = C % 4 == 0 && (reinterpret_cast<uintptr_t>(xp) & 15) == 0 &&
+                      (reinterpret_cast<uintptr_t>(op) & 15) == 0 && (reinterpret_cast<uintptr_t>(w.wmat) & 15) == 0;
+    const int64_t total = static_cast<int64_t>(N) * OH * OW * (vec4 ? C / 4 : C);
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 32));
+    if (vec4)
+      depthwise_nhwc_kernel<4><<<blocks, 256, 0, ctx->stream>>>(op, xp, w.wmat, bias, g);
+    else
+      depthwise_nhwc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(op, xp, w.wmat, bias, g);
+    ctx->launches++;
+    ctx->last_kernel = vec4 ? "depthwise_nhwc<4>" : "depthwise_nhwc<1>";
+    RTG_CUDA(cudaGetLastError());
+    if (!out_nhwc) RTG_TRY(from_nhwc(ctx, op, C, C, out, 0));
+  } else {
+    // Groups whose channel slice is not 16-byte aligned in the shared NHWC tensor get their own gathered copy.
+    const bool per_group = G > 1 && (CG % 4 != 0);
+    const int c_src = per_group ? CG : C;
+    const int cp = static_cast<int>(div_ceil(c_src, 4) * 4);
+    const bool direct_x = !per_group && is_nhwc_dense(x) && cp == C && (reinterpret_cast<uintptr_t>(x.data) & 15) == 0;
+    const float* xp = static_cast<const float*>(x.data);
+    if (!direct_x) {
+      RTG_TRY(x_nhwc.alloc(ctx, static_cast<size_t>(N) * H * W * cp * 4));
+      xp = x_nhwc.f32();
+      if (!per_group) RTG_TRY(to_nhwc(ctx, x, 0, C, cp, x_nhwc.f32()));
+    }
+    const int64_t M = static_cast<int64_t>(N) * OH * OW;
+    const int khw = static_cast<int>(p.kh * p.kw);
+    for (int g = 0; g < G; ++g) {
+      if (per_group) RTG_TRY(to_nhwc(ctx, x, g * CG, CG, cp, x_nhwc.f32()));
+      Epilogue ep;
+      ep.bias = bias ? bias + g * OG : nullptr;
+      ep.bias_mode = BIAS_COL;
+      ep.act = act, ep.act_lo = act_lo, ep.act_hi = act_hi;
+      OutMap dm;
+      if (out_nhwc) dm = OutMap{O, 0, 0, g * OG};
+      else dm = OutMap{0, OH * OW, O, g * OG};
+      if (residual) {
+        ep.R = static_cast<const float*>(residual->data);
+        ep.beta = 1.f;
+        ep.rmap = dm;
+      }
+      float* D = static_cast<float*>(out.data);
+      if (w.direct) {
+        // pointwise: A = activations [M, C] (pitch cp), B = W [O][C]
+        RTG_TRY(gemm_device(ctx, MatView{xp, M, C, cp, 1}, MatView{w.wmat, C, O, 1, C}, D, dm, ep));
+        continue;
+      }
+      const int64_t kmat = static_cast<int64_t>(khw) * w.kpt;
+      const float* wg = w.wmat + static_cast<int64_t>(g) * OG * kmat;
+      ConvGeom cg = {N, H, W, cp, per_group ? 0 : g * CG, CG, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
+                     static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.pads[0]),
+                     static_cast<int>(p.pads[1]), static_cast<int>(p.pads[2]), static_cast<int>(p.pads[3]),
+                     static_cast<int>(p.dil_h), static_cast<int>(p.dil_w)};
+      if (conv_im2col_supported(cg)) {
+        RTG_TRY(conv_gemm_device(ctx, xp, cg, wg, OG, D, dm, ep));
+      } else {
+        // outside the TMA im2col limits: materialise the patch matrix, then a plain GEMM
+        Scratch cols;
+        RTG_TRY(cols.alloc(ctx, static_cast<size_t>(M) * kmat * 4));
+        Im2colGeom ig = {N, H, W, cp, cg.c_off, CG, cg.kh, cg.kw, OH, OW, cg.stride_h, cg.stride_w,
+                         cg.pad_t, cg.pad_l, cg.dil_h, cg.dil_w, w.kpt};
+        const int64_t total = M * kmat;
+        const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 32));
+        im2col_nhwc_kernel<<<blocks, 256, 0, ctx->stream>>>(cols.f32(), xp, ig);
+        ctx->launches++;
+        RTG_CUDA(cudaGetLastError());
+        RTG_TRY(gemm_device(ctx, MatView{cols.f32(), M, kmat, kmat, 1}, MatView{wg, kmat, OG, 1, kmat}, D, dm, ep));
+      }
+    }
+  }
+  if (need_out_tmp) RTG_TRY(copy_view(ctx, out_final, out));
+  return RTG_OK;
+}
+
+}  // namespace rtg

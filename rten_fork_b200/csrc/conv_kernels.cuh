@@ -1,0 +1,175 @@
+// CUDA-core kernels around the convolution path: layout changes, weight pre-arrangement, explicit im2col (fallback for
+// geometries outside the TMA im2col limits) and the direct depthwise convolution.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vecmath.cuh"
+
+namespace rtg {
+
+// ---------------------------------------------------------------- NCHW <-> NHWC
+// src: channels [c_off, c_off + c) of an NCHW tensor given by element strides (sn, sc, sp) where the H*W plane is
+// contiguous-with-stride sp (sp = 1 for dense NCHW).  dst: [n, hw, cp] dense, channels >= c zero-filled.
+// One 32(pixels) x 32(channels) tile per block, transposed through shared memory so both sides are coalesced.
+__global__ void nchw_to_nhwc_kernel(float* __restrict__ dst, const float* __restrict__ src, int c, int hw, int cp,
+                                    int64_t sn, int64_t sc, int64_t sp, int c_off) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
+  const float* s = src + n * sn + static_cast<int64_t>(c_off) * sc;
+  for (int i = ty; i < 32; i += 8) {
+    const int ch = c0 + i, p = p0 + tx;
+    tile[i][tx] = (ch < c && p < hw) ? s[ch * sc + p * sp] : 0.f;
+  }
+  __syncthreads();
+  float* d = dst + static_cast<int64_t>(n) * hw * cp;
+  for (int i = ty; i < 32; i += 8) {
+    const int p = p0 + i, ch = c0 + tx;
+    if (p < hw && ch < cp) d[static_cast<int64_t>(p) * cp + ch] = tile[tx][i];
+  }
+}
+
+// src: [n, hw, cp] dense NHWC (first c channels valid) -> dst NCHW-like with strides (dn, dc, dp), channel offset.
+__global__ void nhwc_to_nchw_kernel(float* __restrict__ dst, const float* __restrict__ src, int c, int hw, int cp,
+                                    int64_t dn, int64_t dc, int64_t dp, int c_off) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const float* s = src + static_cast<int64_t>(n) * hw * cp;
+  for (int i = ty; i < 32; i += 8) {
+    const int p = p0 + i, ch = c0 + tx;
+    tile[i][tx] = (p < hw && ch < c) ? s[static_cast<int64_t>(p) * cp + ch] : 0.f;
+  }
+  __syncthreads();
+  float* d = dst + n * dn + static_cast<int64_t>(c_off) * dc;
+  for (int i = ty; i < 32; i += 8) {
+    const int ch = c0 + i, p = p0 + tx;
+    if (ch < c && p < hw) d[ch * dc + p * dp] = tile[tx][i];
+  }
+}
+
+// ---------------------------------------------------------------- weights
+// OIHW [O, Cg, Kh, Kw] -> per group g: [Og][Kh*Kw][c_blocks*32], zero padded.  This is the GPU counterpart of
+// prepack_a on the reshaped kernel matrix (reference: src/ops/conv.rs:231-241); K order is (ky, kx, c) to match
+// the order in which TMA im2col delivers activation columns.
+__global__ void arrange_conv_weights_kernel(float* __restrict__ dst, const float* __restrict__ w, int o_total, int cg,
+                                            int khw, int kpt /* c_blocks*32 */) {
+  const int64_t total = static_cast<int64_t>(o_total) * khw * kpt;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int ci = static_cast<int>(i % kpt);
+    const int tap = static_cast<int>((i / kpt) % khw);
+    const int o = static_cast<int>(i / (static_cast<int64_t>(kpt) * khw));
+    dst[i] = ci < cg ? w[(static_cast<int64_t>(o) * cg + ci) * khw + tap] : 0.f;
+  }
+}
+
+// ---------------------------------------------------------------- explicit im2col (fallback)
+struct Im2colGeom {
+  int n, h, w, cp;     // input NHWC dense, channel pitch cp
+  int c_off, cg;
+  int kh, kw, oh, ow;
+  int stride_h, stride_w, pad_t, pad_l, dil_h, dil_w;
+  int kpt;             // c_blocks*32 columns per tap
+};
+// dst: [n*oh*ow][kh*kw*kpt]; same column order as the arranged weights.  Index-driven: values are copies or zeros.
+// reference: VirtualIm2Col::pack_b_impl masked gather (src/ops/conv/im2col.rs:190-260).
+__global__ void im2col_nhwc_kernel(float* __restrict__ dst, const float* __restrict__ x, Im2colGeom g) {
+  const int64_t kmat = static_cast<int64_t>(g.kh) * g.kw * g.kpt;
+  const int64_t total = static_cast<int64_t>(g.n) * g.oh * g.ow * kmat;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t col = i % kmat, m = i / kmat;
+    const int ci = static_cast<int>(col % g.kpt);
+    const int tap = static_cast<int>(col / g.kpt);
+    const int ky = tap / g.kw, kx = tap % g.kw;
+    const int ox = static_cast<int>(m % g.ow);
+    const int oy = static_cast<int>((m / g.ow) % g.oh);
+    const int n = static_cast<int>(m / (static_cast<int64_t>(g.ow) * g.oh));
+    const int iy = oy * g.stride_h + ky * g.dil_h - g.pad_t;
+    const int ix = ox * g.stride_w + kx * g.dil_w - g.pad_l;
+    float v = 0.f;
+    if (ci < g.cg && iy >= 0 && iy < g.h && ix >= 0 && ix < g.w)
+      v = x[((static_cast<int64_t>(n) * g.h + iy) * g.w + ix) * g.cp + g.c_off + ci];
+    dst[i] = v;
+  }
+}
+
+// ---------------------------------------------------------------- depthwise
+struct DwGeom {
+  int n, h, w, c;      // NHWC dense, channel pitch cp
+  int cp_in, cp_out;
+  int kh, kw, oh, ow;
+  int stride_h, stride_w, pad_t, pad_l, dil_h, dil_w;
+  int act;
+  float act_lo, act_hi;
+};
+// Direct depthwise convolution over NHWC, 4 channels per thread (float4), one output pixel row-segment per thread.
+// Accumulation order equals the reference's (bias first, then ky-major / kx-minor, separate multiply and add:
+// src/ops/conv/depthwise.rs:49-120), so results are bit-identical to it.
+// wt: [kh*kw][c] (tap-major, transposed once from the reference's [c,1,kh,kw]).
+// HBM-bound: per output element 4 B written and ~4 B/stride^2 read (taps re-read from L1/L2).
+template <int VEC>
+__global__ void depthwise_nhwc_kernel(float* __restrict__ out, const float* __restrict__ x,
+                                      const float* __restrict__ wt, const float* __restrict__ bias, DwGeom g) {
+  const int cv = (g.c + VEC - 1) / VEC;
+  const int64_t total = static_cast<int64_t>(g.n) * g.oh * g.ow * cv;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % cv) * VEC;
+    const int64_t pix = i / cv;
+    const int ox = static_cast<int>(pix % g.ow);
+    const int oy = static_cast<int>((pix / g.ow) % g.oh);
+    const int n = static_cast<int>(pix / (static_cast<int64_t>(g.ow) * g.oh));
+    float acc[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) acc[v] = (bias != nullptr && c0 + v < g.c) ? bias[c0 + v] : 0.f;
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int iy = oy * g.stride_h + ky * g.dil_h - g.pad_t;
+      if (iy < 0 || iy >= g.h) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int ix = ox * g.stride_w + kx * g.dil_w - g.pad_l;
+        if (ix < 0 || ix >= g.w) continue;
+        const float* xp = x + ((static_cast<int64_t>(n) * g.h + iy) * g.w + ix) * g.cp_in + c0;
+        const float* wp = wt + static_cast<int64_t>(ky * g.kw + kx) * g.c + c0;
+        if (VEC == 4) {
+          const float4 xv = *reinterpret_cast<const float4*>(xp);
+          const float4 wv = *reinterpret_cast<const float4*>(wp);
+          acc[0] = __fadd_rn(acc[0], __fmul_rn(xv.x, wv.x));
+          acc[1 % VEC] = __fadd_rn(acc[1 % VEC], __fmul_rn(xv.y, wv.y));
+          acc[2 % VEC] = __fadd_rn(acc[2 % VEC], __fmul_rn(xv.z, wv.z));
+          acc[3 % VEC] = __fadd_rn(acc[3 % VEC], __fmul_rn(xv.w, wv.w));
+        } else {
+#pragma unroll
+          for (int v = 0; v < VEC; ++v)
+            if (c0 + v < g.c) acc[v] = __fadd_rn(acc[v], __fmul_rn(xp[v], wp[v]));
+        }
+      }
+    }
+    float* op = out + pix * g.cp_out + c0;
+    if (VEC == 4) {
+      *reinterpret_cast<float4*>(op) = make_float4(apply_act(acc[0], g.act, g.act_lo, g.act_hi),
+                                                   apply_act(acc[1 % VEC], g.act, g.act_lo, g.act_hi),
+                                                   apply_act(acc[2 % VEC], g.act, g.act_lo, g.act_hi),
+                                                   apply_act(acc[3 % VEC], g.act, g.act_lo, g.act_hi));
+    } else {
+#pragma unroll
+      for (int v = 0; v < VEC; ++v)
+        if (c0 + v < g.c) op[v] = apply_act(acc[v], g.act, g.act_lo, g.act_hi);
+    }
+  }
+}
+
+// [c][khw] -> [khw][c]
+__global__ void transpose_dw_weights_kernel(float* __restrict__ dst, const float* __restrict__ w, int c, int khw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < c * khw) {
+    const int ch = i % c, tap = i / c;
+    dst[i] = w[ch * khw + tap];
+  }
+}
+
+}  // namespace rtg

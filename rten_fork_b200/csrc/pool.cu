@@ -1,0 +1,169 @@
+// MaxPool / AveragePool / GlobalAveragePool (reference: src/ops/pooling.rs:104-420).  HBM-bound CUDA-core kernels that
+// address input and output through element strides, so NCHW-dense and NHWC-dense tensors are both handled without a
+// layout change; the thread order follows whichever dimension is contiguous.
+#include "ops.h"
+
+namespace rtg {
+
+namespace {
+
+struct PoolGeom {
+  int n, c, h, w, oh, ow;
+  int kh, kw, stride_h, stride_w, pad_t, pad_l;
+  int64_t is[4], os[4];   // element strides of input / output in (n, c, h, w) order
+  int kind, count_include_pad;
+  int chan_fastest;       // 1: thread index varies fastest over channels (NHWC), 0: over ow (NCHW)
+};
+
+__global__ void pool2d_kernel(float* __restrict__ out, const float* __restrict__ in, PoolGeom g) {
+  const int64_t total = static_cast<int64_t>(g.n) * g.c * g.oh * g.ow;
+  const int64_t step = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+    int n, c, oy, ox;
+    int64_t r = i;
+    if (g.chan_fastest) {
+      c = static_cast<int>(r % g.c), r /= g.c;
+      ox = static_cast<int>(r % g.ow), r /= g.ow;
+      oy = static_cast<int>(r % g.oh), r /= g.oh;
+      n = static_cast<int>(r);
+    } else {
+      ox = static_cast<int>(r % g.ow), r /= g.ow;
+      oy = static_cast<int>(r % g.oh), r /= g.oh;
+      c = static_cast<int>(r % g.c), r /= g.c;
+      n = static_cast<int>(r);
+    }
+    const float* ip = in + n * g.is[0] + c * g.is[1];
+    // fold in (ky, kx) order over the non-padding window, as pool_chans does (src/ops/pooling.rs:150-176)
+    float acc = g.kind == RTG_POOL_MAX ? __int_as_float(0xff800000) : 0.f;
+    int count = 0;
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int iy = oy * g.stride_h + ky - g.pad_t;
+      if (iy < 0 || iy >= g.h) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int ix = ox * g.stride_w + kx - g.pad_l;
+        if (ix < 0 || ix >= g.w) continue;
+        const float v = ip[iy * g.is[2] + ix * g.is[3]];
+        acc = g.kind == RTG_POOL_MAX ? fmaxf(acc, v) : __fadd_rn(acc, v);
+        ++count;
+      }
+    }
+    if (g.kind == RTG_POOL_AVG)
+      acc = __fdiv_rn(acc, static_cast<float>(g.count_include_pad ? g.kh * g.kw : count));
+    out[n * g.os[0] + c * g.os[1] + oy * g.os[2] + ox * g.os[3]] = acc;
+  }
+}
+
+// One warp per (n, c) for NCHW (contiguous plane, shuffle reduction); for NHWC one thread per (n, c) column walks the
+// pixels so that a warp reads 32 consecutive channels per pixel (coalesced).
+__global__ void gap_nchw_kernel(float* __restrict__ out, const float* __restrict__ in, int64_t nc, int hw, int c,
+                                int64_t sn, int64_t sc, int64_t sp, int64_t on, int64_t oc) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t i = warp; i < nc; i += nwarps) {
+    const int64_t n = i / c, ch = i % c;
+    const float* p = in + n * sn + ch * sc;
+    float s = 0.f;
+    for (int j = lane; j < hw; j += 32) s += p[j * sp];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[n * on + ch * oc] = __fdiv_rn(s, static_cast<float>(hw));
+  }
+}
+__global__ void gap_nhwc_kernel(float* __restrict__ out, const float* __restrict__ in, int n, int hw, int c,
+                                int64_t on, int64_t oc) {
+  // grid: (ceil(c/32), n); block: 32 x 8 -> 8 pixel-slices per channel, reduced through shared memory
+  __shared__ float part[8][33];
+  const int ch = blockIdx.x * 32 + threadIdx.x;
+  const int img = blockIdx.y;
+  float s = 0.f;
+  if (ch < c) {
+    const float* p = in + static_cast<int64_t>(img) * hw * c + ch;
+    for (int j = threadIdx.y; j < hw; j += 8) s += p[static_cast<int64_t>(j) * c];
+  }
+  part[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && ch < c) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
+    out[img * on + ch * oc] = __fdiv_rn(t, static_cast<float>(hw));
+  }
+}
+
+}  // namespace
+
+rtg_status pool_out_shape(const rtg_tensor* in, const rtg_pool_attrs* a, int64_t* shape, int64_t* pads_out) {
+  if (!in) return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
+  if (in->dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  if (in->ndim != 4) return set_error(RTG_ERR_INVALID_VALUE, "input must have 4 dims (NCHW)");
+  const int64_t h = in->shape[2], w = in->shape[3];
+  if (a->strides[0] <= 0 || a->strides[1] <= 0) return set_error(RTG_ERR_INVALID_VALUE, "Strides must be > 0");
+  if (a->kernel[0] <= 0 || a->kernel[1] <= 0) return set_error(RTG_ERR_PANIC, "kernel size must be > 0");
+  int64_t pads[4] = {0, 0, 0, 0}, oh, ow;
+  if (a->pad_mode == RTG_PAD_SAME) {
+    oh = div_ceil(h, a->strides[0]), ow = div_ceil(w, a->strides[1]);
+    if (oh == 0 || ow == 0) return set_error(RTG_ERR_PANIC, "attempt to subtract with overflow");
+    const int64_t th = std::max<int64_t>(0, (oh - 1) * a->strides[0] + a->kernel[0] - h);
+    const int64_t tw = std::max<int64_t>(0, (ow - 1) * a->strides[1] + a->kernel[1] - w);
+    pads[0] = th / 2, pads[1] = tw / 2, pads[2] = div_ceil(th, 2), pads[3] = div_ceil(tw, 2);
+  } else {
+    for (int i = 0; i < 4; ++i) pads[i] = a->pads[i];
+    const int64_t ph = h + pads[0] + pads[2], pw = w + pads[1] + pads[3];
+    if (ph < a->kernel[0] || pw < a->kernel[1]) return set_error(RTG_ERR_INVALID_VALUE, "Input too small for kernel size");
+    oh = (ph - a->kernel[0]) / a->strides[0] + 1;
+    ow = (pw - a->kernel[1]) / a->strides[1] + 1;
+  }
+  shape[0] = in->shape[0], shape[1] = in->shape[1], shape[2] = oh, shape[3] = ow;
+  if (pads_out)
+    for (int i = 0; i < 4; ++i) pads_out[i] = pads[i];
+  return RTG_OK;
+}
+
+rtg_status pool2d_forward(Context* ctx, int kind, const rtg_tensor& in, const rtg_pool_attrs& a, const rtg_tensor& out) {
+  int64_t shape[4], pads[4];
+  RTG_TRY(pool_out_shape(&in, &a, shape, pads));
+  const int64_t total = shape[0] * shape[1] * shape[2] * shape[3];
+  if (total == 0) return RTG_OK;
+  PoolGeom g = {};
+  g.n = static_cast<int>(shape[0]), g.c = static_cast<int>(shape[1]), g.h = static_cast<int>(in.shape[2]);
+  g.w = static_cast<int>(in.shape[3]), g.oh = static_cast<int>(shape[2]), g.ow = static_cast<int>(shape[3]);
+  g.kh = static_cast<int>(a.kernel[0]), g.kw = static_cast<int>(a.kernel[1]);
+  g.stride_h = static_cast<int>(a.strides[0]), g.stride_w = static_cast<int>(a.strides[1]);
+  g.pad_t = static_cast<int>(pads[0]), g.pad_l = static_cast<int>(pads[1]);
+  for (int i = 0; i < 4; ++i) g.is[i] = in.strides[i], g.os[i] = out.strides[i];
+  g.kind = kind, g.count_include_pad = a.count_include_pad;
+  g.chan_fastest = (out.strides[1] == 1 && g.c > 1) ? 1 : 0;
+  const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+  pool2d_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(out.data), static_cast<const float*>(in.data), g);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+rtg_status global_avg_pool_forward(Context* ctx, const rtg_tensor& in, const rtg_tensor& out) {
+  if (in.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  if (in.ndim != 4) return set_error(RTG_ERR_INVALID_VALUE, "input must have 4 dims (NCHW)");
+  const int64_t n = in.shape[0], c = in.shape[1];
+  const int hw = static_cast<int>(in.shape[2] * in.shape[3]);
+  if (n * c == 0) return RTG_OK;
+  if (is_nhwc_dense(in) && c > 1) {
+    dim3 grid(static_cast<unsigned>(div_ceil(c, 32)), static_cast<unsigned>(n));
+    gap_nhwc_kernel<<<grid, dim3(32, 8), 0, ctx->stream>>>(static_cast<float*>(out.data),
+                                                          static_cast<const float*>(in.data), static_cast<int>(n), hw,
+                                                          static_cast<int>(c), out.strides[0], out.strides[1]);
+  } else {
+    if (!(in.shape[2] == 1 || in.strides[2] == in.shape[3] * in.strides[3]))
+      return set_error(RTG_ERR_UNSUPPORTED_VALUE, "GlobalAveragePool input plane must be collapsible");
+    const int64_t sp = (in.shape[3] == 1 && in.shape[2] > 1) ? in.strides[2] : in.strides[3];
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(n * c * 32, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+    gap_nchw_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(out.data), static_cast<const float*>(in.data),
+                                                    n * c, hw, static_cast<int>(c), in.strides[0], in.strides[1], sp,
+                                                    out.strides[0], out.strides[1]);
+  }
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+}  // namespace rtg

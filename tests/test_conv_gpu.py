@@ -1,0 +1,227 @@
+"""Conv parity: CUDA path (C-ABI, host buffers) vs the oracle restatement and the reference's golden literals.
+
+Cases restate src/ops/conv.rs:706-1153 (basic, SAME padding, uneven padding, pointwise incl. non-contiguous input /
+batch / stride 2, depthwise, grouped, strided sweep, dilation sweep, 1-D, error strings).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import expect_equal
+
+pytestmark = pytest.mark.gpu
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_literals.json")))
+
+
+def check_conv(rtg, oracle, tol, x, w, b, pads, groups, strides, dilations):
+    """check_conv (src/ops/conv.rs:677-702): optimized result vs reference result, same inputs."""
+    from rten_fork_b200 import ops
+
+    got = ops.conv(x, w, b, pads, groups, strides, dilations)
+    want = oracle.conv2d(x, w, b, padding=pads, groups=groups, strides=strides, dilations=dilations)
+    expect_equal(got, want, rtol=tol)
+    return got
+
+
+def test_conv_golden_literals(rtg, ctx, oracle, math_mode):
+    from rten_fork_b200 import ops
+
+    g = GOLD["conv_3x3"]
+    x = np.array(g["input"], np.float32).reshape(g["input_shape"])
+    w = np.array(g["kernel"], np.float32).reshape(g["kernel_shape"])
+    tol = max(g["tol"], math_mode["rtol"])
+    for name in ("same_padding", "no_padding", "with_bias"):
+        c = g[name]
+        b = np.array(c["bias"], np.float32) if "bias" in c else None
+        got = ops.conv(x, w, b, c["pads"], 1, (1, 1), (1, 1))
+        want = np.array(c["expected"], np.float32).reshape(c["shape"])
+        np.testing.assert_allclose(got, want, rtol=tol, atol=tol)
+    d = GOLD["conv_depthwise"]
+    x = np.array(d["input"], np.float32).reshape(d["input_shape"])
+    w = np.array(d["kernel"], np.float32).reshape(d["kernel_shape"])
+    b = np.array(d["bias"], np.float32)
+    got = ops.conv(x, w, b, (0, 0, 0, 0), d["groups"], (1, 1), (1, 1))
+    want = (np.array(d["expected_minus_bias"], np.float32) + b).reshape(d["shape"])
+    expect_equal(got, want, rtol=1e-5, atol=1e-7)
+
+
+def test_conv_same_padding(rtg, ctx, oracle, math_mode):  # src/ops/conv.rs:769-811
+    from rten_fork_b200 import ops
+
+    g = GOLD["conv_3x3"]
+    x = np.array(g["input"], np.float32).reshape(g["input_shape"])
+    w = np.array(g["kernel"], np.float32).reshape(g["kernel_shape"])
+    got = ops.Conv(padding="same", groups=1, strides=(1, 1), dilations=(1, 1)).run([x, w])[0]
+    expect_equal(got, oracle.conv2d(x, w, None, padding=(1, 1, 1, 1)), rtol=math_mode["rtol"])
+
+
+def test_conv_uneven_padding(rtg, ctx, oracle, math_mode):  # :813-831
+    rng = oracle.XorShiftRng(1234)
+    w, x, b = rng.fill((10, 5, 3, 3)), rng.fill((1, 5, 10, 10)), rng.fill((10,))
+    check_conv(rtg, oracle, math_mode["rtol"], x, w, b, (0, 0, 1, 1), 1, (1, 1), (1, 1))
+
+
+def test_conv_depthwise_uneven_padding(rtg, ctx, oracle):  # :833-851
+    rng = oracle.XorShiftRng(1234)
+    w, x, b = rng.fill((10, 1, 3, 3)), rng.fill((1, 10, 10, 10)), rng.fill((10,))
+    check_conv(rtg, oracle, 1e-5, x, w, b, (0, 0, 1, 1), 10, (1, 1), (1, 1))
+
+
+def test_conv_pointwise(rtg, ctx, oracle, math_mode):  # :854-916
+    tol = math_mode["rtol"]
+    rng = oracle.XorShiftRng(1234)
+    w, x, b = rng.fill((10, 5, 1, 1)), rng.fill((1, 5, 20, 20)), rng.fill((10,))
+    assert check_conv(rtg, oracle, tol, x, w, b, (0, 0, 0, 0), 1, (1, 1), (1, 1)).shape == (1, 10, 20, 20)
+    xt = x.transpose(0, 1, 3, 2)  # non-contiguous input
+    assert not xt.flags.c_contiguous
+    from rten_fork_b200 import ops
+
+    got = ops.conv(xt, w, b, (0, 0, 0, 0), 1, (1, 1), (1, 1))
+    expect_equal(got, oracle.conv2d(np.ascontiguousarray(xt), w, b), rtol=tol)
+    x2 = rng.fill((2, 5, 20, 20))
+    assert check_conv(rtg, oracle, tol, x2, w, b, (0, 0, 0, 0), 1, (1, 1), (1, 1)).shape == (2, 10, 20, 20)
+    x3 = rng.fill((1, 5, 20, 20))
+    assert check_conv(rtg, oracle, tol, x3, w, b, (0, 0, 0, 0), 1, (2, 2), (1, 1)).shape == (1, 10, 10, 10)
+
+
+def test_conv_grouped(rtg, ctx, oracle, math_mode):  # :963-981 test_conv_not_depthwise_or_pointwise
+    rng = oracle.XorShiftRng(1234)
+    w, x, b = rng.fill((4, 2, 3, 3)), rng.fill((2, 4, 20, 20)), rng.fill((4,))
+    check_conv(rtg, oracle, math_mode["rtol"], x, w, b, (1, 1, 1, 1), 2, (1, 1), (1, 1))
+    # aligned group slices (C/g % 4 == 0) take the shared-NHWC path
+    w, x, b = rng.fill((16, 8, 3, 3)), rng.fill((2, 32, 9, 11)), rng.fill((16,))
+    check_conv(rtg, oracle, math_mode["rtol"], x, w, b, (1, 1, 1, 1), 4, (1, 1), (1, 1))
+
+
+@pytest.mark.parametrize("strides", [(2, 2), (3, 3), (1, 3)])
+@pytest.mark.parametrize("pad", [0, 1])
+def test_conv_strided(rtg, ctx, oracle, math_mode, strides, pad):  # :983-1005
+    rng = oracle.XorShiftRng(1234)
+    w = rng.fill((4, 3, 3, 3))
+    for size in (3, 4, 5, 10, 20):
+        x = rng.fill((2, 3, size, size))
+        check_conv(rtg, oracle, math_mode["rtol"], x, w, None, (pad,) * 4, 1, strides, (1, 1))
+
+
+@pytest.mark.parametrize("strides", [(2, 2), (3, 3), (1, 3)])
+@pytest.mark.parametrize("pad", [0, 1])
+def test_conv_strided_depthwise(rtg, ctx, oracle, strides, pad):  # :1007-1031
+    rng = oracle.XorShiftRng(1234)
+    w = rng.fill((3, 1, 3, 3))
+    for size in (3, 4, 5, 10, 20):
+        x = rng.fill((1, 3, size, size))
+        check_conv(rtg, oracle, 1e-5, x, w, None, (pad,) * 4, 3, strides, (1, 1))
+
+
+@pytest.mark.parametrize("dilations", [(2, 2), (3, 3), (1, 3)])
+@pytest.mark.parametrize("pad", [0, 1])
+def test_conv_dilated(rtg, ctx, oracle, math_mode, dilations, pad):  # :1081-1104
+    rng = oracle.XorShiftRng(1234)
+    w = rng.fill((4, 3, 3, 3))
+    for size in (7, 10, 20):
+        x = rng.fill((2, 3, size, size))
+        check_conv(rtg, oracle, math_mode["rtol"], x, w, None, (pad,) * 4, 1, (1, 1), dilations)
+
+
+@pytest.mark.parametrize("dilations", [(2, 2), (3, 3), (1, 3)])
+@pytest.mark.parametrize("pad", [0, 1])
+def test_conv_dilated_depthwise(rtg, ctx, oracle, dilations, pad):  # :1106-1130
+    rng = oracle.XorShiftRng(1234)
+    w = rng.fill((3, 1, 3, 3))
+    for size in (7, 10, 20):
+        x = rng.fill((2, 3, size, size))
+        check_conv(rtg, oracle, 1e-5, x, w, None, (pad,) * 4, 3, (1, 1), dilations)
+
+
+def test_conv_1d(rtg, ctx, oracle, math_mode):  # :1132-1153
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    x, w = rng.fill((1, 5, 20)), rng.fill((10, 5, 3))
+    got = ops.conv(x, w, None, "same", 1, (1,), (1,))
+    assert got.shape == (1, 10, 20)
+    expect_equal(got, oracle.conv2d(x, w, None, padding="same", strides=(1,), dilations=(1,)), rtol=math_mode["rtol"])
+
+
+def test_conv_errors(rtg, ctx, oracle):  # :1033-1079 and conv() checks :98-197
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    with pytest.raises(rtg.RtgError, match="Input too small for kernel size") as e:
+        ops.conv(rng.fill((1, 1, 2, 2)), rng.fill((1, 1, 3, 3)), None, (0, 0, 0, 0), 1, (1, 1), (1, 1))
+    assert e.value.kind == "InvalidValue"
+    with pytest.raises(rtg.RtgError, match="Strides must be > 0"):
+        ops.conv(rng.fill((1, 1, 2, 2)), rng.fill((1, 1, 2, 2)), None, (0, 0, 0, 0), 1, (0, 0), (1, 1))
+    with pytest.raises(rtg.RtgError, match="Dilations must be > 0"):
+        ops.conv(rng.fill((1, 1, 2, 2)), rng.fill((1, 1, 2, 2)), None, (0, 0, 0, 0), 1, (1, 1), (0, 1))
+    with pytest.raises(rtg.RtgError, match=r"Input channels \(per group\) does not match kernel input channels") as e:
+        ops.conv(rng.fill((1, 4, 5, 5)), rng.fill((4, 3, 3, 3)), None, (0, 0, 0, 0), 1, (1, 1), (1, 1))
+    assert e.value.kind == "IncompatibleInputShapes"
+    with pytest.raises(rtg.RtgError, match="must be divisible by group count"):
+        ops.conv(rng.fill((1, 5, 5, 5)), rng.fill((4, 2, 3, 3)), None, (0, 0, 0, 0), 2, (1, 1), (1, 1))
+    with pytest.raises(rtg.RtgError, match="expected 2 stride values"):
+        ops.conv(rng.fill((1, 1, 4, 4)), rng.fill((1, 1, 3, 3)), None, (0, 0, 0, 0), 1, (1,), (1, 1))
+    with pytest.raises(rtg.RtgError, match=r"kernel must have 4 dims \(OCHW\)"):
+        ops.conv(rng.fill((1, 1, 4, 4)), rng.fill((1, 3, 3)), None, (0, 0, 0, 0), 1, (1, 1), (1, 1))
+    with pytest.raises(rtg.RtgError, match="expected 2 pad values"):
+        ops.conv(rng.fill((1, 1, 8)), rng.fill((1, 1, 3)), None, (0, 0, 0, 0), 1, (1,), (1,))
+
+
+# ResNet-50 / MobileNetV2 layer shapes at reduced batch (BASELINE.json configs 2 and 4): every distinct
+# (kernel, stride, channel) family the graphs contain.
+RESNET_LAYERS = [
+    # (C, O, H, k, stride, pad, groups)
+    (3, 64, 64, 7, 2, 3, 1),      # conv1 (C=3: channel padding path)
+    (64, 64, 28, 1, 1, 0, 1),     # pointwise
+    (64, 64, 28, 3, 1, 1, 1),     # 3x3
+    (64, 256, 28, 1, 1, 0, 1),
+    (256, 128, 28, 1, 1, 0, 1),
+    (128, 128, 28, 3, 2, 1, 1),   # 3x3 stride 2
+    (256, 512, 28, 1, 2, 0, 1),   # 1x1 stride 2 downsample (im2col path in the reference)
+    (512, 512, 7, 3, 1, 1, 1),    # K = 4608
+    (512, 2048, 7, 1, 1, 0, 1),
+    (32, 32, 28, 3, 1, 1, 32),    # MobileNetV2 depthwise
+    (96, 96, 28, 3, 2, 1, 96),    # depthwise stride 2
+    (144, 24, 14, 1, 1, 0, 1),    # MobileNetV2 projection (C % 32 != 0)
+]
+
+
+@pytest.mark.parametrize("C,O,H,k,s,p,g", RESNET_LAYERS)
+def test_conv_model_layers(rtg, ctx, oracle, math_mode, C, O, H, k, s, p, g):
+    rng = oracle.XorShiftRng(1234)
+    x = rng.fill((2, C, H, H)) - 0.5
+    x = np.abs(x) + 0.1  # keep sums away from cancellation so that the relative rule is meaningful
+    w = rng.fill((O, C // g, k, k))
+    b = rng.fill((O,))
+    tol = 1e-5 if g == C else math_mode["rtol"]
+    check_conv(rtg, oracle, tol, x.astype(np.float32), w, b, (p,) * 4, g, (s, s), (1, 1))
+
+
+def test_conv_fused_epilogue_matches_unfused(rtg, ctx, oracle, math_mode):
+    """act(conv + bias + residual) fused in the GEMM epilogue == Conv -> Add -> Relu run as separate operators."""
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    x, w, b = rng.fill((2, 64, 14, 14)), rng.fill((128, 64, 3, 3)), rng.fill((128,))
+    res = rng.fill((2, 128, 14, 14))
+    fused = ops.conv(x, w, b, (1, 1, 1, 1), 1, (1, 1), (1, 1), residual=res, activation="relu")
+    want = oracle.unary("relu", oracle.binary("add", oracle.conv2d(x, w, b, padding=(1, 1, 1, 1)), res))
+    expect_equal(fused, want, rtol=math_mode["rtol"])
+
+
+def test_conv_nhwc_device_views(rtg, ctx, oracle, math_mode):
+    """NHWC-strided device views are consumed and produced without layout copies (the graph executor's fast path)."""
+    import torch
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    x, w, b = rng.fill((3, 32, 12, 10)), rng.fill((48, 32, 3, 3)), rng.fill((48,))
+    xd = torch.from_numpy(x).cuda().permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)  # NCHW shape, NHWC memory
+    out = ops.conv(xd, torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda(), (1, 1, 1, 1), 1, (2, 2), (1, 1),
+                   out_nhwc=True)
+    ctx.sync()
+    assert out.stride(1) == 1
+    expect_equal(out.cpu().numpy(), oracle.conv2d(x, w, b, padding=(1, 1, 1, 1), strides=(2, 2)), rtol=math_mode["rtol"])
