@@ -98,7 +98,7 @@ rtg_status rtg_gemm(rtg_ctx* ctx, int32_t device, float* out, size_t out_len, si
 enum { RTG_PAD_FIXED = 0, RTG_PAD_SAME = 1 }; /* Padding::{Fixed,Same}  src/ops/mod.rs:127-166 */
 enum {
   RTG_ACT_NONE = 0, RTG_ACT_RELU = 1, RTG_ACT_CLIP = 2, RTG_ACT_GELU = 3, RTG_ACT_SIGMOID = 4, RTG_ACT_SILU = 5,
-  RTG_ACT_ERF = 6
+  RTG_ACT_ERF = 6, RTG_ACT_TANH = 7, RTG_ACT_SQRT = 8
 };
 
 typedef struct rtg_conv_attrs {   /* struct Conv {groups, dilations, padding, strides}  src/ops/conv.rs:282-293 */
@@ -134,7 +134,7 @@ rtg_status rtg_gemm_op(rtg_ctx* ctx, const rtg_tensor* a, const rtg_tensor* b, c
 /* UnaryFloatOp::{run,run_in_place} for Relu/Clip/Gelu/Sigmoid/Silu/Erf   src/ops/unary_elementwise.rs:22-63
  * In place when output->data == input->data. */
 rtg_status rtg_unary(rtg_ctx* ctx, int32_t act, const rtg_tensor* input, float lo, float hi, rtg_tensor* output);
-enum { RTG_BIN_ADD = 0, RTG_BIN_SUB = 1, RTG_BIN_MUL = 2, RTG_BIN_DIV = 3 };
+enum { RTG_BIN_ADD = 0, RTG_BIN_SUB = 1, RTG_BIN_MUL = 2, RTG_BIN_DIV = 3, RTG_BIN_POW = 4 };
 /* binary_op / binary_op_in_place with numpy broadcasting          src/ops/binary_elementwise.rs:65-157,261-322 */
 rtg_status rtg_binary_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* out_shape, int32_t* out_ndim);
 rtg_status rtg_binary(rtg_ctx* ctx, int32_t op, const rtg_tensor* a, const rtg_tensor* b, rtg_tensor* output);

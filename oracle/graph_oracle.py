@@ -1,0 +1,98 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.
+
+Evaluates a graph (the node list of a ``ModelBuilder``) on the CPU with the oracle's restatement of each reference
+operator, in the order ``Graph::run`` would (src/graph.rs:797-1073: nodes are stored topologically).  Used by
+``tests/`` and ``bench.py --impl reference`` / ``cpu_baseline``; never imported by the product package.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+import oracle as o
+
+
+def _attrs(nd):
+    if nd["attrs"] is None:
+        return {}
+    return {fid: val for fid, _kind, val in nd["attrs"][1]}
+
+
+def _padding(a, auto_field, pads_field):
+    if a.get(auto_field, 0) == 0:
+        return "same"
+    p = a.get(pads_field)
+    return tuple(p) if p is not None else (0, 0, 0, 0)
+
+
+def run_graph(builder, inputs, outputs=None):
+    """``inputs``: arrays in graph-input order.  Returns the graph outputs (or the requested node ids)."""
+    vals = {}
+    for nid, x in zip(builder.inputs, inputs):
+        vals[nid] = np.asarray(x)
+    for i, nd in enumerate(builder.nodes):
+        if nd["kind"] == "const":
+            vals[i] = nd["data"]
+    for nd in builder.nodes:
+        if nd["kind"] != "op":
+            continue
+        ins = [vals[i] if i is not None and i >= 0 else None for i in nd["inputs"]]
+        a = _attrs(nd)
+        t = nd["type"]
+        if t == "Conv":
+            y = o.conv2d(ins[0], ins[1], ins[2] if len(ins) > 2 else None, padding=_padding(a, 0, 1),
+                         groups=a.get(2, 1), strides=tuple(a.get(3) or (1, 1)), dilations=tuple(a.get(4) or (1, 1)))
+        elif t in ("Relu", "Gelu", "Sigmoid", "Erf"):
+            y = o.unary(t.lower(), ins[0])
+        elif t == "Sqrt":
+            y = np.sqrt(ins[0].astype(np.float32))
+        elif t == "Tanh":
+            y = np.tanh(ins[0].astype(np.float64)).astype(np.float32)
+        elif t == "Clip":
+            lo = float(np.asarray(ins[1]).reshape(-1)[0]) if len(ins) > 1 and ins[1] is not None else None
+            hi = float(np.asarray(ins[2]).reshape(-1)[0]) if len(ins) > 2 and ins[2] is not None else None
+            y = o.unary("clip", ins[0], lo, hi)
+        elif t == "Pow":
+            y = np.power(ins[0].astype(np.float32), ins[1].astype(np.float32))
+        elif t in ("Add", "Sub", "Mul", "Div"):
+            y = o.binary(t.lower(), ins[0].astype(np.float32), ins[1].astype(np.float32))
+        elif t in ("MaxPool", "AveragePool"):
+            y = o.pool2d("max" if t == "MaxPool" else "avg", ins[0], tuple(a[0]), tuple(a.get(3) or (1, 1)),
+                         _padding(a, 1, 2), bool(a.get(4, 0)))
+        elif t == "GlobalAveragePool":
+            y = o.global_average_pool(ins[0])
+        elif t == "Flatten":
+            ax = a.get(0, 0)
+            x = ins[0]
+            ax = ax + x.ndim if ax < 0 else ax
+            y = np.ascontiguousarray(x).reshape(int(np.prod(x.shape[:ax])), -1)
+        elif t == "Reshape":
+            shape = [int(s) for s in ins[1]]
+            shape = [ins[0].shape[k] if s == 0 and not a.get(0) else s for k, s in enumerate(shape)]
+            y = np.ascontiguousarray(ins[0]).reshape(shape)
+        elif t == "Gemm":
+            y = o.gemm_op(ins[0], ins[1], ins[2] if len(ins) > 2 else None, a.get(0, 0.0), a.get(1, 0.0),
+                          bool(a.get(2)), bool(a.get(3)))
+        elif t == "MatMul":
+            y = o.matmul(np.ascontiguousarray(ins[0]), np.ascontiguousarray(ins[1]))
+        elif t == "Transpose":
+            y = np.ascontiguousarray(np.transpose(ins[0], a.get(0)))
+        elif t == "Softmax":
+            y = o.softmax(ins[0], a.get(0, 0))
+        elif t == "LayerNormalization":
+            y = o.layer_norm(ins[0], ins[1], ins[2] if len(ins) > 2 else None, a.get(0, 0), a.get(1, 0.0))
+        elif t == "Gather":
+            assert a.get(0, 0) == 0
+            y = ins[0][ins[1]]
+        elif t == "Cast":
+            y = ins[0].astype(np.float32 if a.get(0, 0) == 1 else np.int32)
+        elif t == "Unsqueeze":
+            y = ins[0]
+            for ax in sorted(int(v) for v in ins[1]):
+                y = np.expand_dims(y, ax)
+        elif t == "Identity":
+            y = ins[0].copy()
+        else:
+            raise NotImplementedError(t)
+        vals[nd["outputs"][0]] = y
+    ids = outputs if outputs is not None else builder.outputs
+    return [vals[i] for i in ids]

@@ -298,3 +298,30 @@ def gemm_op(a, b, c=None, alpha=1.0, beta=1.0, transpose_a=False, transpose_b=Fa
                              _pd(_estrides(b)), *cargs, C.c_float(alpha), C.c_float(beta), C.c_int(transpose_a),
                              C.c_int(transpose_b), _fp(out), C.c_size_t(out.size), oshape))
     return out
+
+
+def softmax(x, axis=-1):
+    """src/ops/norm.rs softmax over rten-vecmath/src/softmax.rs: exp(x - max) with the vecmath exp, then / sum."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    xm = np.moveaxis(x, axis, -1)
+    m = xm.max(axis=-1, keepdims=True)
+    if xm.size <= 4096:
+        e = np.array([vm_scalar("exp", float(v)) for v in (xm - m).reshape(-1)], dtype=np.float32).reshape(xm.shape)
+    else:
+        e = np.exp((xm - m).astype(np.float64)).astype(np.float32)
+    s = e.sum(axis=-1, keepdims=True, dtype=np.float32)
+    return np.ascontiguousarray(np.moveaxis(e / s, -1, axis))
+
+
+def layer_norm(x, scale, bias, axis, eps):
+    """src/ops/norm.rs:245-299: mean, centre, inverse RMS of the centred values, scale, shift (f32 throughout)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    axis = axis + x.ndim if axis < 0 else axis
+    axes = tuple(range(axis, x.ndim))
+    mean = x.mean(axis=axes, keepdims=True, dtype=np.float32)
+    d = x - mean
+    inv = (1.0 / np.sqrt((d * d).mean(axis=axes, keepdims=True, dtype=np.float32) + np.float32(eps))).astype(np.float32)
+    y = d * inv * scale
+    if bias is not None:
+        y = y + bias
+    return y.astype(np.float32)

@@ -6,3 +6,6 @@ host-side mirror of the reference interface for that path.  There is no CPU fall
 from ._native import MATH_3XTF32, MATH_TF32, RtgError  # noqa: F401
 from .context import Context, default_context  # noqa: F401
 from .gemm import GemmExecutor, gemm  # noqa: F401
+from . import ops, synth  # noqa: F401
+from .model import Model  # noqa: F401
+from .rten_builder import ModelBuilder  # noqa: F401

@@ -197,7 +197,7 @@ rtg_status rtg_binary(rtg_ctx* ctx_, int32_t op, const rtg_tensor* a, const rtg_
   RTG_TRY(check_tensor(a, "a"));
   RTG_TRY(check_tensor(b, "b"));
   if (!output) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
-  if (op < RTG_BIN_ADD || op > RTG_BIN_DIV) return set_error(RTG_ERR_INVALID_VALUE, "unknown binary op");
+  if (op < RTG_BIN_ADD || op > RTG_BIN_POW) return set_error(RTG_ERR_INVALID_VALUE, "unknown binary op");
   int64_t os[RTG_MAX_DIMS];
   int32_t ond;
   RTG_TRY(binary_out_shape(a, b, os, &ond));

@@ -23,7 +23,11 @@ __device__ __forceinline__ float bin_op(int op, float a, float b) {
     case RTG_BIN_ADD: return __fadd_rn(a, b);
     case RTG_BIN_SUB: return __fsub_rn(a, b);
     case RTG_BIN_MUL: return __fmul_rn(a, b);
-    default: return __fdiv_rn(a, b);
+    case RTG_BIN_DIV: return __fdiv_rn(a, b);
+    default:  // Pow, with the reference's fast paths (src/ops/binary_elementwise.rs:743-751)
+      if (b == 2.f) return __fmul_rn(a, a);
+      if (b == 3.f) return __fmul_rn(__fmul_rn(a, a), a);
+      return powf(a, b);
   }
 }
 

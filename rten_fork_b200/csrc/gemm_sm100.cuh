@@ -298,9 +298,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int j = 0; j < 32; ++j) {
           const int n = n0 + c0 + j;
           float x = args.alpha * v[j];
-          if (args.R != nullptr && j < ncols) x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
+          // bias before the residual: a fused Conv -> Add computes (acc + bias) + r exactly as the unfused pair does
           if (args.bias_mode == BIAS_ROW) x += row_bias;
           if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
+          if (args.R != nullptr && j < ncols) x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
           v[j] = apply_act(x, args.act, args.act_lo, args.act_hi);
         }
         if (vec_ok) {

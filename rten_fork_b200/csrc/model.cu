@@ -1,0 +1,312 @@
+// `.rten` loading (reference: src/header.rs:60-110 V2 container, src/model.rs:265-522 load_impl / load_graph /
+// add_graph_* , docs/rten-file-format.md) and the load-time graph optimiser.
+#include <stdio.h>
+
+#include <fstream>
+#include <set>
+
+#include "operators.h"
+#include "schema_ids.h"
+
+namespace rtg {
+
+using namespace schema;
+
+namespace {
+
+struct Header {
+  bool present = false;
+  uint64_t model_offset = 0, model_len = 0, tensor_data_offset = 0;
+};
+
+// Header::from_buf.  Returns RTG_OK with present=false for headerless (V1) files, i.e. when the magic is absent.
+rtg_status read_header(const uint8_t* p, size_t n, Header* h) {
+  if (n < 4 || memcmp(p, "RTEN", 4) != 0) return RTG_OK;  // HeaderError::InvalidMagic => V1 format
+  if (n < 32) return set_error(RTG_ERR_FORMAT, "invalid header: TooShort");
+  uint32_t version;
+  memcpy(&version, p + 4, 4);
+  if (version != 2) return set_error(RTG_ERR_FORMAT, "invalid header: UnsupportedVersion");
+  memcpy(&h->model_offset, p + 8, 8);
+  memcpy(&h->model_len, p + 16, 8);
+  memcpy(&h->tensor_data_offset, p + 24, 8);
+  if (h->model_offset < 32 || h->model_offset > n) return set_error(RTG_ERR_FORMAT, "invalid header: InvalidOffset");
+  if (h->model_len > n - h->model_offset) return set_error(RTG_ERR_FORMAT, "invalid header: InvalidLength");
+  if (h->tensor_data_offset < 32 || h->tensor_data_offset > n)
+    return set_error(RTG_ERR_FORMAT, "invalid header: InvalidOffset");
+  h->present = true;
+  return RTG_OK;
+}
+
+// Upload a constant; small tensors also keep a host mirror for shape-consuming operators.
+rtg_status make_constant(Context* ctx, int dtype, const std::vector<int64_t>& shape, const void* host, Node* node) {
+  Value v;
+  int64_t n = 1;
+  for (int64_t d : shape) n *= d;
+  if (shape.size() > RTG_MAX_DIMS) return set_error(RTG_ERR_FORMAT, "constant has too many dimensions");
+  RTG_TRY(alloc_value(ctx, dtype, static_cast<int>(shape.size()), shape.data(), false, &v));
+  if (n > 0) RTG_CUDA(cudaMemcpyAsync(v.t.data, host, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (n <= 4096) {
+    if (dtype == RTG_I32)
+      v.host_i32 = std::make_shared<std::vector<int32_t>>(static_cast<const int32_t*>(host), static_cast<const int32_t*>(host) + n);
+    else
+      v.host_f32 = std::make_shared<std::vector<float>>(static_cast<const float*>(host), static_cast<const float*>(host) + n);
+  }
+  node->constant = v;
+  return RTG_OK;
+}
+
+}  // namespace
+
+rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimize, Model** out) {
+  Header hdr;
+  RTG_TRY(read_header(data, len, &hdr));
+  const uint8_t* model_data = hdr.present ? data + hdr.model_offset : data;
+  const size_t model_len = hdr.present ? static_cast<size_t>(hdr.model_len) : len;
+  std::unique_ptr<Model> model(new Model());
+  model->ctx = ctx;
+  const OpRegistry& registry = OpRegistry::with_all_ops();
+  try {
+    if (model_len < 8) throw fb::Error("file too short");
+    fb::Table root = fb::root(model_data, model_len);
+    // Model: schema_version:0 graph:1 metadata:2
+    if (root.scalar<int32_t>(0, 0) != 1) return set_error(RTG_ERR_FORMAT, "unsupported schema version");
+    fb::Table graph = root.table(1);
+    if (!graph.valid) return set_error(RTG_ERR_FORMAT, "parse error: model has no graph");
+    // Graph: nodes:0 inputs:1 outputs:2 captures:3
+    fb::Vec<uint32_t> nodes = graph.vec<uint32_t>(0);
+    Graph& g = model->graph;
+    g.nodes.resize(nodes.size());
+    for (uint32_t i = 0; i < nodes.size(); ++i) {
+      fb::Table nt = graph.vec_table(nodes, i);
+      Node& node = g.nodes[i];
+      node.name = nt.str(0);  // Node: name:0 data_type:1 data:2
+      const uint8_t kind = nt.scalar<uint8_t>(1, Kind_NONE);
+      fb::Table d = nt.table(2);
+      if (kind == Kind_OperatorNode) {
+        // OperatorNode: type:0 attrs_type:1 attrs:2 inputs:3 outputs:4   (add_graph_operator, src/model.rs:384-445)
+        node.kind = NodeKind::Operator;
+        OpNodeView view;
+        view.type = d.scalar<uint8_t>(0, 0);
+        view.attrs_type = d.scalar<uint8_t>(1, 0);
+        view.attrs = d.table(2);
+        node.op_type = view.type;
+        rtg_status st = registry.read_op(view, &node.op);
+        if (st != RTG_OK) {
+          std::string msg = rtg_last_error();
+          for (Node& nd : g.nodes) if (nd.kind == NodeKind::Constant) release_value(ctx, &nd.constant);
+          return set_errorf(st, "operator error: in node \"%s\": %s", node.name.c_str(), msg.c_str());
+        }
+        fb::Vec<int32_t> ins = d.vec<int32_t>(3), outs = d.vec<int32_t>(4);
+        for (uint32_t k = 0; k < ins.size(); ++k) node.inputs.push_back(ins[k]);
+        for (uint32_t k = 0; k < outs.size(); ++k) node.outputs.push_back(outs[k]);
+        for (int32_t id : node.inputs)
+          if (id >= static_cast<int32_t>(nodes.size())) return set_error(RTG_ERR_FORMAT, "graph error: operator input id out of range");
+        for (int32_t id : node.outputs)
+          if (id >= static_cast<int32_t>(nodes.size())) return set_error(RTG_ERR_FORMAT, "graph error: operator output id out of range");
+      } else if (kind == Kind_ConstantNode) {
+        // ConstantNode: shape:0 data_type:1 data:2 dtype:3 data_offset:4   (add_graph_constant, src/model.rs:468-522)
+        node.kind = NodeKind::Constant;
+        fb::Vec<uint32_t> shp = d.vec<uint32_t>(0);
+        std::vector<int64_t> shape;
+        int64_t n = 1;
+        for (uint32_t k = 0; k < shp.size(); ++k) {
+          shape.push_back(shp[k]);
+          n *= shp[k];
+        }
+        const uint8_t data_kind = d.scalar<uint8_t>(1, Data_NONE);
+        if (d.has(4)) {
+          // tensor data stored after the model buffer (V2 only)
+          if (!hdr.present) return set_error(RTG_ERR_FORMAT, "graph error: tensor data section missing");
+          const uint64_t off = hdr.tensor_data_offset + d.scalar<uint64_t>(4, 0);
+          if (!d.has(3)) return set_error(RTG_ERR_FORMAT, "graph error: constant with data offset has no dtype");
+          const uint16_t dt = d.scalar<uint16_t>(3, 0);
+          if (dt > 1) return set_error(RTG_ERR_FORMAT, "graph error: unsupported data type for external constant");
+          if (off > len || static_cast<uint64_t>(n) * 4 > len - off)
+            return set_error(RTG_ERR_FORMAT, "graph error: invalid tensor data offset");
+          RTG_TRY(make_constant(ctx, dt == 0 ? RTG_I32 : RTG_F32, shape, data + off, &node));
+        } else if (data_kind == Data_FloatData || data_kind == Data_IntData) {
+          fb::Table dt = d.table(2);
+          fb::Vec<uint32_t> raw = dt.vec<uint32_t>(0);  // 4-byte elements either way
+          if (!raw.present || static_cast<int64_t>(raw.size()) != n)
+            return set_error(RTG_ERR_FORMAT, "graph error: constant data length does not match shape");
+          RTG_TRY(make_constant(ctx, data_kind == Data_IntData ? RTG_I32 : RTG_F32, shape, raw.data(), &node));
+        } else {
+          return set_error(RTG_ERR_FORMAT, "graph error: unsupported constant data type");
+        }
+      } else if (kind == Kind_ValueNode) {
+        // ValueNode: shape:0 ([Dim{value:0, name:1}])   (add_graph_value, src/model.rs:447-466)
+        node.kind = NodeKind::Value;
+        fb::Vec<uint32_t> dims = d.vec<uint32_t>(0);
+        node.has_shape = dims.present;
+        for (uint32_t k = 0; k < dims.size(); ++k) {
+          fb::Table dim = d.vec_table(dims, k);
+          DimSpec ds;
+          ds.name = dim.str(1);
+          ds.value = ds.name.empty() ? static_cast<int64_t>(dim.scalar<uint32_t>(0, 0)) : -1;
+          node.shape.push_back(ds);
+        }
+      } else {
+        return set_error(RTG_ERR_FORMAT, "graph error: unknown node type");
+      }
+    }
+    fb::Vec<uint32_t> ins = graph.vec<uint32_t>(1), outs = graph.vec<uint32_t>(2);
+    for (uint32_t i = 0; i < ins.size(); ++i) g.input_ids.push_back(static_cast<int32_t>(ins[i]));
+    for (uint32_t i = 0; i < outs.size(); ++i) g.output_ids.push_back(static_cast<int32_t>(outs[i]));
+    for (int32_t id : g.input_ids)
+      if (id < 0 || id >= static_cast<int32_t>(g.nodes.size())) return set_error(RTG_ERR_FORMAT, "graph error: input id out of range");
+    for (int32_t id : g.output_ids)
+      if (id < 0 || id >= static_cast<int32_t>(g.nodes.size())) return set_error(RTG_ERR_FORMAT, "graph error: output id out of range");
+  } catch (const fb::Error& e) {
+    model->graph.release(ctx);
+    return set_errorf(RTG_ERR_FORMAT, "parse error: %s", e.what());
+  }
+  RTG_CUDA(cudaStreamSynchronize(ctx->stream));  // constants are uploaded from the caller's buffer
+
+  if (optimize) optimize_graph(&model->graph);
+
+  // Let operators pre-arrange constant operands (weights) once.
+  Graph& g = model->graph;
+  for (Node& node : g.nodes) {
+    if (node.kind != NodeKind::Operator) continue;
+    OpInputs consts;
+    for (int32_t id : node.inputs)
+      consts.v.push_back(id >= 0 && g.nodes[id].kind == NodeKind::Constant ? &g.nodes[id].constant : nullptr);
+    rtg_status st = node.op->prepare(ctx, consts);
+    if (st != RTG_OK) {
+      g.release(ctx);
+      return st;
+    }
+  }
+  *out = model.release();
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- optimiser
+// The reference's GraphOptimizer fuses Transpose->MatMul, Silu, Gelu and LayerNormalization patterns
+// (src/optimize.rs:286-297).  On the GPU the profitable fusions are the epilogues, because every separate
+// elementwise operator costs a full read + write of the activation tensor:
+//     Conv -> [Add(residual)] -> [Relu | Clip]          => one FusedConv launch
+//     MatMul -> Add(bias vector) -> [Gelu | Relu | ...]  => one FusedMatMul launch
+// Each fused node computes exactly the same expression in the same order as the unfused chain, so results stay
+// within the parity tolerance (the intermediate values are simply never stored).
+int optimize_graph(Graph* g) {
+  const int32_t n = static_cast<int32_t>(g->nodes.size());
+  std::vector<int32_t> uses(n, 0), producer(n, -1);
+  std::vector<std::vector<int32_t>> consumers(n);
+  for (int32_t i = 0; i < n; ++i) {
+    Node& nd = g->nodes[i];
+    if (nd.kind != NodeKind::Operator) continue;
+    for (int32_t in : nd.inputs)
+      if (in >= 0) {
+        uses[in]++;
+        consumers[in].push_back(i);
+      }
+    for (int32_t o : nd.outputs)
+      if (o >= 0) producer[o] = i;
+  }
+  for (int32_t o : g->output_ids) uses[o] += 1000;  // graph outputs must stay materialised
+  auto single_consumer = [&](int32_t value) -> int32_t {
+    if (value < 0 || uses[value] != 1 || consumers[value].size() != 1) return -1;
+    return consumers[value][0];
+  };
+  auto act_of = [&](const Node& nd, int* act, float* lo, float* hi) -> bool {
+    UnaryOp* u = dynamic_cast<UnaryOp*>(nd.op.get());
+    if (!u) return false;
+    *lo = 0.f, *hi = 0.f;
+    if (u->act == ACT_CLIP) {
+      // min / max must be constants to be folded into the epilogue
+      *lo = -3.40282347e+38f, *hi = 3.40282347e+38f;
+      for (size_t k = 1; k < nd.inputs.size() && k < 3; ++k) {
+        const int32_t id = nd.inputs[k];
+        if (id < 0) continue;
+        const Node& c = g->nodes[id];
+        if (c.kind != NodeKind::Constant || !c.constant.host_f32 || c.constant.host_f32->size() != 1) return false;
+        (k == 1 ? *lo : *hi) = (*c.constant.host_f32)[0];
+      }
+    }
+    *act = u->act;
+    return true;
+  };
+  int fused = 0;
+  std::vector<char> dead(n, 0);
+  for (int32_t i = 0; i < n; ++i) {
+    Node& nd = g->nodes[i];
+    if (nd.kind != NodeKind::Operator || dead[i] || nd.outputs.size() != 1 || nd.outputs[0] < 0) continue;
+    ConvOp* conv = dynamic_cast<ConvOp*>(nd.op.get());
+    MatMulOp* mm = dynamic_cast<MatMulOp*>(nd.op.get());
+    if (!conv && !mm) continue;
+    if (conv && (conv->has_residual || conv->act != ACT_NONE)) continue;
+    int32_t cur_out = nd.outputs[0];
+    // --- optional Add
+    int32_t next = single_consumer(cur_out);
+    if (next >= 0 && !dead[next]) {
+      Node& add = g->nodes[next];
+      BinaryOp* b = dynamic_cast<BinaryOp*>(add.op.get());
+      if (b && b->op == RTG_BIN_ADD && add.inputs.size() == 2 && add.outputs.size() == 1) {
+        const int32_t other = add.inputs[0] == cur_out ? add.inputs[1] : add.inputs[0];
+        bool ok = other >= 0 && other != cur_out;
+        if (ok && conv) {
+          // the residual must not depend on this convolution (it is a sibling branch or the block input)
+          ok = g->nodes[other].kind != NodeKind::Constant && nd.inputs.size() <= 3;
+          // cheap cycle check: the residual's producer must come from an earlier value than our output
+          std::vector<int32_t> stack = {other};
+          std::set<int32_t> seen;
+          while (ok && !stack.empty()) {
+            const int32_t v = stack.back();
+            stack.pop_back();
+            if (v == cur_out) ok = false;
+            if (v < 0 || !seen.insert(v).second || producer[v] < 0) continue;
+            for (int32_t in : g->nodes[producer[v]].inputs) stack.push_back(in);
+          }
+          if (ok) {
+            while (nd.inputs.size() < 3) nd.inputs.push_back(-1);
+            nd.inputs.push_back(other);
+            conv->has_residual = true;
+          }
+        } else if (ok && mm) {
+          // bias must be a constant vector [N]
+          const Node& c = g->nodes[other];
+          ok = c.kind == NodeKind::Constant && c.constant.t.ndim == 1 && c.constant.t.dtype == RTG_F32 && nd.inputs.size() == 2;
+          if (ok) {
+            nd.inputs.push_back(other);
+            mm->has_bias = true;
+          }
+        }
+        if (ok) {
+          dead[next] = 1;
+          nd.outputs[0] = add.outputs[0];
+          cur_out = add.outputs[0];
+          ++fused;
+        }
+      }
+    }
+    // --- optional activation
+    next = single_consumer(cur_out);
+    if (next >= 0 && !dead[next] && (conv || mm->has_bias)) {
+      Node& an = g->nodes[next];
+      int act;
+      float lo, hi;
+      if (an.outputs.size() == 1 && act_of(an, &act, &lo, &hi) &&
+          (act == ACT_RELU || act == ACT_CLIP || act == ACT_GELU || act == ACT_SIGMOID || act == ACT_TANH)) {
+        if (conv) conv->act = act, conv->act_lo = lo, conv->act_hi = hi;
+        else if (act != ACT_CLIP) mm->act = act;
+        if (conv || act != ACT_CLIP) {
+          dead[next] = 1;
+          nd.outputs[0] = an.outputs[0];
+          ++fused;
+        }
+      }
+    }
+  }
+  // dead operators become value-less placeholders (ids of other nodes must not shift)
+  for (int32_t i = 0; i < n; ++i)
+    if (dead[i]) {
+      g->nodes[i].kind = NodeKind::Value;
+      g->nodes[i].op.reset();
+      g->nodes[i].inputs.clear();
+      g->nodes[i].outputs.clear();
+    }
+  return fused;
+}
+
+}  // namespace rtg

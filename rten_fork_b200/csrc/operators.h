@@ -1,0 +1,154 @@
+// Operator classes used by the graph executor (declarations; see operators.cu / operators_nn.cu).
+#pragma once
+#include "graph.h"
+
+namespace rtg {
+
+// struct Conv {groups, dilations, padding, strides}  src/ops/conv.rs:282-311
+class ConvOp : public Operator {
+ public:
+  rtg_conv_attrs attrs = {};
+  // fused epilogue (set by optimize_graph): out = act(conv + bias + residual); input 3 is the residual
+  bool has_residual = false;
+  int act = ACT_NONE;
+  float act_lo = 0.f, act_hi = 0.f;
+  const char* name() const override { return act != ACT_NONE || has_residual ? "FusedConv" : "Conv"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status prepare(Context* ctx, const OpInputs& consts) override;
+  void release(Context* ctx) override;
+
+ private:
+  rtg_status partial_plan(const rtg_tensor& w, ConvPlan* p) const;
+  ConvWeights weights;
+  bool prepared = false, prepared_pointwise = false, prepared_depthwise = false;
+  const void* prepared_from = nullptr;
+};
+
+// UnaryFloatOp blanket impl  src/ops/unary_elementwise.rs:22-63 ; Clip :335-383
+class UnaryOp : public Operator {
+ public:
+  int act;
+  float act_lo = 0.f, act_hi = 0.f;
+  const char* op_name;
+  UnaryOp(int a, const char* n) : act(a), op_name(n) {}
+  const char* name() const override { return op_name; }
+  bool can_run_in_place() const override { return true; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+
+ private:
+  rtg_status bounds(Context* ctx, const Value* lo_v, const Value* hi_v, float* lo, float* hi) const;
+};
+
+// Add / Sub / Mul / Div  src/ops/binary_elementwise.rs:395-560
+class BinaryOp : public Operator {
+ public:
+  int op;
+  const char* op_name;
+  BinaryOp(int o, const char* n) : op(o), op_name(n) {}
+  const char* name() const override { return op_name; }
+  bool can_run_in_place() const override { return true; }
+  bool is_commutative() const override { return op == RTG_BIN_ADD || op == RTG_BIN_MUL; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+};
+
+// MaxPool / AveragePool / GlobalAveragePool  src/ops/pooling.rs
+class PoolOp : public Operator {
+ public:
+  int kind = RTG_POOL_MAX;
+  bool global = false;
+  rtg_pool_attrs attrs = {};
+  const char* name() const override { return global ? "GlobalAveragePool" : kind == RTG_POOL_MAX ? "MaxPool" : "AveragePool"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+
+// Flatten {axis} / Reshape {allow_zero}  src/ops/layout.rs:131-340
+class ReshapeOp : public Operator {
+ public:
+  bool flatten = false;
+  int64_t axis = 1;
+  bool allow_zero = false;
+  const char* name() const override { return flatten ? "Flatten" : "Reshape"; }
+  bool can_run_in_place() const override { return true; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+
+ private:
+  rtg_status target_shape(Context* ctx, const rtg_tensor& x, const Value* shape_v, int64_t* shape, int* nd) const;
+};
+
+class IdentityOp : public Operator {
+ public:
+  const char* name() const override { return "Identity"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+
+// struct Gemm {alpha, beta, transpose_a, transpose_b}  src/ops/matmul.rs:13-19,83-117
+class GemmOp : public Operator {
+ public:
+  float alpha = 1.f, beta = 1.f;
+  bool trans_a = false, trans_b = false;
+  const char* name() const override { return "Gemm"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+
+// MatMul  src/ops/matmul.rs:241-254 ; FusedTranspose(MatMul) is expressed by a TransposeOp whose result is a view
+class MatMulOp : public Operator {
+ public:
+  bool has_bias = false;  // fused `+ bias[N]` (input 2) and activation, set by optimize_graph
+  int act = ACT_NONE;
+  const char* name() const override { return has_bias || act != ACT_NONE ? "FusedMatMul" : "MatMul"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+
+// operators_nn.cu: the remaining operators BERT-class graphs need
+class SoftmaxOp : public Operator {
+ public:
+  int64_t axis = -1;
+  const char* name() const override { return "Softmax"; }
+  bool can_run_in_place() const override { return true; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+};
+class LayerNormOp : public Operator {
+ public:
+  int64_t axis = -1;
+  float epsilon = 1e-5f;
+  const char* name() const override { return "LayerNormalization"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class TransposeOp : public Operator {
+ public:
+  std::vector<int64_t> perm;
+  bool has_perm = false;
+  const char* name() const override { return "Transpose"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class GatherOp : public Operator {
+ public:
+  int64_t axis = 0;
+  const char* name() const override { return "Gather"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class BatchNormOp : public Operator {
+ public:
+  float epsilon = 1e-5f;
+  const char* name() const override { return "BatchNormalization"; }
+  bool can_run_in_place() const override { return true; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+};
+class ShapeOpsOp : public Operator {  // Unsqueeze / Squeeze: metadata-only changes of a contiguous tensor
+ public:
+  bool squeeze = false;
+  const char* name() const override { return squeeze ? "Squeeze" : "Unsqueeze"; }
+  bool can_run_in_place() const override { return true; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+
+ private:
+  rtg_status new_shape(Context* ctx, const rtg_tensor& x, const Value* axes, int64_t* shape, int* nd) const;
+};
+
+}  // namespace rtg

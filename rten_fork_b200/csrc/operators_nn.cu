@@ -1,0 +1,413 @@
+// The remaining operators the target graphs need: Softmax, LayerNormalization, Transpose, Gather,
+// BatchNormalization, Unsqueeze / Squeeze.  Row reductions use warp shuffles; everything is HBM-bound.
+#include "operators.h"
+#include "vecmath.cuh"
+
+namespace rtg {
+
+namespace {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// softmax over `len` elements spaced `stride` apart; one warp per lane (outer, inner).
+// reference: rten-vecmath/src/softmax.rs (max-subtract, exp, normalise), src/ops/norm.rs softmax.
+__global__ void softmax_kernel(float* __restrict__ out, const float* __restrict__ in, int64_t lanes, int len,
+                               int64_t inner) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp; r < lanes; r += nwarps) {
+    const int64_t base = (r / inner) * len * inner + (r % inner);
+    float m = __int_as_float(0xff800000);
+    for (int i = lane; i < len; i += 32) m = fmaxf(m, in[base + i * inner]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int i = lane; i < len; i += 32) {
+      const float e = vm_exp(in[base + i * inner] - m);
+      out[base + i * inner] = e;
+      s += e;
+    }
+    s = warp_sum(s);
+    const float inv = __fdiv_rn(1.0f, s);
+    for (int i = lane; i < len; i += 32) out[base + i * inner] = out[base + i * inner] * inv;
+  }
+}
+
+// One warp per row of `len` contiguous elements (src/ops/norm.rs:245-299).
+__global__ void layer_norm_kernel(float* __restrict__ out, const float* __restrict__ in,
+                                  const float* __restrict__ scale, const float* __restrict__ bias, int64_t rows,
+                                  int len, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nwarps) {
+    const float* x = in + r * len;
+    float* y = out + r * len;
+    float s = 0.f;
+    for (int i = lane; i < len; i += 32) s += x[i];
+    const float mean = warp_sum(s) / static_cast<float>(len);
+    float q = 0.f;
+    for (int i = lane; i < len; i += 32) {
+      const float d = x[i] - mean;
+      q += d * d;
+    }
+    const float inv = 1.0f / sqrtf(warp_sum(q) / static_cast<float>(len) + eps);
+    for (int i = lane; i < len; i += 32) {
+      float v = (x[i] - mean) * inv * scale[i];
+      if (bias) v += bias[i];
+      y[i] = v;
+    }
+  }
+}
+
+// out[i, :] = table[idx[i], :]   (Gather on axis 0, the embedding lookup; src/ops/gather.rs)
+__global__ void gather_rows_kernel(uint32_t* __restrict__ out, const uint32_t* __restrict__ table,
+                                   const int32_t* __restrict__ idx, int64_t n_idx, int64_t row, int64_t n_rows,
+                                   int* __restrict__ err) {
+  const int64_t total = n_idx * row;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / row, c = i % row;
+    int64_t k = idx[r];
+    if (k < 0) k += n_rows;
+    if (k < 0 || k >= n_rows) {
+      *err = 1;
+      continue;
+    }
+    out[i] = table[k * row + c];
+  }
+}
+
+// y = (x - mean[c]) * (scale[c] / sqrt(var[c] + eps)) + bias[c]  with channel stride handling (NCHW or NHWC)
+__global__ void batch_norm_kernel(float* __restrict__ out, const float* __restrict__ in, const float* __restrict__ scale,
+                                  const float* __restrict__ bias, const float* __restrict__ mean,
+                                  const float* __restrict__ var, int64_t n, int c, int64_t inner, int chan_fastest,
+                                  float eps) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int ch = chan_fastest ? static_cast<int>(i % c) : static_cast<int>((i / inner) % c);
+    const float k = __fdiv_rn(scale[ch], __fsqrt_rn(__fadd_rn(var[ch], eps)));
+    out[i] = __fadd_rn(__fmul_rn(__fsub_rn(in[i], mean[ch]), k), bias[ch]);
+  }
+}
+
+int blocks_for(Context* ctx, int64_t items) {
+  return static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(div_ceil(items, 256), static_cast<int64_t>(ctx->num_sms) * 16)));
+}
+
+rtg_status resolve_axis(int ndim, int64_t axis, int* out) {
+  if (axis < -ndim || axis >= ndim) return set_error(RTG_ERR_INVALID_VALUE, "Axis is invalid");
+  *out = static_cast<int>(axis < 0 ? axis + ndim : axis);
+  return RTG_OK;
+}
+
+rtg_status make_contiguous(Context* ctx, const Value& v, Value* tmp, rtg_tensor* view) {
+  if (is_contiguous(v.t)) {
+    *view = v.t;
+    return RTG_OK;
+  }
+  RTG_TRY(alloc_value(ctx, v.t.dtype, v.t.ndim, v.t.shape, false, tmp));
+  RTG_TRY(copy_view(ctx, tmp->t, v.t));
+  *view = tmp->t;
+  return RTG_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- Softmax
+static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_attr, const rtg_tensor& y) {
+  if (x.ndim == 0) return set_error(RTG_ERR_INVALID_VALUE, "Axis is invalid");
+  int axis;
+  RTG_TRY(resolve_axis(x.ndim, axis_attr, &axis));
+  const int64_t len = x.shape[axis];
+  int64_t inner = 1, outer = 1;
+  for (int i = axis + 1; i < x.ndim; ++i) inner *= x.shape[i];
+  for (int i = 0; i < axis; ++i) outer *= x.shape[i];
+  const int64_t lanes = outer * inner;
+  if (lanes == 0 || len == 0) return RTG_OK;
+  softmax_kernel<<<blocks_for(ctx, lanes * 32), 256, 0, ctx->stream>>>(static_cast<float*>(y.data),
+                                                                      static_cast<const float*>(x.data), lanes,
+                                                                      static_cast<int>(len), inner);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+rtg_status SoftmaxOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  if (x->t.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  Value tmp, y;
+  rtg_tensor xv;
+  RTG_TRY(make_contiguous(ctx, *x, &tmp, &xv));
+  rtg_status st = alloc_value(ctx, RTG_F32, xv.ndim, xv.shape, false, &y);
+  if (st == RTG_OK) st = softmax_impl(ctx, xv, axis, y.t);
+  release_value(ctx, &tmp);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
+rtg_status SoftmaxOp::run_in_place(Context* ctx, Value* io, const OpInputs&) {
+  if (io->t.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  if (!is_contiguous(io->t)) {
+    OpInputs in;
+    in.v = {io};
+    std::vector<Value> outs;
+    RTG_TRY(run(ctx, in, &outs));
+    release_value(ctx, io);
+    *io = outs[0];
+    return RTG_OK;
+  }
+  return softmax_impl(ctx, io->t, axis, io->t);
+}
+
+// ---------------------------------------------------------------- LayerNormalization
+rtg_status LayerNormOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value *x, *scale;
+  RTG_TRY(in.require(0, &x));
+  RTG_TRY(in.require(1, &scale));
+  const Value* bias = in.get(2);
+  int ax;
+  RTG_TRY(resolve_axis(x->t.ndim, axis, &ax));
+  int64_t len = 1, rows = 1;
+  for (int i = ax; i < x->t.ndim; ++i) len *= x->t.shape[i];
+  for (int i = 0; i < ax; ++i) rows *= x->t.shape[i];
+  // scale / bias must cover exactly the normalised dims (the common case; general broadcast is not implemented)
+  if (numel(scale->t) != len) return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES, "`scale` cannot be broadcast to input shape");
+  if (bias && numel(bias->t) != len) return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES, "`bias` cannot be broadcast to input shape");
+  Value tmp, y;
+  rtg_tensor xv;
+  RTG_TRY(make_contiguous(ctx, *x, &tmp, &xv));
+  rtg_status st = alloc_value(ctx, RTG_F32, xv.ndim, xv.shape, false, &y);
+  if (st == RTG_OK && rows * len > 0) {
+    layer_norm_kernel<<<blocks_for(ctx, rows * 32), 256, 0, ctx->stream>>>(
+        static_cast<float*>(y.t.data), static_cast<const float*>(xv.data), static_cast<const float*>(scale->t.data),
+        bias ? static_cast<const float*>(bias->t.data) : nullptr, rows, static_cast<int>(len), epsilon);
+    ctx->launches++;
+    if (cudaGetLastError() != cudaSuccess) st = set_error(RTG_ERR_CUDA, "layer_norm launch failed");
+  }
+  release_value(ctx, &tmp);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- Transpose
+rtg_status TransposeOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  const int nd = x->t.ndim;
+  std::vector<int64_t> p = perm;
+  if (!has_perm) {
+    p.clear();
+    for (int i = nd - 1; i >= 0; --i) p.push_back(i);  // default: reverse the dims
+  }
+  if (static_cast<int>(p.size()) != nd) return set_error(RTG_ERR_INVALID_VALUE, "Permutation is invalid");
+  std::vector<char> seen(nd, 0);
+  for (int64_t a : p) {
+    if (a < 0 || a >= nd || seen[a]) return set_error(RTG_ERR_INVALID_VALUE, "Permutation is invalid");
+    seen[a] = 1;
+  }
+  rtg_tensor view = x->t;  // permuted view of the input
+  for (int i = 0; i < nd; ++i) view.shape[i] = x->t.shape[p[i]], view.strides[i] = x->t.strides[p[i]];
+  Value y;
+  RTG_TRY(alloc_value(ctx, x->t.dtype, nd, view.shape, false, &y));
+  rtg_status st = copy_view(ctx, y.t, view);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- Gather (axis 0 fast path: embedding lookup)
+rtg_status GatherOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value *x, *idx;
+  RTG_TRY(in.require(0, &x));
+  RTG_TRY(in.require(1, &idx));
+  if (idx->t.dtype != RTG_I32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  int ax;
+  RTG_TRY(resolve_axis(x->t.ndim, axis, &ax));
+  if (ax != 0) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "Gather is implemented for axis 0 only on the GPU path");
+  Value xt, it;
+  rtg_tensor xv, iv;
+  RTG_TRY(make_contiguous(ctx, *x, &xt, &xv));
+  rtg_status st = make_contiguous(ctx, *idx, &it, &iv);
+  int64_t shape[RTG_MAX_DIMS];
+  int nd = 0;
+  for (int i = 0; i < iv.ndim; ++i) shape[nd++] = iv.shape[i];
+  for (int i = 1; i < xv.ndim; ++i) {
+    if (nd >= RTG_MAX_DIMS) st = set_error(RTG_ERR_UNSUPPORTED_VALUE, "too many dimensions");
+    else shape[nd++] = xv.shape[i];
+  }
+  Value y;
+  if (st == RTG_OK) st = alloc_value(ctx, xv.dtype, nd, shape, false, &y);
+  if (st == RTG_OK) {
+    const int64_t n_idx = numel(iv), row = xv.shape[0] ? numel(xv) / xv.shape[0] : 0;
+    if (n_idx * row > 0) {
+      Scratch flag;
+      st = flag.alloc(ctx, 4);
+      if (st == RTG_OK) {
+        cudaMemsetAsync(flag.p, 0, 4, ctx->stream);
+        gather_rows_kernel<<<blocks_for(ctx, n_idx * row), 256, 0, ctx->stream>>>(
+            static_cast<uint32_t*>(y.t.data), static_cast<const uint32_t*>(xv.data),
+            static_cast<const int32_t*>(iv.data), n_idx, row, xv.shape[0], static_cast<int*>(flag.p));
+        ctx->launches++;
+        int bad = 0;
+        cudaMemcpyAsync(&bad, flag.p, 4, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        if (bad) st = set_error(RTG_ERR_INVALID_VALUE, "Entry in `indices` is out of range");
+      }
+    }
+  }
+  release_value(ctx, &xt);
+  release_value(ctx, &it);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- BatchNormalization
+static rtg_status batch_norm_impl(Context* ctx, float eps, const rtg_tensor& x, const OpInputs& params, size_t first,
+                                  const rtg_tensor& y) {
+  const Value* p[4];
+  for (int i = 0; i < 4; ++i) {
+    RTG_TRY(params.require(first + i, &p[i]));
+    if (p[i]->t.ndim != 1) return set_error(RTG_ERR_INVALID_VALUE, "scale must have 1 dims");
+    if (!is_contiguous(p[i]->t)) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "batch norm parameters must be dense");
+  }
+  if (x.ndim < 3) return set_error(RTG_ERR_INVALID_VALUE, "Input must have at least 3 dims");
+  const int c = static_cast<int>(x.shape[1]);
+  for (int i = 0; i < 4; ++i)
+    if (p[i]->t.shape[0] != c) return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES, "batch norm parameter length must match channels");
+  const int64_t n = numel(x);
+  if (n == 0) return RTG_OK;
+  const bool nhwc = x.ndim == 4 && is_nhwc_dense(x) && !is_contiguous(x);
+  if (!nhwc && !is_contiguous(x)) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "batch norm input must be dense");
+  int64_t inner = 1;
+  for (int i = 2; i < x.ndim; ++i) inner *= x.shape[i];
+  batch_norm_kernel<<<blocks_for(ctx, n), 256, 0, ctx->stream>>>(
+      static_cast<float*>(y.data), static_cast<const float*>(x.data), static_cast<const float*>(p[0]->t.data),
+      static_cast<const float*>(p[1]->t.data), static_cast<const float*>(p[2]->t.data),
+      static_cast<const float*>(p[3]->t.data), n, c, inner, nhwc ? 1 : 0, eps);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
+rtg_status BatchNormOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  Value y;
+  const bool nhwc = x->t.ndim == 4 && is_nhwc_dense(x->t) && !is_contiguous(x->t);
+  RTG_TRY(alloc_value(ctx, RTG_F32, x->t.ndim, x->t.shape, nhwc, &y));
+  rtg_status st = batch_norm_impl(ctx, epsilon, x->t, in, 1, y.t);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+rtg_status BatchNormOp::run_in_place(Context* ctx, Value* io, const OpInputs& rest) {
+  return batch_norm_impl(ctx, epsilon, io->t, rest, 0, io->t);
+}
+
+// ---------------------------------------------------------------- Unsqueeze / Squeeze
+rtg_status ShapeOpsOp::new_shape(Context* ctx, const rtg_tensor& x, const Value* axes_v, int64_t* shape, int* nd) const {
+  std::vector<int64_t> axes;
+  if (axes_v) RTG_TRY(host_ints(ctx, *axes_v, &axes));
+  if (squeeze) {
+    std::vector<char> drop(x.ndim, 0);
+    if (!axes_v) {
+      for (int i = 0; i < x.ndim; ++i) drop[i] = x.shape[i] == 1;
+    } else {
+      for (int64_t a : axes) {
+        int r;
+        RTG_TRY(resolve_axis(x.ndim, a, &r));
+        if (x.shape[r] != 1) return set_error(RTG_ERR_INVALID_VALUE, "Can only remove dimensions of size 1");
+        drop[r] = 1;
+      }
+    }
+    *nd = 0;
+    for (int i = 0; i < x.ndim; ++i)
+      if (!drop[i]) shape[(*nd)++] = x.shape[i];
+    return RTG_OK;
+  }
+  if (!axes_v) return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
+  const int out_nd = x.ndim + static_cast<int>(axes.size());
+  if (out_nd > RTG_MAX_DIMS) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "too many dimensions");
+  std::vector<char> is_new(out_nd, 0);
+  for (int64_t a : axes) {
+    int r;
+    RTG_TRY(resolve_axis(out_nd, a, &r));
+    if (is_new[r]) return set_error(RTG_ERR_INVALID_VALUE, "Axes must be unique");
+    is_new[r] = 1;
+  }
+  int src = 0;
+  for (int i = 0; i < out_nd; ++i) shape[i] = is_new[i] ? 1 : x.shape[src++];
+  *nd = out_nd;
+  return RTG_OK;
+}
+
+rtg_status ShapeOpsOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  int64_t shape[RTG_MAX_DIMS];
+  int nd;
+  RTG_TRY(new_shape(ctx, x->t, in.get(1), shape, &nd));
+  Value y;
+  RTG_TRY(alloc_value(ctx, x->t.dtype, x->t.ndim, x->t.shape, false, &y));
+  rtg_status st = copy_view(ctx, y.t, x->t);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  y.t.ndim = nd;
+  for (int i = 0; i < nd; ++i) y.t.shape[i] = shape[i];
+  set_contiguous_strides(y.t);
+  y.host_i32 = x->host_i32, y.host_f32 = x->host_f32;
+  out->push_back(y);
+  return RTG_OK;
+}
+
+rtg_status ShapeOpsOp::run_in_place(Context* ctx, Value* io, const OpInputs& rest) {
+  int64_t shape[RTG_MAX_DIMS];
+  int nd;
+  RTG_TRY(new_shape(ctx, io->t, rest.get(0), shape, &nd));
+  if (!is_contiguous(io->t)) {
+    OpInputs in;
+    in.v = {io, rest.get(0)};
+    std::vector<Value> outs;
+    RTG_TRY(run(ctx, in, &outs));
+    release_value(ctx, io);
+    *io = outs[0];
+    return RTG_OK;
+  }
+  io->t.ndim = nd;
+  for (int i = 0; i < nd; ++i) io->t.shape[i] = shape[i];
+  set_contiguous_strides(io->t);
+  return RTG_OK;
+}
+
+}  // namespace rtg

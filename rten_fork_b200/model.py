@@ -1,0 +1,117 @@
+"""``Model`` — mirror of the reference's model API (src/model.rs:214-263 load / load_file, :580-646 run / run_one)
+over the C-ABI ``rtg_model_*`` entry points.  The graph executes on the GPU; inputs may be numpy arrays (uploaded
+inside ``run``) or torch CUDA tensors (consumed in place), outputs come back in the reference layout."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .context import Context, as_tensor, default_context
+
+
+class Model:
+    def __init__(self, handle, ctx: Context):
+        self._h, self.ctx = handle, ctx
+
+    # -- loading (ModelOptions::{with_all_ops, enable_optimization}, src/model.rs:155-207)
+    @classmethod
+    def load(cls, data: bytes, optimize: bool = True, ctx: Context | None = None) -> "Model":
+        ctx = ctx or default_context()
+        h = C.c_void_p()
+        buf = (C.c_char * len(data)).from_buffer_copy(data)
+        N.check(N.lib().rtg_model_load(ctx.handle, buf, C.c_size_t(len(data)), C.c_int32(bool(optimize)), C.byref(h)))
+        return cls(h, ctx)
+
+    @classmethod
+    def load_file(cls, path: str, optimize: bool = True, ctx: Context | None = None) -> "Model":
+        ctx = ctx or default_context()
+        h = C.c_void_p()
+        N.check(N.lib().rtg_model_load_file(ctx.handle, path.encode(), C.c_int32(bool(optimize)), C.byref(h)))
+        return cls(h, ctx)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().rtg_model_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- metadata (Model::input_ids / output_ids / node_info, src/model.rs:524-578)
+    def _info(self, fn, i):
+        name = C.c_char_p()
+        shape = (C.c_int64 * N.RTG_MAX_DIMS)()
+        nd, dt = C.c_int32(), C.c_int32()
+        N.check(fn(self._h, C.c_int32(i), C.byref(name), shape, C.byref(nd), C.byref(dt)))
+        dims = None if nd.value < 0 else [None if shape[k] < 0 else shape[k] for k in range(nd.value)]
+        return {"name": (name.value or b"").decode(), "shape": dims}
+
+    @property
+    def inputs(self):
+        n = C.c_int32()
+        N.check(N.lib().rtg_model_num_inputs(self._h, C.byref(n)))
+        return [self._info(N.lib().rtg_model_input_info, i) for i in range(n.value)]
+
+    @property
+    def outputs(self):
+        n = C.c_int32()
+        N.check(N.lib().rtg_model_num_outputs(self._h, C.byref(n)))
+        return [self._info(N.lib().rtg_model_output_info, i) for i in range(n.value)]
+
+    @property
+    def num_ops(self) -> int:
+        n = C.c_int32()
+        N.check(N.lib().rtg_model_num_ops(self._h, C.byref(n)))
+        return n.value
+
+    # -- RunOptions {timing} (src/graph.rs:467-483)
+    def set_timing(self, enabled: bool):
+        N.check(N.lib().rtg_model_set_timing(self._h, C.c_int32(bool(enabled))))
+
+    def timing_report(self) -> str:
+        N.lib().rtg_model_timing_report.restype = C.c_char_p
+        return N.lib().rtg_model_timing_report(self._h).decode()
+
+    # -- Model::run: inputs in graph-input order; returns numpy arrays (or fills ``out`` buffers)
+    def run(self, inputs, out=None):
+        descs = (N.Tensor * len(inputs))()
+        keep = []
+        for i, x in enumerate(inputs):
+            if isinstance(x, np.ndarray) and not x.flags.c_contiguous:
+                x = np.ascontiguousarray(x)
+            keep.append(x)
+            descs[i] = as_tensor(x)
+        run = C.c_void_p()
+        N.check(N.lib().rtg_model_run(self._h, descs, C.c_int32(len(inputs)), C.byref(run)))
+        try:
+            n = C.c_int32()
+            N.check(N.lib().rtg_run_num_outputs(run, C.byref(n)))
+            results = []
+            for i in range(n.value):
+                shape = (C.c_int64 * N.RTG_MAX_DIMS)()
+                nd, dt = C.c_int32(), C.c_int32()
+                N.check(N.lib().rtg_run_output_info(run, C.c_int32(i), shape, C.byref(nd), C.byref(dt)))
+                shp = tuple(shape[k] for k in range(nd.value))
+                if out is not None and out[i] is not None:
+                    dst = out[i]
+                else:
+                    dst = np.empty(shp, dtype=np.float32 if dt.value == N.RTG_F32 else np.int32)
+                if isinstance(dst, np.ndarray):
+                    ptr, nbytes, dev = dst.ctypes.data, dst.nbytes, N.RTG_HOST
+                else:  # torch tensor (pinned host or CUDA)
+                    ptr, nbytes = dst.data_ptr(), dst.numel() * dst.element_size()
+                    dev = dst.device.index if dst.is_cuda else N.RTG_HOST
+                N.check(N.lib().rtg_run_output_copy(run, C.c_int32(i), C.c_void_p(ptr), C.c_size_t(nbytes), C.c_int32(dev)))
+                results.append(dst)
+            return results
+        finally:
+            N.lib().rtg_run_free(run)
+
+    def run_one(self, x, out=None):
+        """Model::run_one (src/model.rs:620-637): single input, single output."""
+        return self.run([x], None if out is None else [out])[0]

@@ -20,8 +20,8 @@ import numpy as np
 from . import _native as N
 from .context import Context, as_tensor, default_context
 
-ACT = {"none": 0, "relu": 1, "clip": 2, "gelu": 3, "sigmoid": 4, "silu": 5, "erf": 6}
-BIN = {"add": 0, "sub": 1, "mul": 2, "div": 3}
+ACT = {"none": 0, "relu": 1, "clip": 2, "gelu": 3, "sigmoid": 4, "silu": 5, "erf": 6, "tanh": 7, "sqrt": 8}
+BIN = {"add": 0, "sub": 1, "mul": 2, "div": 3, "pow": 4}
 
 
 def _is_torch(x):
@@ -202,6 +202,14 @@ def erf(x, **kw):
     return _unary("erf", x, **kw)
 
 
+def tanh(x, **kw):
+    return _unary("tanh", x, **kw)
+
+
+def sqrt(x, **kw):
+    return _unary("sqrt", x, **kw)
+
+
 def clip(x, min_val=None, max_val=None, **kw):
     lo = float(np.finfo(np.float32).min) if min_val is None else float(min_val)
     hi = float(np.finfo(np.float32).max) if max_val is None else float(max_val)
@@ -235,6 +243,10 @@ def mul(a, b, **kw):
 
 def div(a, b, **kw):
     return _binary("div", a, b, **kw)
+
+
+def pow(a, b, **kw):  # noqa: A001 - mirrors the reference operator name
+    return _binary("pow", a, b, **kw)
 
 
 def _pool_attrs(kernel_size, strides, padding, count_include_pad=False):
