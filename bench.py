@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 batch-32 inference (BASELINE.json configs[1]) through Model.run on B200.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--math 3xtf32|tf32]
+
+One step = one Graph::run over one batch of 32 synthetic 3x224x224 images per GPU (weak scaling: the batch of
+Graph::run is sharded per GPU, no data-path collective).  Prints ONE JSON line on rank 0.
+
+  value      images/s with the input batch already resident in HBM (device-timed, CUDA events, L2 flushed
+             between steps, max over ranks)
+  e2e        the same through the public API with pinned HOST input and HOST output (H2D + D2H inside the timed
+             region)
+  roofline   the tcgen05 contraction kernel (all conv / fc launches): algorithmic flops / measured launch time vs
+             the measured TF32 tensor peak (MEASURED_PEAKS.json bf16 / 2)
+  cpu_baseline  the oracle's CPU restatement of the reference (same graph, same weights) on the host cores
+
+`--impl reference` times only that CPU restatement (the reference is Rust; no Rust toolchain here — DESIGN.md).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BATCH = 32
+IMAGE = 224
+CLASSES = 1000
+FLOP_PER_IMAGE = None  # filled from the graph
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--math", default="3xtf32", choices=["3xtf32", "tf32"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget for the bounded cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def graph_flops(builder, batch):
+    """Algorithmic flops of the contraction operators (2*M*N*K per Conv / Gemm / MatMul) for `batch` images."""
+    shapes = {}
+    for i, nd in enumerate(builder.nodes):
+        if nd["kind"] == "const":
+            shapes[i] = nd["data"].shape
+    total = 0.0
+    # walk with a shape-only evaluation: convs need the spatial size of their output
+    hw = {builder.inputs[0]: (IMAGE, IMAGE)}
+    for nd in builder.nodes:
+        if nd["kind"] != "op":
+            continue
+        t, ins, out = nd["type"], nd["inputs"], nd["outputs"][0]
+        attrs = {fid: val for fid, _k, val in nd["attrs"][1]} if nd["attrs"] else {}
+        if t == "Conv":
+            o, cg, kh, kw = shapes[ins[1]]
+            h, w = hw[ins[0]]
+            pads = attrs.get(1) or (0, 0, 0, 0)
+            s = attrs.get(3) or (1, 1)
+            oh = (h + pads[0] + pads[2] - kh) // s[0] + 1
+            ow = (w + pads[1] + pads[3] - kw) // s[1] + 1
+            hw[out] = (oh, ow)
+            total += 2.0 * batch * oh * ow * o * cg * kh * kw
+        elif t in ("MaxPool", "AveragePool"):
+            h, w = hw[ins[0]]
+            k = attrs[0]
+            pads = attrs.get(2) or (0, 0, 0, 0)
+            s = attrs.get(3) or (1, 1)
+            hw[out] = ((h + pads[0] + pads[2] - k[0]) // s[0] + 1, (w + pads[1] + pads[3] - k[1]) // s[1] + 1)
+        elif t == "Gemm":
+            n, k = shapes[ins[1]]
+            total += 2.0 * batch * n * k
+        elif t == "GlobalAveragePool":
+            hw[out] = (1, 1)
+        else:
+            if ins and ins[0] in hw:
+                hw[out] = hw[ins[0]]
+    return total
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------- CPU restatement arm
+def cpu_resnet(builder, seconds, batch_cap=BATCH, steps=None, warmup=1):
+    """Times the oracle's CPU evaluation of the same ResNet-50 graph (same weights) with every host thread.
+    Returns (images/s, threads, sample description, ms per step, batch)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import graph_oracle
+    import oracle as o
+
+    o.build()
+    threads = o.num_threads()
+    rng = o.XorShiftRng(1234)
+    # calibrate on 2 images so that the bounded sample fits the budget
+    x2 = rng.fill((2, 3, IMAGE, IMAGE))
+    graph_oracle.run_graph(builder, [x2])
+    t0 = time.perf_counter()
+    graph_oracle.run_graph(builder, [x2])
+    per_img = (time.perf_counter() - t0) / 2
+    if steps is None:
+        batch = int(max(1, min(batch_cap, seconds / 3 / per_img)))
+        steps = int(max(1, min(5, seconds / (per_img * batch) - warmup)))
+    else:
+        batch = int(max(1, min(batch_cap, seconds / (steps + warmup) / per_img)))
+    x = rng.fill((batch, 3, IMAGE, IMAGE))
+    for _ in range(warmup):
+        graph_oracle.run_graph(builder, [x])
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        graph_oracle.run_graph(builder, [x])
+    dt = time.perf_counter() - t0
+    sample = (f"ResNet-50 full graph, batch {batch} x {steps} steps ({warmup} warm-up), CPU restatement of the reference "
+              f"(AVX2 6x16 kernel, reference blocking), {threads} threads")
+    return batch * steps / dt, threads, sample, dt / steps * 1e3, batch
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from rten_fork_b200 import synth
+
+    builder = synth.resnet50(image=IMAGE, classes=CLASSES, seed=0)
+    ips, threads, sample, ms, batch = cpu_resnet(builder, seconds=150.0, steps=args.steps, warmup=max(1, min(args.warmup, 3)))
+    line = {
+        "impl": "reference", "metric": "resnet50_b32_images_per_sec", "value": ips, "unit": "images/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ResNet-50 .rten, random-init weights, batch 32 3x224x224", "sample_batch": batch},
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------ GPU arm
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tf32_burst": d["bf16_tflops"] / 2, "tf32_sustained": d["bf16_tflops_sustained"] / 2,
+                "source": "MEASURED_PEAKS.json (bf16 cuBLAS / 2 for TF32)"}
+    return {"hbm_gbs": 6650.0, "tf32_burst": 795.0, "tf32_sustained": 795.0, "source": "fallback (B200_PROFILING.md, bf16 1.59 PF / 2)"}
+
+
+def timed_device_steps(torch, model, stream, x_dev, out_dev, flush, steps):
+    """K steps, each bracketed by CUDA events on the launching stream, L2 flushed (256 MiB write) before each."""
+    evs = []
+    with torch.cuda.stream(stream):
+        for _ in range(steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            model.run([x_dev], out=[out_dev])
+            e1.record(stream)
+            evs.append((e0, e1))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs)
+
+
+def timed_e2e_steps(torch, model, stream, x_host, out_host, flush, steps):
+    """K steps through the public API with pinned host input / output: H2D, graph, D2H and the final synchronise are
+    inside each step's timed span; the L2 flush between steps is not."""
+    total = 0.0
+    with torch.cuda.stream(stream):
+        for _ in range(steps):
+            flush.zero_()
+            stream.synchronize()
+            t0 = time.perf_counter()
+            model.run([x_host], out=[out_host])   # returns after the D2H copy has completed
+            total += time.perf_counter() - t0
+    return total * 1e3
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    import rten_fork_b200 as R
+    from rten_fork_b200 import synth
+
+    ctx = R.Context(local)
+    stream = torch.cuda.Stream(device=local)
+    ctx.set_stream(stream.cuda_stream)
+    math = R.MATH_3XTF32 if args.math == "3xtf32" else R.MATH_TF32
+    ctx.set_math(math)
+    builder = synth.resnet50(image=IMAGE, classes=CLASSES, seed=0)
+    flops_step = graph_flops(builder, args.batch)
+    model = R.Model.load(builder.build(), ctx=ctx)
+
+    gen = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    x_host = torch.rand((args.batch, 3, IMAGE, IMAGE), generator=gen, dtype=torch.float32).pin_memory()
+    out_host = torch.empty((args.batch, CLASSES), dtype=torch.float32).pin_memory()
+    x_dev = x_host.to(f"cuda:{local}")
+    out_dev = torch.empty((args.batch, CLASSES), dtype=torch.float32, device=f"cuda:{local}")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # warm-up (also fills the weight cache, tensor maps and the pool)
+    timed_device_steps(torch, model, stream, x_dev, out_dev, flush, max(args.warmup, 3))
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    l0 = ctx.launch_count
+    ms_total = timed_device_steps(torch, model, stream, x_dev, out_dev, flush, args.steps)
+    launches = ctx.launch_count - l0
+    barrier()
+    ms_total = max_over_ranks(ms_total)
+
+    # end-to-end (host buffers)
+    timed_e2e_steps(torch, model, stream, x_host, out_host, flush, 2)
+    barrier()
+    e2e_ms = timed_e2e_steps(torch, model, stream, x_host, out_host, flush, args.steps)
+    barrier()
+    e2e_ms = max_over_ranks(e2e_ms)
+    clocks = sampler.stop() if rank == 0 else None
+    same = bool(torch.equal(out_host.to(out_dev.device), out_dev))
+
+    # dominant kernel: every launch of the tcgen05 contraction kernel bracketed by events on its own stream
+    ctx.set_kernel_timing(True)
+    timed_device_steps(torch, model, stream, x_dev, out_dev, flush, 3)
+    kt = ctx.kernel_timing()
+    ctx.set_kernel_timing(False)
+
+    # the other contraction mode, for the record
+    other = R.MATH_TF32 if math == R.MATH_3XTF32 else R.MATH_3XTF32
+    ctx.set_math(other)
+    timed_device_steps(torch, model, stream, x_dev, out_dev, flush, 3)
+    other_ms = max_over_ranks(timed_device_steps(torch, model, stream, x_dev, out_dev, flush, args.steps))
+    ctx.set_kernel_timing(True)
+    timed_device_steps(torch, model, stream, x_dev, out_dev, flush, 3)
+    kt_other = ctx.kernel_timing()
+    ctx.set_kernel_timing(False)
+    ctx.set_math(math)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = load_peaks()
+    images = args.batch * world * args.steps
+    tf = lambda k: k["flops"] / (k["ms"] * 1e-3) / 1e12 if k["ms"] > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(args.math)
+    line = {
+        "metric": "resnet50_b32_images_per_sec", "value": images / (ms_total * 1e-3), "unit": "images/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "3xtf32 (fp32-accurate split TF32 on tcgen05, fp32 accumulate)" if args.math == "3xtf32" else "tf32",
+        "data": "synthetic",
+        "config": {"workload": "ResNet-50 .rten, random-init weights, batch 32 3x224x224 per GPU (Conv+MatMul)",
+                   "batch_per_gpu": args.batch, "math": args.math, "l2": "256 MiB flush write before every step",
+                   "gflop_per_step_per_gpu": flops_step / 1e9, "parallelism": f"batch-sharded x{world}, no collective"},
+        "tflops": flops_step * world * args.steps / (ms_total * 1e-3) / 1e12,
+        "clocks": clocks,
+        "e2e": {"value": images / (e2e_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4,
+                "matches_device_run": same},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (all Conv / Gemm launches of a step)",
+                     "achieved": tf(kt), "peak": peaks["tf32_sustained"], "unit": "TFLOP/s",
+                     "frac": tf(kt) / peaks["tf32_sustained"], "traffic": traffic,
+                     "launches_per_step": kt["launches"] // 3, "kernel_ms_per_step": kt["ms"] / 3,
+                     "kernel_share_of_step": (kt["ms"] / 3) / (ms_total / args.steps),
+                     "algorithmic_gbytes_per_step": kt["bytes"] / 3 / 1e9,
+                     "peak_source": peaks["source"] + ", sustained",
+                     "note": "achieved counts algorithmic flops once; 3xTF32 issues 3 MMAs per product"},
+        "other_mode": {"math": "tf32" if other == R.MATH_TF32 else "3xtf32",
+                       "value": images / (other_ms * 1e-3), "ms_per_step": other_ms / args.steps,
+                       "kernel_tflops": tf(kt_other), "kernel_frac": tf(kt_other) / peaks["tf32_sustained"]},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        ips, threads, sample, _ms, _b = cpu_resnet(builder, seconds=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -75,6 +75,12 @@ rtg_status rtg_ctx_sync(rtg_ctx* ctx);
 rtg_status rtg_ctx_launch_count(rtg_ctx* ctx, uint64_t* count);
 /* Name of the GEMM kernel variant chosen by the last contraction call (diagnostics / tests). */
 const char* rtg_ctx_last_kernel(rtg_ctx* ctx);
+/* Measurement aid (no reference counterpart; the reference's RunOptions::timing works per operator, src/graph.rs
+ * :467-483): when enabled, every launch of the tcgen05 contraction kernel is bracketed by CUDA events on the context
+ * stream.  rtg_ctx_kernel_timing synchronises, returns the number of launches recorded since the last call, their summed
+ * device time, and their algorithmic flops (2*M*N*K with the true K) and bytes (operands once + output), then clears. */
+rtg_status rtg_ctx_set_kernel_timing(rtg_ctx* ctx, int32_t enabled);
+rtg_status rtg_ctx_kernel_timing(rtg_ctx* ctx, uint64_t* launches, double* total_ms, double* flops, double* bytes);
 
 /* TensorPool::alloc / add / alloc_count / hit_count / len      src/tensor_pool.rs:129-192 */
 rtg_status rtg_pool_alloc(rtg_ctx* ctx, size_t bytes, void** dptr);

@@ -61,6 +61,16 @@ class Context:
     def last_kernel(self) -> str:
         return N.lib().rtg_ctx_last_kernel(self._h).decode()
 
+    def set_kernel_timing(self, enabled: bool):
+        N.check(N.lib().rtg_ctx_set_kernel_timing(self._h, C.c_int32(bool(enabled))))
+
+    def kernel_timing(self):
+        """Launch count, summed device ms, algorithmic flops and bytes of the contraction-kernel launches recorded
+        since the last call (synchronises the stream)."""
+        n, ms, fl, by = C.c_uint64(), C.c_double(), C.c_double(), C.c_double()
+        N.check(N.lib().rtg_ctx_kernel_timing(self._h, C.byref(n), C.byref(ms), C.byref(fl), C.byref(by)))
+        return {"launches": n.value, "ms": ms.value, "flops": fl.value, "bytes": by.value}
+
     # -- TensorPool surface (alloc / add / stats)
     def pool_alloc(self, nbytes: int) -> int:
         p = C.c_void_p()

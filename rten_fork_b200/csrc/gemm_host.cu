@@ -106,9 +106,20 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
   }
   const int m_tiles = (args.M + kBM - 1) / kBM, n_tiles = (args.N + BN - 1) / BN;
   const int grid = std::min(m_tiles * n_tiles, ctx->num_sms);
+  Context::KernelRec rec{};
+  if (ctx->ktiming) {
+    RTG_CUDA(cudaEventCreate(&rec.a));
+    RTG_CUDA(cudaEventCreate(&rec.b));
+    rec.flops = ctx->pending_flops, rec.bytes = ctx->pending_bytes;
+    RTG_CUDA(cudaEventRecord(rec.a, ctx->stream));
+  }
   kern<<<grid, Cfg::kThreads, Cfg::kSmemBytes, ctx->stream>>>(ma, mb, args);
   ctx->launches++;
   RTG_CUDA(cudaGetLastError());
+  if (ctx->ktiming) {
+    RTG_CUDA(cudaEventRecord(rec.b, ctx->stream));
+    ctx->krecs.push_back(rec);
+  }
   char name[96];
   snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s>", BN, MODE ? "3xTF32" : "TF32",
            A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
@@ -213,6 +224,9 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   g.act_lo = ep.act_lo;
   g.act_hi = ep.act_hi;
   g.flags = debug_flags();
+  ctx->pending_flops = 2.0 * g.M * g.N * g.K;
+  ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
+                              static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
   if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g);
   return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g);
 }
@@ -290,6 +304,12 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   a.ic.kh = g.kh;
   a.ic.c_blocks = c_blocks;
   a.ic.c_off = g.c_off;
+  // algorithmic work of this launch: true K = C/g * kh * kw (not the per-tap padded K the tiles walk); bytes = the
+  // input image slice once + weights + output (+ residual)
+  const double k_true = static_cast<double>(g.cg) * g.kh * g.kw;
+  ctx->pending_flops = 2.0 * M * og * k_true;
+  ctx->pending_bytes = 4.0 * (static_cast<double>(g.n) * g.h * g.w * g.cg + og * k_true +
+                              static_cast<double>(M) * og * (a.R ? 2 : 1));
   return dispatch<1, 0>(ctx, bn, ctx->math, ma, mb, a);
 }
 

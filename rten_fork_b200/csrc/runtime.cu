@@ -181,6 +181,34 @@ rtg_status rtg_ctx_launch_count(rtg_ctx* ctx, uint64_t* count) {
   return RTG_OK;
 }
 
+rtg_status rtg_ctx_set_kernel_timing(rtg_ctx* ctx, int32_t enabled) {
+  Context* c = reinterpret_cast<Context*>(ctx);
+  if (!c) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  c->ktiming = enabled != 0;
+  return RTG_OK;
+}
+
+rtg_status rtg_ctx_kernel_timing(rtg_ctx* ctx, uint64_t* launches, double* total_ms, double* flops, double* bytes) {
+  Context* c = reinterpret_cast<Context*>(ctx);
+  if (!c) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(c->device));
+  RTG_CUDA(cudaStreamSynchronize(c->stream));
+  double ms = 0, fl = 0, by = 0;
+  for (auto& r : c->krecs) {
+    float t = 0;
+    cudaEventElapsedTime(&t, r.a, r.b);
+    ms += t, fl += r.flops, by += r.bytes;
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  if (launches) *launches = c->krecs.size();
+  if (total_ms) *total_ms = ms;
+  if (flops) *flops = fl;
+  if (bytes) *bytes = by;
+  c->krecs.clear();
+  return RTG_OK;
+}
+
 const char* rtg_ctx_last_kernel(rtg_ctx* ctx) {
   Context* c = reinterpret_cast<Context*>(ctx);
   return c ? c->last_kernel.c_str() : "";

@@ -75,6 +75,15 @@ struct Context {
   EncodeTiledFn encode_tiled = nullptr;
   EncodeIm2colFn encode_im2col = nullptr;
   int driver_version = 0;
+  // Optional per-launch timing of the contraction kernel (bench.py's roofline): CUDA events recorded on `stream`
+  // around every gemm_tcgen05 launch together with that launch's algorithmic flops / bytes.
+  struct KernelRec {
+    cudaEvent_t a, b;
+    double flops, bytes;
+  };
+  bool ktiming = false;
+  std::vector<KernelRec> krecs;
+  double pending_flops = 0, pending_bytes = 0;  // set by the caller of the next contraction launch
   // Pre-arranged weights, keyed by (source pointer, tag).  The role of PackedAMatrix / PackedBMatrix
   // (src/gemm.rs:26-92), except that entries persist across calls for constant operands.
   std::mutex cache_mu;
