@@ -96,7 +96,8 @@ static int debug_flags() {
 
 // ---------------------------------------------------------------- launch
 template <int BN, int MODE, int A_KIND, int B_MAJOR>
-static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& args) {
+static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
+                         const CUtensorMap& mr, const GemmArgs& args) {
   using Cfg = GemmCfg<BN, MODE>;
   auto kern = gemm_tcgen05_kernel<BN, MODE, A_KIND, B_MAJOR>;
   static bool configured[16] = {};  // per device
@@ -113,7 +114,7 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     rec.flops = ctx->pending_flops, rec.bytes = ctx->pending_bytes;
     RTG_CUDA(cudaEventRecord(rec.a, ctx->stream));
   }
-  kern<<<grid, Cfg::kThreads, Cfg::kSmemBytes, ctx->stream>>>(ma, mb, args);
+  kern<<<grid, Cfg::kThreads, Cfg::kSmemBytes, ctx->stream>>>(ma, mb, md, mr, args);
   ctx->launches++;
   RTG_CUDA(cudaGetLastError());
   if (ctx->ktiming) {
@@ -129,14 +130,31 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
 
 template <int A_KIND, int B_MAJOR>
 static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           const GemmArgs& args) {
+                           GemmArgs args) {
+  // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
+  CUtensorMap md = ma, mr = ma;
+  auto stageable = [&](const float* p, const OutMap& om) {
+    if (!p || om.hw > 0) return false;
+    if ((reinterpret_cast<uintptr_t>(p + om.chan_off) & 15) != 0) return false;
+    return args.M == 1 || (om.ld > 0 && om.ld % 4 == 0);
+  };
+  if (!(args.flags & 8) && stageable(args.D, args.dmap)) {
+    const uint64_t ld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.dmap.ld;
+    RTG_TRY(encode_2d(ctx, &md, args.D + args.dmap.chan_off, args.N, args.M, ld, 32, 32));
+    args.flags |= kFlagStagedD;
+    if (stageable(args.R, args.rmap)) {
+      const uint64_t rld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.rmap.ld;
+      RTG_TRY(encode_2d(ctx, &mr, args.R + args.rmap.chan_off, args.N, args.M, rld, 32, 32));
+      args.flags |= kFlagStagedR;
+    }
+  }
   if (mode == RTG_MATH_TF32) {
-    if (bn == 64) return launch<64, 0, A_KIND, B_MAJOR>(ctx, ma, mb, args);
-    if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, args);
-    if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, args);
+    if (bn == 64) return launch<64, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
+    if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
+    if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
   } else {
-    if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, args);
-    if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, args);
+    if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
+    if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
   }
   return set_error(RTG_ERR_INTERNAL, "bad BN");
 }

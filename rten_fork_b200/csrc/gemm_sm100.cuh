@@ -67,6 +67,10 @@ struct GemmArgs {
   Im2colArgs ic;
 };
 
+constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
+constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
+constexpr int kFlagStagedR = 4;  // residual arrives by TMA load into the same staging buffer (needs kFlagStagedD)
+
 constexpr int kBM = 128;
 constexpr int kBK = 32;  // floats per k-block (128 bytes)
 constexpr int kABytes = kBM * kBK * 4;
@@ -78,13 +82,19 @@ struct GemmCfg {
   static constexpr int kBBytes = BN * kBK * 4;
   static constexpr int kRawBytes = kABytes + kBBytes;
   static constexpr int kStageBytes = kRawBytes * (MODE ? 2 : 1);
-  static constexpr int kMaxSmem = 227 * 1024 - 2048;  // barriers + alignment slack
+  // Epilogue staging: every epilogue warp owns kEpiBufs buffers of 32 rows x 128 bytes (one 32-column chunk of its
+  // 32 accumulator rows, 128B-swizzled) through which the residual arrives (TMA load) and the result leaves (TMA
+  // store), so that global traffic is whole 128-byte rows instead of one strided 16-byte access per lane.
+  static constexpr int kEpiWarps = MODE ? 8 : 4;
+  static constexpr int kEpiBufs = MODE ? 1 : 2;
+  static constexpr int kEpiBufBytes = 4096;
+  static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
+  static constexpr int kMaxSmem = 227 * 1024 - 2048 - kEpiBytes;  // barriers + alignment slack
   static constexpr int kStagesRaw = kMaxSmem / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 512 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
   // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
   // and 6 split warps so that the operand split keeps up with the tensor core.
-  static constexpr int kEpiWarps = MODE ? 8 : 4;
   static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
   static constexpr int kXfThreads = MODE ? 192 : 0;
   static constexpr int kThreads = (kEpiWarps + 2) * 32 + kXfThreads;
@@ -105,6 +115,7 @@ __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& b
 template <int BN, int MODE, int A_KIND, int B_MAJOR>
 __global__ void __launch_bounds__(GemmCfg<BN, MODE>::kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
                     const GemmArgs args) {
   using Cfg = GemmCfg<BN, MODE>;
   constexpr int kStages = Cfg::kStages;
@@ -113,13 +124,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   // 128B swizzle atoms need 1024-byte aligned tiles.
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  const uint32_t epi_base = smem_base + kStages * Cfg::kStageBytes;
+  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto xf_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (3 * kStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (3 * kStages + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (3 * kStages + 4);
+  auto rbar = [&](int w, int b) { return bar_base + 8u * (3 * kStages + 5 + w * Cfg::kEpiBufs + b); };
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
 
@@ -135,6 +148,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == kTmaWarp && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (args.flags & kFlagStagedD) ptx::prefetch_tmap(&tmD);
+    if (args.flags & kFlagStagedR) ptx::prefetch_tmap(&tmR);
   }
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -146,6 +161,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       ptx::mbar_init(tfull_bar(a), 1);
       ptx::mbar_init(tempty_bar(a), Cfg::kEpiWarps * 32);
     }
+    for (int w = 0; w < Cfg::kEpiWarps; ++w)
+      for (int b = 0; b < Cfg::kEpiBufs; ++b) ptx::mbar_init(rbar(w, b), 1);
     ptx::fence_mbar_init();
   }
   if (warp == kMmaWarp) {
@@ -275,6 +292,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     constexpr int kCols = Cfg::kColsPerThread;
     const int col0 = (warp >> 2) * kCols;  // first tile column this warp handles
+    const bool staged_d = (args.flags & kFlagStagedD) != 0;
+    const bool staged_r = (args.flags & kFlagStagedR) != 0;
+    const uint32_t ebuf0 = epi_base + warp * Cfg::kEpiBufs * Cfg::kEpiBufBytes;
+    int eb = 0;            // staging buffer of the next chunk
+    uint32_t rph = 0;      // phase bit per staging buffer of this warp's residual barriers
     int as = 0;
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -288,12 +310,68 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const float row_bias = (args.bias_mode == BIAS_ROW && row_ok) ? args.bias[m] : 0.f;
       const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 
-      // alpha / beta / bias / activation on 32 consecutive columns starting at n0 + c0, then store
+      // residual chunk (32 rows x 32 columns at column c0 of the tile) -> staging buffer b, by TMA
+      auto fetch_residual = [&](int c0, int b) {
+        if (lane == 0) {
+          ptx::bulk_wait_read<0>();  // earlier stores of this warp no longer read the buffer
+          ptx::mbar_expect_tx(rbar(warp, b), Cfg::kEpiBufBytes);
+          ptx::tma_load_2d(ebuf0 + b * Cfg::kEpiBufBytes, &tmR, rbar(warp, b), n0 + c0, m0 + q * 32);
+        }
+      };
+
+      // alpha / bias / residual / activation on 32 consecutive columns starting at n0 + c0, then store
       auto finish = [&](float (&v)[32], int c0) {
-        if (!row_ok) return;
         const int ncols = min(32, args.N - (n0 + c0));
-        const bool vec_ok = (d_cs == 1) && (ncols == 32) && (((d_base + n0 + c0) & 3) == 0) &&
-                            ((reinterpret_cast<uintptr_t>(args.D) & 15) == 0);
+        if (staged_d) {
+          const uint32_t buf = ebuf0 + eb * Cfg::kEpiBufBytes;
+          if (staged_r) {
+            ptx::mbar_wait(rbar(warp, eb), (rph >> eb) & 1u);
+            rph ^= 1u << eb;
+          } else {
+            if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>();
+            __syncwarp();
+          }
+          const uint32_t row = buf + lane * 128;
+          const uint32_t sw = lane & 7;
+          if (staged_r) {
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 r = ptx::lds_v4(row + ((j4 ^ sw) << 4));
+              const float rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float x = args.alpha * v[4 * j4 + e];
+                if (args.bias_mode == BIAS_ROW) x += row_bias;
+                if (args.bias_mode == BIAS_COL && 4 * j4 + e < ncols) x += __ldg(args.bias + n0 + c0 + 4 * j4 + e);
+                v[4 * j4 + e] = x + args.beta * rr[e];
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int n = n0 + c0 + j;
+              float x = args.alpha * v[j];
+              if (args.bias_mode == BIAS_ROW) x += row_bias;
+              if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
+              if (args.R != nullptr && j < ncols && row_ok)
+                x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
+              v[j] = x;
+            }
+          }
+          apply_act_array(v, args.act, args.act_lo, args.act_hi);
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4)
+            ptx::sts_v4(row + ((j4 ^ sw) << 4), make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]));
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tmD, buf, n0 + c0, m0 + q * 32);  // clipped to [M, N] by the TMA unit
+            ptx::bulk_commit();
+          }
+          if (Cfg::kEpiBufs > 1) eb ^= 1;
+          return;
+        }
+        if (!row_ok) return;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int n = n0 + c0 + j;
@@ -302,29 +380,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (args.bias_mode == BIAS_ROW) x += row_bias;
           if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
           if (args.R != nullptr && j < ncols) x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
-          v[j] = apply_act(x, args.act, args.act_lo, args.act_hi);
+          v[j] = x;
         }
-        if (vec_ok) {
-          float4* dst = reinterpret_cast<float4*>(args.D + d_base + n0 + c0);
+        apply_act_array(v, args.act, args.act_lo, args.act_hi);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
-        }
+        for (int j = 0; j < 32; ++j)
+          if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
       };
+
+      // chunks of this warp that lie inside the matrix
+      const int nch = max(0, min(kCols, args.N - n0 - col0) + 31) / 32;
+      if (staged_r && nch > 0) fetch_residual(col0, eb);
 
       if (!kChunked) {
         ptx::mbar_wait(tfull_bar(as), aph);
         ptx::tc_fence_after();
 #pragma unroll 1
-        for (int c0 = col0; c0 < col0 + kCols; c0 += 32) {
-          if (n0 + c0 >= args.N) break;
+        for (int i = 0; i < nch; ++i) {
+          const int c0 = col0 + i * 32;
+          if (staged_r && Cfg::kEpiBufs > 1 && i + 1 < nch) fetch_residual(c0 + 32, eb ^ 1);
           float v[32];
           ptx::tmem_ld_32x32(lane_addr + as * BN + c0, v);
           ptx::tmem_ld_wait();
           finish(v, c0);
+          if (staged_r && Cfg::kEpiBufs == 1 && i + 1 < nch) fetch_residual(c0 + 32, eb);
         }
         ptx::tc_fence_before();
         ptx::mbar_arrive(tempty_bar(as));
@@ -360,19 +439,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
 #pragma unroll
         for (int c0 = 0; c0 < kCols; c0 += 32) {
-          if (n0 + col0 + c0 < args.N) {
+          if (c0 / 32 < nch) {
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = acc[c0 + j];
             finish(v, col0 + c0);
+            if (staged_r && (c0 / 32) + 1 < nch) fetch_residual(col0 + c0 + 32, eb);
           }
         }
       }
     }
+    if (staged_d && lane == 0) ptx::bulk_wait<0>();  // stores complete before the CTA's shared memory goes away
   } else if (MODE == 1 && warp > kMmaWarp) {
     // ===================================================== 3xTF32 operand split
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
-    const bool store_hi = (args.flags & 1) != 0;  // debug: the tensor core truncates raw bits to the same hi
+    const bool store_hi = (args.flags & kFlagDebugHi) != 0;  // debug: the tensor core truncates raw bits to the same hi
     int s = 0;
     uint32_t ph = 0;
     constexpr int kVecs = Cfg::kRawBytes / 16;
