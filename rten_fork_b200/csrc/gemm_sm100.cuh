@@ -319,43 +319,46 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       };
 
-      // alpha / bias / residual / activation on 32 consecutive columns starting at n0 + c0, then store
+      // alpha / bias / residual / activation on 32 consecutive columns starting at n0 + c0, then store.  Every
+      // selection is warp-uniform and sits outside the element loops, so the executed path stays a few hundred
+      // instructions per chunk.
       auto finish = [&](float (&v)[32], int c0) {
         const int ncols = min(32, args.N - (n0 + c0));
+        if (args.alpha != 1.f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= args.alpha;
+        }
+        // bias before the residual: a fused Conv -> Add computes (acc + bias) + r exactly as the unfused pair does
+        if (args.bias_mode == BIAS_ROW) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += row_bias;
+        } else if (args.bias_mode == BIAS_COL) {
+          const float bl = lane < ncols ? __ldg(args.bias + n0 + c0 + lane) : 0.f;  // one coalesced load per chunk
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, bl, j);
+        }
         if (staged_d) {
           const uint32_t buf = ebuf0 + eb * Cfg::kEpiBufBytes;
-          if (staged_r) {
-            ptx::mbar_wait(rbar(warp, eb), (rph >> eb) & 1u);
-            rph ^= 1u << eb;
-          } else {
-            if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>();
-            __syncwarp();
-          }
           const uint32_t row = buf + lane * 128;
           const uint32_t sw = lane & 7;
           if (staged_r) {
+            ptx::mbar_wait(rbar(warp, eb), (rph >> eb) & 1u);
+            rph ^= 1u << eb;
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
               const float4 r = ptx::lds_v4(row + ((j4 ^ sw) << 4));
-              const float rr[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float x = args.alpha * v[4 * j4 + e];
-                if (args.bias_mode == BIAS_ROW) x += row_bias;
-                if (args.bias_mode == BIAS_COL && 4 * j4 + e < ncols) x += __ldg(args.bias + n0 + c0 + 4 * j4 + e);
-                v[4 * j4 + e] = x + args.beta * rr[e];
-              }
+              v[4 * j4 + 0] += args.beta * r.x;
+              v[4 * j4 + 1] += args.beta * r.y;
+              v[4 * j4 + 2] += args.beta * r.z;
+              v[4 * j4 + 3] += args.beta * r.w;
             }
           } else {
+            if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>();
+            __syncwarp();
+            if (args.R != nullptr && row_ok) {  // residual that TMA cannot address (unaligned / NCHW): direct loads
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int n = n0 + c0 + j;
-              float x = args.alpha * v[j];
-              if (args.bias_mode == BIAS_ROW) x += row_bias;
-              if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
-              if (args.R != nullptr && j < ncols && row_ok)
-                x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
-              v[j] = x;
+              for (int j = 0; j < 32; ++j)
+                if (j < ncols) v[j] += args.beta * args.R[r_base + static_cast<int64_t>(n0 + c0 + j) * r_cs];
             }
           }
           apply_act_array(v, args.act, args.act_lo, args.act_hi);
@@ -372,20 +375,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           return;
         }
         if (!row_ok) return;
+        if (args.R != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = n0 + c0 + j;
-          float x = args.alpha * v[j];
-          // bias before the residual: a fused Conv -> Add computes (acc + bias) + r exactly as the unfused pair does
-          if (args.bias_mode == BIAS_ROW) x += row_bias;
-          if (args.bias_mode == BIAS_COL && j < ncols) x += __ldg(args.bias + n);
-          if (args.R != nullptr && j < ncols) x += args.beta * args.R[r_base + static_cast<int64_t>(n) * r_cs];
-          v[j] = x;
+          for (int j = 0; j < 32; ++j)
+            if (j < ncols) v[j] += args.beta * args.R[r_base + static_cast<int64_t>(n0 + c0 + j) * r_cs];
         }
         apply_act_array(v, args.act, args.act_lo, args.act_hi);
+        if (ncols == 32) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
+          for (int j = 0; j < 32; ++j) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
+        }
       };
 
       // chunks of this warp that lie inside the matrix
