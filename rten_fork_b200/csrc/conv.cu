@@ -91,10 +91,21 @@ rtg_status conv_plan(const rtg_tensor* input, const rtg_tensor* weight, const rt
   return RTG_OK;
 }
 
+// Row-window path: dense convolution whose kernel row (kw taps x channels padded to 4) fits one 32-float k-block.
+// With so few channels the im2col path would fill at most a quarter of every per-tap channel block.
+bool conv_window_supported(const ConvPlan& p) {
+  if (p.pointwise || p.depthwise || p.groups != 1 || p.dil_w != 1) return false;
+  const int64_t cp = div_ceil(p.c, 4) * 4;
+  if (p.c > 8 || p.kw * cp > kBK || p.kh > 32) return false;
+  if (p.stride_w < 1 || p.stride_h < 1) return false;
+  return static_cast<int64_t>(p.stride_w) * cp * 4 % 16 == 0;
+}
+
 // ---------------------------------------------------------------- weights
 rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out) {
   out->wmat = nullptr;
   out->direct = false;
+  out->window = false;
   const int khw = static_cast<int>(p.kh * p.kw);
   if (p.o == 0 || p.cg == 0) return RTG_OK;
   if (p.depthwise) {
@@ -113,6 +124,22 @@ rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_
     out->wmat = const_cast<float*>(w_dev);  // [O][C] is already the K-major B operand
     out->direct = true;
     out->kpt = static_cast<int>(p.c);
+    return RTG_OK;
+  }
+  if (conv_window_supported(p)) {
+    const int cp = static_cast<int>(div_ceil(p.c, 4) * 4);
+    const int64_t total = p.o * p.kh * kBK;
+    void* d = nullptr;
+    RTG_TRY(ctx->pool.alloc(static_cast<size_t>(total) * 4, &d));
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), 148 * 16));
+    arrange_window_weights_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(d), w_dev, static_cast<int>(p.o),
+                                                                   static_cast<int>(p.c), static_cast<int>(p.kh),
+                                                                   static_cast<int>(p.kw), cp);
+    ctx->launches++;
+    RTG_CUDA(cudaGetLastError());
+    out->wmat = static_cast<float*>(d);
+    out->kpt = kBK;
+    out->window = true;
     return RTG_OK;
   }
   const int kpt = static_cast<int>(div_ceil(p.cg, kBK) * kBK);
@@ -266,6 +293,37 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
     RTG_CUDA(cudaGetLastError());
     if (!out_nhwc) RTG_TRY(from_nhwc(ctx, op, C, C, out, 0));
   } else {
+    if (w.window) {
+      // zero-padded NHWC image with channels rounded up to 4; every 32-float window stays inside its row
+      const int cpw = static_cast<int>(div_ceil(C, 4) * 4);
+      const int hp = H + static_cast<int>(p.pads[0] + p.pads[2]);
+      const int wp = std::max(W + static_cast<int>(p.pads[1] + p.pads[3]),
+                              (OW - 1) * static_cast<int>(p.stride_w) + kBK / cpw);
+      Scratch x_pad;
+      RTG_TRY(x_pad.alloc(ctx, static_cast<size_t>(N) * hp * wp * cpw * 4));
+      const int64_t pixels = static_cast<int64_t>(N) * hp * wp;
+      const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(pixels, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+      pad_to_window_layout_kernel<<<blocks, 256, 0, ctx->stream>>>(
+          x_pad.f32(), static_cast<const float*>(x.data), N, C, H, W, cpw, hp, wp, static_cast<int>(p.pads[0]),
+          static_cast<int>(p.pads[1]), x.strides[0], x.strides[1], x.strides[2], x.strides[3]);
+      ctx->launches++;
+      RTG_CUDA(cudaGetLastError());
+      Epilogue ep;
+      ep.bias = bias;
+      ep.bias_mode = BIAS_COL;
+      ep.act = act, ep.act_lo = act_lo, ep.act_hi = act_hi;
+      OutMap dm = out_nhwc ? OutMap{O, 0, 0, 0} : OutMap{0, OH * OW, O, 0};
+      if (residual) {
+        ep.R = static_cast<const float*>(residual->data);
+        ep.beta = 1.f;
+        ep.rmap = dm;
+      }
+      WindowGeom wg = {N, hp, wp, cpw, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
+                       static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.dil_h), C};
+      RTG_TRY(conv_window_gemm_device(ctx, x_pad.f32(), wg, w.wmat, O, static_cast<float*>(out.data), dm, ep));
+      if (need_out_tmp) RTG_TRY(copy_view(ctx, out_final, out));
+      return RTG_OK;
+    }
     // Groups whose channel slice is not 16-byte aligned in the shared NHWC tensor get their own gathered copy.
     const bool per_group = G > 1 && (CG % 4 != 0);
     const int c_src = per_group ? CG : C;

@@ -67,6 +67,52 @@ __global__ void arrange_conv_weights_kernel(float* __restrict__ dst, const float
   }
 }
 
+// ---------------------------------------------------------------- row-window layout (first-layer convolutions)
+// Few input channels (C <= 8) make the per-tap channel block of the im2col path almost empty (C = 3 fills 3 of 32
+// columns).  The row-window path instead reads, for every output pixel and kernel row, ONE contiguous run of
+// kw * cp floats from a zero-padded NHWC image (cp = C rounded up to 4), so a k-block is a whole kernel row.
+//
+// dst: [n][hp][wp][cp] with the image at (pad_t, pad_l), zeros elsewhere (borders, channel padding, right slack).
+// src: x[n*sn + c*sc + y*sy + x*sx] (any layout).  One thread per destination pixel; index-driven (copies or zeros).
+__global__ void pad_to_window_layout_kernel(float* __restrict__ dst, const float* __restrict__ src, int n, int c,
+                                            int h, int w, int cp, int hp, int wp, int pad_t, int pad_l, int64_t sn,
+                                            int64_t sc, int64_t sy, int64_t sx) {
+  const int64_t total = static_cast<int64_t>(n) * hp * wp;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int px = static_cast<int>(i % wp);
+    const int py = static_cast<int>((i / wp) % hp);
+    const int img = static_cast<int>(i / (static_cast<int64_t>(wp) * hp));
+    const int x = px - pad_l, y = py - pad_t;
+    const bool in = x >= 0 && x < w && y >= 0 && y < h;
+    const float* s = src + img * sn + y * sy + x * sx;
+    float* d = dst + i * cp;
+    for (int ch = 0; ch < cp; ch += 4) {
+      float4 v;
+      v.x = (in && ch + 0 < c) ? s[(ch + 0) * sc] : 0.f;
+      v.y = (in && ch + 1 < c) ? s[(ch + 1) * sc] : 0.f;
+      v.z = (in && ch + 2 < c) ? s[(ch + 2) * sc] : 0.f;
+      v.w = (in && ch + 3 < c) ? s[(ch + 3) * sc] : 0.f;
+      *reinterpret_cast<float4*>(d + ch) = v;
+    }
+  }
+}
+
+// OIHW [O, C, Kh, Kw] -> [O][Kh][32]: column j of kernel row ky holds w[o][j % cp][ky][j / cp], zero where the
+// channel or tap does not exist (those columns meet padding channels / the pixels right of the window).
+__global__ void arrange_window_weights_kernel(float* __restrict__ dst, const float* __restrict__ w, int o_total, int c,
+                                              int kh, int kw, int cp) {
+  const int64_t total = static_cast<int64_t>(o_total) * kh * 32;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int j = static_cast<int>(i % 32);
+    const int ky = static_cast<int>((i / 32) % kh);
+    const int o = static_cast<int>(i / (32 * static_cast<int64_t>(kh)));
+    const int kx = j / cp, ch = j % cp;
+    dst[i] = (kx < kw && ch < c) ? w[((static_cast<int64_t>(o) * c + ch) * kh + ky) * kw + kx] : 0.f;
+  }
+}
+
 // ---------------------------------------------------------------- explicit im2col (fallback)
 struct Im2colGeom {
   int n, h, w, cp;     // input NHWC dense, channel pitch cp

@@ -78,6 +78,23 @@ static rtg_status encode_2d(Context* ctx, CUtensorMap* map, const float* base, u
   return RTG_OK;
 }
 
+// {columns, rows, planes} view of a row-major output / residual for the staged epilogue: box 32 x 32 x 1.
+static rtg_status encode_out_3d(Context* ctx, CUtensorMap* map, const float* base, uint64_t cols, uint64_t rows,
+                                uint64_t planes, uint64_t ld) {
+  cuuint64_t dims[3] = {cols, rows, planes};
+  cuuint64_t strides[2] = {ld * sizeof(float), ld * rows * sizeof(float)};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (output) failed (%d): base %p dims [%llu,%llu,%llu] ld %llu",
+                      (int)r, base, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)planes,
+                      (unsigned long long)ld);
+  return RTG_OK;
+}
+
 // Can TMA address this operand in place?  The contiguous dimension must have stride 1, the base must be 16-byte
 // aligned and the pitch of the other dimension a positive multiple of 16 bytes (irrelevant when it has one entry).
 static bool direct_ok(const float* p, int64_t inner_stride, int64_t outer_stride, int64_t outer_count) {
@@ -123,14 +140,14 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
   }
   char name[96];
   snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s>", BN, MODE ? "3xTF32" : "TF32",
-           A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
+           A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
   ctx->last_kernel = name;
   return RTG_OK;
 }
 
 template <int A_KIND, int B_MAJOR>
 static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           GemmArgs args) {
+                           GemmArgs args, int plane_rows = 0) {
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;
   auto stageable = [&](const float* p, const OutMap& om) {
@@ -139,12 +156,15 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
     return args.M == 1 || (om.ld > 0 && om.ld % 4 == 0);
   };
   if (!(args.flags & 8) && stageable(args.D, args.dmap)) {
+    // plane_rows > 0 (row-window convolution): rows are output columns of one image row, planes the image rows
+    const uint64_t rows = plane_rows > 0 ? plane_rows : args.M;
+    const uint64_t planes = plane_rows > 0 ? args.M / plane_rows : 1;
     const uint64_t ld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.dmap.ld;
-    RTG_TRY(encode_2d(ctx, &md, args.D + args.dmap.chan_off, args.N, args.M, ld, 32, 32));
+    RTG_TRY(encode_out_3d(ctx, &md, args.D + args.dmap.chan_off, args.N, rows, planes, ld));
     args.flags |= kFlagStagedD;
     if (stageable(args.R, args.rmap)) {
       const uint64_t rld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.rmap.ld;
-      RTG_TRY(encode_2d(ctx, &mr, args.R + args.rmap.chan_off, args.N, args.M, rld, 32, 32));
+      RTG_TRY(encode_out_3d(ctx, &mr, args.R + args.rmap.chan_off, args.N, rows, planes, rld));
       args.flags |= kFlagStagedR;
     }
   }
@@ -329,6 +349,60 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.n) * g.h * g.w * g.cg + og * k_true +
                               static_cast<double>(M) * og * (a.R ? 2 : 1));
   return dispatch<1, 0>(ctx, bn, ctx->math, ma, mb, a);
+}
+
+// ---------------------------------------------------------------- row-window convolution
+rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const WindowGeom& g, const float* wmat, int og,
+                                   float* D, OutMap dmap, const Epilogue& ep) {
+  const int64_t M = static_cast<int64_t>(g.n) * g.oh * g.ow;
+  if (M == 0 || og == 0) return RTG_OK;
+  if (M > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "conv output pixels exceed i32");
+  CUtensorMap ma, mb;
+  {
+    // {32-float window, output column, padded input row, image}; consecutive windows overlap (pitch stride_w * cp)
+    cuuint64_t dims[4] = {32, static_cast<cuuint64_t>(g.ow), static_cast<cuuint64_t>(g.hp), static_cast<cuuint64_t>(g.n)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(g.stride_w) * g.cp * 4, static_cast<cuuint64_t>(g.wp) * g.cp * 4,
+                             static_cast<cuuint64_t>(g.hp) * g.wp * g.cp * 4};
+    cuuint32_t box[4] = {32, kBM, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = ctx->encode_tiled(&ma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(x_pad), dims, strides,
+                                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (row window) failed (%d): padded image [%d,%d,%d,%d]",
+                        (int)r, g.n, g.hp, g.wp, g.cp);
+  }
+  const int64_t Kmat = static_cast<int64_t>(g.kh) * kBK;
+  const int bn = choose_bn(ctx, M, og);
+  RTG_TRY(encode_2d(ctx, &mb, wmat, Kmat, og, Kmat, kBK, bn));
+  GemmArgs a = {};
+  a.M = static_cast<int>(M);
+  a.N = og;
+  a.K = static_cast<int>(Kmat);
+  a.num_kb = g.kh;
+  a.alpha = ep.alpha;
+  a.beta = ep.beta;
+  a.bias = ep.bias;
+  a.bias_mode = ep.bias ? ep.bias_mode : BIAS_NONE;
+  a.R = (ep.R && ep.beta != 0.f) ? ep.R : nullptr;
+  a.D = D;
+  a.dmap = dmap;
+  a.rmap = ep.rmap;
+  a.act = ep.act;
+  a.act_lo = ep.act_lo;
+  a.act_hi = ep.act_hi;
+  a.flags = debug_flags();
+  a.ic.ow = g.ow;
+  a.ic.oh = g.oh;
+  a.ic.stride_h = g.stride_h;
+  a.ic.dil_h = g.dil_h;
+  a.ic.win_tpr = static_cast<int>(div_ceil(g.ow, kBM));
+  a.ic.win_rows = g.n * g.oh;
+  const double k_true = static_cast<double>(g.c) * g.kh * g.kw;
+  ctx->pending_flops = 2.0 * M * og * k_true;
+  ctx->pending_bytes = 4.0 * (static_cast<double>(g.n) * g.hp * g.wp * g.cp + og * k_true +
+                              static_cast<double>(M) * og * (a.R ? 2 : 1));
+  return dispatch<2, 0>(ctx, bn, ctx->math, ma, mb, a, g.ow);
 }
 
 }  // namespace rtg

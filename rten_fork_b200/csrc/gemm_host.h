@@ -36,6 +36,18 @@ rtg_status conv_gemm_device(Context* ctx, const float* x_nhwc, const ConvGeom& g
                             float* D, OutMap dmap, const Epilogue& ep);
 bool conv_im2col_supported(const ConvGeom& g);
 
+// Row-window convolution (few input channels): x_pad is the zero-padded [n][hp][wp][cp] image written by
+// pad_to_window_layout_kernel, wmat the [Og][kh][32] matrix of arrange_window_weights_kernel.  One k-block per kernel
+// row; an M tile is 128 consecutive output pixels of ONE output row.
+struct WindowGeom {
+  int n, hp, wp, cp;
+  int kh, kw, oh, ow;
+  int stride_h, stride_w, dil_h;
+  int c;  // real input channels (algorithmic flops)
+};
+rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const WindowGeom& g, const float* wmat, int og,
+                                   float* D, OutMap dmap, const Epilogue& ep);
+
 // dst[r*dst_ld + c] = src[r*rs + c*cs]
 rtg_status copy_strided_2d(Context* ctx, float* dst, int64_t dst_ld, const float* src, int64_t rows, int64_t cols,
                            int64_t rs, int64_t cs);

@@ -50,6 +50,9 @@ struct Im2colArgs {  // A operand produced by TMA im2col over NHWC input (A_KIND
   int32_t kw, kh;
   int32_t c_blocks;  // ceil(C / 32): k-blocks per filter tap
   int32_t c_off;     // first channel of this group
+  // A_KIND 2 (row window): an M tile is 128 consecutive pixels of one output row; k-block kb is kernel row kb
+  int32_t win_tpr;   // tiles per output row = ceil(ow / 128)
+  int32_t win_rows;  // n * oh output rows
 };
 
 struct GemmArgs {
@@ -139,7 +142,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const int m_tiles = (args.M + kBM - 1) / kBM;
+  const int m_tiles = A_KIND == 2 ? args.ic.win_rows * args.ic.win_tpr : (args.M + kBM - 1) / kBM;
   const int n_tiles = (args.N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int num_kb = args.num_kb;
@@ -183,6 +186,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m0 = (tile / n_tiles) * kBM;
         const int n0 = (tile % n_tiles) * BN;
         int pix_w = 0, pix_h = 0, pix_n = 0;
+        if (A_KIND == 2) {
+          const int rowidx = (tile / n_tiles) / args.ic.win_tpr;
+          pix_w = ((tile / n_tiles) % args.ic.win_tpr) * kBM;  // first output column of the tile
+          pix_n = rowidx / args.ic.oh;
+          pix_h = (rowidx - pix_n * args.ic.oh) * args.ic.stride_h;
+        }
         if (A_KIND == 1) {
           const int ohw = args.ic.oh * args.ic.ow;
           pix_n = m0 / ohw;
@@ -200,6 +209,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::mbar_expect_tx(full_bar(s), Cfg::kRawBytes);
           if (A_KIND == 0) {
             ptx::tma_load_2d(a_dst, &tmA, full_bar(s), kb * kBK, m0);
+          } else if (A_KIND == 2) {
+            // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
+            ptx::tma_load_4d(a_dst, &tmA, full_bar(s), 0, pix_w, pix_h + kb * args.ic.dil_h, pix_n);
           } else {
             ptx::tma_load_im2col_4d(a_dst, &tmA, full_bar(s), args.ic.c_off + cb * kBK, pix_w, pix_h, pix_n,
                                     static_cast<uint16_t>(tap_x * args.ic.dil_w),
@@ -300,10 +312,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int as = 0;
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / n_tiles) * kBM;
       const int n0 = (tile % n_tiles) * BN;
-      const int m = m0 + q * 32 + lane;
-      const bool row_ok = m < args.M;
+      // store coordinates of this warp's 32 rows: (st_r, st_z) in the {columns, rows, planes} view of D / R
+      int m, st_r, st_z = 0;
+      bool row_ok;
+      if (A_KIND == 2) {
+        st_z = (tile / n_tiles) / args.ic.win_tpr;
+        st_r = ((tile / n_tiles) % args.ic.win_tpr) * kBM + q * 32;
+        m = st_z * args.ic.ow + st_r + lane;
+        row_ok = st_r + lane < args.ic.ow;
+      } else {
+        st_r = (tile / n_tiles) * kBM + q * 32;
+        m = st_r + lane;
+        row_ok = m < args.M;
+      }
       int64_t d_base, r_base, d_cs, r_cs;
       out_row_base(args.dmap, m, d_base, d_cs);
       out_row_base(args.rmap, m, r_base, r_cs);
@@ -315,7 +337,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
           ptx::bulk_wait_read<0>();  // earlier stores of this warp no longer read the buffer
           ptx::mbar_expect_tx(rbar(warp, b), Cfg::kEpiBufBytes);
-          ptx::tma_load_2d(ebuf0 + b * Cfg::kEpiBufBytes, &tmR, rbar(warp, b), n0 + c0, m0 + q * 32);
+          ptx::tma_load_3d(ebuf0 + b * Cfg::kEpiBufBytes, &tmR, rbar(warp, b), n0 + c0, st_r, st_z);
         }
       };
 
@@ -368,7 +390,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            ptx::tma_store_2d(&tmD, buf, n0 + c0, m0 + q * 32);  // clipped to [M, N] by the TMA unit
+            ptx::tma_store_3d(&tmD, buf, n0 + c0, st_r, st_z);  // clipped to the tensor bounds by the TMA unit
             ptx::bulk_commit();
           }
           if (Cfg::kEpiBufs > 1) eb ^= 1;

@@ -75,7 +75,9 @@ struct ConvWeights {
   float* wmat = nullptr;     // dense/grouped: [O][Kh*Kw][c_blocks*32]; depthwise: [Kh*Kw][C]
   int kpt = 0;               // c_blocks*32
   bool direct = false;       // pointwise with C % 4 == 0: the OIHW tensor already is the K-major matrix
+  bool window = false;       // row-window path (few input channels): wmat is [O][Kh][32]
 };
+bool conv_window_supported(const ConvPlan& p);
 rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out);
 void conv_release_weights(Context* ctx, ConvWeights* w);
 
