@@ -1,6 +1,7 @@
 // Host side of the tcgen05 contraction engine: operand legalisation, TMA descriptor encoding, tile-shape choice,
 // launch.  Reference role: GemmExecutor::{gemm_bias, prepack_*} front-end (src/gemm.rs:448-542).
 #include "gemm_host.h"
+#include <vector>
 
 #include <stdio.h>
 #include <stdlib.h>
@@ -124,6 +125,16 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
   }
   const int m_tiles = (args.M + kBM - 1) / kBM, n_tiles = (args.N + BN - 1) / BN;
   const int grid = std::min(m_tiles * n_tiles, ctx->num_sms);
+#ifdef RTG_PROF
+  static unsigned long long* prof_buf = nullptr;
+  GemmArgs pargs = args;
+  if (getenv("RTG_PROF_PRINT")) {
+    if (!prof_buf) RTG_CUDA(cudaMalloc(&prof_buf, 148 * 32 * 8));
+    RTG_CUDA(cudaMemsetAsync(prof_buf, 0, 148 * 32 * 8, ctx->stream));
+    pargs.prof = prof_buf;
+  }
+#define args pargs
+#endif
   Context::KernelRec rec{};
   if (ctx->ktiming) {
     RTG_CUDA(cudaEventCreate(&rec.a));
@@ -138,6 +149,31 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     RTG_CUDA(cudaEventRecord(rec.b, ctx->stream));
     ctx->krecs.push_back(rec);
   }
+#ifdef RTG_PROF
+#undef args
+  if (pargs.prof) {
+    std::vector<unsigned long long> h(148 * 32);
+    RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+    RTG_CUDA(cudaMemcpy(h.data(), prof_buf, h.size() * 8, cudaMemcpyDeviceToHost));
+    static const char* roles[4] = {"tma", "mma", "epi", "split"};
+    static const char* slots[4][4] = {{"wait_empty", "issue", "-", "-"},
+                                      {"wait_tempty", "wait_full", "issue", "-"},
+                                      {"wait_tfull", "wait_resid", "wait_stread", "wait_stdone"},
+                                      {"wait_full", "-", "-", "-"}};
+    fprintf(stderr, "[prof] BN=%d mode=%d akind=%d grid=%d M=%d N=%d kb=%d:", BN, MODE, A_KIND, grid, args.M, args.N,
+            args.num_kb);
+    for (int r = 0; r < 4; ++r) {
+      double acc[5] = {0, 0, 0, 0, 0};
+      for (int b = 0; b < grid; ++b)
+        for (int i = 0; i < 5; ++i) acc[i] += static_cast<double>(h[(b * 4 + r) * 8 + i]) / grid;
+      if (acc[4] == 0) continue;
+      fprintf(stderr, " | %s total %.0f", roles[r], acc[4]);
+      for (int i = 0; i < 4; ++i)
+        if (slots[r][i][0] != '-') fprintf(stderr, " %s %.0f", slots[r][i], acc[i]);
+    }
+    fprintf(stderr, "\n");
+  }
+#endif
   char name[96];
   snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s>", BN, MODE ? "3xTF32" : "TF32",
            A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
@@ -180,24 +216,29 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
 }
 
 // Largest tile that still fills the machine; smaller tiles when the problem has too few of them.
-static int choose_bn(Context* ctx, int64_t M, int64_t N) {
-  const int max_bn = ctx->math == RTG_MATH_TF32 ? 256 : 128;
+static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb) {
+  // Cycle model fitted to the per-role counters of the PROF build (profiles/): the MMA thread needs
+  // max(64, BN/2) cycles per 128 x BN x 8 instruction (64 is the dispatch floor, so BN = 64 runs the tensor pipe at
+  // half rate) plus ~150 cycles of barrier traffic per k-block; the epilogue drains a tile in ~1000 + 12*BN cycles
+  // with four warps (3xTF32 has eight); MMA and epilogue of consecutive tiles overlap.
+  const bool x3 = ctx->math != RTG_MATH_TF32;
+  const int max_bn = x3 ? 128 : 256;
   const int64_t m_tiles = div_ceil(M, kBM);
   int best = 64;
-  double best_score = -1;
+  double best_cost = 1e300;
   const int cands[3] = {256, 128, 64};
-  const double weight[3] = {1.0, 0.92, 0.75};  // bigger tiles reuse A more and amortise the epilogue
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
     if (bn > max_bn) continue;
     if (bn > 64 && N <= bn / 2) continue;  // mostly padding
     const int64_t tiles = m_tiles * div_ceil(N, bn);
-    const int64_t waves = div_ceil(tiles, ctx->num_sms);
-    const double eff = static_cast<double>(tiles) / static_cast<double>(waves * ctx->num_sms);
-    const double useful = static_cast<double>(N) / static_cast<double>(div_ceil(N, bn) * bn);
-    const double score = eff * useful * weight[i];
-    if (score > best_score) {
-      best_score = score;
+    const int64_t rounds = div_ceil(tiles, ctx->num_sms);
+    const double kb_cycles = 4.0 * std::max(64, bn / 2) * (x3 ? 3 : 1) + 150.0;
+    const double main_cycles = static_cast<double>(num_kb) * kb_cycles;
+    const double epi_cycles = x3 ? 800.0 + 6.0 * bn : 1000.0 + 12.0 * bn;
+    const double cost = static_cast<double>(rounds) * std::max(main_cycles, epi_cycles) + epi_cycles + 3000.0;
+    if (cost < best_cost) {
+      best_cost = cost;
       best = bn;
     }
   }
@@ -238,7 +279,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   }
 
   CUtensorMap ma, mb;
-  const int bn = choose_bn(ctx, M, N);
+  const int bn = choose_bn(ctx, M, N, div_ceil(K, kBK));
   RTG_TRY(encode_2d(ctx, &ma, a.p, K, M, a.rs, kBK, kBM));
   if (b_major == 0)
     RTG_TRY(encode_2d(ctx, &mb, b.p, K, N, b.cs, kBK, bn));
@@ -310,7 +351,7 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
     const uint64_t bytes = static_cast<uint64_t>(g.n) * g.h * g.w * g.c_total * 4;
     if (ctx->driver_version <= 13010 && bytes < 131072) reinterpret_cast<uint64_t*>(&ma)[1] &= ~(1ull << 21);
   }
-  const int bn = choose_bn(ctx, M, og);
+  const int bn = choose_bn(ctx, M, og, Kmat / kBK);
   RTG_TRY(encode_2d(ctx, &mb, wmat, Kmat, og, Kmat, kBK, bn));
 
   GemmArgs a = {};
@@ -373,7 +414,7 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
                         (int)r, g.n, g.hp, g.wp, g.cp);
   }
   const int64_t Kmat = static_cast<int64_t>(g.kh) * kBK;
-  const int bn = choose_bn(ctx, M, og);
+  const int bn = choose_bn(ctx, M, og, g.kh);
   RTG_TRY(encode_2d(ctx, &mb, wmat, Kmat, og, Kmat, kBK, bn));
   GemmArgs a = {};
   a.M = static_cast<int>(M);

@@ -68,7 +68,31 @@ struct GemmArgs {
   float act_lo, act_hi;
   int32_t flags;   // bit 0: (debug) MODE 1 also overwrites the raw operand tile with its hi part
   Im2colArgs ic;
+  unsigned long long* prof;  // RTG_PROF builds: per-CTA wait / busy cycle counters (see PROF_* below), else unused
 };
+
+// Developer instrumentation (make PROF=1): cycles each role spends waiting on its barriers.
+#ifdef RTG_PROF
+#define PROF_DECL long long prof_t0_ = clock64(), prof_acc_[4] = {0, 0, 0, 0}
+#define PROF_WAIT(slot, stmt)          \
+  do {                                 \
+    const long long t_ = clock64();    \
+    stmt;                              \
+    prof_acc_[slot] += clock64() - t_; \
+  } while (0)
+#define PROF_DUMP(role)                                                              \
+  do {                                                                               \
+    if (args.prof) {                                                                 \
+      unsigned long long* p_ = args.prof + (blockIdx.x * 4 + (role)) * 8;            \
+      for (int i_ = 0; i_ < 4; ++i_) p_[i_] = static_cast<unsigned long long>(prof_acc_[i_]); \
+      p_[4] = static_cast<unsigned long long>(clock64() - prof_t0_);                 \
+    }                                                                                \
+  } while (0)
+#else
+#define PROF_DECL
+#define PROF_WAIT(slot, stmt) stmt
+#define PROF_DUMP(role)
+#endif
 
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
 constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
@@ -158,11 +182,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
-      ptx::mbar_init(xf_bar(s), Cfg::kXfThreads);
+      ptx::mbar_init(xf_bar(s), Cfg::kXfThreads / 32 > 0 ? Cfg::kXfThreads / 32 : 1);  // one arrival per split warp
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
-      ptx::mbar_init(tempty_bar(a), Cfg::kEpiWarps * 32);
+      ptx::mbar_init(tempty_bar(a), Cfg::kEpiWarps);  // one arrival per epilogue warp
     }
     for (int w = 0; w < Cfg::kEpiWarps; ++w)
       for (int b = 0; b < Cfg::kEpiBufs; ++b) ptx::mbar_init(rbar(w, b), 1);
@@ -180,8 +204,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == kTmaWarp) {
     // ===================================================== TMA producer
     if (lane == 0) {
+      PROF_DECL;
       int s = 0;
       uint32_t ph = 0;
+      const int ic_dil_h = args.ic.dil_h, ic_dil_w = args.ic.dil_w, ic_c_off = args.ic.c_off;
+      const int ic_c_blocks = args.ic.c_blocks, ic_kw = args.ic.kw;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile / n_tiles) * kBM;
         const int n0 = (tile % n_tiles) * BN;
@@ -203,22 +230,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         int tap_x = 0, tap_y = 0, cb = 0;
         for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+          PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
           const uint32_t a_dst = smem_base + s * Cfg::kStageBytes;
           const uint32_t b_dst = a_dst + kABytes;
-          ptx::mbar_expect_tx(full_bar(s), Cfg::kRawBytes);
+          const uint32_t fb = full_bar(s);
+#ifdef RTG_PROF
+          const long long ti_ = clock64();
+#endif
+          ptx::mbar_expect_tx(fb, Cfg::kRawBytes);
           if (A_KIND == 0) {
-            ptx::tma_load_2d(a_dst, &tmA, full_bar(s), kb * kBK, m0);
+            ptx::tma_load_2d(a_dst, &tmA, fb, kb * kBK, m0);
           } else if (A_KIND == 2) {
             // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
-            ptx::tma_load_4d(a_dst, &tmA, full_bar(s), 0, pix_w, pix_h + kb * args.ic.dil_h, pix_n);
+            ptx::tma_load_4d(a_dst, &tmA, fb, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
           } else {
-            ptx::tma_load_im2col_4d(a_dst, &tmA, full_bar(s), args.ic.c_off + cb * kBK, pix_w, pix_h, pix_n,
-                                    static_cast<uint16_t>(tap_x * args.ic.dil_w),
-                                    static_cast<uint16_t>(tap_y * args.ic.dil_h));
-            if (++cb == args.ic.c_blocks) {
+            ptx::tma_load_im2col_4d(a_dst, &tmA, fb, ic_c_off + cb * kBK, pix_w, pix_h, pix_n,
+                                    static_cast<uint16_t>(tap_x * ic_dil_w), static_cast<uint16_t>(tap_y * ic_dil_h));
+            if (++cb == ic_c_blocks) {
               cb = 0;
-              if (++tap_x == args.ic.kw) {
+              if (++tap_x == ic_kw) {
                 tap_x = 0;
                 ++tap_y;
               }
@@ -226,19 +256,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           if (B_MAJOR == 0) {
             // B stored [N][K] (K contiguous): one box of BN rows x 128 bytes
-            ptx::tma_load_2d(b_dst, &tmB, full_bar(s), kb * kBK, n0);
+            ptx::tma_load_2d(b_dst, &tmB, fb, kb * kBK, n0);
           } else {
             // B stored [K][N] (N contiguous): BN/32 boxes of 32 k-rows x 128 bytes, 4 KB apart
 #pragma unroll
-            for (int c = 0; c < BN / 32; ++c)
-              ptx::tma_load_2d(b_dst + c * 4096, &tmB, full_bar(s), n0 + c * 32, kb * kBK);
+            for (int c = 0; c < BN / 32; ++c) ptx::tma_load_2d(b_dst + c * 4096, &tmB, fb, n0 + c * 32, kb * kBK);
           }
+#ifdef RTG_PROF
+          prof_acc_[1] += clock64() - ti_;
+#endif
           if (++s == kStages) {
             s = 0;
             ph ^= 1u;
           }
         }
       }
+      PROF_DUMP(0);
     }
   } else if (warp == kMmaWarp) {
     // ===================================================== MMA issuer
@@ -249,45 +282,53 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       constexpr uint32_t b_layout = B_MAJOR ? ptx::kSwizzle128Base32 : ptx::kSwizzle128;
       constexpr uint32_t b_lbo = B_MAJOR ? 4096 : 16;
       constexpr uint32_t b_sbo = B_MAJOR ? 512 : 1024;
+      // descriptor words of stage 0; a stage / k-step only moves the 14-bit "address >> 4" field of the low word
+      const uint64_t a_d0 = ptx::make_smem_desc(smem_base, 16, 1024);
+      const uint64_t b_d0 = ptx::make_smem_desc(smem_base + kABytes, b_lbo, b_sbo, b_layout);
+      const uint32_t a_hi = static_cast<uint32_t>(a_d0 >> 32), b_hi = static_cast<uint32_t>(b_d0 >> 32);
+      const uint32_t a_lo0 = static_cast<uint32_t>(a_d0), b_lo0 = static_cast<uint32_t>(b_d0);
+      constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4, kLoStep = Cfg::kRawBytes >> 4;
+      constexpr uint32_t kAStep = 32 >> 4;                       // 8 floats along the swizzled 128-byte row
+      constexpr uint32_t kBStep = (B_MAJOR ? 1024 : 32) >> 4;    // MN-major: 8 k-rows = 1024 bytes further
       int s = 0;
+      uint32_t so = 0;  // s * kStageStep
       uint32_t ph = 0;
       int as = 0;
       uint32_t aph = 0;
+      PROF_DECL;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
-          ptx::mbar_wait(tempty_bar(as), aph ^ 1u);
+          PROF_WAIT(0, ptx::mbar_wait(tempty_bar(as), aph ^ 1u));
           ptx::tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BN;
           const int kb1 = min(num_kb, kb0 + chunk_kb);
           for (int kb = kb0; kb < kb1; ++kb) {
-            ptx::mbar_wait(MODE ? xf_bar(s) : full_bar(s), ph);
+            PROF_WAIT(1, ptx::mbar_wait(MODE ? xf_bar(s) : full_bar(s), ph));
             ptx::tc_fence_after();
-            const uint32_t a_raw = smem_base + s * Cfg::kStageBytes;
-            const uint32_t b_raw = a_raw + kABytes;
-            const uint32_t a_lo = a_raw + Cfg::kRawBytes;
-            const uint32_t b_lo = b_raw + Cfg::kRawBytes;
+#ifdef RTG_PROF
+            const long long ti_ = clock64();
+#endif
+            const uint32_t a_lo = a_lo0 + so, b_lo = b_lo0 + so;
 #pragma unroll
             for (int k = 0; k < kBK / 8; ++k) {
-              // K-major: 8 floats = 32 bytes further along the swizzled 128-byte row.
-              // MN-major: 8 k-rows = 1024 bytes further.
-              const uint32_t a_off = k * 32;
-              const uint32_t b_off = B_MAJOR ? k * 1024 : k * 32;
-              const uint64_t da = ptx::make_smem_desc(a_raw + a_off, 16, 1024);
-              const uint64_t db = ptx::make_smem_desc(b_raw + b_off, b_lbo, b_sbo, b_layout);
               const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
               if (MODE == 0) {
-                ptx::mma_tf32_ss(d_tmem, da, db, idesc, acc);
+                ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, acc);
               } else {
-                const uint64_t dal = ptx::make_smem_desc(a_lo + a_off, 16, 1024);
-                const uint64_t dbl = ptx::make_smem_desc(b_lo + b_off, b_lbo, b_sbo, b_layout);
-                ptx::mma_tf32_ss(d_tmem, dal, db, idesc, acc);
-                ptx::mma_tf32_ss(d_tmem, da, dbl, idesc, 1);
-                ptx::mma_tf32_ss(d_tmem, da, db, idesc, 1);
+                // lo(A) * B, A * lo(B), A * B: smallest terms first
+                ptx::mma_tf32_ss_w(d_tmem, a_lo + kLoStep + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, acc);
+                ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + kLoStep + k * kBStep, b_hi, idesc, 1);
+                ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, 1);
               }
             }
             ptx::mma_commit(empty_bar(s));
+#ifdef RTG_PROF
+            prof_acc_[2] += clock64() - ti_;
+#endif
+            so += kStageStep;
             if (++s == kStages) {
               s = 0;
+              so = 0;
               ph ^= 1u;
             }
           }
@@ -298,6 +339,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
+      PROF_DUMP(1);
     }
   } else if (warp < Cfg::kEpiWarps) {
     // ===================================================== epilogue
@@ -311,6 +353,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t rph = 0;      // phase bit per staging buffer of this warp's residual barriers
     int as = 0;
     uint32_t aph = 0;
+    PROF_DECL;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int n0 = (tile % n_tiles) * BN;
       // store coordinates of this warp's 32 rows: (st_r, st_z) in the {columns, rows, planes} view of D / R
@@ -364,7 +407,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t row = buf + lane * 128;
           const uint32_t sw = lane & 7;
           if (staged_r) {
-            ptx::mbar_wait(rbar(warp, eb), (rph >> eb) & 1u);
+            PROF_WAIT(1, ptx::mbar_wait_parked(rbar(warp, eb), (rph >> eb) & 1u));
             rph ^= 1u << eb;
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
@@ -375,8 +418,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               v[4 * j4 + 3] += args.beta * r.w;
             }
           } else {
-            if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>();
-            __syncwarp();
+            PROF_WAIT(2, if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>(); __syncwarp());
             if (args.R != nullptr && row_ok) {  // residual that TMA cannot address (unaligned / NCHW): direct loads
 #pragma unroll
               for (int j = 0; j < 32; ++j)
@@ -418,7 +460,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (staged_r && nch > 0) fetch_residual(col0, eb);
 
       if (!kChunked) {
-        ptx::mbar_wait(tfull_bar(as), aph);
+        PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
         ptx::tc_fence_after();
 #pragma unroll 1
         for (int i = 0; i < nch; ++i) {
@@ -431,7 +473,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (staged_r && Cfg::kEpiBufs == 1 && i + 1 < nch) fetch_residual(c0 + 32, eb);
         }
         ptx::tc_fence_before();
-        ptx::mbar_arrive(tempty_bar(as));
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
         if (++as == 2) {
           as = 0;
           aph ^= 1u;
@@ -440,7 +483,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // running sums in registers, one per output column of this thread's row
         float acc[kCols];
         for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
-          ptx::mbar_wait(tfull_bar(as), aph);
+          PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
           ptx::tc_fence_after();
 #pragma unroll
           for (int c0 = 0; c0 < kCols; c0 += 32) {
@@ -456,7 +499,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           ptx::tc_fence_before();
-          ptx::mbar_arrive(tempty_bar(as));
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
           if (++as == 2) {
             as = 0;
             aph ^= 1u;
@@ -474,44 +518,43 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
-    if (staged_d && lane == 0) ptx::bulk_wait<0>();  // stores complete before the CTA's shared memory goes away
+    PROF_WAIT(3, if (staged_d && lane == 0) ptx::bulk_wait<0>());  // stores complete before shared memory goes away
+    if (warp == 0 && lane == 0) PROF_DUMP(2);
   } else if (MODE == 1 && warp > kMmaWarp) {
     // ===================================================== 3xTF32 operand split
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
-    const bool store_hi = (args.flags & kFlagDebugHi) != 0;  // debug: the tensor core truncates raw bits to the same hi
     int s = 0;
     uint32_t ph = 0;
     constexpr int kVecs = Cfg::kRawBytes / 16;
+    PROF_DECL;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       for (int kb = 0; kb < num_kb; ++kb) {
-        ptx::mbar_wait(full_bar(s), ph);
+        PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
         uint8_t* raw = smem_raw + (smem_base - ptx::smem_u32(smem_raw)) + s * Cfg::kStageBytes;
         float4* rawv = reinterpret_cast<float4*>(raw);
         float4* lov = reinterpret_cast<float4*>(raw + Cfg::kRawBytes);
 #pragma unroll 4
         for (int i = t; i < kVecs; i += Cfg::kXfThreads) {
+          // x = hi + lo with hi = x truncated to TF32 (what the tensor core reads from the raw tile) and lo = x - hi
+          // (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
           const float4 x = rawv[i];
-          float4 hi;
-          hi.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
-          hi.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
-          hi.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
-          hi.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
-          uint32_t l0, l1, l2, l3;
-          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l0) : "f"(x.x - hi.x));
-          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l1) : "f"(x.y - hi.y));
-          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l2) : "f"(x.z - hi.z));
-          asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l3) : "f"(x.w - hi.w));
-          if (store_hi) rawv[i] = hi;
-          lov[i] = make_float4(__uint_as_float(l0), __uint_as_float(l1), __uint_as_float(l2), __uint_as_float(l3));
+          float4 lo;
+          lo.x = __uint_as_float(__float_as_uint(x.x - __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u)) + 0x1000u);
+          lo.y = __uint_as_float(__float_as_uint(x.y - __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u)) + 0x1000u);
+          lo.z = __uint_as_float(__float_as_uint(x.z - __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u)) + 0x1000u);
+          lo.w = __uint_as_float(__float_as_uint(x.w - __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u)) + 0x1000u);
+          lov[i] = lo;
         }
         ptx::fence_proxy_async_smem();
-        ptx::mbar_arrive(xf_bar(s));
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(xf_bar(s));
         if (++s == kStages) {
           s = 0;
           ph ^= 1u;
         }
       }
     }
+    if (t == 0) PROF_DUMP(3);
   }
 
   ptx::tc_fence_before();
