@@ -1,0 +1,95 @@
+"""Multi-GPU partitioning of the hot path (one process per GPU, ``torch.distributed``).
+
+Two partitionings, both from BASELINE.json's north_star:
+
+* **Batch-sharded Graph::run** — every rank owns a contiguous slice of the batch and runs the whole graph on it.  The
+  data path has no exchange step, so there is no collective; ``gather_outputs`` exists only for callers that want the
+  full result on every rank (it is not part of the timed path in ``bench.py``).
+* **N-split GEMM** — a single large ``A[M,K] @ B[K,N]`` is split by output columns: rank r multiplies A by its column
+  block of B and the blocks are gathered with one all-gather (NCCL over NVLink on GPUs; gloo in the CPU tests).
+
+The reference is single-process (src/threading.rs: one rayon pool); these helpers are the multi-GPU counterpart of its
+per-thread column partition ``nc = clamp(N / threads, 128..1024)`` (src/gemm.rs:546-571): one column block per GPU.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_range(total: int, world: int, rank: int) -> tuple[int, int]:
+    """Contiguous [start, stop) of ``total`` items for ``rank``; the first ``total % world`` ranks get one extra."""
+    if world <= 0 or not 0 <= rank < world:
+        raise ValueError(f"bad rank {rank} for world size {world}")
+    base, extra = divmod(total, world)
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+def column_blocks(n: int, world: int, align: int = 128) -> list[tuple[int, int]]:
+    """Column ranges of an N-split GEMM: blocks are multiples of ``align`` (one tcgen05 tile column, so that no rank
+    runs a partial tile except the last) and differ by at most one tile; trailing ranks may be empty when N is small."""
+    tiles = -(-n // align)
+    out = []
+    for r in range(world):
+        t0, t1 = shard_range(tiles, world, r)
+        out.append((min(t0 * align, n), min(t1 * align, n)))
+    return out
+
+
+def run_batch_sharded(model, inputs, world: int, rank: int, batch_axis: int = 0):
+    """Model::run on this rank's slice of the batch (no communication).  Returns (outputs, (start, stop))."""
+    n = inputs[0].shape[batch_axis]
+    lo, hi = shard_range(n, world, rank)
+    local = [x[lo:hi] if batch_axis == 0 else np.take(x, range(lo, hi), axis=batch_axis) for x in inputs]
+    if hi == lo:
+        return [], (lo, hi)
+    return model.run(local), (lo, hi)
+
+
+def gather_outputs(local, total_rows: int, group=None):
+    """All-gather of ragged per-rank row blocks (torch tensors on the backend's device).  Not on the timed path."""
+    import torch
+    import torch.distributed as dist
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    rows = [shard_range(total_rows, world, r) for r in range(world)]
+    width = max(hi - lo for lo, hi in rows)
+    pad = torch.zeros((width,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    pad[: local.shape[0]] = local
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    return torch.cat([p[: hi - lo] for p, (lo, hi) in zip(parts, rows)], dim=0)
+
+
+def gemm_nsplit(a, b, group=None, local_gemm=None, align: int = 128):
+    """``A @ B`` with B's columns split over the ranks of ``group`` and the result gathered on every rank.
+
+    ``a``: [M, K], ``b``: [K, N] torch tensors on this rank's device.  ``local_gemm(a, b_block) -> [M, n_r]`` defaults
+    to the tcgen05 GEMM of this package (CUDA tensors); the CPU tests pass a stand-in so that only the partition /
+    gather logic is exercised.  The gather is ONE all-gather of equal-sized padded blocks (NCCL needs equal sizes);
+    the padding columns are dropped when the blocks are laid side by side.
+    """
+    import torch
+    import torch.distributed as dist
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    m, n = a.shape[0], b.shape[1]
+    blocks = column_blocks(n, world, align)
+    lo, hi = blocks[rank]
+    if local_gemm is None:
+        from . import ops
+
+        def local_gemm(x, y):
+            out = torch.empty((x.shape[0], y.shape[1]), dtype=torch.float32, device=x.device)
+            return ops.matmul(x, y, out=out)
+
+    width = max(h - l for l, h in blocks)
+    mine = torch.zeros((m, width), dtype=torch.float32, device=a.device)
+    if hi > lo:
+        mine[:, : hi - lo] = local_gemm(a, b[:, lo:hi])
+    flat = torch.empty((world * m, width), dtype=torch.float32, device=a.device)
+    dist.all_gather_into_tensor(flat, mine, group=group)  # rank r's block lands in rows [r*m, (r+1)*m)
+    gathered = flat.view(world, m, width)
+    if all(h - l == width for l, h in blocks):
+        return gathered.permute(1, 0, 2).reshape(m, world * width)  # one strided copy
+    return torch.cat([gathered[r, :, : h - l] for r, (l, h) in enumerate(blocks)], dim=1)

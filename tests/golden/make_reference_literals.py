@@ -35,6 +35,54 @@ cases = {
         "shape": [1, 3, 1, 1],
         "expected_minus_bias": [0.09020272, -0.09061745, 1.1822754],
     },
+    # src/ops/pooling.rs:416-470 test_average_pool / :568-600 test_max_pool (shared 4x4 input)
+    "pool_4x4": {
+        "cite": "src/ops/pooling.rs:416-470, 568-600",
+        "tol": 1e-5,
+        "input_shape": [1, 1, 4, 4],
+        "input": [0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.1, 0.2, 0.3, 0.4, 0.6, 0.7, 0.8, 0.9],
+        "average": [
+            {"kernel": [2, 2], "strides": [2, 2], "shape": [1, 1, 2, 2], "expected": [0.35, 0.55, 0.4, 0.6]},
+            {"kernel": [4, 4], "strides": [4, 4], "shape": [1, 1, 1, 1], "expected": [0.475]},
+            {"kernel": [2, 4], "strides": [2, 4], "shape": [1, 1, 2, 1], "expected": [0.45, 0.5]},
+            {"kernel": [2, 2], "strides": [1, 2], "shape": [1, 1, 3, 2], "expected": [0.35, 0.55, 0.35, 0.55, 0.4, 0.6]},
+        ],
+        "max": [
+            {"kernel": [2, 2], "strides": [2, 2], "shape": [1, 1, 2, 2], "expected": [0.6, 0.8, 0.7, 0.9]},
+            {"kernel": [4, 4], "strides": [4, 4], "shape": [1, 1, 1, 1], "expected": [0.9]},
+        ],
+    },
+    # src/ops/pooling.rs:498-556 test_average_pool_padding (PyTorch avg_pool2d, padding=1), tolerance 1e-4
+    "average_pool_padding": {
+        "cite": "src/ops/pooling.rs:498-556",
+        "tol": 1e-4,
+        "channels": 5,
+        "plane": [[0.0809, 0.5529, 0.1534, 0.7507], [0.4698, 0.7771, 0.9896, 0.4873],
+                  [0.9750, 0.5160, 0.6419, 0.3670], [0.4101, 0.3762, 0.9689, 0.4389]],
+        "kernel": [2, 2], "strides": [2, 2], "pads": [1, 1, 1, 1],
+        "expected_exclude_pad": [[0.0809, 0.3531, 0.7507], [0.7224, 0.7312, 0.4271], [0.4101, 0.6725, 0.4389]],
+        "expected_include_pad": [[0.0202, 0.1766, 0.1877], [0.3612, 0.7312, 0.2136], [0.1025, 0.3363, 0.1097]],
+    },
+    # src/ops/pooling.rs:558-566 test_global_average_pool
+    "global_average_pool": {"cite": "src/ops/pooling.rs:558-566", "input_shape": [1, 2, 2, 2],
+                            "input": [1.0, 2.0, 3.0, 4.0, 10.0, 20.0, 30.0, 40.0], "expected": [2.5, 25.0]},
+    # src/ops/norm.rs:708-743 test_softmax, tolerance 1e-4
+    "softmax": {
+        "cite": "src/ops/norm.rs:708-743",
+        "tol": 1e-4,
+        "input": [0.1634, 0.8647, 0.6401, 0.8265, 0.0560, 0.2304],
+        "expected_1d": [0.1172, 0.2362, 0.1887, 0.2274, 0.1052, 0.1253],
+        "expected_2x3_axis1": [[0.2161, 0.4358, 0.3481], [0.4966, 0.2298, 0.2736]],
+        "expected_2x3_axis0": [[0.3400, 0.6918, 0.6010], [0.6600, 0.3082, 0.3990]],
+    },
+    # src/ops/norm.rs:635-668 test_layer_normalization (axis -1, default epsilon 1e-5), tolerance 1e-4
+    "layer_normalization": {
+        "cite": "src/ops/norm.rs:635-668",
+        "tol": 1e-4,
+        "input": [[[0.9562, 0.0572], [0.4366, 0.5655], [0.2017, 0.0230], [0.7941, 0.1554], [0.3226, 0.120]]],
+        "scale": [0.0751, 0.6952], "bias": [0.9993, 0.7632], "axis": -1, "epsilon": 1e-5,
+        "expected": [[[1.0744, 0.0680], [0.9243, 1.4576], [1.0744, 0.0684], [1.0744, 0.0680], [1.0744, 0.0683]]],
+    },
     # rten-vecmath/src/erf.rs:138 MAX_EXPECTED_DIFF vs libm; exp.rs:256,260 ULP bounds
     "vecmath": {"cite": "rten-vecmath/src/erf.rs:138; rten-vecmath/src/exp.rs:256-260",
                 "erf_max_abs_diff": 6.631017e-7, "exp_max_ulps": 1.0, "sigmoid_max_ulps": 4.0},
