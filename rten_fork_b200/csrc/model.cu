@@ -193,18 +193,74 @@ int optimize_graph(Graph* g) {
   const int32_t n = static_cast<int32_t>(g->nodes.size());
   std::vector<int32_t> uses(n, 0), producer(n, -1);
   std::vector<std::vector<int32_t>> consumers(n);
+  std::vector<char> dead(n, 0);
+  auto rebuild = [&]() {
+    std::fill(uses.begin(), uses.end(), 0);
+    std::fill(producer.begin(), producer.end(), -1);
+    for (auto& c : consumers) c.clear();
+    for (int32_t i = 0; i < n; ++i) {
+      Node& nd = g->nodes[i];
+      if (nd.kind != NodeKind::Operator || dead[i]) continue;
+      for (int32_t in : nd.inputs)
+        if (in >= 0) {
+          uses[in]++;
+          consumers[in].push_back(i);
+        }
+      for (int32_t o : nd.outputs)
+        if (o >= 0) producer[o] = i;
+    }
+    for (int32_t o : g->output_ids) uses[o] += 1000;  // graph outputs must stay materialised
+  };
+  rebuild();
+  int fused = 0;
+
+  // ---- Gelu: x * (Erf(x / sqrt(2)) + 1) * 0.5  =>  Gelu(x)      (GraphOptimizer::fuse_gelu, src/optimize.rs:401-424)
+  auto scalar_const = [&](int32_t id, float want) {
+    if (id < 0) return false;
+    const Node& c = g->nodes[id];
+    if (c.kind != NodeKind::Constant || !c.constant.host_f32 || c.constant.host_f32->size() != 1) return false;
+    const float v = (*c.constant.host_f32)[0];
+    return fabsf(v - want) <= 1e-6f * fabsf(want);
+  };
+  auto bin_node = [&](int32_t value, int op) -> Node* {  // the binary operator of kind `op` producing `value`
+    if (value < 0 || producer[value] < 0 || dead[producer[value]]) return nullptr;
+    Node& nd = g->nodes[producer[value]];
+    BinaryOp* b = dynamic_cast<BinaryOp*>(nd.op.get());
+    return (b && b->op == op && nd.inputs.size() == 2 && nd.outputs.size() == 1) ? &nd : nullptr;
+  };
   for (int32_t i = 0; i < n; ++i) {
-    Node& nd = g->nodes[i];
-    if (nd.kind != NodeKind::Operator) continue;
-    for (int32_t in : nd.inputs)
-      if (in >= 0) {
-        uses[in]++;
-        consumers[in].push_back(i);
-      }
-    for (int32_t o : nd.outputs)
-      if (o >= 0) producer[o] = i;
+    Node& half = g->nodes[i];
+    if (half.kind != NodeKind::Operator || dead[i]) continue;
+    BinaryOp* hb = dynamic_cast<BinaryOp*>(half.op.get());
+    if (!hb || hb->op != RTG_BIN_MUL || half.inputs.size() != 2 || half.outputs.size() != 1) continue;
+    const int hc = scalar_const(half.inputs[1], 0.5f) ? 1 : (scalar_const(half.inputs[0], 0.5f) ? 0 : -1);
+    if (hc < 0) continue;
+    const int32_t t_val = half.inputs[1 - hc];
+    Node* mul = bin_node(t_val, RTG_BIN_MUL);
+    if (!mul || uses[t_val] != 1) continue;
+    for (int side = 0; side < 2; ++side) {
+      const int32_t x = mul->inputs[side], a_val = mul->inputs[1 - side];
+      Node* add = bin_node(a_val, RTG_BIN_ADD);
+      if (!add || uses[a_val] != 1) continue;
+      const int ac = scalar_const(add->inputs[1], 1.f) ? 1 : (scalar_const(add->inputs[0], 1.f) ? 0 : -1);
+      if (ac < 0) continue;
+      const int32_t e_val = add->inputs[1 - ac];
+      if (e_val < 0 || producer[e_val] < 0 || uses[e_val] != 1) continue;
+      Node& erf = g->nodes[producer[e_val]];
+      UnaryOp* eu = dynamic_cast<UnaryOp*>(erf.op.get());
+      if (!eu || eu->act != ACT_ERF || erf.inputs.size() != 1) continue;
+      const int32_t d_val = erf.inputs[0];
+      Node* div = bin_node(d_val, RTG_BIN_DIV);
+      if (!div || uses[d_val] != 1 || div->inputs[0] != x || !scalar_const(div->inputs[1], 1.41421356237f)) continue;
+      // rewrite: the final Mul becomes Gelu(x); the four inner operators die
+      dead[producer[t_val]] = dead[producer[a_val]] = dead[producer[e_val]] = dead[producer[d_val]] = 1;
+      half.op.reset(new UnaryOp(ACT_GELU, "Gelu"));
+      half.inputs.assign(1, x);
+      ++fused;
+      break;
+    }
   }
-  for (int32_t o : g->output_ids) uses[o] += 1000;  // graph outputs must stay materialised
+  if (fused) rebuild();
   auto single_consumer = [&](int32_t value) -> int32_t {
     if (value < 0 || uses[value] != 1 || consumers[value].size() != 1) return -1;
     return consumers[value][0];
@@ -227,8 +283,6 @@ int optimize_graph(Graph* g) {
     *act = u->act;
     return true;
   };
-  int fused = 0;
-  std::vector<char> dead(n, 0);
   for (int32_t i = 0; i < n; ++i) {
     Node& nd = g->nodes[i];
     if (nd.kind != NodeKind::Operator || dead[i] || nd.outputs.size() != 1 || nd.outputs[0] < 0) continue;

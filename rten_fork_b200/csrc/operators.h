@@ -131,6 +131,13 @@ class GatherOp : public Operator {
   const char* name() const override { return "Gather"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
 };
+// Cast  src/ops/convert.rs: f32 <-> i32 (`as` conversion: truncation toward zero, saturating, NaN -> 0)
+class CastOp : public Operator {
+ public:
+  int to = RTG_F32;
+  const char* name() const override { return "Cast"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
 class BatchNormOp : public Operator {
  public:
   float epsilon = 1e-5f;

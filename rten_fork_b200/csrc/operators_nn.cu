@@ -238,6 +238,63 @@ rtg_status TransposeOp::run(Context* ctx, const OpInputs& in, std::vector<Value>
 }
 
 // ---------------------------------------------------------------- Gather (axis 0 fast path: embedding lookup)
+// ---------------------------------------------------------------- Cast
+namespace {
+__global__ void cast_i32_f32_kernel(float* __restrict__ y, const int32_t* __restrict__ x, int64_t n) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    y[i] = static_cast<float>(x[i]);  // round to nearest even, like Rust's `as f32`
+}
+__global__ void cast_f32_i32_kernel(int32_t* __restrict__ y, const float* __restrict__ x, int64_t n) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    // Rust `as i32`: truncate toward zero, saturate, NaN -> 0
+    y[i] = v != v ? 0 : (v >= 2147483648.f ? INT32_MAX : (v <= -2147483648.f ? INT32_MIN : static_cast<int32_t>(v)));
+  }
+}
+}  // namespace
+
+rtg_status CastOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  Value xt;
+  rtg_tensor xv;
+  RTG_TRY(make_contiguous(ctx, *x, &xt, &xv));
+  Value y;
+  rtg_status st = alloc_value(ctx, to, xv.ndim, xv.shape, false, &y);
+  if (st == RTG_OK) {
+    const int64_t n = numel(xv);
+    if (n > 0) {
+      if (xv.dtype == to) {
+        cudaMemcpyAsync(y.t.data, xv.data, static_cast<size_t>(n) * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+      } else if (to == RTG_F32) {
+        cast_i32_f32_kernel<<<blocks_for(ctx, n), 256, 0, ctx->stream>>>(static_cast<float*>(y.t.data),
+                                                                         static_cast<const int32_t*>(xv.data), n);
+        ctx->launches++;
+      } else {
+        cast_f32_i32_kernel<<<blocks_for(ctx, n), 256, 0, ctx->stream>>>(static_cast<int32_t*>(y.t.data),
+                                                                         static_cast<const float*>(xv.data), n);
+        ctx->launches++;
+      }
+    }
+    if (to == RTG_I32 && x->host_f32) {
+      auto h = std::make_shared<std::vector<int32_t>>();
+      for (float v : *x->host_f32) h->push_back(static_cast<int32_t>(v));
+      y.host_i32 = h;
+    }
+    if (to == RTG_F32 && x->host_i32) {
+      auto h = std::make_shared<std::vector<float>>();
+      for (int32_t v : *x->host_i32) h->push_back(static_cast<float>(v));
+      y.host_f32 = h;
+    }
+  }
+  release_value(ctx, &xt);
+  if (st != RTG_OK) return st;
+  out->push_back(y);
+  return RTG_OK;
+}
+
 rtg_status GatherOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
   const Value *x, *idx;
   RTG_TRY(in.require(0, &x));

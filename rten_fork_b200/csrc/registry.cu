@@ -194,6 +194,14 @@ const OpRegistry& OpRegistry::with_all_ops() {
       out->reset(op);
       return RTG_OK;
     });
+    r->register_op(Op_Cast, [](const OpNodeView& n, std::unique_ptr<Operator>* out) -> rtg_status {
+      if (n.attrs_type != Attrs_CastAttrs || !n.attrs.valid) return attr_error("CastAttrs");
+      CastOp* op = new CastOp();  // CastAttrs: to:0 (DataType: Int32 = 0, Float = 1; src/schema.fbs)
+      const uint8_t to = n.attrs.scalar<uint8_t>(0, DataType_Int32);
+      op->to = to == DataType_Float ? RTG_F32 : RTG_I32;
+      out->reset(op);
+      return RTG_OK;
+    });
     r->register_op(Op_Unsqueeze, simple<ShapeOpsOp>());
     r->register_op(Op_Squeeze, simple<ShapeOpsOp>([](ShapeOpsOp* p) { p->squeeze = true; }));
     return r;

@@ -15,9 +15,9 @@ import numpy as np
 import torch
 import torch.distributed as dist
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "oracle"))
-rank = int(sys.argv[3])
+rank, world = int(sys.argv[3]), int(sys.argv[4])
 torch.cuda.set_device(rank)
-dist.init_process_group("nccl", init_method="tcp://127.0.0.1:" + sys.argv[2], rank=rank, world_size=2,
+dist.init_process_group("nccl", init_method="tcp://127.0.0.1:" + sys.argv[2], rank=rank, world_size=world,
                         device_id=torch.device("cuda", rank))
 import rten_fork_b200 as R
 from rten_fork_b200 import synth
@@ -25,6 +25,7 @@ from rten_fork_b200.parallel import gemm_nsplit, run_batch_sharded, gather_outpu
 import oracle as o, graph_oracle
 ctx = R.default_context(rank)
 ctx.set_math(R.MATH_3XTF32)
+ctx.set_stream(torch.cuda.current_stream().cuda_stream)   # kernels and NCCL are ordered on torch's stream
 rng = o.XorShiftRng(1234)
 for (m, k, n) in ((200, 300, 1000), (64, 128, 512)):
     a, b = rng.fill((m, k)), rng.fill((k, n))
@@ -34,7 +35,7 @@ for (m, k, n) in ((200, 300, 1000), (64, 128, 512)):
 bld = synth.resnet50(image=32, width=8, blocks=(1, 1, 1, 1), classes=10, seed=0)
 x = rng.fill((5, 3, 32, 32))
 m = R.Model.load(bld.build(), ctx=ctx)
-outs, (lo, hi) = run_batch_sharded(m, [x], 2, rank)
+outs, (lo, hi) = run_batch_sharded(m, [x], world, rank)
 full = gather_outputs(torch.from_numpy(outs[0]).cuda(), 5).cpu().numpy()
 want = graph_oracle.run_graph(bld, [x])[0]
 scale = float(np.abs(want).max())
@@ -44,19 +45,44 @@ print("ok", rank)
 """
 
 
-def test_two_gpu_nsplit_and_batch_shard(tmp_path):
-    import torch
+def _launch(tmp_path, world):
+    import time
 
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = str(s.getsockname()[1])
     s.close()
     script = tmp_path / "worker.py"
     script.write_text(_WORKER)
-    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
-                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
-    outs = [p.communicate(timeout=600)[0] for p in procs]
+    logs = [open(tmp_path / f"rank{r}.log", "w+") for r in range(world)]
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r), str(world)], stdout=logs[r],
+                              stderr=subprocess.STDOUT) for r in range(world)]
+    deadline = time.time() + 240
+    # a rank that dies leaves its peers blocked inside the collective: stop everything as soon as one fails
+    while time.time() < deadline and any(p.poll() is None for p in procs):
+        if any(p.poll() not in (None, 0) for p in procs):
+            break
+        time.sleep(0.5)
+    for p in procs:
+        if p.poll() is None:
+            p.kill()
+    outs = []
+    for f in logs:
+        f.seek(0)
+        outs.append(f.read())
+        f.close()
     for r, (p, out) in enumerate(zip(procs, outs)):
-        assert p.returncode == 0 and f"ok {r}" in out, f"rank {r}:\n{out[-3000:]}"
+        assert p.returncode == 0 and f"ok {r}" in out, "\n".join(f"--- rank {i}:\n{o[-2500:]}" for i, o in enumerate(outs))
+
+
+def test_nsplit_and_batch_shard_world_1(tmp_path):
+    """The same worker with a one-rank NCCL group: every code path except the cross-GPU transfer."""
+    _launch(tmp_path, 1)
+
+
+def test_two_gpu_nsplit_and_batch_shard(tmp_path):
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    _launch(tmp_path, 2)
