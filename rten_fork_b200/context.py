@@ -107,6 +107,21 @@ def default_context(device: int = 0) -> Context:
         return ctx
 
 
+def context_for(x) -> Context:
+    """Default context of the device ``x`` lives on (torch CUDA tensor), else of the current / first device."""
+    if not isinstance(x, np.ndarray) and getattr(x, "is_cuda", False):
+        return default_context(x.device.index)
+    try:
+        import sys
+
+        torch = sys.modules.get("torch")
+        if torch is not None and torch.cuda.is_available():
+            return default_context(torch.cuda.current_device())
+    except Exception:
+        pass
+    return default_context(0)
+
+
 def as_tensor(x, device=None) -> N.Tensor:
     """Describe a numpy array (host) or a torch CUDA tensor (device) as an ``rtg_tensor`` view.  The caller keeps the
     object alive for the duration of the call."""

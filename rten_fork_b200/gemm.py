@@ -33,7 +33,7 @@ class GemmExecutor:
     """
 
     def __init__(self, ctx: Context | None = None):
-        self.ctx = ctx or default_context()
+        self.ctx = ctx or default_context()  # host-slice API: device 0 unless a context is given
 
     # reference: GemmExecutor::kernel_type / b_panel_width are CPU-kernel properties; the GPU analogue is the tile.
     def kernel_name(self) -> str:

@@ -18,7 +18,7 @@ import ctypes as C
 import numpy as np
 
 from . import _native as N
-from .context import Context, as_tensor, default_context
+from .context import context_for, Context, as_tensor, default_context
 
 ACT = {"none": 0, "relu": 1, "clip": 2, "gelu": 3, "sigmoid": 4, "silu": 5, "erf": 6, "tanh": 7, "sqrt": 8}
 BIN = {"add": 0, "sub": 1, "mul": 2, "div": 3, "pow": 4}
@@ -85,7 +85,7 @@ def conv(input, kernel, bias=None, padding=(0, 0, 0, 0), groups=1, strides=(1, 1
     ``residual`` / ``activation`` select the fused epilogue ``act(conv + bias + residual)``; the defaults give the
     reference operator.
     """
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(input)
     a = _conv_attrs(padding, groups, strides, dilations)
     ti, tw = as_tensor(input), as_tensor(kernel)
     tb = as_tensor(bias) if bias is not None else None
@@ -119,7 +119,7 @@ class Conv:
 
 
 def matmul(a, b, *, out=None, ctx: Context | None = None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(a)
     ta, tb = as_tensor(a), as_tensor(b)
     shape = (C.c_int64 * N.RTG_MAX_DIMS)()
     nd = C.c_int32()
@@ -141,7 +141,7 @@ class MatMul:
 
 
 def gemm_op(a, b, c=None, alpha=1.0, beta=1.0, transpose_a=False, transpose_b=False, *, ctx: Context | None = None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(a)
     ta, tb = as_tensor(a), as_tensor(b)
     tc = as_tensor(c) if c is not None else None
     if ta.ndim != 2:
@@ -172,7 +172,7 @@ class Gemm:
 
 
 def _unary(kind, x, lo=0.0, hi=0.0, in_place=False, ctx=None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(x)
     ti = as_tensor(x)
     out = x if in_place else _empty_like_kind(x, x.shape)
     if in_place and not _is_torch(x) and not x.flags.c_contiguous:
@@ -217,7 +217,7 @@ def clip(x, min_val=None, max_val=None, **kw):
 
 
 def _binary(kind, a, b, out=None, ctx=None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(a)
     ta, tb = as_tensor(a), as_tensor(b)
     shape = (C.c_int64 * N.RTG_MAX_DIMS)()
     nd = C.c_int32()
@@ -266,7 +266,7 @@ def _pool_attrs(kernel_size, strides, padding, count_include_pad=False):
 
 
 def _pool(kind, x, kernel_size, strides, padding, count_include_pad=False, ctx=None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(x)
     a = _pool_attrs(kernel_size, strides, padding, count_include_pad)
     ti = as_tensor(x)
     shape = (C.c_int64 * 4)()
@@ -286,7 +286,7 @@ def average_pool(x, kernel_size, strides, padding=(0, 0, 0, 0), count_include_pa
 
 
 def global_average_pool(x, *, ctx=None):
-    ctx = ctx or default_context()
+    ctx = ctx or context_for(x)
     ti = as_tensor(x)
     if ti.ndim != 4:
         raise N.RtgError(5, "input must have 4 dims (NCHW)")
