@@ -33,6 +33,12 @@ rtg_status ConvOp::partial_plan(const rtg_tensor& w, ConvPlan* p) const {
   p->kh = w.ndim == 4 ? w.shape[2] : 1, p->kw = w.ndim == 4 ? w.shape[3] : w.shape[2];
   p->groups = attrs.groups;
   p->c = p->cg * attrs.groups;
+  // strides / dilations as conv_plan resolves them (1-D convolutions carry theirs in the W slot)
+  const bool one_d = w.ndim == 3;
+  p->stride_h = one_d ? 1 : (attrs.n_strides > 0 ? attrs.strides[0] : 1);
+  p->stride_w = one_d ? (attrs.n_strides > 0 ? attrs.strides[0] : 1) : (attrs.n_strides > 1 ? attrs.strides[1] : 1);
+  p->dil_h = one_d ? 1 : (attrs.n_dilations > 0 ? attrs.dilations[0] : 1);
+  p->dil_w = one_d ? (attrs.n_dilations > 0 ? attrs.dilations[0] : 1) : (attrs.n_dilations > 1 ? attrs.dilations[1] : 1);
   bool unit = true, nopad = attrs.pad_mode == RTG_PAD_SAME;
   for (int i = 0; i < attrs.n_strides; ++i) unit = unit && attrs.strides[i] == 1;
   for (int i = 0; i < attrs.n_dilations; ++i) unit = unit && attrs.dilations[i] == 1;
@@ -82,7 +88,8 @@ rtg_status ConvOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
   ConvWeights local;
   const ConvWeights* cw = &weights;
   const bool use_prepared = prepared && prepared_from == w->t.data && prepared_pointwise == p.pointwise &&
-                            prepared_depthwise == p.depthwise;
+                            prepared_depthwise == p.depthwise &&
+                            weights.window == (!p.pointwise && !p.depthwise && conv_window_supported(p));
   if (st == RTG_OK && !use_prepared) {
     st = conv_prepare_weights(ctx, p, static_cast<const float*>(wv.data), &local);
     cw = &local;

@@ -53,6 +53,47 @@ __global__ void pool2d_kernel(float* __restrict__ out, const float* __restrict__
   }
 }
 
+// NHWC-dense fast path: one thread per (pixel, 4 channels), float4 loads coalesced over channels, 32-bit index math.
+// Same fold order per element as pool2d_kernel, so results are bit-identical.
+__global__ void pool2d_nhwc4_kernel(float* __restrict__ out, const float* __restrict__ in, PoolGeom g) {
+  const int c4 = g.c >> 2;
+  const int total = g.n * g.oh * g.ow * c4;  // host guarantees < 2^31
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int r = i;
+    const int cq = r % c4;
+    r /= c4;
+    const int ox = r % g.ow;
+    r /= g.ow;
+    const int oy = r % g.oh;
+    const int n = r / g.oh;
+    const float4* ip = reinterpret_cast<const float4*>(in + static_cast<int64_t>(n) * g.h * g.w * g.c) + cq;
+    const float ninf = __int_as_float(0xff800000);
+    float4 acc = g.kind == RTG_POOL_MAX ? make_float4(ninf, ninf, ninf, ninf) : make_float4(0.f, 0.f, 0.f, 0.f);
+    int count = 0;
+    for (int ky = 0; ky < g.kh; ++ky) {
+      const int iy = oy * g.stride_h + ky - g.pad_t;
+      if (iy < 0 || iy >= g.h) continue;
+      for (int kx = 0; kx < g.kw; ++kx) {
+        const int ix = ox * g.stride_w + kx - g.pad_l;
+        if (ix < 0 || ix >= g.w) continue;
+        const float4 v = __ldg(ip + (iy * g.w + ix) * c4);
+        if (g.kind == RTG_POOL_MAX) {
+          acc.x = fmaxf(acc.x, v.x), acc.y = fmaxf(acc.y, v.y), acc.z = fmaxf(acc.z, v.z), acc.w = fmaxf(acc.w, v.w);
+        } else {
+          acc.x = __fadd_rn(acc.x, v.x), acc.y = __fadd_rn(acc.y, v.y);
+          acc.z = __fadd_rn(acc.z, v.z), acc.w = __fadd_rn(acc.w, v.w);
+        }
+        ++count;
+      }
+    }
+    if (g.kind == RTG_POOL_AVG) {
+      const float d = static_cast<float>(g.count_include_pad ? g.kh * g.kw : count);
+      acc.x = __fdiv_rn(acc.x, d), acc.y = __fdiv_rn(acc.y, d), acc.z = __fdiv_rn(acc.z, d), acc.w = __fdiv_rn(acc.w, d);
+    }
+    reinterpret_cast<float4*>(out)[i] = acc;
+  }
+}
+
 // One warp per (n, c) for NCHW (contiguous plane, shuffle reduction); for NHWC one thread per (n, c) column walks the
 // pixels so that a warp reads 32 consecutive channels per pixel (coalesced).
 __global__ void gap_nchw_kernel(float* __restrict__ out, const float* __restrict__ in, int64_t nc, int hw, int c,
@@ -134,6 +175,15 @@ rtg_status pool2d_forward(Context* ctx, int kind, const rtg_tensor& in, const rt
   for (int i = 0; i < 4; ++i) g.is[i] = in.strides[i], g.os[i] = out.strides[i];
   g.kind = kind, g.count_include_pad = a.count_include_pad;
   g.chan_fastest = (out.strides[1] == 1 && g.c > 1) ? 1 : 0;
+  if (is_nhwc_dense(in) && is_nhwc_dense(out) && g.c % 4 == 0 && total < (1ll << 31) &&
+      (reinterpret_cast<uintptr_t>(in.data) & 15) == 0 && (reinterpret_cast<uintptr_t>(out.data) & 15) == 0) {
+    const int blocks4 = static_cast<int>(std::min<int64_t>(div_ceil(total / 4, 256), static_cast<int64_t>(ctx->num_sms) * 32));
+    pool2d_nhwc4_kernel<<<blocks4, 256, 0, ctx->stream>>>(static_cast<float*>(out.data),
+                                                         static_cast<const float*>(in.data), g);
+    ctx->launches++;
+    RTG_CUDA(cudaGetLastError());
+    return RTG_OK;
+  }
   const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 16));
   pool2d_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(out.data), static_cast<const float*>(in.data), g);
   ctx->launches++;
