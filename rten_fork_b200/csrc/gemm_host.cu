@@ -142,7 +142,25 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     rec.flops = ctx->pending_flops, rec.bytes = ctx->pending_bytes;
     RTG_CUDA(cudaEventRecord(rec.a, ctx->stream));
   }
-  kern<<<grid, Cfg::kThreads, Cfg::kSmemBytes, ctx->stream>>>(ma, mb, md, mr, args);
+  {
+    // Programmatic stream serialisation: the kernel's prologue (barrier init, TMEM allocation, tensor-map prefetch)
+    // overlaps the tail of the previous kernel; it synchronises itself with griddepcontrol.wait.
+    static const bool pdl = []() {
+      const char* e = getenv("RTG_PDL");
+      return !e || atoi(e) != 0;
+    }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(Cfg::kThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    RTG_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, md, mr, args));
+  }
   ctx->launches++;
   RTG_CUDA(cudaGetLastError());
   if (ctx->ktiming) {
@@ -170,7 +188,23 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
       fprintf(stderr, " | %s total %.0f", roles[r], acc[4]);
       for (int i = 0; i < 4; ++i)
         if (slots[r][i][0] != '-') fprintf(stderr, " %s %.0f", slots[r][i], acc[i]);
+      double m5 = 0, m6 = 0, m7 = 0;
+      for (int b = 0; b < grid; ++b) {
+        m5 += static_cast<double>(h[(b * 4 + r) * 8 + 5]) / grid;
+        m6 += static_cast<double>(h[(b * 4 + r) * 8 + 6]) / grid;
+        m7 += static_cast<double>(h[(b * 4 + r) * 8 + 7]) / grid;
+      }
+      if (r == 0) fprintf(stderr, " first_tma@%.0f", m5);
+      if (r == 1) fprintf(stderr, " first_mma@%.0f last_commit@%.0f", m5, m6);
+      if (r == 2) fprintf(stderr, " setup_done@%.0f epi_drained@%.0f cta_end@%.0f", m7, m5, m6);
     }
+    unsigned long long t0 = ~0ull, t0max = 0, t1 = 0, t1min = ~0ull;
+    for (int b = 0; b < grid; ++b) {
+      const unsigned long long a = h[(b * 4 + 3) * 8 + 5], e = h[(b * 4 + 3) * 8 + 6];
+      t0 = std::min(t0, a), t0max = std::max(t0max, a), t1 = std::max(t1, e), t1min = std::min(t1min, e);
+    }
+    fprintf(stderr, " | wall: first CTA start -> last CTA end %.1f us, start skew %.1f us, end skew %.1f us",
+            (t1 - t0) * 1e-3, (t0max - t0) * 1e-3, (t1 - t1min) * 1e-3);
     fprintf(stderr, "\n");
   }
 #endif

@@ -80,6 +80,18 @@ struct GemmArgs {
     stmt;                              \
     prof_acc_[slot] += clock64() - t_; \
   } while (0)
+#define PROF_MARK(role, slot)                                                                                     \
+  do {                                                                                                            \
+    if (args.prof) {                                                                                              \
+      unsigned long long* p_ = args.prof + (blockIdx.x * 4 + (role)) * 8 + (slot);                                \
+      if (*p_ == 0) *p_ = static_cast<unsigned long long>(clock64() - prof_entry_);                               \
+    }                                                                                                             \
+  } while (0)
+#define PROF_MARK_LAST(role, slot)                                                                                \
+  do {                                                                                                            \
+    if (args.prof)                                                                                                \
+      args.prof[(blockIdx.x * 4 + (role)) * 8 + (slot)] = static_cast<unsigned long long>(clock64() - prof_entry_); \
+  } while (0)
 #define PROF_DUMP(role)                                                              \
   do {                                                                               \
     if (args.prof) {                                                                 \
@@ -92,6 +104,8 @@ struct GemmArgs {
 #define PROF_DECL
 #define PROF_WAIT(slot, stmt) stmt
 #define PROF_DUMP(role)
+#define PROF_MARK(role, slot)
+#define PROF_MARK_LAST(role, slot)
 #endif
 
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
@@ -108,7 +122,11 @@ struct GemmCfg {
   static_assert(MODE == 0 || BN <= 128, "3xTF32 keeps BN/2 running sums per epilogue thread in registers");
   static constexpr int kBBytes = BN * kBK * 4;
   static constexpr int kRawBytes = kABytes + kBBytes;
-  static constexpr int kStageBytes = kRawBytes * (MODE ? 2 : 1);
+  // MODE 1 (3xTF32): a stage is [A raw][B raw][B lo].  The A operand of the MMAs lives in tensor memory: the split
+  // warps write hi (= raw bits) and lo of every A row into a 64-column TMEM slot per stage, so the three MMAs of a
+  // k-step read only B from shared memory (shared-memory bandwidth, not the tensor pipe, is what bounds this mode).
+  static constexpr int kStageBytes = MODE ? kRawBytes + kBBytes : kRawBytes;
+  static constexpr int kTmemAStageCols = 2 * kBK;  // hi plane + lo plane, one 32-bit column per k
   // Epilogue staging: every epilogue warp owns kEpiBufs buffers of 32 rows x 128 bytes (one 32-column chunk of its
   // 32 accumulator rows, 128B-swizzled) through which the residual arrives (TMA load) and the result leaves (TMA
   // store), so that global traffic is whole 128-byte rows instead of one strided 16-byte access per lane.
@@ -117,7 +135,9 @@ struct GemmCfg {
   static constexpr int kEpiBufBytes = 4096;
   static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
   static constexpr int kMaxSmem = 227 * 1024 - 2048 - kEpiBytes;  // barriers + alignment slack
-  static constexpr int kStagesRaw = kMaxSmem / kStageBytes;
+  static constexpr int kStagesSmem = kMaxSmem / kStageBytes;
+  static constexpr int kStagesTmem = MODE ? (512 - 2 * BN) / kTmemAStageCols : 8;  // accumulators take 2 * BN columns
+  static constexpr int kStagesRaw = kStagesSmem < kStagesTmem ? kStagesSmem : kStagesTmem;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
   // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
@@ -125,7 +145,7 @@ struct GemmCfg {
   static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
   static constexpr int kXfThreads = MODE ? 192 : 0;
   static constexpr int kThreads = (kEpiWarps + 2) * 32 + kXfThreads;
-  static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int kTmemCols = MODE ? 512 : (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
 };
 
 __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& base, int64_t& cs) {
@@ -145,6 +165,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
                     const GemmArgs args) {
   using Cfg = GemmCfg<BN, MODE>;
+#ifdef RTG_PROF
+  const long long prof_entry_ = clock64();
+  if (threadIdx.x == 0 && args.prof) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    args.prof[(blockIdx.x * 4 + 3) * 8 + 5] = gt;
+  }
+#endif
   constexpr int kStages = Cfg::kStages;
   constexpr bool kChunked = MODE == 1;
   constexpr int kTmaWarp = Cfg::kEpiWarps, kMmaWarp = Cfg::kEpiWarps + 1;
@@ -200,6 +228,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) PROF_MARK(2, 7);  // setup (barriers, TMEM allocation) done
+  // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may run
+  // while the previous kernel in the stream drains.  From here on global memory is read and written: wait for the
+  // predecessor's results (and its last reads of buffers this launch overwrites), then let the successor start its
+  // own prologue early.  Both are no-ops when the launch did not ask for programmatic serialisation.
+  ptx::grid_dependency_wait();
+  ptx::grid_launch_dependents();
 
   if (warp == kTmaWarp) {
     // ===================================================== TMA producer
@@ -237,6 +272,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #ifdef RTG_PROF
           const long long ti_ = clock64();
 #endif
+          PROF_MARK(0, 5);  // first TMA issue
           ptx::mbar_expect_tx(fb, Cfg::kRawBytes);
           if (A_KIND == 0) {
             ptx::tma_load_2d(a_dst, &tmA, fb, kb * kBK, m0);
@@ -287,7 +323,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint64_t b_d0 = ptx::make_smem_desc(smem_base + kABytes, b_lbo, b_sbo, b_layout);
       const uint32_t a_hi = static_cast<uint32_t>(a_d0 >> 32), b_hi = static_cast<uint32_t>(b_d0 >> 32);
       const uint32_t a_lo0 = static_cast<uint32_t>(a_d0), b_lo0 = static_cast<uint32_t>(b_d0);
-      constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4, kLoStep = Cfg::kRawBytes >> 4;
+      constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4;
+      constexpr uint32_t kBLoStep = Cfg::kBBytes >> 4;  // MODE 1: the lo plane of B follows the raw B tile
       constexpr uint32_t kAStep = 32 >> 4;                       // 8 floats along the swizzled 128-byte row
       constexpr uint32_t kBStep = (B_MAJOR ? 1024 : 32) >> 4;    // MN-major: 8 k-rows = 1024 bytes further
       int s = 0;
@@ -308,6 +345,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #ifdef RTG_PROF
             const long long ti_ = clock64();
 #endif
+            PROF_MARK(1, 5);  // first operands ready
             const uint32_t a_lo = a_lo0 + so, b_lo = b_lo0 + so;
 #pragma unroll
             for (int k = 0; k < kBK / 8; ++k) {
@@ -315,10 +353,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               if (MODE == 0) {
                 ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, acc);
               } else {
-                // lo(A) * B, A * lo(B), A * B: smallest terms first
-                ptx::mma_tf32_ss_w(d_tmem, a_lo + kLoStep + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, acc);
-                ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + kLoStep + k * kBStep, b_hi, idesc, 1);
-                ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, 1);
+                // lo(A) * B, A * lo(B), A * B: smallest terms first.  A planes: TMEM columns [0,32) hi, [32,64) lo
+                const uint32_t a_t = tmem_base + 2 * BN + s * Cfg::kTmemAStageCols + k * 8;
+                ptx::mma_tf32_ts_w(d_tmem, a_t + kBK, b_lo + k * kBStep, b_hi, idesc, acc);
+                ptx::mma_tf32_ts_w(d_tmem, a_t, b_lo + kBLoStep + k * kBStep, b_hi, idesc, 1);
+                ptx::mma_tf32_ts_w(d_tmem, a_t, b_lo + k * kBStep, b_hi, idesc, 1);
               }
             }
             ptx::mma_commit(empty_bar(s));
@@ -333,6 +372,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           ptx::mma_commit(tfull_bar(as));
+          PROF_MARK_LAST(1, 6);  // last accumulator commit
           if (++as == 2) {
             as = 0;
             aph ^= 1u;
@@ -375,6 +415,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const float row_bias = (args.bias_mode == BIAS_ROW && row_ok) ? args.bias[m] : 0.f;
       const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 
+      // per-column bias of this warp's chunks: one coalesced load per chunk, issued now so that its latency hides
+      // behind the wait for the accumulators
+      float bias_lane[kCols / 32];
+#pragma unroll
+      for (int i = 0; i < kCols / 32; ++i) {
+        const int n = n0 + col0 + i * 32 + lane;
+        bias_lane[i] = (args.bias_mode == BIAS_COL && n < args.N) ? __ldg(args.bias + n) : 0.f;
+      }
+
       // residual chunk (32 rows x 32 columns at column c0 of the tile) -> staging buffer b, by TMA
       auto fetch_residual = [&](int c0, int b) {
         if (lane == 0) {
@@ -398,7 +447,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += row_bias;
         } else if (args.bias_mode == BIAS_COL) {
-          const float bl = lane < ncols ? __ldg(args.bias + n0 + c0 + lane) : 0.f;  // one coalesced load per chunk
+          const float bl = bias_lane[(c0 - col0) >> 5];  // lane j holds the bias of column c0 + j (loaded at tile start)
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, bl, j);
         }
@@ -462,8 +511,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (!kChunked) {
         PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
         ptx::tc_fence_after();
-#pragma unroll 1
-        for (int i = 0; i < nch; ++i) {
+#pragma unroll
+        for (int i = 0; i < kCols / 32; ++i) {
+          if (i >= nch) break;
           const int c0 = col0 + i * 32;
           if (staged_r && Cfg::kEpiBufs > 1 && i + 1 < nch) fetch_residual(c0 + 32, eb ^ 1);
           float v[32];
@@ -519,33 +569,58 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
     PROF_WAIT(3, if (staged_d && lane == 0) ptx::bulk_wait<0>());  // stores complete before shared memory goes away
-    if (warp == 0 && lane == 0) PROF_DUMP(2);
+    if (warp == 0 && lane == 0) {
+      PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
+      PROF_DUMP(2);
+    }
   } else if (MODE == 1 && warp > kMmaWarp) {
     // ===================================================== 3xTF32 operand split
+    // x = hi + lo with hi = x truncated to TF32 (the tensor core reads that from the raw fp32 bits by itself) and
+    // lo = x - hi (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
+    // Warps 0-3 of this role own the A tile, one row per thread: the row goes to tensor memory as a hi plane (raw
+    // bits) and a lo plane, from where the MMAs read it.  Warps 4-5 write the lo plane of B next to the raw B tile.
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
+    const int sw = t >> 5;
+    auto lo_of = [](float x) {
+      return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u)) + 0x1000u;
+    };
     int s = 0;
     uint32_t ph = 0;
-    constexpr int kVecs = Cfg::kRawBytes / 16;
     PROF_DECL;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       for (int kb = 0; kb < num_kb; ++kb) {
         PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
-        uint8_t* raw = smem_raw + (smem_base - ptx::smem_u32(smem_raw)) + s * Cfg::kStageBytes;
-        float4* rawv = reinterpret_cast<float4*>(raw);
-        float4* lov = reinterpret_cast<float4*>(raw + Cfg::kRawBytes);
+        const uint32_t stage = smem_base + s * Cfg::kStageBytes;
+        if (sw < 4) {
+          const int q = warp & 3;  // TMEM lane quarter this warp may write
+          const int row = q * 32 + lane;
+          const uint32_t src = stage + row * 128;
+          const uint32_t swz = row & 7;
+          uint32_t hi[32], lo[32];
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 x = ptx::lds_v4(src + ((j4 ^ swz) << 4));
+            hi[4 * j4 + 0] = __float_as_uint(x.x), lo[4 * j4 + 0] = lo_of(x.x);
+            hi[4 * j4 + 1] = __float_as_uint(x.y), lo[4 * j4 + 1] = lo_of(x.y);
+            hi[4 * j4 + 2] = __float_as_uint(x.z), lo[4 * j4 + 2] = lo_of(x.z);
+            hi[4 * j4 + 3] = __float_as_uint(x.w), lo[4 * j4 + 3] = lo_of(x.w);
+          }
+          const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
+          ptx::tmem_st_32x32(dst, hi);
+          ptx::tmem_st_32x32(dst + kBK, lo);
+          ptx::tmem_st_wait();
+          ptx::tc_fence_before();
+        } else {
+          constexpr int kBVecs = Cfg::kBBytes / 16;
+          const uint32_t braw = stage + kABytes, blo = braw + Cfg::kBBytes;
 #pragma unroll 4
-        for (int i = t; i < kVecs; i += Cfg::kXfThreads) {
-          // x = hi + lo with hi = x truncated to TF32 (what the tensor core reads from the raw tile) and lo = x - hi
-          // (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
-          const float4 x = rawv[i];
-          float4 lo;
-          lo.x = __uint_as_float(__float_as_uint(x.x - __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u)) + 0x1000u);
-          lo.y = __uint_as_float(__float_as_uint(x.y - __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u)) + 0x1000u);
-          lo.z = __uint_as_float(__float_as_uint(x.z - __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u)) + 0x1000u);
-          lo.w = __uint_as_float(__float_as_uint(x.w - __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u)) + 0x1000u);
-          lov[i] = lo;
+          for (int i = t - 128; i < kBVecs; i += 64) {
+            const float4 x = ptx::lds_v4(braw + i * 16);
+            ptx::sts_v4(blo + i * 16, make_float4(__uint_as_float(lo_of(x.x)), __uint_as_float(lo_of(x.y)),
+                                                  __uint_as_float(lo_of(x.z)), __uint_as_float(lo_of(x.w))));
+          }
+          ptx::fence_proxy_async_smem();
         }
-        ptx::fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(xf_bar(s));
         if (++s == kStages) {
@@ -563,6 +638,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
+  if (threadIdx.x == 0) PROF_MARK_LAST(2, 6);  // CTA end
+#ifdef RTG_PROF
+  if (threadIdx.x == 0 && args.prof) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    args.prof[(blockIdx.x * 4 + 3) * 8 + 6] = gt;
+  }
+#endif
 }
 
 }  // namespace rtg
