@@ -130,10 +130,14 @@ struct GemmCfg {
   // Epilogue staging: every epilogue warp owns kEpiBufs buffers of 32 rows x 128 bytes (one 32-column chunk of its
   // 32 accumulator rows, 128B-swizzled) through which the residual arrives (TMA load) and the result leaves (TMA
   // store), so that global traffic is whole 128-byte rows instead of one strided 16-byte access per lane.
-  static constexpr int kEpiWarps = MODE ? 8 : 4;
-  static constexpr int kEpiBufs = MODE ? 1 : 2;
+  // Eight epilogue warps in both modes (two per TMEM lane quarter, each owning half of the tile's columns): a chunk
+  // is a latency-bound chain (tcgen05.ld -> math -> st.shared -> fence -> TMA store), so throughput comes from
+  // running more chunks side by side.
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kEpiBufs = 1;
   static constexpr int kEpiBufBytes = 4096;
-  static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
+  static constexpr int kEpiBiasBytes = kEpiWarps * (BN / 2) * 4;  // per-warp copy of its columns' bias
+  static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes + kEpiBiasBytes;
   static constexpr int kMaxSmem = 227 * 1024 - 2048 - kEpiBytes;  // barriers + alignment slack
   static constexpr int kStagesSmem = kMaxSmem / kStageBytes;
   static constexpr int kStagesTmem = MODE ? (512 - 2 * BN) / kTmemAStageCols : 8;  // accumulators take 2 * BN columns
@@ -389,6 +393,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const bool staged_d = (args.flags & kFlagStagedD) != 0;
     const bool staged_r = (args.flags & kFlagStagedR) != 0;
     const uint32_t ebuf0 = epi_base + warp * Cfg::kEpiBufs * Cfg::kEpiBufBytes;
+    const uint32_t ebias = epi_base + Cfg::kEpiWarps * Cfg::kEpiBufs * Cfg::kEpiBufBytes + warp * (BN / 2) * 4;
     int eb = 0;            // staging buffer of the next chunk
     uint32_t rph = 0;      // phase bit per staging buffer of this warp's residual barriers
     int as = 0;
@@ -415,13 +420,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const float row_bias = (args.bias_mode == BIAS_ROW && row_ok) ? args.bias[m] : 0.f;
       const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 
-      // per-column bias of this warp's chunks: one coalesced load per chunk, issued now so that its latency hides
-      // behind the wait for the accumulators
-      float bias_lane[kCols / 32];
+      // this warp's slice of the per-column bias -> shared memory (read back as broadcast loads in finish), issued
+      // before the wait for the accumulators so that the global-load latency is hidden
+      if (args.bias_mode == BIAS_COL) {
 #pragma unroll
-      for (int i = 0; i < kCols / 32; ++i) {
-        const int n = n0 + col0 + i * 32 + lane;
-        bias_lane[i] = (args.bias_mode == BIAS_COL && n < args.N) ? __ldg(args.bias + n) : 0.f;
+        for (int i = 0; i < kCols / 32; ++i) {
+          const int n = n0 + col0 + i * 32 + lane;
+          ptx::sts_f32(ebias + (i * 32 + lane) * 4, n < args.N ? __ldg(args.bias + n) : 0.f);
+        }
+        __syncwarp();
       }
 
       // residual chunk (32 rows x 32 columns at column c0 of the tile) -> staging buffer b, by TMA
@@ -447,9 +454,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += row_bias;
         } else if (args.bias_mode == BIAS_COL) {
-          const float bl = bias_lane[(c0 - col0) >> 5];  // lane j holds the bias of column c0 + j (loaded at tile start)
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, bl, j);
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b4 = ptx::lds_v4(ebias + (c0 - col0 + 4 * j4) * 4);  // same address in every lane: broadcast
+            v[4 * j4 + 0] += b4.x, v[4 * j4 + 1] += b4.y, v[4 * j4 + 2] += b4.z, v[4 * j4 + 3] += b4.w;
+          }
         }
         if (staged_d) {
           const uint32_t buf = ebuf0 + eb * Cfg::kEpiBufBytes;
@@ -511,9 +520,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (!kChunked) {
         PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
         ptx::tc_fence_after();
-#pragma unroll
-        for (int i = 0; i < kCols / 32; ++i) {
-          if (i >= nch) break;
+#pragma unroll 1
+        for (int i = 0; i < nch; ++i) {
           const int c0 = col0 + i * 32;
           if (staged_r && Cfg::kEpiBufs > 1 && i + 1 < nch) fetch_residual(c0 + 32, eb ^ 1);
           float v[32];
