@@ -123,8 +123,11 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     RTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     configured[ctx->device & 15] = true;
   }
-  const int m_tiles = (args.M + kBM - 1) / kBM, n_tiles = (args.N + BN - 1) / BN;
-  const int grid = std::min(m_tiles * n_tiles, ctx->num_sms);
+  const int m_tiles_1 = (args.M + kBM - 1) / kBM, n_tiles = (args.N + BN - 1) / BN;
+  const int64_t m_tiles = A_KIND == 2 ? static_cast<int64_t>(args.ic.win_rows) * args.ic.win_tpr
+                                      : A_KIND == 3 ? static_cast<int64_t>(args.ic.bat_count) * m_tiles_1 : m_tiles_1;
+  if (m_tiles * n_tiles > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "too many output tiles");
+  const int grid = static_cast<int>(std::min<int64_t>(m_tiles * n_tiles, ctx->num_sms));
 #ifdef RTG_PROF
   static unsigned long long* prof_buf = nullptr;
   GemmArgs pargs = args;
@@ -210,30 +213,30 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
 #endif
   char name[96];
   snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s>", BN, MODE ? "3xTF32" : "TF32",
-           A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
+           A_KIND == 3 ? "batched" : A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
   ctx->last_kernel = name;
   return RTG_OK;
 }
 
 template <int A_KIND, int B_MAJOR>
 static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           GemmArgs args, int plane_rows = 0) {
+                           GemmArgs args, int plane_rows = 0, int64_t num_planes = 0) {
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;
   auto stageable = [&](const float* p, const OutMap& om) {
     if (!p || om.hw > 0) return false;
     if ((reinterpret_cast<uintptr_t>(p + om.chan_off) & 15) != 0) return false;
-    return args.M == 1 || (om.ld > 0 && om.ld % 4 == 0);
+    return (args.M == 1 && num_planes <= 1) || (om.ld > 0 && om.ld % 4 == 0);
   };
   if (!(args.flags & 8) && stageable(args.D, args.dmap)) {
     // plane_rows > 0 (row-window convolution): rows are output columns of one image row, planes the image rows
     const uint64_t rows = plane_rows > 0 ? plane_rows : args.M;
-    const uint64_t planes = plane_rows > 0 ? args.M / plane_rows : 1;
-    const uint64_t ld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.dmap.ld;
+    const uint64_t planes = num_planes > 0 ? num_planes : plane_rows > 0 ? args.M / plane_rows : 1;
+    const uint64_t ld = (args.M == 1 && num_planes <= 1) ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.dmap.ld;
     RTG_TRY(encode_out_3d(ctx, &md, args.D + args.dmap.chan_off, args.N, rows, planes, ld));
     args.flags |= kFlagStagedD;
     if (stageable(args.R, args.rmap)) {
-      const uint64_t rld = args.M == 1 ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.rmap.ld;
+      const uint64_t rld = (args.M == 1 && num_planes <= 1) ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.rmap.ld;
       RTG_TRY(encode_out_3d(ctx, &mr, args.R + args.rmap.chan_off, args.N, rows, planes, rld));
       args.flags |= kFlagStagedR;
     }
@@ -250,14 +253,14 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
 }
 
 // Largest tile that still fills the machine; smaller tiles when the problem has too few of them.
-static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb) {
+static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t batch = 1) {
   // Cycle model fitted to the per-role counters of the PROF build (profiles/): the MMA thread needs
   // max(64, BN/2) cycles per 128 x BN x 8 instruction (64 is the dispatch floor, so BN = 64 runs the tensor pipe at
   // half rate) plus ~150 cycles of barrier traffic per k-block; the epilogue drains a tile in ~1000 + 12*BN cycles
   // with four warps (3xTF32 has eight); MMA and epilogue of consecutive tiles overlap.
   const bool x3 = ctx->math != RTG_MATH_TF32;
   const int max_bn = x3 ? 128 : 256;
-  const int64_t m_tiles = div_ceil(M, kBM);
+  const int64_t m_tiles = div_ceil(M, kBM) * batch;
   int best = 64;
   double best_cost = 1e300;
   const int cands[3] = {256, 128, 64};
@@ -342,6 +345,99 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
   if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g);
   return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g);
+}
+
+// ---------------------------------------------------------------- batched GEMM (one launch for all batch entries)
+static rtg_status encode_4d(Context* ctx, CUtensorMap* map, const float* base, const uint64_t dims_in[4],
+                            const uint64_t strides_elems[3], uint32_t box_inner, uint32_t box_outer,
+                            CUtensorMapSwizzle swz) {
+  cuuint64_t dims[4] = {dims_in[0], dims_in[1], dims_in[2], dims_in[3]};
+  cuuint64_t strides[3] = {strides_elems[0] * sizeof(float), strides_elems[1] * sizeof(float),
+                           strides_elems[2] * sizeof(float)};
+  cuuint32_t box[4] = {box_inner, box_outer, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (batched) failed (%d): base %p dims [%llu,%llu,%llu,%llu]",
+                      (int)r, base, (unsigned long long)dims[0], (unsigned long long)dims[1],
+                      (unsigned long long)dims[2], (unsigned long long)dims[3]);
+  return RTG_OK;
+}
+
+bool gemm_batched_supported(const BatchedView& a, const BatchedView& b, int64_t n0, int64_t n1, int64_t N) {
+  auto batch_ok = [&](const BatchedView& v) {
+    const bool ok0 = n0 == 1 || v.bs0 == 0 || (v.bs0 > 0 && v.bs0 % 4 == 0);
+    const bool ok1 = n1 == 1 || v.bs1 == 0 || (v.bs1 > 0 && v.bs1 % 4 == 0);
+    return ok0 && ok1;
+  };
+  if (!batch_ok(a) || !batch_ok(b)) return false;
+  if (n0 > INT32_MAX || n1 > INT32_MAX || n0 * n1 > INT32_MAX) return false;
+  if (a.rows > INT32_MAX || a.cols > INT32_MAX || N > INT32_MAX) return false;
+  if (!direct_ok(a.p, a.cs, a.rs, a.rows)) return false;
+  return direct_ok(b.p, b.rs, b.cs, N) || direct_ok(b.p, b.cs, b.rs, b.rows);
+}
+
+rtg_status gemm_batched_device(Context* ctx, BatchedView a, BatchedView b, int64_t n0, int64_t n1, float* D,
+                               const Epilogue& ep) {
+  const int64_t M = a.rows, K = a.cols, N = b.cols, batch = n0 * n1;
+  if (M == 0 || N == 0 || batch == 0) return RTG_OK;
+  if (!gemm_batched_supported(a, b, n0, n1, N)) return set_error(RTG_ERR_INTERNAL, "batched GEMM operands not addressable");
+  const int64_t Kp = div_ceil(K, 4) * 4, Np = div_ceil(N, 4) * 4;
+  const int b_major = direct_ok(b.p, b.rs, b.cs, N) ? 0 : 1;
+  const int bn = choose_bn(ctx, M, N, div_ceil(K, kBK), batch);
+  // a broadcast batch dimension is encoded with extent 1 (the kernel keeps its coordinate at 0); its stride only has
+  // to be a valid multiple of 16 bytes
+  auto dim = [](int64_t n, int64_t bs) { return static_cast<uint64_t>(bs == 0 ? 1 : n); };
+  auto str = [](int64_t bs, int64_t fallback) { return static_cast<uint64_t>(bs > 0 ? bs : fallback); };
+  CUtensorMap ma, mb;
+  {
+    const int64_t pitch = M == 1 ? Kp : a.rs;
+    const uint64_t dims[4] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M), dim(n0, a.bs0), dim(n1, a.bs1)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(pitch), str(n0 == 1 ? 0 : a.bs0, pitch), str(n1 == 1 ? 0 : a.bs1, pitch)};
+    RTG_TRY(encode_4d(ctx, &ma, a.p, dims, strides, kBK, kBM, CU_TENSOR_MAP_SWIZZLE_128B));
+  }
+  if (b_major == 0) {
+    const int64_t pitch = N == 1 ? Kp : b.cs;
+    const uint64_t dims[4] = {static_cast<uint64_t>(K), static_cast<uint64_t>(N), dim(n0, b.bs0), dim(n1, b.bs1)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(pitch), str(n0 == 1 ? 0 : b.bs0, pitch), str(n1 == 1 ? 0 : b.bs1, pitch)};
+    RTG_TRY(encode_4d(ctx, &mb, b.p, dims, strides, kBK, bn, CU_TENSOR_MAP_SWIZZLE_128B));
+  } else {
+    const int64_t pitch = K == 1 ? Np : b.rs;
+    const uint64_t dims[4] = {static_cast<uint64_t>(N), static_cast<uint64_t>(K), dim(n0, b.bs0), dim(n1, b.bs1)};
+    const uint64_t strides[3] = {static_cast<uint64_t>(pitch), str(n0 == 1 ? 0 : b.bs0, pitch), str(n1 == 1 ? 0 : b.bs1, pitch)};
+    RTG_TRY(encode_4d(ctx, &mb, b.p, dims, strides, 32, kBK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B));
+  }
+  GemmArgs g = {};
+  g.M = static_cast<int>(M);
+  g.N = static_cast<int>(N);
+  g.K = static_cast<int>(K);
+  g.num_kb = static_cast<int>(div_ceil(K, kBK));
+  g.alpha = ep.alpha;
+  g.beta = ep.beta;
+  g.bias = ep.bias;
+  g.bias_mode = ep.bias ? ep.bias_mode : BIAS_NONE;
+  g.R = (ep.R && ep.beta != 0.f) ? ep.R : nullptr;
+  g.D = D;
+  g.dmap = OutMap{N, 0, 0, 0};
+  g.rmap = ep.rmap;
+  g.act = ep.act;
+  g.act_lo = ep.act_lo;
+  g.act_hi = ep.act_hi;
+  g.flags = debug_flags();
+  g.ic.bat_count = static_cast<int>(batch);
+  g.ic.bat_n0 = static_cast<int>(n0);
+  g.ic.bat_a0 = (n0 > 1 && a.bs0 != 0) ? 1 : 0;
+  g.ic.bat_a1 = (n1 > 1 && a.bs1 != 0) ? 1 : 0;
+  g.ic.bat_b0 = (n0 > 1 && b.bs0 != 0) ? 1 : 0;
+  g.ic.bat_b1 = (n1 > 1 && b.bs1 != 0) ? 1 : 0;
+  const double fb = static_cast<double>(batch);
+  ctx->pending_flops = 2.0 * fb * g.M * g.N * g.K;
+  ctx->pending_bytes = 4.0 * fb * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
+                                   static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
+  if (b_major == 0) return dispatch<3, 0>(ctx, bn, ctx->math, ma, mb, g, static_cast<int>(M), batch);
+  return dispatch<3, 1>(ctx, bn, ctx->math, ma, mb, g, static_cast<int>(M), batch);
 }
 
 // ---------------------------------------------------------------- implicit-GEMM convolution

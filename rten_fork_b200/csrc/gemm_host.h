@@ -24,6 +24,18 @@ struct Epilogue {
 // dimension contiguous, unaligned base or pitch) are first gathered into pool scratch by a copy kernel.
 rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap, const Epilogue& ep);
 
+// Batched product in ONE launch: batch index z = z1 * n0 + z0, entry z of A at a.p + z0*a.bs0 + z1*a.bs1 (a stride of
+// 0 broadcasts the operand along that batch dimension), D contiguous [n1*n0][M][N].  The operands must be addressable
+// by TMA in place (gemm_batched_supported); callers fall back to one gemm_device per entry otherwise.
+struct BatchedView {
+  const float* p;
+  int64_t rows, cols, rs, cs;  // one matrix
+  int64_t bs0, bs1;            // element strides of the two batch dimensions
+};
+bool gemm_batched_supported(const BatchedView& a, const BatchedView& b, int64_t n0, int64_t n1, int64_t N);
+rtg_status gemm_batched_device(Context* ctx, BatchedView a, BatchedView b, int64_t n0, int64_t n1, float* D,
+                               const Epilogue& ep);
+
 // Implicit-GEMM convolution over an NHWC activation tensor using TMA im2col loads.
 struct ConvGeom {
   int n, h, w, c_total;        // input tensor [n, h, w, c_total] NHWC dense

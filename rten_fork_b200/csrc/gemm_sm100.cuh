@@ -53,6 +53,10 @@ struct Im2colArgs {  // A operand produced by TMA im2col over NHWC input (A_KIND
   // A_KIND 2 (row window): an M tile is 128 consecutive pixels of one output row; k-block kb is kernel row kb
   int32_t win_tpr;   // tiles per output row = ceil(ow / 128)
   int32_t win_rows;  // n * oh output rows
+  // A_KIND 3 (batched GEMM): batch index z = z1 * bat_n0 + z0; 4-D maps {K, rows, z0, z1}; a broadcast operand keeps
+  // coordinate 0 in the batch dimensions it does not have
+  int32_t bat_count, bat_n0;
+  int32_t bat_a0, bat_a1, bat_b0, bat_b1;  // 1: the operand varies along that batch dimension, 0: broadcast
 };
 
 struct GemmArgs {
@@ -198,7 +202,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const int m_tiles = A_KIND == 2 ? args.ic.win_rows * args.ic.win_tpr : (args.M + kBM - 1) / kBM;
+  const int m_tiles_1 = (args.M + kBM - 1) / kBM;  // per batch entry (A_KIND 3: args.M is the per-entry row count)
+  const int m_tiles = A_KIND == 2 ? args.ic.win_rows * args.ic.win_tpr
+                                  : A_KIND == 3 ? args.ic.bat_count * m_tiles_1 : m_tiles_1;
   const int n_tiles = (args.N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int num_kb = args.num_kb;
@@ -249,9 +255,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int ic_dil_h = args.ic.dil_h, ic_dil_w = args.ic.dil_w, ic_c_off = args.ic.c_off;
       const int ic_c_blocks = args.ic.c_blocks, ic_kw = args.ic.kw;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / n_tiles) * kBM;
+        int m0 = (tile / n_tiles) * kBM;
         const int n0 = (tile % n_tiles) * BN;
         int pix_w = 0, pix_h = 0, pix_n = 0;
+        int z0 = 0, z1 = 0;
+        if (A_KIND == 3) {
+          const int z = (tile / n_tiles) / m_tiles_1;
+          m0 = ((tile / n_tiles) - z * m_tiles_1) * kBM;
+          z1 = z / args.ic.bat_n0;
+          z0 = z - z1 * args.ic.bat_n0;
+        }
         if (A_KIND == 2) {
           const int rowidx = (tile / n_tiles) / args.ic.win_tpr;
           pix_w = ((tile / n_tiles) % args.ic.win_tpr) * kBM;  // first output column of the tile
@@ -280,6 +293,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::mbar_expect_tx(fb, Cfg::kRawBytes);
           if (A_KIND == 0) {
             ptx::tma_load_2d(a_dst, &tmA, fb, kb * kBK, m0);
+          } else if (A_KIND == 3) {
+            ptx::tma_load_4d(a_dst, &tmA, fb, kb * kBK, m0, z0 * args.ic.bat_a0, z1 * args.ic.bat_a1);
           } else if (A_KIND == 2) {
             // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
             ptx::tma_load_4d(a_dst, &tmA, fb, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
@@ -294,7 +309,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             }
           }
-          if (B_MAJOR == 0) {
+          if (A_KIND == 3) {
+            const int bz0 = z0 * args.ic.bat_b0, bz1 = z1 * args.ic.bat_b1;
+            if (B_MAJOR == 0) {
+              ptx::tma_load_4d(b_dst, &tmB, fb, kb * kBK, n0, bz0, bz1);
+            } else {
+#pragma unroll
+              for (int c = 0; c < BN / 32; ++c) ptx::tma_load_4d(b_dst + c * 4096, &tmB, fb, n0 + c * 32, kb * kBK, bz0, bz1);
+            }
+          } else if (B_MAJOR == 0) {
             // B stored [N][K] (K contiguous): one box of BN rows x 128 bytes
             ptx::tma_load_2d(b_dst, &tmB, fb, kb * kBK, n0);
           } else {
@@ -409,6 +432,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         st_r = ((tile / n_tiles) % args.ic.win_tpr) * kBM + q * 32;
         m = st_z * args.ic.ow + st_r + lane;
         row_ok = st_r + lane < args.ic.ow;
+      } else if (A_KIND == 3) {
+        st_z = (tile / n_tiles) / m_tiles_1;
+        st_r = ((tile / n_tiles) - st_z * m_tiles_1) * kBM + q * 32;
+        m = st_z * args.M + st_r + lane;
+        row_ok = st_r + lane < args.M;
       } else {
         st_r = (tile / n_tiles) * kBM + q * 32;
         m = st_r + lane;

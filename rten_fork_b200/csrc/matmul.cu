@@ -73,8 +73,33 @@ rtg_status matmul_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& b
                        ep);
   }
 
-  // general case: one product per broadcast batch index (src/ops/matmul.rs:171-238)
+  // general case (src/ops/matmul.rs:171-238): one product per broadcast batch index.  Batch dimensions whose strides
+  // nest are merged; up to two remaining dimensions run as ONE batched launch (TMA walks the batch coordinates).
   const int pn = ond - 2;
+  {
+    int64_t size[RTG_MAX_DIMS], sa[RTG_MAX_DIMS], sb[RTG_MAX_DIMS];
+    int nd = 0;  // outermost first
+    for (int i = 0; i < pn; ++i) {
+      if (oshape[i] == 1) continue;
+      const int ia = i - (pn - (a.ndim - 2)), ib = i - (pn - (b.ndim - 2));
+      const int64_t ta = (ia >= 0 && a.shape[ia] != 1) ? a.strides[ia] : 0;
+      const int64_t tb = (ib >= 0 && b.shape[ib] != 1) ? b.strides[ib] : 0;
+      if (nd > 0 && sa[nd - 1] == oshape[i] * ta && sb[nd - 1] == oshape[i] * tb) {
+        size[nd - 1] *= oshape[i], sa[nd - 1] = ta, sb[nd - 1] = tb;  // merge with the dimension outside it
+      } else {
+        size[nd] = oshape[i], sa[nd] = ta, sb[nd] = tb, ++nd;
+      }
+    }
+    if (nd >= 1 && nd <= 2) {
+      const int64_t n0 = size[nd - 1], n1 = nd == 2 ? size[0] : 1;
+      BatchedView va{pa, M, K, a_rs, a_cs, sa[nd - 1], nd == 2 ? sa[0] : 0};
+      BatchedView vb{pb, K, N, b_rs, b_cs, sb[nd - 1], nd == 2 ? sb[0] : 0};
+      if (gemm_batched_supported(va, vb, n0, n1, N)) {
+        ep.rmap = OutMap{N, 0, 0, 0};
+        return gemm_batched_device(ctx, va, vb, n0, n1, D, ep);
+      }
+    }
+  }
   int64_t idx[RTG_MAX_DIMS] = {0};
   const int64_t batches = total / (M * N);
   for (int64_t it = 0; it < batches; ++it) {

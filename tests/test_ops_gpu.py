@@ -39,6 +39,38 @@ def test_matmul_transposed_view(rtg, ctx, oracle, math_mode):
     expect_equal(ops.matmul(q, kt), oracle.matmul(q, np.ascontiguousarray(kt)), rtol=math_mode["rtol"])
 
 
+@pytest.mark.parametrize("a_shape,b_shape,kmajor_b", [
+    ((4, 12, 128, 64), (4, 12, 64, 128), False),   # nested batch dims merge into one
+    ((4, 1, 130, 64), (1, 3, 64, 36), False),      # two batch dims, each operand broadcast along one of them
+    ((5, 200, 32), (5, 32, 20), False),            # partial M tile per entry
+    ((2, 3, 4, 16, 8), (2, 3, 4, 8, 12), False),   # three nested dims -> one
+    ((2, 3, 2, 16, 8), (2, 1, 2, 8, 12), False),   # not mergeable into two dims: per-entry launches
+    ((6, 1, 64), (6, 64, 32), False),              # single-row entries
+    ((3, 16, 8), (3, 8, 7), True),                 # N % 4 != 0: un-staged stores
+    ((7, 300, 100), (7, 100, 260), True),          # K tail, several N tiles, K-major B
+    ((2, 5, 64, 40), (5, 40, 48), False),          # B lacks the outer batch dim
+])
+def test_matmul_batched_single_launch(rtg, ctx, oracle, math_mode, a_shape, b_shape, kmajor_b):
+    """Batched products run as one launch when TMA can walk the batch (src/ops/matmul.rs:171-238 loops per entry)."""
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(77)
+    a = rng.fill(a_shape)
+    if kmajor_b:
+        bt = rng.fill(b_shape[:-2] + (b_shape[-1], b_shape[-2]))
+        b = np.swapaxes(bt, -1, -2)
+    else:
+        b = rng.fill(b_shape)
+    l0 = ctx.launch_count
+    got = ops.matmul(a, b)
+    launches = ctx.launch_count - l0
+    expect_equal(got, oracle.matmul(a, np.ascontiguousarray(b)), rtol=math_mode["rtol"])
+    if a_shape != (2, 3, 2, 16, 8):
+        assert launches == 1 and "batched" in ctx.last_kernel, (launches, ctx.last_kernel)
+    else:
+        assert launches == 12
+
+
 def test_matmul_errors_and_empty(rtg, ctx, oracle):  # src/ops/matmul.rs:484-561
     from rten_fork_b200 import ops
 
