@@ -89,49 +89,80 @@ def graph_flops(builder, batch):
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    """Samples the SM clock and the clock-event (throttle) reasons during the timed region: NVML polled every ~2 ms from
+    a thread (the timed region lasts tens of milliseconds, too short for `nvidia-smi -lms`), nvidia-smi as the
+    fallback (B200_PROFILING.md clocks line)."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index, uuid=None):
+        self.index, self.uuid = index, uuid
+        self.sm, self.reasons, self.max_mhz = [], set(), None
+        self.thread, self.stop_flag, self.source = None, threading.Event(), None
+
+    def _nvml_handle(self):
+        import pynvml
+
+        pynvml.nvmlInit()
+        if self.uuid:
+            try:
+                return pynvml, pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(self.uuid)).encode())
+            except Exception:
+                pass
+        return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
+
+    def _poll_nvml(self, nv, h):
+        names = {nv.nvmlClocksEventReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksEventReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksEventReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksEventReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                for bit, nm in names.items():
+                    if mask & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def _poll_smi(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+                r = [c.strip() for c in out.strip().split(",")]
+                self.sm.append(float(r[0]))
+                self.max_mhz = max(self.max_mhz or 0.0, float(r[1]))
+                for nm, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nm)
+            except Exception:
+                time.sleep(0.05)
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
+            nv, h = self._nvml_handle()
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.source = "nvml"
+            self.thread = threading.Thread(target=self._poll_nvml, args=(nv, h), daemon=True)
         except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.source = "nvidia-smi"
+            self.thread = threading.Thread(target=self._poll_smi, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-            except Exception:
-                continue
-            for nm, v in zip(names, r[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        if not self.thread:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["not sampled"]}
+        self.stop_flag.set()
+        self.thread.join(timeout=15)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "samples": 0, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_min_mhz": float(min(self.sm)), "sm_max_mhz": self.max_mhz,
+                "samples": len(self.sm), "source": self.source, "reasons": sorted(self.reasons)}
 
 
 # ------------------------------------------------------------------------------------------- CPU restatement arm
@@ -273,7 +304,7 @@ def run_ours(args):
 
     # warm-up (also fills the weight cache, tensor maps and the pool)
     timed_device_steps(torch, model, stream, x_dev, out_dev, flush, max(args.warmup, 3))
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, getattr(torch.cuda.get_device_properties(local), "uuid", None))
     if rank == 0:
         sampler.start()
     barrier()
@@ -317,10 +348,11 @@ def run_ours(args):
     peaks = load_peaks()
     images = args.batch * world * args.steps
     tf = lambda k: k["flops"] / (k["ms"] * 1e-3) / 1e12 if k["ms"] > 0 else 0.0
-    traffic = None
+    traffic = traffic_note = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(args.math)
+        tj = json.load(open(tpath))
+        traffic, traffic_note = tj.get(args.math), tj.get("note")
     line = {
         "metric": "resnet50_b32_images_per_sec", "value": images / (ms_total * 1e-3), "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
@@ -338,12 +370,16 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (all Conv / Gemm launches of a step)",
                      "achieved": tf(kt), "peak": peaks["tf32_sustained"], "unit": "TFLOP/s",
-                     "frac": tf(kt) / peaks["tf32_sustained"], "traffic": traffic,
+                     "frac": tf(kt) / peaks["tf32_sustained"], "traffic": traffic, "traffic_note": traffic_note,
                      "launches_per_step": kt["launches"] // 3, "kernel_ms_per_step": kt["ms"] / 3,
                      "kernel_share_of_step": (kt["ms"] / 3) / (ms_total / args.steps),
                      "algorithmic_gbytes_per_step": kt["bytes"] / 3 / 1e9,
                      "peak_source": peaks["source"] + ", sustained",
-                     "note": "achieved counts algorithmic flops once; 3xTF32 issues 3 MMAs per product"},
+                     "note": "achieved counts algorithmic flops once; 3xTF32 issues 3 MMAs per product.  Kernel times come "
+                             "from a separate pass with an event pair around every launch, which serialises launches "
+                             "that otherwise overlap their prologue with the previous kernel's tail (programmatic "
+                             "dependent launch) and adds event overhead, so their sum can exceed the plain step "
+                             "(share > 1); the ncu launch list in profiles/ gives the share under serialisation"},
         "other_mode": {"math": "tf32" if other == R.MATH_TF32 else "3xtf32",
                        "value": images / (other_ms * 1e-3), "ms_per_step": other_ms / args.steps,
                        "kernel_tflops": tf(kt_other), "kernel_frac": tf(kt_other) / peaks["tf32_sustained"]},

@@ -98,6 +98,102 @@ __global__ void binary_strided_kernel(float* __restrict__ out, const float* __re
   }
 }
 
+// Broadcast binary operator on a contiguous output seen as [rows][L]: `rows` enumerates up to four outer dimensions
+// (after merging nested ones), the inner dimension is dense in the output and either dense or broadcast (stride 0) in
+// each operand.  A thread owns one float4 column of the row and walks rows with an odometer, so there is no division
+// per element; grid.y splits long inner dimensions (a scalar operand collapses the whole tensor into one row).
+struct RowGeom {
+  uint32_t size[4];  // outer dimensions, outermost first, right-aligned (unused leading slots: huge size, stride 0)
+  int64_t sa[4], sb[4];
+  int64_t L, rows;
+  int32_t a_in, b_in;  // inner strides: 1 or 0
+};
+
+template <bool VEC>
+__global__ void binary_rows_kernel(float* __restrict__ out, const float* __restrict__ a, const float* __restrict__ b,
+                                   RowGeom g, int op, int64_t rows_per_block, int64_t seg) {
+  const int64_t r_begin = static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t r_end = min(g.rows, r_begin + rows_per_block);
+  const int64_t c_begin = static_cast<int64_t>(blockIdx.y) * seg, c_end = min(g.L, c_begin + seg);
+  int64_t r = r_begin + threadIdx.y;
+  if (r >= r_end) return;
+  uint32_t idx[4] = {0, 0, 0, 0};
+  {
+    int64_t t = r;
+#pragma unroll
+    for (int d = 3; d >= 0; --d) {
+      idx[d] = static_cast<uint32_t>(t % g.size[d]);
+      t /= g.size[d];
+    }
+  }
+  for (; r < r_end; r += blockDim.y) {
+    int64_t oa = 0, ob = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) oa += idx[d] * g.sa[d], ob += idx[d] * g.sb[d];
+    const float* pa = a + oa;
+    const float* pb = b + ob;
+    float* po = out + r * g.L;
+    if (VEC) {
+      for (int64_t c = c_begin + 4 * threadIdx.x; c < c_end; c += 4 * blockDim.x) {
+        float4 x, y;
+        if (g.a_in) x = *reinterpret_cast<const float4*>(pa + c);
+        else x.x = x.y = x.z = x.w = __ldg(pa);
+        if (g.b_in) y = *reinterpret_cast<const float4*>(pb + c);
+        else y.x = y.y = y.z = y.w = __ldg(pb);
+        *reinterpret_cast<float4*>(po + c) =
+            make_float4(bin_op(op, x.x, y.x), bin_op(op, x.y, y.y), bin_op(op, x.z, y.z), bin_op(op, x.w, y.w));
+      }
+    } else {
+      for (int64_t c = c_begin + threadIdx.x; c < c_end; c += blockDim.x)
+        po[c] = bin_op(op, pa[g.a_in ? c : 0], pb[g.b_in ? c : 0]);
+    }
+    // advance the odometer by blockDim.y rows
+    idx[3] += blockDim.y;
+#pragma unroll
+    for (int d = 3; d > 0; --d) {
+      while (idx[d] >= g.size[d]) idx[d] -= g.size[d], idx[d - 1]++;
+    }
+  }
+}
+
+// Permuting copy that keeps the innermost dimension: dense output [rows][L], source rows located by the odometer.
+template <bool VEC>
+__global__ void copy_rows_kernel(uint32_t* __restrict__ out, const uint32_t* __restrict__ in, RowGeom g,
+                                 int64_t rows_per_block, int64_t seg) {
+  const int64_t r_begin = static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t r_end = min(g.rows, r_begin + rows_per_block);
+  const int64_t c_begin = static_cast<int64_t>(blockIdx.y) * seg, c_end = min(g.L, c_begin + seg);
+  int64_t r = r_begin + threadIdx.y;
+  if (r >= r_end) return;
+  uint32_t idx[4];
+  {
+    int64_t t = r;
+#pragma unroll
+    for (int d = 3; d >= 0; --d) {
+      idx[d] = static_cast<uint32_t>(t % g.size[d]);
+      t /= g.size[d];
+    }
+  }
+  for (; r < r_end; r += blockDim.y) {
+    int64_t oa = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) oa += idx[d] * g.sa[d];
+    const uint32_t* pi = in + oa;
+    uint32_t* po = out + r * g.L;
+    if (VEC) {
+      for (int64_t c = c_begin + 4 * threadIdx.x; c < c_end; c += 4 * blockDim.x)
+        *reinterpret_cast<uint4*>(po + c) = *reinterpret_cast<const uint4*>(pi + c);
+    } else {
+      for (int64_t c = c_begin + threadIdx.x; c < c_end; c += blockDim.x) po[c] = pi[c];
+    }
+    idx[3] += blockDim.y;
+#pragma unroll
+    for (int d = 3; d > 0; --d) {
+      while (idx[d] >= g.size[d]) idx[d] -= g.size[d], idx[d - 1]++;
+    }
+  }
+}
+
 __global__ void copy_strided_nd_kernel(uint32_t* __restrict__ out, const uint32_t* __restrict__ in, int64_t n,
                                        Strides8 s) {
   const int64_t step = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -129,6 +225,31 @@ bool same_dense_order(const rtg_tensor& a, const rtg_tensor& b) {
   return span_of(a) == numel(a);  // a permutation of a dense block
 }
 
+// Block / grid shape shared by the row kernels: tx threads along the inner dimension, ty rows per pass.
+struct RowLaunch {
+  dim3 grid, block;
+  int64_t rpb, seg;
+  bool ok;
+};
+RowLaunch row_launch(Context* ctx, const RowGeom& g, bool vec) {
+  RowLaunch l = {};
+  const int64_t per_thread = vec ? 4 : 1;
+  int tx = 8;
+  while (tx < 256 && tx * per_thread < g.L) tx *= 2;
+  const int ty = 256 / tx;
+  const int64_t span = static_cast<int64_t>(tx) * per_thread;
+  l.seg = std::min<int64_t>(g.L, span * 4);
+  if (div_ceil(g.L, l.seg) > 65535) l.seg = div_ceil(div_ceil(g.L, 65535), span) * span;
+  const int64_t gy = div_ceil(g.L, l.seg);
+  const int64_t want_x = std::max<int64_t>(1, static_cast<int64_t>(ctx->num_sms) * 16 / gy);
+  l.rpb = std::max<int64_t>(ty, div_ceil(div_ceil(g.rows, want_x), ty) * ty);
+  const int64_t gx = div_ceil(g.rows, l.rpb);
+  l.ok = gy <= 65535 && gx <= 0x7fffffff;
+  l.grid = dim3(static_cast<unsigned>(gx), static_cast<unsigned>(gy));
+  l.block = dim3(tx, ty);
+  return l;
+}
+
 }  // namespace
 
 rtg_status copy_view(Context* ctx, const rtg_tensor& dst, const rtg_tensor& src) {
@@ -142,6 +263,38 @@ rtg_status copy_view(Context* ctx, const rtg_tensor& dst, const rtg_tensor& src)
   if (dst.ndim == 2 && is_contiguous(dst))
     return copy_strided_2d(ctx, static_cast<float*>(dst.data), dst.shape[1], static_cast<const float*>(src.data),
                            dst.shape[0], dst.shape[1], src.strides[0], src.strides[1]);
+  // permutations that keep the innermost dimension: rows x inner, vectorised
+  if (is_contiguous(dst)) {
+    int64_t shp[RTG_MAX_DIMS], sa[RTG_MAX_DIMS];
+    int nd = 0;
+    for (int i = 0; i < dst.ndim; ++i) {
+      if (dst.shape[i] == 1) continue;
+      if (nd > 0 && sa[nd - 1] == dst.shape[i] * src.strides[i]) shp[nd - 1] *= dst.shape[i], sa[nd - 1] = src.strides[i];
+      else shp[nd] = dst.shape[i], sa[nd] = src.strides[i], ++nd;
+    }
+    bool ok = nd >= 2 && nd <= 5 && sa[nd - 1] == 1 && shp[nd - 1] >= 4;
+    for (int i = 0; ok && i + 1 < nd; ++i) ok = shp[i] <= 0x7fffffff && sa[i] >= 0;
+    if (ok) {
+      RowGeom g = {};
+      g.rows = 1;
+      const int lead = 4 - (nd - 1);
+      for (int i = 0; i < lead; ++i) g.size[i] = 0x7fffffffu;
+      for (int i = 0; i + 1 < nd; ++i) g.size[lead + i] = static_cast<uint32_t>(shp[i]), g.sa[lead + i] = sa[i], g.rows *= shp[i];
+      g.L = shp[nd - 1];
+      bool vec = g.L % 4 == 0 && aligned16(dst.data) && aligned16(src.data);
+      for (int i = 0; vec && i + 1 < nd; ++i) vec = sa[i] % 4 == 0;
+      const RowLaunch l = row_launch(ctx, g, vec);
+      if (l.ok) {
+        uint32_t* po = static_cast<uint32_t*>(dst.data);
+        const uint32_t* pi = static_cast<const uint32_t*>(src.data);
+        if (vec) copy_rows_kernel<true><<<l.grid, l.block, 0, ctx->stream>>>(po, pi, g, l.rpb, l.seg);
+        else copy_rows_kernel<false><<<l.grid, l.block, 0, ctx->stream>>>(po, pi, g, l.rpb, l.seg);
+        ctx->launches++;
+        RTG_CUDA(cudaGetLastError());
+        return RTG_OK;
+      }
+    }
+  }
   Strides8 s = {};
   s.ndim = dst.ndim;
   for (int i = 0; i < dst.ndim; ++i) s.shape[i] = dst.shape[i], s.sa[i] = src.strides[i], s.so[i] = dst.strides[i];
@@ -207,6 +360,44 @@ rtg_status binary_forward(Context* ctx, int op, const rtg_tensor& a, const rtg_t
     ctx->launches++;
     RTG_CUDA(cudaGetLastError());
     return RTG_OK;
+  }
+  // broadcast onto a dense output: merge nested dimensions, then rows x inner with an odometer (no per-element division)
+  if (is_contiguous(out)) {
+    int64_t shp[RTG_MAX_DIMS], sa[RTG_MAX_DIMS], sb[RTG_MAX_DIMS];
+    int nd = 0;
+    for (int i = 0; i < out.ndim; ++i) {
+      if (out.shape[i] == 1) continue;
+      const int ia = i - (out.ndim - a.ndim), ib = i - (out.ndim - b.ndim);
+      const int64_t ta = (ia >= 0 && a.shape[ia] != 1) ? a.strides[ia] : 0;
+      const int64_t tb = (ib >= 0 && b.shape[ib] != 1) ? b.strides[ib] : 0;
+      if (nd > 0 && sa[nd - 1] == out.shape[i] * ta && sb[nd - 1] == out.shape[i] * tb) {
+        shp[nd - 1] *= out.shape[i], sa[nd - 1] = ta, sb[nd - 1] = tb;
+      } else {
+        shp[nd] = out.shape[i], sa[nd] = ta, sb[nd] = tb, ++nd;
+      }
+    }
+    bool ok = nd >= 1 && nd <= 5 && (sa[nd - 1] == 0 || sa[nd - 1] == 1) && (sb[nd - 1] == 0 || sb[nd - 1] == 1);
+    for (int i = 0; ok && i + 1 < nd; ++i) ok = shp[i] <= 0x7fffffff;
+    if (ok) {
+      RowGeom g = {};
+      g.rows = 1;
+      const int lead = 4 - (nd - 1);
+      for (int i = 0; i < lead; ++i) g.size[i] = 0x7fffffffu;
+      for (int i = 0; i + 1 < nd; ++i)
+        g.size[lead + i] = static_cast<uint32_t>(shp[i]), g.sa[lead + i] = sa[i], g.sb[lead + i] = sb[i], g.rows *= shp[i];
+      g.L = shp[nd - 1];
+      g.a_in = static_cast<int32_t>(sa[nd - 1]), g.b_in = static_cast<int32_t>(sb[nd - 1]);
+      bool vec = g.L % 4 == 0 && aligned16(po) && (!g.a_in || aligned16(pa)) && (!g.b_in || aligned16(pb));
+      for (int i = 0; vec && i + 1 < nd; ++i) vec = (!g.a_in || sa[i] % 4 == 0) && (!g.b_in || sb[i] % 4 == 0);
+      const RowLaunch l = row_launch(ctx, g, vec);
+      if (l.ok) {
+        if (vec) binary_rows_kernel<true><<<l.grid, l.block, 0, ctx->stream>>>(po, pa, pb, g, op, l.rpb, l.seg);
+        else binary_rows_kernel<false><<<l.grid, l.block, 0, ctx->stream>>>(po, pa, pb, g, op, l.rpb, l.seg);
+        ctx->launches++;
+        RTG_CUDA(cudaGetLastError());
+        return RTG_OK;
+      }
+    }
   }
   // general broadcast: per-element index arithmetic with zero strides on broadcast dims
   Strides8 s = {};

@@ -339,7 +339,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   g.act = ep.act;
   g.act_lo = ep.act_lo;
   g.act_hi = ep.act_hi;
-  g.flags = debug_flags();
+  g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0);
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
@@ -425,7 +425,7 @@ rtg_status gemm_batched_device(Context* ctx, BatchedView a, BatchedView b, int64
   g.act = ep.act;
   g.act_lo = ep.act_lo;
   g.act_hi = ep.act_hi;
-  g.flags = debug_flags();
+  g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0);
   g.ic.bat_count = static_cast<int>(batch);
   g.ic.bat_n0 = static_cast<int>(n0);
   g.ic.bat_a0 = (n0 > 1 && a.bs0 != 0) ? 1 : 0;

@@ -12,6 +12,7 @@ struct MatView {      // [rows, cols] f32 matrix view on the device, element str
 
 struct Epilogue {
   float alpha = 1.f, beta = 0.f;
+  bool alpha_div = false;     // D = acc / alpha instead of acc * alpha (fused MatMul -> Div by a scalar)
   const float* bias = nullptr;
   int bias_mode = BIAS_NONE;
   const float* R = nullptr;   // residual / beta source

@@ -115,6 +115,7 @@ struct GemmArgs {
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
 constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
 constexpr int kFlagStagedR = 4;  // residual arrives by TMA load into the same staging buffer (needs kFlagStagedD)
+constexpr int kFlagAlphaDiv = 16;  // alpha is a divisor: D = acc / alpha (8 is the debug "no staging" switch)
 
 constexpr int kBM = 128;
 constexpr int kBK = 32;  // floats per k-block (128 bytes)
@@ -473,7 +474,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // instructions per chunk.
       auto finish = [&](float (&v)[32], int c0) {
         const int ncols = min(32, args.N - (n0 + c0));
-        if (args.alpha != 1.f) {
+        if (args.flags & kFlagAlphaDiv) {  // fused `MatMul -> Div(scalar)`: IEEE division, as the unfused operator
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], args.alpha);
+        } else if (args.alpha != 1.f) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] *= args.alpha;
         }

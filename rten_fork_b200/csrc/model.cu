@@ -261,6 +261,40 @@ int optimize_graph(Graph* g) {
     }
   }
   if (fused) rebuild();
+
+  // ---- Transpose -> MatMul  =>  FusedTranspose(MatMul): the permuted view feeds the TMA maps directly
+  //      (GraphOptimizer::fuse_transpose, src/optimize.rs:333-377)
+  {
+    int tf = 0;
+    for (int32_t i = 0; i < n; ++i) {
+      Node& nd = g->nodes[i];
+      if (nd.kind != NodeKind::Operator || dead[i]) continue;
+      MatMulOp* mm = dynamic_cast<MatMulOp*>(nd.op.get());
+      if (!mm || nd.inputs.size() < 2) continue;
+      for (int side = 0; side < 2; ++side) {
+        const int32_t v = nd.inputs[side];
+        if (v < 0 || producer[v] < 0 || dead[producer[v]] || mm->has_perm[side]) continue;
+        Node& tn = g->nodes[producer[v]];
+        TransposeOp* tp = dynamic_cast<TransposeOp*>(tn.op.get());
+        if (!tp || tn.inputs.size() != 1 || tn.inputs[0] < 0) continue;
+        nd.inputs[side] = tn.inputs[0];
+        mm->has_perm[side] = true;
+        mm->perm_reverse[side] = !tp->has_perm;
+        mm->perm[side] = tp->perm;
+        if (--uses[v] == 0) dead[producer[v]] = 1;
+        ++tf;
+      }
+    }
+    if (tf) rebuild();
+    fused += tf;
+  }
+  auto scalar_value = [&](int32_t id, float* v) {
+    if (id < 0) return false;
+    const Node& c = g->nodes[id];
+    if (c.kind != NodeKind::Constant || !c.constant.host_f32 || c.constant.host_f32->size() != 1) return false;
+    *v = (*c.constant.host_f32)[0];
+    return true;
+  };
   auto single_consumer = [&](int32_t value) -> int32_t {
     if (value < 0 || uses[value] != 1 || consumers[value].size() != 1) return -1;
     return consumers[value][0];
@@ -291,8 +325,30 @@ int optimize_graph(Graph* g) {
     if (!conv && !mm) continue;
     if (conv && (conv->has_residual || conv->act != ACT_NONE)) continue;
     int32_t cur_out = nd.outputs[0];
-    // --- optional Add
     int32_t next = single_consumer(cur_out);
+    // --- MatMul -> Mul / Div by a scalar constant: the epilogue's alpha (the unfused operators would cost a read and
+    //     a write of the whole score tensor)
+    if (mm && next >= 0 && !dead[next] && mm->scale == 1.f) {
+      Node& sn = g->nodes[next];
+      BinaryOp* b = dynamic_cast<BinaryOp*>(sn.op.get());
+      float c = 1.f;
+      bool ok = false, div = false;
+      if (b && sn.inputs.size() == 2 && sn.outputs.size() == 1) {
+        if (b->op == RTG_BIN_DIV && sn.inputs[0] == cur_out && scalar_value(sn.inputs[1], &c)) ok = div = true;
+        else if (b->op == RTG_BIN_MUL && sn.inputs[0] == cur_out && scalar_value(sn.inputs[1], &c)) ok = true;
+        else if (b->op == RTG_BIN_MUL && sn.inputs[1] == cur_out && scalar_value(sn.inputs[0], &c)) ok = true;
+      }
+      if (ok && c != 1.f) {
+        mm->scale = c;
+        mm->scale_div = div;
+        dead[next] = 1;
+        nd.outputs[0] = sn.outputs[0];
+        cur_out = sn.outputs[0];
+        ++fused;
+      }
+    }
+    // --- optional Add
+    next = single_consumer(cur_out);
     if (next >= 0 && !dead[next]) {
       Node& add = g->nodes[next];
       BinaryOp* b = dynamic_cast<BinaryOp*>(add.op.get());

@@ -370,9 +370,25 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
   const Value *a, *b;
   RTG_TRY(in.require(0, &a));
   RTG_TRY(in.require(1, &b));
+  rtg_tensor ta = a->t, tb = b->t;
+  for (int side = 0; side < 2; ++side) {
+    if (!has_perm[side]) continue;
+    rtg_tensor& t = side == 0 ? ta : tb;
+    const rtg_tensor src = t;
+    const int r = src.ndim;
+    if (!perm_reverse[side] && static_cast<int>(perm[side].size()) != r)
+      return set_error(RTG_ERR_INVALID_VALUE, "Permutation is invalid");
+    unsigned seen = 0;
+    for (int i = 0; i < r; ++i) {
+      const int64_t ax = perm_reverse[side] ? r - 1 - i : perm[side][i];
+      if (ax < 0 || ax >= r || (seen >> ax) & 1u) return set_error(RTG_ERR_INVALID_VALUE, "Permutation is invalid");
+      seen |= 1u << ax;
+      t.shape[i] = src.shape[ax], t.strides[i] = src.strides[ax];
+    }
+  }
   int64_t shape[RTG_MAX_DIMS];
   int32_t nd;
-  RTG_TRY(matmul_out_shape(&a->t, &b->t, shape, &nd));
+  RTG_TRY(matmul_out_shape(&ta, &tb, shape, &nd));
   Value y;
   RTG_TRY(alloc_value(ctx, RTG_F32, nd, shape, false, &y));
   Epilogue ep;
@@ -387,11 +403,13 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     ep.bias = static_cast<const float*>(bias->t.data);
     ep.bias_mode = BIAS_COL;
   }
-  if (has_bias || act != ACT_NONE) {
+  if (has_bias || act != ACT_NONE || scale != 1.f) {
     ep.act = act;
+    ep.alpha = scale;
+    ep.alpha_div = scale_div;
     epp = &ep;
   }
-  rtg_status st = matmul_forward(ctx, a->t, b->t, y.t, epp);
+  rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;

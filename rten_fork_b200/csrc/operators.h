@@ -98,7 +98,16 @@ class MatMulOp : public Operator {
  public:
   bool has_bias = false;  // fused `+ bias[N]` (input 2) and activation, set by optimize_graph
   int act = ACT_NONE;
-  const char* name() const override { return has_bias || act != ACT_NONE ? "FusedMatMul" : "MatMul"; }
+  // fused `MatMul -> Mul(scalar)` / `MatMul -> Div(scalar)` (attention score scaling)
+  float scale = 1.f;
+  bool scale_div = false;
+  // FusedTranspose(MatMul) (src/ops/fused.rs:46-78, GraphOptimizer::fuse_transpose src/optimize.rs:333-377): the
+  // operand is consumed through a permuted view instead of a materialised Transpose
+  bool has_perm[2] = {false, false};
+  bool perm_reverse[2] = {false, false};  // Transpose without `perm`: reverse the dims
+  std::vector<int64_t> perm[2];
+  bool fused() const { return has_bias || act != ACT_NONE || scale != 1.f || has_perm[0] || has_perm[1]; }
+  const char* name() const override { return fused() ? "FusedMatMul" : "MatMul"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
 };
 

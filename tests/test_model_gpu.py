@@ -157,3 +157,35 @@ def test_timing_report(rtg, ctx, oracle):
     m.run([oracle.XorShiftRng(1).fill((1, 3, 32, 32))])
     rep = m.timing_report()
     assert "Conv" in rep and "Graph run of" in rep
+
+
+@pytest.mark.parametrize("optimize", [False, True])
+@pytest.mark.parametrize("divisor", [8.0, 3.0])
+def test_fused_transpose_matmul_and_scale(rtg, ctx, oracle, math_mode, optimize, divisor):
+    """Transpose -> MatMul runs on permuted views (GraphOptimizer::fuse_transpose, src/optimize.rs:333-377) and
+    MatMul -> Div / Mul by a scalar folds into the epilogue; both must give what the unfused operators give."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = oracle.XorShiftRng(99)
+    b = ModelBuilder()
+    q = b.add_value("q", [2, 20, 3, 8])   # [batch, seq, heads, d]
+    k = b.add_value("k", [2, 20, 3, 8])
+    b.inputs = [q, k]
+    perm = lambda p: ("TransposeAttrs", [(0, "vec_u32", list(p))])
+    qt = b.op("Transpose", [q], perm((0, 2, 1, 3)))
+    kt = b.op("Transpose", [k], perm((0, 2, 3, 1)))
+    s = b.op("MatMul", [qt, kt])
+    s = b.op("Div", [s, b.add_constant("c", np.array(divisor, np.float32))])
+    s = b.op("Mul", [b.add_constant("h", np.array(0.3, np.float32)), s])
+    vt = b.op("Transpose", [k], perm((0, 2, 1, 3)))
+    c = b.op("MatMul", [s, vt])
+    c = b.op("Transpose", [c], perm((0, 2, 1, 3)))   # materialised: keeps the innermost dimension
+    r = b.op("Transpose", [c], ("TransposeAttrs", []))  # no perm: full reversal, materialised
+    b.outputs = [c, r]
+    m, got, want = _run_both(ctx, b, [rng.fill((2, 20, 3, 8)), rng.fill((2, 20, 3, 8))], optimize)
+    assert got[0].shape == (2, 20, 3, 8) and got[1].shape == (8, 3, 20, 2)
+    for g, w in zip(got, want):
+        expect_equal(g, w, rtol=math_mode["rtol"] * 2, atol=1e-6)
+    assert got[1].tobytes() == np.ascontiguousarray(got[0].transpose()).tobytes()
+    if optimize:
+        assert m.num_ops == 5  # 2 MatMuls (+3 fused transposes, Div), the second Mul, 2 Transposes

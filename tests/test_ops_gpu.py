@@ -163,6 +163,12 @@ def test_vecmath_error_bounds(rtg, ctx):
 @pytest.mark.parametrize("a_shape,b_shape", [
     ((2, 8, 5, 5), (2, 8, 5, 5)), ((2, 8, 5, 5), (8, 1, 1)), ((2, 8, 5, 5), (1,)), ((5,), (3, 1)),
     ((4, 1, 6), (1, 7, 1)), ((128, 768), (768,)),
+    ((4, 3, 16, 16), (4, 1, 1, 16)),       # attention mask onto scores
+    ((4, 3, 16, 16), ()), ((), (3, 40)),   # scalar operand on either side
+    ((6, 20), (6, 1)), ((6, 1), (6, 20)),  # inner-broadcast operand
+    ((2, 3, 4, 5, 8), (3, 1, 5, 1)),       # four outer dims after merging
+    ((3, 5, 7), (5, 1)), ((70000,), (1,)),
+    ((2, 3, 2, 3, 2, 3, 4), (3, 1, 3, 1, 3, 1)),  # too many outer dims for the row kernel
 ])
 def test_binary_bit_exact(rtg, ctx, oracle, kind, a_shape, b_shape):
     from rten_fork_b200 import ops
