@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librten_gpu.so")
+# RTG_PROF_LIB=1 selects the developer build with per-role cycle counters (`make PROF=1`); never the default.
+LIB_PATH = os.path.join(_HERE, "librten_gpu_prof.so" if os.environ.get("RTG_PROF_LIB") == "1" else "librten_gpu.so")
 
 RTG_HOST = -1
 RTG_F32, RTG_I32 = 0, 1

@@ -1,6 +1,6 @@
 // Host side of the tcgen05 contraction engine: operand legalisation, TMA descriptor encoding, tile-shape choice,
 // launch.  Reference role: GemmExecutor::{gemm_bias, prepack_*} front-end (src/gemm.rs:448-542).
-#include "gemm_host.h"
+#include "gemm_launch.cuh"
 #include <vector>
 
 #include <stdio.h>
@@ -112,109 +112,78 @@ static int debug_flags() {
   return f;
 }
 
-// ---------------------------------------------------------------- launch
-template <int BN, int MODE, int A_KIND, int B_MAJOR>
-static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
-                         const CUtensorMap& mr, const GemmArgs& args) {
-  using Cfg = GemmCfg<BN, MODE>;
-  auto kern = gemm_tcgen05_kernel<BN, MODE, A_KIND, B_MAJOR>;
-  static bool configured[16] = {};  // per device
-  if (!configured[ctx->device & 15]) {
-    RTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    configured[ctx->device & 15] = true;
-  }
-  const int m_tiles_1 = (args.M + kBM - 1) / kBM, n_tiles = (args.N + BN - 1) / BN;
-  const int64_t m_tiles = A_KIND == 2 ? static_cast<int64_t>(args.ic.win_rows) * args.ic.win_tpr
-                                      : A_KIND == 3 ? static_cast<int64_t>(args.ic.bat_count) * m_tiles_1 : m_tiles_1;
-  if (m_tiles * n_tiles > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "too many output tiles");
-  const int grid = static_cast<int>(std::min<int64_t>(m_tiles * n_tiles, ctx->num_sms));
-#ifdef RTG_PROF
-  static unsigned long long* prof_buf = nullptr;
-  GemmArgs pargs = args;
-  if (getenv("RTG_PROF_PRINT")) {
-    if (!prof_buf) RTG_CUDA(cudaMalloc(&prof_buf, 148 * 32 * 8));
-    RTG_CUDA(cudaMemsetAsync(prof_buf, 0, 148 * 32 * 8, ctx->stream));
-    pargs.prof = prof_buf;
-  }
-#define args pargs
-#endif
-  Context::KernelRec rec{};
-  if (ctx->ktiming) {
-    RTG_CUDA(cudaEventCreate(&rec.a));
-    RTG_CUDA(cudaEventCreate(&rec.b));
-    rec.flops = ctx->pending_flops, rec.bytes = ctx->pending_bytes;
-    RTG_CUDA(cudaEventRecord(rec.a, ctx->stream));
-  }
-  {
-    // Programmatic stream serialisation: the kernel's prologue (barrier init, TMEM allocation, tensor-map prefetch)
-    // overlaps the tail of the previous kernel; it synchronises itself with griddepcontrol.wait.
-    static const bool pdl = []() {
-      const char* e = getenv("RTG_PDL");
-      return !e || atoi(e) != 0;
-    }();
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(Cfg::kThreads);
-    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
-    cfg.stream = ctx->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    RTG_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, md, mr, args));
-  }
-  ctx->launches++;
-  RTG_CUDA(cudaGetLastError());
-  if (ctx->ktiming) {
-    RTG_CUDA(cudaEventRecord(rec.b, ctx->stream));
-    ctx->krecs.push_back(rec);
-  }
-#ifdef RTG_PROF
-#undef args
-  if (pargs.prof) {
-    std::vector<unsigned long long> h(148 * 32);
-    RTG_CUDA(cudaStreamSynchronize(ctx->stream));
-    RTG_CUDA(cudaMemcpy(h.data(), prof_buf, h.size() * 8, cudaMemcpyDeviceToHost));
-    static const char* roles[4] = {"tma", "mma", "epi", "split"};
-    static const char* slots[4][4] = {{"wait_empty", "issue", "-", "-"},
-                                      {"wait_tempty", "wait_full", "issue", "-"},
-                                      {"wait_tfull", "wait_resid", "wait_stread", "wait_stdone"},
-                                      {"wait_full", "-", "-", "-"}};
-    fprintf(stderr, "[prof] BN=%d mode=%d akind=%d grid=%d M=%d N=%d kb=%d:", BN, MODE, A_KIND, grid, args.M, args.N,
-            args.num_kb);
-    for (int r = 0; r < 4; ++r) {
-      double acc[5] = {0, 0, 0, 0, 0};
-      for (int b = 0; b < grid; ++b)
-        for (int i = 0; i < 5; ++i) acc[i] += static_cast<double>(h[(b * 4 + r) * 8 + i]) / grid;
-      if (acc[4] == 0) continue;
-      fprintf(stderr, " | %s total %.0f", roles[r], acc[4]);
-      for (int i = 0; i < 4; ++i)
-        if (slots[r][i][0] != '-') fprintf(stderr, " %s %.0f", slots[r][i], acc[i]);
-      double m5 = 0, m6 = 0, m7 = 0;
-      for (int b = 0; b < grid; ++b) {
-        m5 += static_cast<double>(h[(b * 4 + r) * 8 + 5]) / grid;
-        m6 += static_cast<double>(h[(b * 4 + r) * 8 + 6]) / grid;
-        m7 += static_cast<double>(h[(b * 4 + r) * 8 + 7]) / grid;
+// ---------------------------------------------------------------- split-K reduction
+// Adds the partial-sum planes of a split-K launch in split order (fixed, so repeated runs are bit-identical) and
+// applies the epilogue in the order of the kernel's own `finish`: alpha, bias, residual, activation.
+
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const ReduceArgs a) {
+  ptx::grid_dependency_wait();  // the partial sums come from the kernel launched just before
+  const int nv = (a.N + 3) >> 2;
+  const int64_t total = static_cast<int64_t>(a.M) * nv;
+  const int64_t step = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int m = static_cast<int>(i / nv);
+    const int c = static_cast<int>(i - static_cast<int64_t>(m) * nv) << 2;
+    const float* w = a.ws + static_cast<int64_t>(m) * a.ws_ld + c;
+    const float4 x0 = *reinterpret_cast<const float4*>(w);
+    float v[4] = {x0.x, x0.y, x0.z, x0.w};
+    for (int s = 1; s < a.splits; ++s) {
+      const float4 x = *reinterpret_cast<const float4*>(w + s * a.plane);
+      v[0] = __fadd_rn(v[0], x.x), v[1] = __fadd_rn(v[1], x.y), v[2] = __fadd_rn(v[2], x.z), v[3] = __fadd_rn(v[3], x.w);
+    }
+    if (a.alpha_div) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = __fdiv_rn(v[j], a.alpha);
+    } else if (a.alpha != 1.f) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] *= a.alpha;
+    }
+    const int ncols = min(4, a.N - c);
+    if (a.bias_mode == BIAS_ROW) {
+      const float b = __ldg(a.bias + m);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] += b;
+    } else if (a.bias_mode == BIAS_COL) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < ncols) v[j] += __ldg(a.bias + c + j);
+    }
+    if (a.R != nullptr) {
+      const float* r = a.R + static_cast<int64_t>(m) * a.r_ld + c;
+      if (a.vec_r) {
+        const float4 r4 = *reinterpret_cast<const float4*>(r);
+        v[0] += a.beta * r4.x, v[1] += a.beta * r4.y, v[2] += a.beta * r4.z, v[3] += a.beta * r4.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < ncols) v[j] += a.beta * r[j];
       }
-      if (r == 0) fprintf(stderr, " first_tma@%.0f", m5);
-      if (r == 1) fprintf(stderr, " first_mma@%.0f last_commit@%.0f", m5, m6);
-      if (r == 2) fprintf(stderr, " setup_done@%.0f epi_drained@%.0f cta_end@%.0f", m7, m5, m6);
     }
-    unsigned long long t0 = ~0ull, t0max = 0, t1 = 0, t1min = ~0ull;
-    for (int b = 0; b < grid; ++b) {
-      const unsigned long long a = h[(b * 4 + 3) * 8 + 5], e = h[(b * 4 + 3) * 8 + 6];
-      t0 = std::min(t0, a), t0max = std::max(t0max, a), t1 = std::max(t1, e), t1min = std::min(t1min, e);
+    apply_act_array(v, a.act, a.act_lo, a.act_hi);
+    float* d = a.D + static_cast<int64_t>(m) * a.d_ld + c;
+    if (a.vec_d) {
+      *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < ncols) d[j] = v[j];
     }
-    fprintf(stderr, " | wall: first CTA start -> last CTA end %.1f us, start skew %.1f us, end skew %.1f us",
-            (t1 - t0) * 1e-3, (t0max - t0) * 1e-3, (t1 - t1min) * 1e-3);
-    fprintf(stderr, "\n");
   }
-#endif
-  char name[96];
-  snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s>", BN, MODE ? "3xTF32" : "TF32",
-           A_KIND == 3 ? "batched" : A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K");
-  ctx->last_kernel = name;
+}
+
+rtg_status launch_reduce(Context* ctx, const ReduceArgs& ra) {
+  const int64_t total = static_cast<int64_t>(ra.M) * ((ra.N + 3) / 4);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(std::min<int64_t>(div_ceil(total, 256), ctx->num_sms * 8)));
+  cfg.blockDim = dim3(256);
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  RTG_CUDA(cudaLaunchKernelEx(&cfg, splitk_reduce_kernel, ra));
+  ctx->launches++;
   return RTG_OK;
 }
 
@@ -223,12 +192,52 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
                            GemmArgs args, int plane_rows = 0, int64_t num_planes = 0) {
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;
+  Scratch ws;
+  ReduceArgs red = {};
+  const ReduceArgs* redp = nullptr;
   auto stageable = [&](const float* p, const OutMap& om) {
     if (!p || om.hw > 0) return false;
     if ((reinterpret_cast<uintptr_t>(p + om.chan_off) & 15) != 0) return false;
     return (args.M == 1 && num_planes <= 1) || (om.ld > 0 && om.ld % 4 == 0);
   };
-  if (!(args.flags & 8) && stageable(args.D, args.dmap)) {
+  // Split-K: the kernel leaves raw partial sums in a {N, M, splits} workspace through the staged (TMA store) path and
+  // splitk_reduce_kernel applies the epilogue.  Row-major D / R only; plain and im2col A operands.
+  if (args.splits > 1 && ((A_KIND != 0 && A_KIND != 1) || args.dmap.hw > 0 || (args.R && args.rmap.hw > 0) ||
+                          (args.flags & 8) || args.num_kb < 2))
+    args.splits = 1;
+  if (args.splits > 1) {
+    int kbs = static_cast<int>(div_ceil(args.num_kb, args.splits));
+    if (mode != RTG_MATH_TF32) kbs = static_cast<int>(div_ceil(kbs, kChunkKb)) * kChunkKb;  // whole accumulation chunks
+    args.kb_per_split = kbs;
+    args.splits = static_cast<int>(div_ceil(args.num_kb, kbs));  // every split owns at least one k-block
+  }
+  if (args.splits > 1) {
+    const int64_t ws_ld = div_ceil(args.N, 4) * 4, plane = ws_ld * args.M;
+    RTG_TRY(ws.alloc(ctx, static_cast<size_t>(plane) * args.splits * sizeof(float)));
+    red.ws = ws.f32(), red.plane = plane, red.ws_ld = ws_ld;
+    red.splits = args.splits, red.M = args.M, red.N = args.N;
+    red.alpha = args.alpha, red.beta = args.beta;
+    red.alpha_div = (args.flags & kFlagAlphaDiv) ? 1 : 0;
+    red.bias_mode = args.bias_mode, red.bias = args.bias;
+    red.R = args.R, red.r_ld = args.rmap.ld;
+    if (args.R) red.R += args.rmap.chan_off;
+    red.D = args.D + args.dmap.chan_off, red.d_ld = args.dmap.ld;
+    red.act = args.act, red.act_lo = args.act_lo, red.act_hi = args.act_hi;
+    auto vec_ok = [&](const float* p, int64_t ld) {
+      return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && ld % 4 == 0 && args.N % 4 == 0;
+    };
+    red.vec_d = vec_ok(red.D, red.d_ld);
+    red.vec_r = red.R ? vec_ok(red.R, red.r_ld) : 0;
+    redp = &red;
+    // the kernel itself only accumulates
+    args.alpha = 1.f, args.beta = 0.f, args.bias = nullptr, args.bias_mode = BIAS_NONE, args.R = nullptr;
+    args.act = ACT_NONE;
+    args.flags &= ~kFlagAlphaDiv;
+    args.D = ws.f32();
+    args.dmap = OutMap{ws_ld, 0, 0, 0};
+    RTG_TRY(encode_out_3d(ctx, &md, ws.f32(), args.N, args.M, args.splits, ws_ld));
+    args.flags |= kFlagStagedD;
+  } else if (!(args.flags & 8) && stageable(args.D, args.dmap)) {
     // plane_rows > 0 (row-window convolution): rows are output columns of one image row, planes the image rows
     const uint64_t rows = plane_rows > 0 ? plane_rows : args.M;
     const uint64_t planes = num_planes > 0 ? num_planes : plane_rows > 0 ? args.M / plane_rows : 1;
@@ -241,19 +250,13 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
       args.flags |= kFlagStagedR;
     }
   }
-  if (mode == RTG_MATH_TF32) {
-    if (bn == 64) return launch<64, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
-    if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
-    if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
-  } else {
-    if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
-    if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args);
-  }
-  return set_error(RTG_ERR_INTERNAL, "bad BN");
+  return launch_variants<A_KIND, B_MAJOR>(ctx, bn, mode, ma, mb, md, mr, args, redp);
 }
 
-// Largest tile that still fills the machine; smaller tiles when the problem has too few of them.
-static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t batch = 1) {
+// Largest tile that still fills the machine; smaller tiles when the problem has too few of them.  With `splits` the
+// choice is joint over (BN, split-K factor): layers whose tile count is a poor fit for 148 SMs (98 or 196 tiles)
+// divide K so that the work units fill whole waves; the price is one pass over the partial sums (L2 resident).
+static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t batch = 1, int* splits = nullptr) {
   // Cycle model fitted to the per-role counters of the PROF build (profiles/): the MMA thread needs
   // max(64, BN/2) cycles per 128 x BN x 8 instruction (64 is the dispatch floor, so BN = 64 runs the tensor pipe at
   // half rate) plus ~150 cycles of barrier traffic per k-block; the epilogue drains a tile in ~1000 + 12*BN cycles
@@ -261,7 +264,11 @@ static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t
   const bool x3 = ctx->math != RTG_MATH_TF32;
   const int max_bn = x3 ? 128 : 256;
   const int64_t m_tiles = div_ceil(M, kBM) * batch;
-  int best = 64;
+  static const int max_splits = []() {
+    const char* e = getenv("RTG_SPLITK");  // developer switch: 1 disables split-K
+    return e ? std::max(1, atoi(e)) : 8;
+  }();
+  int best = 64, best_s = 1;
   double best_cost = 1e300;
   const int cands[3] = {256, 128, 64};
   for (int i = 0; i < 3; ++i) {
@@ -269,16 +276,28 @@ static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t
     if (bn > max_bn) continue;
     if (bn > 64 && N <= bn / 2) continue;  // mostly padding
     const int64_t tiles = m_tiles * div_ceil(N, bn);
-    const int64_t rounds = div_ceil(tiles, ctx->num_sms);
-    const double kb_cycles = 4.0 * std::max(64, bn / 2) * (x3 ? 3 : 1) + 150.0;
-    const double main_cycles = static_cast<double>(num_kb) * kb_cycles;
+    // measured per-k-block cost of a busy CTA (PROF build, ResNet-50 layers): 3xTF32 is bounded by the TMA -> split
+    // -> tcgen05.st -> MMA chain over its 3-5 stages (~1250-1400 cycles), TF32 by shared-memory operand reads
+    const double kb_cycles = x3 ? (bn == 128 ? 1350.0 : 1250.0) : 6.4 * std::max(64, bn / 2) + 150.0;
     const double epi_cycles = x3 ? 800.0 + 6.0 * bn : 1000.0 + 12.0 * bn;
-    const double cost = static_cast<double>(rounds) * std::max(main_cycles, epi_cycles) + epi_cycles + 3000.0;
-    if (cost < best_cost) {
-      best_cost = cost;
-      best = bn;
+    for (int s = 1; s <= (splits ? max_splits : 1); ++s) {
+      int64_t kbs = div_ceil(num_kb, s);
+      if (s > 1 && x3) kbs = div_ceil(kbs, kChunkKb) * kChunkKb;
+      const int64_t s_eff = div_ceil(num_kb, std::max<int64_t>(kbs, 1));
+      if (s > 1 && (s_eff != s || kbs < 4)) continue;
+      const int64_t rounds = div_ceil(tiles * s, ctx->num_sms);
+      const double main_cycles = static_cast<double>(kbs) * kb_cycles;
+      double cost = static_cast<double>(rounds) * std::max(main_cycles, epi_cycles) + epi_cycles + 3000.0;
+      // reduction pass: launch + (s partial planes read, one result written) out of L2 at ~2500 B/clk
+      if (s > 1) cost += 5000.0 + static_cast<double>(s + 1) * M * N * 4.0 / 2500.0;
+      if (cost < best_cost * (s > 1 ? 0.9 : 1.0)) {  // a split has to pay for itself clearly
+        best_cost = cost;
+        best = bn;
+        best_s = s;
+      }
     }
   }
+  if (splits) *splits = best_s;
   return best;
 }
 
@@ -316,7 +335,8 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   }
 
   CUtensorMap ma, mb;
-  const int bn = choose_bn(ctx, M, N, div_ceil(K, kBK));
+  int splits = 1;
+  const int bn = choose_bn(ctx, M, N, div_ceil(K, kBK), 1, dmap.hw > 0 ? nullptr : &splits);
   RTG_TRY(encode_2d(ctx, &ma, a.p, K, M, a.rs, kBK, kBM));
   if (b_major == 0)
     RTG_TRY(encode_2d(ctx, &mb, b.p, K, N, b.cs, kBK, bn));
@@ -340,6 +360,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   g.act_lo = ep.act_lo;
   g.act_hi = ep.act_hi;
   g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0);
+  g.splits = splits;
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
@@ -481,7 +502,8 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
     const uint64_t bytes = static_cast<uint64_t>(g.n) * g.h * g.w * g.c_total * 4;
     if (ctx->driver_version <= 13010 && bytes < 131072) reinterpret_cast<uint64_t*>(&ma)[1] &= ~(1ull << 21);
   }
-  const int bn = choose_bn(ctx, M, og, Kmat / kBK);
+  int splits = 1;
+  const int bn = choose_bn(ctx, M, og, Kmat / kBK, 1, dmap.hw > 0 ? nullptr : &splits);
   RTG_TRY(encode_2d(ctx, &mb, wmat, Kmat, og, Kmat, kBK, bn));
 
   GemmArgs a = {};
@@ -501,6 +523,7 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   a.act_lo = ep.act_lo;
   a.act_hi = ep.act_hi;
   a.flags = debug_flags();
+  a.splits = splits;
   a.ic.ow = g.ow;
   a.ic.oh = g.oh;
   a.ic.stride_w = g.stride_w;

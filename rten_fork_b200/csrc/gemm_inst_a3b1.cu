@@ -1,0 +1,9 @@
+// Kernel variants of the contraction engine for A_KIND 3, B_MAJOR 1 (see gemm_launch.cuh).
+#define RTG_GEMM_INSTANTIATE
+#include "gemm_launch.cuh"
+
+namespace rtg {
+template rtg_status launch_variants<3, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&,
+                                            const CUtensorMap&, const CUtensorMap&, const GemmArgs&,
+                                            const ReduceArgs*);
+}  // namespace rtg

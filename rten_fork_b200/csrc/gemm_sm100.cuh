@@ -71,6 +71,10 @@ struct GemmArgs {
   int32_t act;
   float act_lo, act_hi;
   int32_t flags;   // bit 0: (debug) MODE 1 also overwrites the raw operand tile with its hi part
+  // Split-K (splits > 1): work unit u = split * num_tiles + tile walks k-blocks [split * kb_per_split, +kb_per_split)
+  // and leaves its raw partial sums in plane `split` of a {N, M, splits} workspace (tmD); splitk_reduce_kernel adds
+  // the planes in a fixed order and applies the epilogue.  Used when a layer has too few output tiles for 148 SMs.
+  int32_t splits, kb_per_split;
   Im2colArgs ic;
   unsigned long long* prof;  // RTG_PROF builds: per-CTA wait / busy cycle counters (see PROF_* below), else unused
 };
@@ -139,9 +143,17 @@ struct GemmCfg {
   // is a latency-bound chain (tcgen05.ld -> math -> st.shared -> fence -> TMA store), so throughput comes from
   // running more chunks side by side.
   static constexpr int kEpiWarps = 8;
-  static constexpr int kEpiBufs = 1;
+  // Two staging buffers per warp: the residual of chunk i+1 is already in flight (TMA load) while chunk i is being
+  // finished, and the TMA store of chunk i may still read its buffer while chunk i+1 is written.  With one buffer the
+  // short-K layers (ResNet layer1/2 pointwise convs, K = 64..128) were bound by this chain, not by HBM.
+  // 3xTF32 with BN = 64 keeps one buffer: there a warp has a single chunk per tile and the fifth pipeline stage the
+  // extra 32 KB would cost is worth more (that mode is bound by the TMA -> split -> MMA chain).
+  static constexpr int kEpiBufs = (MODE == 1 && BN == 64) ? 1 : 2;
   static constexpr int kEpiBufBytes = 4096;
-  static constexpr int kEpiBiasBytes = kEpiWarps * (BN / 2) * 4;  // per-warp copy of its columns' bias
+  // Column bias of the whole launch (zero padded to n_tiles * BN entries), loaded once per CTA; launches with more
+  // output columns than this fall back to a per-tile slice per warp at the start of the same region.
+  static constexpr int kBiasTable = 2048;
+  static constexpr int kEpiBiasBytes = kBiasTable * 4;
   static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes + kEpiBiasBytes;
   static constexpr int kMaxSmem = 227 * 1024 - 2048 - kEpiBytes;  // barriers + alignment slack
   static constexpr int kStagesSmem = kMaxSmem / kStageBytes;
@@ -210,6 +222,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int num_tiles = m_tiles * n_tiles;
   const int num_kb = args.num_kb;
   const int chunk_kb = kChunked ? kChunkKb : num_kb;  // k-blocks per TMEM accumulation chunk
+  const int splits = args.splits > 1 ? args.splits : 1;
+  const int num_units = num_tiles * splits;  // work units: (split, tile), tile fastest
+  const int kb_per_split = splits > 1 ? args.kb_per_split : num_kb;
 
   if (warp == kTmaWarp && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -246,16 +261,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // own prologue early.  Both are no-ops when the launch did not ask for programmatic serialisation.
   ptx::grid_dependency_wait();
   ptx::grid_launch_dependents();
+  // MODE 1: 512 threads start with 128 registers each.  An epilogue thread carries BN/2 running sums plus a 32-column
+  // chunk and spilled at that size; the TMA / MMA / operand-split warpgroups need fewer, so every role branch starts
+  // by re-balancing the register file: 8 x 32 x kRegsEpi + 8 x 32 x kRegsOther = 64 K.
+  constexpr int kRegsEpi = 152, kRegsOther = 104;
+  const bool bias_table = args.bias_mode == BIAS_COL && n_tiles * BN <= Cfg::kBiasTable;
 
   if (warp == kTmaWarp) {
     // ===================================================== TMA producer
+    if (MODE == 1) ptx::reg_dealloc<kRegsOther>();
     if (lane == 0) {
       PROF_DECL;
       int s = 0;
       uint32_t ph = 0;
       const int ic_dil_h = args.ic.dil_h, ic_dil_w = args.ic.dil_w, ic_c_off = args.ic.c_off;
       const int ic_c_blocks = args.ic.c_blocks, ic_kw = args.ic.kw;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int split = unit / num_tiles, tile = unit - split * num_tiles;
+        const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
         int m0 = (tile / n_tiles) * kBM;
         const int n0 = (tile % n_tiles) * BN;
         int pix_w = 0, pix_h = 0, pix_n = 0;
@@ -282,7 +305,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           pix_h = oy * args.ic.stride_h - args.ic.pad_t;
         }
         int tap_x = 0, tap_y = 0, cb = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        if (A_KIND == 1 && kb_begin != 0) {  // k-block -> (tap row, tap column, channel block)
+          const int tap = kb_begin / ic_c_blocks;
+          cb = kb_begin - tap * ic_c_blocks;
+          tap_y = tap / ic_kw;
+          tap_x = tap - tap_y * ic_kw;
+        }
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
           PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
           const uint32_t a_dst = smem_base + s * Cfg::kStageBytes;
           const uint32_t b_dst = a_dst + kABytes;
@@ -339,6 +368,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp == kMmaWarp) {
     // ===================================================== MMA issuer
+    if (MODE == 1) ptx::reg_dealloc<kRegsOther>();
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::make_idesc_tf32(kBM, BN, 0, B_MAJOR);
       // K-major operands: 128B swizzle, 8-row groups 1024 B apart.  MN-major fp32 operands must use the
@@ -361,12 +391,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int as = 0;
       uint32_t aph = 0;
       PROF_DECL;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+        for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
           PROF_WAIT(0, ptx::mbar_wait(tempty_bar(as), aph ^ 1u));
           ptx::tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BN;
-          const int kb1 = min(num_kb, kb0 + chunk_kb);
+          const int kb1 = min(kb_end, kb0 + chunk_kb);
           for (int kb = kb0; kb < kb1; ++kb) {
             PROF_WAIT(1, ptx::mbar_wait(MODE ? xf_bar(s) : full_bar(s), ph));
             ptx::tc_fence_after();
@@ -411,19 +442,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp < Cfg::kEpiWarps) {
     // ===================================================== epilogue
+    if (MODE == 1) ptx::reg_alloc<kRegsEpi>();
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     constexpr int kCols = Cfg::kColsPerThread;
     const int col0 = (warp >> 2) * kCols;  // first tile column this warp handles
     const bool staged_d = (args.flags & kFlagStagedD) != 0;
     const bool staged_r = (args.flags & kFlagStagedR) != 0;
     const uint32_t ebuf0 = epi_base + warp * Cfg::kEpiBufs * Cfg::kEpiBufBytes;
-    const uint32_t ebias = epi_base + Cfg::kEpiWarps * Cfg::kEpiBufs * Cfg::kEpiBufBytes + warp * (BN / 2) * 4;
+    const uint32_t ebias_tab = epi_base + Cfg::kEpiWarps * Cfg::kEpiBufs * Cfg::kEpiBufBytes;
+    if (bias_table) {
+      for (int n = threadIdx.x; n < n_tiles * BN; n += Cfg::kEpiWarps * 32)
+        ptx::sts_f32(ebias_tab + n * 4, n < args.N ? __ldg(args.bias + n) : 0.f);
+      asm volatile("bar.sync 1, %0;" ::"n"(Cfg::kEpiWarps * 32) : "memory");  // the epilogue warps only
+    }
     int eb = 0;            // staging buffer of the next chunk
     uint32_t rph = 0;      // phase bit per staging buffer of this warp's residual barriers
     int as = 0;
     uint32_t aph = 0;
     PROF_DECL;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      const int split = unit / num_tiles, tile = unit - split * num_tiles;
+      const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
       const int n0 = (tile % n_tiles) * BN;
       // store coordinates of this warp's 32 rows: (st_r, st_z) in the {columns, rows, planes} view of D / R
       int m, st_r, st_z = 0;
@@ -440,6 +479,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         row_ok = st_r + lane < args.M;
       } else {
         st_r = (tile / n_tiles) * kBM + q * 32;
+        st_z = split;  // split-K: plane of the partial-sum workspace (0 otherwise)
         m = st_r + lane;
         row_ok = m < args.M;
       }
@@ -451,7 +491,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
       // this warp's slice of the per-column bias -> shared memory (read back as broadcast loads in finish), issued
       // before the wait for the accumulators so that the global-load latency is hidden
-      if (args.bias_mode == BIAS_COL) {
+      uint32_t ebias = ebias_tab + (n0 + col0) * 4;
+      if (args.bias_mode == BIAS_COL && !bias_table) {
+        ebias = ebias_tab + warp * (BN / 2) * 4;
 #pragma unroll
         for (int i = 0; i < kCols / 32; ++i) {
           const int n = n0 + col0 + i * 32 + lane;
@@ -461,9 +503,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
 
       // residual chunk (32 rows x 32 columns at column c0 of the tile) -> staging buffer b, by TMA
-      auto fetch_residual = [&](int c0, int b) {
+      // `newer` = stores issued after the last one that used buffer b (they may still be reading the other buffer)
+      auto fetch_residual = [&](int c0, int b, int newer) {
         if (lane == 0) {
-          ptx::bulk_wait_read<0>();  // earlier stores of this warp no longer read the buffer
+          // earlier stores of this warp no longer read the buffer
+          if (newer > 0) {
+            PROF_WAIT(2, ptx::bulk_wait_read<1>());
+          } else {
+            PROF_WAIT(2, ptx::bulk_wait_read<0>());
+          }
           ptx::mbar_expect_tx(rbar(warp, b), Cfg::kEpiBufBytes);
           ptx::tma_load_3d(ebuf0 + b * Cfg::kEpiBufBytes, &tmR, rbar(warp, b), n0 + c0, st_r, st_z);
         }
@@ -547,7 +595,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
       // chunks of this warp that lie inside the matrix
       const int nch = max(0, min(kCols, args.N - n0 - col0) + 31) / 32;
-      if (staged_r && nch > 0) fetch_residual(col0, eb);
+      // buffers alternate strictly, also across tiles: the last store used eb ^ 1, the one before it eb
+      constexpr int kOther = Cfg::kEpiBufs > 1 ? 1 : 0;  // eb ^ kOther: the other staging buffer (or the only one)
+      constexpr int kAhead = Cfg::kEpiBufs;              // residual chunks in flight
+      if (staged_r && nch > 0) fetch_residual(col0, eb, kOther);
+      if (Cfg::kEpiBufs > 1 && staged_r && nch > 1) fetch_residual(col0 + 32, eb ^ 1, 0);
 
       if (!kChunked) {
         PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
@@ -555,12 +607,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll 1
         for (int i = 0; i < nch; ++i) {
           const int c0 = col0 + i * 32;
-          if (staged_r && Cfg::kEpiBufs > 1 && i + 1 < nch) fetch_residual(c0 + 32, eb ^ 1);
           float v[32];
           ptx::tmem_ld_32x32(lane_addr + as * BN + c0, v);
           ptx::tmem_ld_wait();
           finish(v, c0);
-          if (staged_r && Cfg::kEpiBufs == 1 && i + 1 < nch) fetch_residual(c0 + 32, eb);
+          // chunk i + 2 reuses the buffer whose store was just issued (eb has toggled: it is eb ^ 1 now)
+          if (staged_r && i + kAhead < nch) fetch_residual(c0 + 32 * kAhead, eb ^ kOther, 0);
         }
         ptx::tc_fence_before();
         __syncwarp();
@@ -572,7 +624,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       } else {
         // running sums in registers, one per output column of this thread's row
         float acc[kCols];
-        for (int kb0 = 0; kb0 < num_kb; kb0 += chunk_kb) {
+        for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
           PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
           ptx::tc_fence_after();
 #pragma unroll
@@ -580,7 +632,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             float v[32];
             ptx::tmem_ld_32x32(lane_addr + as * BN + col0 + c0, v);
             ptx::tmem_ld_wait();
-            if (kb0 == 0) {
+            if (kb0 == kb_begin) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) acc[c0 + j] = v[j];
             } else {
@@ -603,7 +655,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = acc[c0 + j];
             finish(v, col0 + c0);
-            if (staged_r && (c0 / 32) + 1 < nch) fetch_residual(col0 + c0 + 32, eb);
+            if (staged_r && (c0 / 32) + kAhead < nch) fetch_residual(col0 + c0 + 32 * kAhead, eb ^ kOther, 0);
           }
         }
       }
@@ -619,6 +671,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // lo = x - hi (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
     // Warps 0-3 of this role own the A tile, one row per thread: the row goes to tensor memory as a hi plane (raw
     // bits) and a lo plane, from where the MMAs read it.  Warps 4-5 write the lo plane of B next to the raw B tile.
+    ptx::reg_dealloc<kRegsOther>();
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
     const int sw = t >> 5;
     auto lo_of = [](float x) {
@@ -627,8 +680,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int s = 0;
     uint32_t ph = 0;
     PROF_DECL;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      for (int kb = 0; kb < num_kb; ++kb) {
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
         const uint32_t stage = smem_base + s * Cfg::kStageBytes;
         if (sw < 4) {

@@ -217,6 +217,11 @@ def clip(x, min_val=None, max_val=None, **kw):
 
 
 def _binary(kind, a, b, out=None, ctx=None):
+    # numpy hands back scalars (np.float32) for 0-d results; describe them as 0-d arrays kept alive for the call
+    if isinstance(a, np.generic):
+        a = np.asarray(a)
+    if isinstance(b, np.generic):
+        b = np.asarray(b)
     ctx = ctx or context_for(a)
     ta, tb = as_tensor(a), as_tensor(b)
     shape = (C.c_int64 * N.RTG_MAX_DIMS)()

@@ -225,3 +225,24 @@ def test_conv_nhwc_device_views(rtg, ctx, oracle, math_mode):
     ctx.sync()
     assert out.stride(1) == 1
     expect_equal(out.cpu().numpy(), oracle.conv2d(x, w, b, padding=(1, 1, 1, 1), strides=(2, 2)), rtol=math_mode["rtol"])
+
+
+@pytest.mark.parametrize("C,O,H,k,s", [(256, 256, 14, 3, 1), (512, 512, 7, 3, 1), (1024, 256, 14, 1, 1), (128, 128, 28, 3, 2)])
+def test_conv_split_k_nhwc(rtg, ctx, oracle, math_mode, C, O, H, k, s):
+    """ResNet-50 layer3 / layer4 shapes have 50-200 output tiles for 148 SMs: the im2col launch splits K (tap and
+    channel-block ranges per work unit) and the reduction pass applies bias + residual + Relu."""
+    import torch
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    p = k // 2
+    x, w, b = rng.fill((4, C, H, H)) + 0.1, rng.fill((O, C, k, k)), rng.fill((O,))
+    oh = (H + 2 * p - k) // s + 1
+    res = rng.fill((4, O, oh, oh))
+    nhwc = lambda a: torch.from_numpy(a).cuda().contiguous(memory_format=torch.channels_last)  # noqa: E731
+    out = ops.conv(nhwc(x), torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda(), (p, p, p, p), 1, (s, s), (1, 1),
+                   residual=nhwc(res), activation="relu", out_nhwc=True)
+    ctx.sync()
+    assert "splitK" in ctx.last_kernel, ctx.last_kernel
+    want = oracle.unary("relu", oracle.binary("add", oracle.conv2d(x, w, b, padding=(p, p, p, p), strides=(s, s)), res))
+    expect_equal(out.cpu().numpy(), want, rtol=math_mode["rtol"])

@@ -140,3 +140,20 @@ def test_gemm_device_resident(rtg, ctx, oracle, math_mode):
     rtg.GemmExecutor(ctx).gemm(out.view(-1), 640, ta, tbt)
     ctx.sync()
     expect_equal(out.cpu().numpy(), oracle.gemm(a, b), rtol=math_mode["rtol"])
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 4096), (300, 200, 2000), (128, 128, 8224), (1024, 1024, 1024)])
+def test_gemm_split_k(rtg, ctx, oracle, math_mode, m, n, k):
+    """Few output tiles and a long K: the launch divides K over several CTAs per tile (partial sums in a workspace,
+    fixed-order reduction with the epilogue).  Same tolerance as the unsplit kernel; repeated runs are bit-identical
+    (Operator::is_deterministic, src/ops/mod.rs:850-861)."""
+    rng = oracle.XorShiftRng(1234)
+    a, b = rng.fill((m, k)), rng.fill((k, n))
+    bias = rng.fill((m,))
+    c0 = rng.fill((m, n))
+    got = _run(rtg, ctx, a, b, alpha=0.5, beta=2.0, bias=bias, out=c0.copy())
+    if k >= 2000:
+        assert "splitK" in ctx.last_kernel, ctx.last_kernel
+    expect_equal(got, oracle.gemm(a, b, alpha=0.5, beta=2.0, bias=bias, out=c0.copy()), rtol=math_mode["rtol"])
+    again = _run(rtg, ctx, a, b, alpha=0.5, beta=2.0, bias=bias, out=c0.copy())
+    assert again.tobytes() == got.tobytes()
