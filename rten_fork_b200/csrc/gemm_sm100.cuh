@@ -131,10 +131,16 @@ struct GemmCfg {
   static_assert(MODE == 0 || BN <= 128, "3xTF32 keeps BN/2 running sums per epilogue thread in registers");
   static constexpr int kBBytes = BN * kBK * 4;
   static constexpr int kRawBytes = kABytes + kBBytes;
-  // MODE 1 (3xTF32): a stage is [A raw][B raw][B lo].  The A operand of the MMAs lives in tensor memory: the split
-  // warps write hi (= raw bits) and lo of every A row into a 64-column TMEM slot per stage, so the three MMAs of a
-  // k-step read only B from shared memory (shared-memory bandwidth, not the tensor pipe, is what bounds this mode).
-  static constexpr int kStageBytes = MODE ? kRawBytes + kBBytes : kRawBytes;
+  // MODE 0: a stage is [A raw][B raw], one ring.
+  // MODE 1 (3xTF32): two rings.  The A operand of the MMAs lives in tensor memory: the split warps write hi (= raw
+  // bits) and lo of every A row into a 64-column TMEM slot per stage, so the three MMAs of a k-step read only B from
+  // shared memory.  A raw tile is therefore dead as soon as it has been split, long before the MMAs that use it have
+  // run, and sits in its own short ring of kAStages slots; a pipeline stage proper is [B raw][B lo] plus its TMEM slot.
+  // That buys a fourth stage at BN = 128 (sixth at BN = 64) in the same shared memory; this mode is bound by the
+  // TMA -> split -> tcgen05.st -> MMA chain, i.e. by how many k-blocks are in flight.
+  static constexpr int kAStages = MODE ? 3 : 0;
+  static constexpr int kStageBytes = MODE ? 2 * kBBytes : kRawBytes;
+  static constexpr int kARingBytes = kAStages * kABytes;
   static constexpr int kTmemAStageCols = 2 * kBK;  // hi plane + lo plane, one 32-bit column per k
   // Epilogue staging: every epilogue warp owns kEpiBufs buffers of 32 rows x 128 bytes (one 32-column chunk of its
   // 32 accumulator rows, 128B-swizzled) through which the residual arrives (TMA load) and the result leaves (TMA
@@ -146,9 +152,8 @@ struct GemmCfg {
   // Two staging buffers per warp: the residual of chunk i+1 is already in flight (TMA load) while chunk i is being
   // finished, and the TMA store of chunk i may still read its buffer while chunk i+1 is written.  With one buffer the
   // short-K layers (ResNet layer1/2 pointwise convs, K = 64..128) were bound by this chain, not by HBM.
-  // 3xTF32 with BN = 64 keeps one buffer: there a warp has a single chunk per tile and the fifth pipeline stage the
-  // extra 32 KB would cost is worth more (that mode is bound by the TMA -> split -> MMA chain).
-  static constexpr int kEpiBufs = (MODE == 1 && BN == 64) ? 1 : 2;
+  // 3xTF32 keeps one buffer: the pipeline stage the extra 32 KB would cost is worth more there.
+  static constexpr int kEpiBufs = MODE == 1 ? 1 : 2;
   static constexpr int kEpiBufBytes = 4096;
   // Column bias of the whole launch (zero padded to n_tiles * BN entries), loaded once per CTA; launches with more
   // output columns than this fall back to a per-tile slice per warp at the start of the same region.
@@ -156,11 +161,11 @@ struct GemmCfg {
   static constexpr int kEpiBiasBytes = kBiasTable * 4;
   static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes + kEpiBiasBytes;
   static constexpr int kMaxSmem = 227 * 1024 - 2048 - kEpiBytes;  // barriers + alignment slack
-  static constexpr int kStagesSmem = kMaxSmem / kStageBytes;
+  static constexpr int kStagesSmem = (kMaxSmem - kARingBytes) / kStageBytes;
   static constexpr int kStagesTmem = MODE ? (512 - 2 * BN) / kTmemAStageCols : 8;  // accumulators take 2 * BN columns
   static constexpr int kStagesRaw = kStagesSmem < kStagesTmem ? kStagesSmem : kStagesTmem;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
+  static constexpr int kSmemBytes = kARingBytes + kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
   // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
   // and 6 split warps so that the operand split keeps up with the tensor core.
   static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
@@ -200,7 +205,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   // 128B swizzle atoms need 1024-byte aligned tiles.
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t epi_base = smem_base + kStages * Cfg::kStageBytes;
+  const uint32_t ring_base = smem_base + Cfg::kARingBytes;  // MODE 1: the A ring comes first
+  const uint32_t epi_base = ring_base + kStages * Cfg::kStageBytes;
+  constexpr int kAStages = Cfg::kAStages;
   const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
@@ -209,6 +216,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   auto tempty_bar = [&](int a) { return bar_base + 8u * (3 * kStages + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (3 * kStages + 4);
   auto rbar = [&](int w, int b) { return bar_base + 8u * (3 * kStages + 5 + w * Cfg::kEpiBufs + b); };
+  auto afull_bar = [&](int i) { return bar_base + 8u * (3 * kStages + 5 + Cfg::kEpiWarps * Cfg::kEpiBufs + i); };
+  auto aempty_bar = [&](int i) { return bar_base + 8u * (3 * kStages + 5 + Cfg::kEpiWarps * Cfg::kEpiBufs + kAStages + i); };
+  static_assert(8 * (3 * kStages + 5 + Cfg::kEpiWarps * Cfg::kEpiBufs + 2 * kAStages) <= 512, "barrier region");
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
 
@@ -244,6 +254,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int w = 0; w < Cfg::kEpiWarps; ++w)
       for (int b = 0; b < Cfg::kEpiBufs; ++b) ptx::mbar_init(rbar(w, b), 1);
+    for (int i = 0; i < kAStages; ++i) {
+      ptx::mbar_init(afull_bar(i), 1);
+      ptx::mbar_init(aempty_bar(i), 4);  // one arrival per A-split warp
+    }
     ptx::fence_mbar_init();
   }
   if (warp == kMmaWarp) {
@@ -274,6 +288,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       PROF_DECL;
       int s = 0;
       uint32_t ph = 0;
+      int ia = 0;  // MODE 1: slot / phase of the A ring
+      uint32_t pa = 0;
       const int ic_dil_h = args.ic.dil_h, ic_dil_w = args.ic.dil_w, ic_c_off = args.ic.c_off;
       const int ic_c_blocks = args.ic.c_blocks, ic_kw = args.ic.kw;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
@@ -312,24 +328,33 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tap_x = tap - tap_y * ic_kw;
         }
         for (int kb = kb_begin; kb < kb_end; ++kb) {
-          PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
-          const uint32_t a_dst = smem_base + s * Cfg::kStageBytes;
-          const uint32_t b_dst = a_dst + kABytes;
+          uint32_t a_dst, b_dst, fa;
           const uint32_t fb = full_bar(s);
+          if (MODE == 1) {
+            PROF_WAIT(0, ptx::mbar_wait(aempty_bar(ia), pa ^ 1u));
+            a_dst = smem_base + ia * kABytes;
+            fa = afull_bar(ia);
+            b_dst = ring_base + s * Cfg::kStageBytes;
+          } else {
+            PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
+            a_dst = ring_base + s * Cfg::kStageBytes;
+            fa = fb;
+            b_dst = a_dst + kABytes;
+          }
 #ifdef RTG_PROF
           const long long ti_ = clock64();
 #endif
           PROF_MARK(0, 5);  // first TMA issue
-          ptx::mbar_expect_tx(fb, Cfg::kRawBytes);
+          ptx::mbar_expect_tx(fa, MODE == 1 ? kABytes : Cfg::kRawBytes);
           if (A_KIND == 0) {
-            ptx::tma_load_2d(a_dst, &tmA, fb, kb * kBK, m0);
+            ptx::tma_load_2d(a_dst, &tmA, fa, kb * kBK, m0);
           } else if (A_KIND == 3) {
-            ptx::tma_load_4d(a_dst, &tmA, fb, kb * kBK, m0, z0 * args.ic.bat_a0, z1 * args.ic.bat_a1);
+            ptx::tma_load_4d(a_dst, &tmA, fa, kb * kBK, m0, z0 * args.ic.bat_a0, z1 * args.ic.bat_a1);
           } else if (A_KIND == 2) {
             // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
-            ptx::tma_load_4d(a_dst, &tmA, fb, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
+            ptx::tma_load_4d(a_dst, &tmA, fa, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
           } else {
-            ptx::tma_load_im2col_4d(a_dst, &tmA, fb, ic_c_off + cb * kBK, pix_w, pix_h, pix_n,
+            ptx::tma_load_im2col_4d(a_dst, &tmA, fa, ic_c_off + cb * kBK, pix_w, pix_h, pix_n,
                                     static_cast<uint16_t>(tap_x * ic_dil_w), static_cast<uint16_t>(tap_y * ic_dil_h));
             if (++cb == ic_c_blocks) {
               cb = 0;
@@ -338,6 +363,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 ++tap_y;
               }
             }
+          }
+          if (MODE == 1) {  // the B slot (and its TMEM slot) is free once the MMAs of its previous use have completed
+            if (++ia == kAStages) {
+              ia = 0;
+              pa ^= 1u;
+            }
+            PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
+            ptx::mbar_expect_tx(fb, Cfg::kBBytes);
           }
           if (A_KIND == 3) {
             const int bz0 = z0 * args.ic.bat_b0, bz1 = z1 * args.ic.bat_b1;
@@ -377,8 +410,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       constexpr uint32_t b_lbo = B_MAJOR ? 4096 : 16;
       constexpr uint32_t b_sbo = B_MAJOR ? 512 : 1024;
       // descriptor words of stage 0; a stage / k-step only moves the 14-bit "address >> 4" field of the low word
-      const uint64_t a_d0 = ptx::make_smem_desc(smem_base, 16, 1024);
-      const uint64_t b_d0 = ptx::make_smem_desc(smem_base + kABytes, b_lbo, b_sbo, b_layout);
+      const uint64_t a_d0 = ptx::make_smem_desc(ring_base, 16, 1024);  // MODE 0 only (MODE 1 reads A from TMEM)
+      const uint64_t b_d0 = ptx::make_smem_desc(ring_base + (MODE ? 0 : kABytes), b_lbo, b_sbo, b_layout);
       const uint32_t a_hi = static_cast<uint32_t>(a_d0 >> 32), b_hi = static_cast<uint32_t>(b_d0 >> 32);
       const uint32_t a_lo0 = static_cast<uint32_t>(a_d0), b_lo0 = static_cast<uint32_t>(b_d0);
       constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4;
@@ -679,16 +712,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     };
     int s = 0;
     uint32_t ph = 0;
+    int ia = 0;
+    uint32_t pa = 0;
     PROF_DECL;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
       for (int kb = kb_begin; kb < kb_end; ++kb) {
-        PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
-        const uint32_t stage = smem_base + s * Cfg::kStageBytes;
+        const uint32_t stage = ring_base + s * Cfg::kStageBytes;  // [B raw][B lo]
         if (sw < 4) {
+          PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
           const int q = warp & 3;  // TMEM lane quarter this warp may write
           const int row = q * 32 + lane;
-          const uint32_t src = stage + row * 128;
+          const uint32_t src = smem_base + ia * kABytes + row * 128;
           const uint32_t swz = row & 7;
           uint32_t hi[32], lo[32];
 #pragma unroll
@@ -699,14 +734,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             hi[4 * j4 + 2] = __float_as_uint(x.z), lo[4 * j4 + 2] = lo_of(x.z);
             hi[4 * j4 + 3] = __float_as_uint(x.w), lo[4 * j4 + 3] = lo_of(x.w);
           }
+          // the raw tile is in registers: hand its slot back to the TMA producer
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
+          if (++ia == kAStages) {
+            ia = 0;
+            pa ^= 1u;
+          }
+          // the TMEM slot of this stage is free once the MMAs of its previous use have completed
+          PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
+          ptx::tc_fence_after();
           const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
           ptx::tmem_st_32x32(dst, hi);
           ptx::tmem_st_32x32(dst + kBK, lo);
           ptx::tmem_st_wait();
           ptx::tc_fence_before();
         } else {
+          PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
           constexpr int kBVecs = Cfg::kBBytes / 16;
-          const uint32_t braw = stage + kABytes, blo = braw + Cfg::kBBytes;
+          const uint32_t braw = stage, blo = braw + Cfg::kBBytes;
 #pragma unroll 4
           for (int i = t - 128; i < kBVecs; i += 64) {
             const float4 x = ptx::lds_v4(braw + i * 16);
