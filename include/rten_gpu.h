@@ -100,6 +100,24 @@ rtg_status rtg_gemm(rtg_ctx* ctx, int32_t device, float* out, size_t out_len, si
                     size_t m, size_t k, ptrdiff_t a_rs, ptrdiff_t a_cs, const float* b, size_t b_rows, size_t n,
                     ptrdiff_t b_rs, ptrdiff_t b_cs, float alpha, float beta, const float* bias, size_t bias_len);
 
+/* N-split GEMM across GPUs (BASELINE.json configs[4]).  The reference has no multi-device path: this is
+ * the exchange step the split adds after GemmExecutor::gemm (src/gemm.rs:448-542), fused into the GEMM epilogue.
+ * Every rank owns a peer-visible row-major [m, n_total] result buffer (rtg_symm_alloc; the 64-byte handle is sent to the
+ * other ranks, which map it with rtg_symm_open).  rtg_gemm_scatter computes a[m,k] . b[k,n_block] and writes the
+ * block into columns [col_offset, col_offset + n_block) of dst[0] (this rank's buffer) AND of dst[1..n_dst) (the peers'
+ * buffers): each finished tile leaves shared memory by one TMA store per destination, over NVLink for the peers, so
+ * the gather overlaps the contraction tile by tile.  All pointers are device pointers on `device`; a and b may have
+ * any element strides.  After the call returns and the stream has drained, a cross-rank barrier makes every buffer
+ * complete.  n_dst <= 8; col_offset and n_total must be multiples of 4 (16-byte aligned windows). */
+#define RTG_SYMM_HANDLE_BYTES 64
+rtg_status rtg_symm_alloc(rtg_ctx* ctx, size_t bytes, void** dptr, uint8_t handle[RTG_SYMM_HANDLE_BYTES]);
+rtg_status rtg_symm_free(rtg_ctx* ctx, void* dptr);
+rtg_status rtg_symm_open(rtg_ctx* ctx, const uint8_t handle[RTG_SYMM_HANDLE_BYTES], void** peer_dptr);
+rtg_status rtg_symm_close(rtg_ctx* ctx, void* peer_dptr);
+rtg_status rtg_gemm_scatter(rtg_ctx* ctx, const float* a, size_t m, size_t k, ptrdiff_t a_rs, ptrdiff_t a_cs,
+                            const float* b, size_t n_block, ptrdiff_t b_rs, ptrdiff_t b_cs, size_t col_offset,
+                            size_t n_total, float* const* dst, int32_t n_dst);
+
 /* ------------------------------------------------------------------------------------------------ operators */
 enum { RTG_PAD_FIXED = 0, RTG_PAD_SAME = 1 }; /* Padding::{Fixed,Same}  src/ops/mod.rs:127-166 */
 enum {

@@ -1,6 +1,8 @@
 // C ABI: rtg_gemm — the GemmExecutor entry point (reference: src/gemm.rs:448-542, 733-765).
 #include "gemm_host.h"
 
+#include <string.h>
+
 using namespace rtg;
 
 namespace rtg {
@@ -82,4 +84,76 @@ extern "C" rtg_status rtg_gemm(rtg_ctx* ctx_, int32_t device, float* out, size_t
     RTG_CUDA(cudaStreamSynchronize(ctx->stream));
   }
   return RTG_OK;
+}
+
+// ---------------------------------------------------------------- N-split GEMM with peer stores
+extern "C" rtg_status rtg_symm_alloc(rtg_ctx* ctx_, size_t bytes, void** dptr, uint8_t handle[RTG_SYMM_HANDLE_BYTES]) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx || !dptr || !handle) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == RTG_SYMM_HANDLE_BYTES, "handle size");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  // a dedicated allocation: IPC handles name whole cudaMalloc regions, not pool slices
+  RTG_CUDA(cudaMalloc(dptr, bytes ? bytes : 16));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, *dptr);
+  if (e != cudaSuccess) {
+    cudaFree(*dptr);
+    *dptr = nullptr;
+    return set_errorf(RTG_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  }
+  memcpy(handle, &h, sizeof(h));
+  return RTG_OK;
+}
+
+extern "C" rtg_status rtg_symm_free(rtg_ctx* ctx_, void* dptr) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+  RTG_CUDA(cudaFree(dptr));
+  return RTG_OK;
+}
+
+extern "C" rtg_status rtg_symm_open(rtg_ctx* ctx_, const uint8_t handle[RTG_SYMM_HANDLE_BYTES], void** peer_dptr) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx || !handle || !peer_dptr) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  // maps the peer's allocation into this process and enables peer access to its device on first use
+  RTG_CUDA(cudaIpcOpenMemHandle(peer_dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RTG_OK;
+}
+
+extern "C" rtg_status rtg_symm_close(rtg_ctx* ctx_, void* peer_dptr) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+  RTG_CUDA(cudaIpcCloseMemHandle(peer_dptr));
+  return RTG_OK;
+}
+
+extern "C" rtg_status rtg_gemm_scatter(rtg_ctx* ctx_, const float* a, size_t m, size_t k, ptrdiff_t a_rs,
+                                       ptrdiff_t a_cs, const float* b, size_t n_block, ptrdiff_t b_rs, ptrdiff_t b_cs,
+                                       size_t col_offset, size_t n_total, float* const* dst, int32_t n_dst) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx || !dst) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  if (n_dst < 1 || n_dst > 8) return set_error(RTG_ERR_INVALID_VALUE, "n_dst must be in 1..8");
+  if (a_rs < 0 || a_cs < 0 || b_rs < 0 || b_cs < 0) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "negative strides");
+  if (col_offset + n_block > n_total) return set_error(RTG_ERR_PANIC, "Output buffer should be large enough");
+  if (col_offset % 4 != 0 || n_total % 4 != 0)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "col_offset and n_total must be multiples of 4");
+  if (m == 0 || n_block == 0) return RTG_OK;
+  if (k == 0) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "k == 0");
+  for (int i = 0; i < n_dst; ++i)
+    if (!dst[i] || (reinterpret_cast<uintptr_t>(dst[i]) & 15) != 0)
+      return set_error(RTG_ERR_INVALID_VALUE, "dst buffers must be non-NULL and 16-byte aligned");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  Epilogue ep;
+  ep.n_peers = n_dst - 1;
+  for (int i = 1; i < n_dst; ++i) ep.peer_D[i - 1] = dst[i];
+  OutMap om = {static_cast<int64_t>(n_total), 0, 0, static_cast<int32_t>(col_offset)};
+  return gemm_device(ctx, MatView{a, (int64_t)m, (int64_t)k, a_rs, a_cs},
+                     MatView{b, (int64_t)k, (int64_t)n_block, b_rs, b_cs}, dst[0], om, ep);
 }

@@ -189,10 +189,12 @@ rtg_status launch_reduce(Context* ctx, const ReduceArgs& ra) {
 
 template <int A_KIND, int B_MAJOR>
 static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           GemmArgs args, int plane_rows = 0, int64_t num_planes = 0) {
+                           GemmArgs args, int plane_rows = 0, int64_t num_planes = 0, const Epilogue* peers = nullptr) {
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;
-  Scratch ws;
+  Scratch ws, peer_maps;
+  const int n_peers = peers ? peers->n_peers : 0;
+  if (n_peers > 0) args.splits = 1;  // the reduction pass writes the local buffer only
   ReduceArgs red = {};
   const ReduceArgs* redp = nullptr;
   auto stageable = [&](const float* p, const OutMap& om) {
@@ -244,12 +246,26 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
     const uint64_t ld = (args.M == 1 && num_planes <= 1) ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.dmap.ld;
     RTG_TRY(encode_out_3d(ctx, &md, args.D + args.dmap.chan_off, args.N, rows, planes, ld));
     args.flags |= kFlagStagedD;
+    if (n_peers > 0) {
+      CUtensorMap host_maps[7];
+      for (int p = 0; p < n_peers; ++p) {
+        if ((reinterpret_cast<uintptr_t>(peers->peer_D[p] + args.dmap.chan_off) & 15) != 0)
+          return set_error(RTG_ERR_UNSUPPORTED_VALUE, "peer output buffers must be 16-byte aligned");
+        RTG_TRY(encode_out_3d(ctx, &host_maps[p], peers->peer_D[p] + args.dmap.chan_off, args.N, rows, planes, ld));
+      }
+      RTG_TRY(peer_maps.alloc(ctx, sizeof(CUtensorMap) * 7));
+      RTG_CUDA(cudaMemcpyAsync(peer_maps.p, host_maps, sizeof(CUtensorMap) * n_peers, cudaMemcpyHostToDevice, ctx->stream));
+      args.peer_maps = static_cast<const CUtensorMap*>(peer_maps.p);
+      args.n_peers = n_peers;
+    }
     if (stageable(args.R, args.rmap)) {
       const uint64_t rld = (args.M == 1 && num_planes <= 1) ? static_cast<uint64_t>(div_ceil(args.N, 4) * 4) : args.rmap.ld;
       RTG_TRY(encode_out_3d(ctx, &mr, args.R + args.rmap.chan_off, args.N, rows, planes, rld));
       args.flags |= kFlagStagedR;
     }
   }
+  if (n_peers > 0 && args.n_peers == 0)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "peer stores need a row-major, 16-byte aligned output");
   return launch_variants<A_KIND, B_MAJOR>(ctx, bn, mode, ma, mb, md, mr, args, redp);
 }
 
@@ -364,8 +380,8 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
-  if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g);
-  return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g);
+  if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep);
+  return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep);
 }
 
 // ---------------------------------------------------------------- batched GEMM (one launch for all batch entries)

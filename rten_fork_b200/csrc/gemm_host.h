@@ -19,6 +19,10 @@ struct Epilogue {
   OutMap rmap = {0, 0, 0, 0};
   int act = ACT_NONE;
   float act_lo = 0.f, act_hi = 0.f;
+  // peer copies of the output (other GPUs' buffers mapped into this process, same layout as D): every tile is stored
+  // to D and to each of them.  Needs a row-major, 16-byte aligned D (the TMA-store epilogue).
+  int n_peers = 0;
+  float* peer_D[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 // D = epilogue(A[M,K] . B[K,N]).  A and B may have any strides; operands that TMA cannot address directly (neither

@@ -75,6 +75,11 @@ struct GemmArgs {
   // and leaves its raw partial sums in plane `split` of a {N, M, splits} workspace (tmD); splitk_reduce_kernel adds
   // the planes in a fixed order and applies the epilogue.  Used when a layer has too few output tiles for 148 SMs.
   int32_t splits, kb_per_split;
+  // N-split GEMM over several GPUs: every finished chunk is also stored (TMA, NVLink) into the same window of each
+  // peer's output buffer, so the "all-gather" of the column blocks happens tile by tile inside the GEMM.  The maps
+  // live in global memory (host-encoded, copied before the launch).
+  const CUtensorMap* peer_maps;
+  int32_t n_peers;
   Im2colArgs ic;
   unsigned long long* prof;  // RTG_PROF builds: per-CTA wait / busy cycle counters (see PROF_* below), else unused
 };
@@ -604,6 +609,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           __syncwarp();
           if (lane == 0) {
             ptx::tma_store_3d(&tmD, buf, n0 + c0, st_r, st_z);  // clipped to the tensor bounds by the TMA unit
+            for (int p = 0; p < args.n_peers; ++p) ptx::tma_store_3d(args.peer_maps + p, buf, n0 + c0, st_r, st_z);
             ptx::bulk_commit();
           }
           if (Cfg::kEpiBufs > 1) eb ^= 1;

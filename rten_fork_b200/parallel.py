@@ -93,3 +93,105 @@ def gemm_nsplit(a, b, group=None, local_gemm=None, align: int = 128):
     if all(h - l == width for l, h in blocks):
         return gathered.permute(1, 0, 2).reshape(m, world * width)  # one strided copy
     return torch.cat([gathered[r, :, : h - l] for r, (l, h) in enumerate(blocks)], dim=1)
+
+
+class _DevicePtrView:
+    """Minimal ``__cuda_array_interface__`` carrier so that torch can wrap a raw device pointer without a copy."""
+
+    def __init__(self, ptr: int, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class SymmetricMatrix:
+    """A row-major ``[m, n]`` f32 result buffer on every rank of ``group``, each mapped into every other rank's address
+    space (``rtg_symm_alloc`` / ``rtg_symm_open``: CUDA IPC handles exchanged with ``all_gather_object``).  ``ptrs[r]``
+    is rank r's buffer as seen from this process; ``tensor`` is the local buffer as a torch tensor."""
+
+    def __init__(self, m: int, n: int, ctx=None, group=None):
+        import ctypes as C
+
+        import torch
+        import torch.distributed as dist
+
+        from . import _native as N
+        from .context import default_context
+
+        self.ctx = ctx or default_context(torch.cuda.current_device())
+        self.group, self.m, self.n = group, m, n
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if n % 4:
+            raise N.RtgError(6, "n must be a multiple of 4")
+        ptr = C.c_void_p()
+        handle = (C.c_uint8 * 64)()
+        N.check(N.lib().rtg_symm_alloc(self.ctx.handle, C.c_size_t(m * n * 4), C.byref(ptr), handle))
+        self._local = ptr.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        self.ptrs, self._opened = [], []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.ptrs.append(self._local)
+                continue
+            peer = C.c_void_p()
+            buf = (C.c_uint8 * 64).from_buffer_copy(h)
+            N.check(N.lib().rtg_symm_open(self.ctx.handle, buf, C.byref(peer)))
+            self.ptrs.append(peer.value)
+            self._opened.append(peer.value)
+        self.tensor = torch.as_tensor(_DevicePtrView(self._local, (m, n)), device=torch.device("cuda", self.ctx.device))
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.tensor.device)
+
+    def fence(self):
+        """Stream-ordered cross-rank barrier: once it has run on this rank's stream, every rank's GEMM (and with it
+        every peer store into this rank's buffer) has completed.  One 4-byte all-reduce; no host synchronisation."""
+        import torch.distributed as dist
+
+        dist.all_reduce(self._flag, group=self.group)
+
+    def close(self):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from . import _native as N
+
+        dist.barrier(self.group)  # no rank unmaps or frees while a peer may still be writing
+        for p in self._opened:
+            N.check(N.lib().rtg_symm_close(self.ctx.handle, C.c_void_p(p)))
+        self._opened = []
+        dist.barrier(self.group)
+        if self._local:
+            N.check(N.lib().rtg_symm_free(self.ctx.handle, C.c_void_p(self._local)))
+            self._local = None
+        self.tensor = None
+
+
+def gemm_nsplit_fused(a, b, out: SymmetricMatrix, align: int = 128, fence: bool = True):
+    """``A @ B`` with B's columns split over the ranks, the gather fused into the GEMM epilogue: rank r multiplies A by
+    its column block and every finished tile is stored by TMA into columns ``[lo, hi)`` of ALL ranks' ``out`` buffers
+    (its own through HBM, the peers' over NVLink), so no all-gather runs afterwards — only ``out.fence()``, a 4-byte
+    all-reduce that orders the ranks.  ``a``: [M, K], ``b``: [K, N] CUDA tensors (any strides).  Returns the local
+    ``[M, N]`` tensor of ``out`` (complete once the fence has run on the stream).
+
+    ``gemm_nsplit`` (local GEMM, then one NCCL all-gather and a strided copy) is the baseline this replaces."""
+    import ctypes as C
+
+    from . import _native as N
+
+    m, k = a.shape
+    n = b.shape[1]
+    if (m, n) != (out.m, out.n):
+        raise N.RtgError(3, "output buffer shape does not match the product")
+    lo, hi = column_blocks(n, out.world, align)[out.rank]
+    if hi > lo:
+        bb = b[:, lo:hi]
+        order = [out.rank] + [r for r in range(out.world) if r != out.rank]
+        dst = (C.c_void_p * len(order))(*[out.ptrs[r] for r in order])
+        N.check(N.lib().rtg_gemm_scatter(
+            out.ctx.handle, C.c_void_p(a.data_ptr()), C.c_size_t(m), C.c_size_t(k),
+            C.c_ssize_t(a.stride(0)), C.c_ssize_t(a.stride(1)), C.c_void_p(bb.data_ptr()), C.c_size_t(hi - lo),
+            C.c_ssize_t(bb.stride(0)), C.c_ssize_t(bb.stride(1)), C.c_size_t(lo), C.c_size_t(n), dst,
+            C.c_int32(len(order))))
+    if fence:
+        out.fence()
+    return out.tensor

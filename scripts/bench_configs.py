@@ -45,7 +45,21 @@ def main():
             a, b = torch.rand((n, n), device="cuda"), torch.rand((n, n), device="cuda")
             out = torch.empty((n, n), device="cuda")
             ms = timed(lambda: ops.matmul(a, b, out=out, ctx=ctx), steps=10, flush=flush if n <= 2048 else None)
-            print(f"C1/C5 GEMM {n}^3 {math}: {ms * 1e3:9.1f} us  {2 * n ** 3 / ms / 1e9:8.1f} TFLOP/s")
+            # the reference's bench_gemm rule (src/gemm.rs:1780-1903): iters = min(1000, 512^3 * 1000 / (m n k))
+            # back-to-back calls, GFLOPS = 2 m n k iters / t  (operands stay L2-resident below ~2048, as they stay
+            # cache-resident in the reference's loop)
+            iters = max(1, min(1000, 512 ** 3 * 1000 // n ** 3))
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                ops.matmul(a, b, out=out, ctx=ctx)
+            e1.record()
+            torch.cuda.synchronize()
+            loop_ms = e0.elapsed_time(e1) / iters
+            print(f"C1/C5 GEMM {n}^3 {math}: {ms * 1e3:9.1f} us  {2 * n ** 3 / ms / 1e9:8.1f} TFLOP/s (single call, L2 "
+                  f"flushed) | bench_gemm rule x{iters}: {loop_ms * 1e3:9.1f} us  {2 * n ** 3 / loop_ms / 1e9:8.1f} TFLOP/s  "
+                  f"[{ctx.last_kernel}]")
     for tag, build, shape_in in (("c3", lambda: synth.bert_encoder(batch=64, seq=128), None),
                                  ("c4", lambda: synth.mobilenet_v2(), (64, 3, 224, 224))):
         if tag not in which:

@@ -21,7 +21,7 @@ dist.init_process_group("nccl", init_method="tcp://127.0.0.1:" + sys.argv[2], ra
                         device_id=torch.device("cuda", rank))
 import rten_fork_b200 as R
 from rten_fork_b200 import synth
-from rten_fork_b200.parallel import gemm_nsplit, run_batch_sharded, gather_outputs
+from rten_fork_b200.parallel import gemm_nsplit, gemm_nsplit_fused, SymmetricMatrix, run_batch_sharded, gather_outputs
 import oracle as o, graph_oracle
 ctx = R.default_context(rank)
 ctx.set_math(R.MATH_3XTF32)
@@ -32,6 +32,18 @@ for (m, k, n) in ((200, 300, 1000), (64, 128, 512)):
     out = gemm_nsplit(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()).cpu().numpy()
     want = o.gemm(a, b)
     assert np.all(np.abs(out - want) <= 1e-8 + 1e-5 * np.abs(want)), (m, k, n)
+# the same product with the gather fused into the GEMM epilogue (TMA stores into every rank's buffer over NVLink)
+for (m, k, n) in ((200, 300, 1000), (64, 128, 512), (384, 96, 260)):
+    a, b = rng.fill((m, k)), rng.fill((k, n))
+    sym = SymmetricMatrix(m, n, ctx=ctx)
+    sym.tensor.fill_(float("nan"))
+    dist.barrier()
+    out = gemm_nsplit_fused(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda(), sym)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    want = o.gemm(a, b)
+    assert np.all(np.abs(got - want) <= 1e-8 + 1e-5 * np.abs(want)), ("fused", m, k, n)
+    sym.close()
 bld = synth.resnet50(image=32, width=8, blocks=(1, 1, 1, 1), classes=10, seed=0)
 x = rng.fill((5, 3, 32, 32))
 m = R.Model.load(bld.build(), ctx=ctx)
