@@ -284,12 +284,28 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
                       (reinterpret_cast<uintptr_t>(op) & 15) == 0 && (reinterpret_cast<uintptr_t>(w.wmat) & 15) == 0;
     const int64_t total = static_cast<int64_t>(N) * OH * OW * (vec4 ? C / 4 : C);
     const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 32));
-    if (vec4)
+    const bool k3 = vec4 && p.kh == 3 && p.kw == 3 && p.dil_h == 1 && p.dil_w == 1 && p.stride_h == p.stride_w &&
+                    (p.stride_h == 1 || p.stride_h == 2) && cp_in % 4 == 0;
+    if (k3) {
+      // rows per thread: as many as still leave ~512 threads per SM to hide the load latency
+      constexpr int kTX = 4;
+      const int64_t strips = static_cast<int64_t>(N) * div_ceil(OW, kTX) * (C / 4);
+      int ty = 8;
+      while (ty > 1 && strips * div_ceil(OH, ty) < static_cast<int64_t>(ctx->num_sms) * 768) ty >>= 1;
+      const int64_t threads = strips * div_ceil(OH, ty);
+      const int b3 = static_cast<int>(std::min<int64_t>(div_ceil(threads, 128), static_cast<int64_t>(ctx->num_sms) * 64));
+      if (p.stride_h == 1)
+        depthwise3x3_nhwc_kernel<1, kTX><<<b3, 128, 0, ctx->stream>>>(op, xp, w.wmat, bias, g, ty);
+      else
+        depthwise3x3_nhwc_kernel<2, kTX><<<b3, 128, 0, ctx->stream>>>(op, xp, w.wmat, bias, g, ty);
+    } else if (vec4) {
       depthwise_nhwc_kernel<4><<<blocks, 256, 0, ctx->stream>>>(op, xp, w.wmat, bias, g);
-    else
+    } else {
       depthwise_nhwc_kernel<1><<<blocks, 256, 0, ctx->stream>>>(op, xp, w.wmat, bias, g);
+    }
     ctx->launches++;
-    ctx->last_kernel = vec4 ? "depthwise_nhwc<4>" : "depthwise_nhwc<1>";
+    ctx->last_kernel = k3 ? (p.stride_h == 1 ? "depthwise3x3_nhwc<s1>" : "depthwise3x3_nhwc<s2>")
+                          : vec4 ? "depthwise_nhwc<4>" : "depthwise_nhwc<1>";
     RTG_CUDA(cudaGetLastError());
     if (!out_nhwc) RTG_TRY(from_nhwc(ctx, op, C, C, out, 0));
   } else {

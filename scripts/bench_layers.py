@@ -32,23 +32,59 @@ LAYERS = [
 ]
 
 
+# MobileNetV2 (torchvision widths), batch 64: (name, cin, cout, k, stride, pad, in_hw, residual, groups, act)
+MBV2 = [
+    ("conv1 3x3/2 3->32", 3, 32, 3, 2, 1, 224, False, 1, "clip"),
+    ("dw32 @112", 32, 32, 3, 1, 1, 112, False, 32, "clip"),
+    ("pw 32->16 @112", 32, 16, 1, 1, 0, 112, False, 1, "none"),
+    ("pw 16->96 @112", 16, 96, 1, 1, 0, 112, False, 1, "clip"),
+    ("dw96 /2 @112", 96, 96, 3, 2, 1, 112, False, 96, "clip"),
+    ("pw 96->24 @56", 96, 24, 1, 1, 0, 56, False, 1, "none"),
+    ("pw 24->144 @56", 24, 144, 1, 1, 0, 56, False, 1, "clip"),
+    ("dw144 @56", 144, 144, 3, 1, 1, 56, False, 144, "clip"),
+    ("pw 144->24 @56 +res", 144, 24, 1, 1, 0, 56, True, 1, "none"),
+    ("dw144 /2 @56", 144, 144, 3, 2, 1, 56, False, 144, "clip"),
+    ("pw 144->32 @28", 144, 32, 1, 1, 0, 28, False, 1, "none"),
+    ("pw 32->192 @28", 32, 192, 1, 1, 0, 28, False, 1, "clip"),
+    ("dw192 @28", 192, 192, 3, 1, 1, 28, False, 192, "clip"),
+    ("pw 192->32 @28 +res", 192, 32, 1, 1, 0, 28, True, 1, "none"),
+    ("pw 64->384 @14", 64, 384, 1, 1, 0, 14, False, 1, "clip"),
+    ("dw384 @14", 384, 384, 3, 1, 1, 14, False, 384, "clip"),
+    ("pw 384->64 @14 +res", 384, 64, 1, 1, 0, 14, True, 1, "none"),
+    ("pw 96->576 @14", 96, 576, 1, 1, 0, 14, False, 1, "clip"),
+    ("dw576 @14", 576, 576, 3, 1, 1, 14, False, 576, "clip"),
+    ("pw 576->96 @14 +res", 576, 96, 1, 1, 0, 14, True, 1, "none"),
+    ("pw 160->960 @7", 160, 960, 1, 1, 0, 7, False, 1, "clip"),
+    ("dw960 @7", 960, 960, 3, 1, 1, 7, False, 960, "clip"),
+    ("pw 960->160 @7 +res", 960, 160, 1, 1, 0, 7, True, 1, "none"),
+    ("pw 320->1280 @7", 320, 1280, 1, 1, 0, 7, False, 1, "clip"),
+]
+
+
 def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "3xtf32"
     filt = sys.argv[2] if len(sys.argv) > 2 else ""
+    if "--mbv2" in sys.argv:
+        return run_table(mode, "", MBV2, 64)
+    return run_table(mode, filt, [l + (1, "relu") for l in LAYERS], 32)
+
+
+def run_table(mode, filt, layers, B):
     ctx = R.default_context(0)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_math(R.MATH_3XTF32 if mode == "3xtf32" else R.MATH_TF32)
-    B = 32
     tot = 0.0
-    for name, cin, cout, k, s, p, hw, res in LAYERS:
+    for name, cin, cout, k, s, p, hw, res, groups, act in layers:
         if filt and filt not in name:
             continue
         x = torch.rand((B, cin, hw, hw), device="cuda").contiguous(memory_format=torch.channels_last)
-        w = torch.rand((cout, cin, k, k), device="cuda") - 0.5
+        w = torch.rand((cout, cin // groups, k, k), device="cuda") - 0.5
         b = torch.rand((cout,), device="cuda")
         ohw = (hw + 2 * p - k) // s + 1
         out = torch.empty((B, cout, ohw, ohw), device="cuda").contiguous(memory_format=torch.channels_last)
         r = torch.rand((B, cout, ohw, ohw), device="cuda").contiguous(memory_format=torch.channels_last) if res else None
-        kw = dict(padding=(p, p, p, p), strides=(s, s), residual=r, activation="relu", out=out, ctx=ctx)
+        kw = dict(padding=(p, p, p, p), groups=groups, strides=(s, s), residual=r, activation=act, clip=(0.0, 6.0),
+                  out=out, ctx=ctx)
         for _ in range(3):
             ops.conv(x, w, b, **kw)
         ctx.set_kernel_timing(True)
@@ -57,6 +93,17 @@ def main():
             ops.conv(x, w, b, **kw)
         kt = ctx.kernel_timing()
         ctx.set_kernel_timing(False)
+        if not kt["launches"]:  # not the contraction kernel (depthwise): events around back-to-back calls
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                ops.conv(x, w, b, **kw)
+            e1.record()
+            torch.cuda.synchronize()
+            nbytes = 4.0 * (x.numel() + out.numel() * (2 if res else 1) + w.numel())
+            kt = {"ms": e0.elapsed_time(e1), "launches": n, "flops": 2.0 * out.numel() * (cin // groups) * k * k * n,
+                  "bytes": nbytes * n}
         us = kt["ms"] / kt["launches"] * 1e3
         tot += us
         print(f"{name:24s} {us:8.1f} us  {kt['flops'] / kt['launches'] / us / 1e6:7.1f} TF/s  "
