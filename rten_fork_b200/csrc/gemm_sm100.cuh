@@ -190,6 +190,46 @@ __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& b
   }
 }
 
+// ---------------------------------------------------------------- out-of-line epilogue paths
+// The epilogue is latency-bound and its code used to be ~40 K instructions (every activation, the IEEE division, the
+// strided store paths, each unrolled over 32 columns and inlined per call site); ncu attributed a third of the
+// epilogue warps' stall samples on the short-K layers to instruction fetch (stall_no_inst).  Everything that is not on
+// the path of a fused Conv / MatMul (+bias, +residual, Relu / Clip) into a row-major tensor now lives in these
+// functions, called through a scratch copy so that the chunk itself stays in registers on the hot path.
+__device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
+  for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], alpha);
+}
+__device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi) {
+  for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], act, lo, hi);
+}
+__device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
+  for (int j = 0; j < ncols; ++j) v[j] += beta * r[j * cs];
+}
+__device__ __noinline__ void epi_cold_store(const float* v, float* d, int64_t cs, int ncols) {
+  for (int j = 0; j < ncols; ++j) d[j * cs] = v[j];
+}
+#define RTG_EPI_COLD(call_on_t)                  \
+  do {                                           \
+    float t_[32];                                \
+    _Pragma("unroll") for (int j_ = 0; j_ < 32; ++j_) t_[j_] = v[j_]; \
+    call_on_t;                                   \
+    _Pragma("unroll") for (int j_ = 0; j_ < 32; ++j_) v[j_] = t_[j_]; \
+  } while (0)
+
+// Relu / Clip inline, everything else out of line
+__device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float hi) {
+  if (act == ACT_NONE) return;
+  if (act == ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  } else if (act == ACT_CLIP) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = v[j] < lo ? lo : (v[j] > hi ? hi : v[j]);
+  } else {
+    RTG_EPI_COLD(epi_cold_act(t_, act, lo, hi));
+  }
+}
+
 template <int BN, int MODE, int A_KIND, int B_MAJOR>
 __global__ void __launch_bounds__(GemmCfg<BN, MODE>::kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -561,8 +601,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       auto finish = [&](float (&v)[32], int c0) {
         const int ncols = min(32, args.N - (n0 + c0));
         if (args.flags & kFlagAlphaDiv) {  // fused `MatMul -> Div(scalar)`: IEEE division, as the unfused operator
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], args.alpha);
+          RTG_EPI_COLD(epi_cold_alpha_div(t_, args.alpha));
         } else if (args.alpha != 1.f) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] *= args.alpha;
@@ -595,13 +634,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           } else {
             PROF_WAIT(2, if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>(); __syncwarp());
-            if (args.R != nullptr && row_ok) {  // residual that TMA cannot address (unaligned / NCHW): direct loads
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (j < ncols) v[j] += args.beta * args.R[r_base + static_cast<int64_t>(n0 + c0 + j) * r_cs];
-            }
+            if (args.R != nullptr && row_ok)  // residual that TMA cannot address (unaligned / NCHW): direct loads
+              RTG_EPI_COLD(epi_cold_residual(t_, args.R + r_base + static_cast<int64_t>(n0 + c0) * r_cs, r_cs, args.beta, ncols));
           }
-          apply_act_array(v, args.act, args.act_lo, args.act_hi);
+          epi_act(v, args.act, args.act_lo, args.act_hi);
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4)
             ptx::sts_v4(row + ((j4 ^ sw) << 4), make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]));
@@ -615,21 +651,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (Cfg::kEpiBufs > 1) eb ^= 1;
           return;
         }
+        // outputs TMA cannot address (NCHW for a host caller, unaligned rows): strided stores, out of line
         if (!row_ok) return;
-        if (args.R != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncols) v[j] += args.beta * args.R[r_base + static_cast<int64_t>(n0 + c0 + j) * r_cs];
-        }
-        apply_act_array(v, args.act, args.act_lo, args.act_hi);
-        if (ncols == 32) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncols) args.D[d_base + static_cast<int64_t>(n0 + c0 + j) * d_cs] = v[j];
-        }
+        if (args.R != nullptr)
+          RTG_EPI_COLD(epi_cold_residual(t_, args.R + r_base + static_cast<int64_t>(n0 + c0) * r_cs, r_cs, args.beta, ncols));
+        epi_act(v, args.act, args.act_lo, args.act_hi);
+        RTG_EPI_COLD(epi_cold_store(t_, args.D + d_base + static_cast<int64_t>(n0 + c0) * d_cs, d_cs, ncols));
       };
 
       // chunks of this warp that lie inside the matrix
@@ -687,15 +714,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             aph ^= 1u;
           }
         }
+#pragma unroll 1
+        for (int ci = 0; ci < nch; ++ci) {  // one call site of `finish`: the chunk is selected, not unrolled
+          float v[32];
 #pragma unroll
-        for (int c0 = 0; c0 < kCols; c0 += 32) {
-          if (c0 / 32 < nch) {
-            float v[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = acc[c0 + j];
-            finish(v, col0 + c0);
-            if (staged_r && (c0 / 32) + kAhead < nch) fetch_residual(col0 + c0 + 32 * kAhead, eb ^ kOther, 0);
-          }
+          for (int j = 0; j < 32; ++j) v[j] = (kCols > 32 && ci > 0) ? acc[(32 + j) % kCols] : acc[j];
+          finish(v, col0 + ci * 32);
+          if (staged_r && ci + kAhead < nch) fetch_residual(col0 + (ci + kAhead) * 32, eb ^ kOther, 0);
         }
       }
     }
