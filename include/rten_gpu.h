@@ -61,13 +61,16 @@ typedef struct rtg_tensor {
  * cache of device-resident, pre-arranged weights (the role of prepack_a/prepack_b, src/gemm.rs:337-438). */
 typedef struct rtg_ctx rtg_ctx;
 
-enum { RTG_MATH_TF32 = 0, RTG_MATH_3XTF32 = 1 };
+enum { RTG_MATH_TF32 = 0, RTG_MATH_3XTF32 = 1, RTG_MATH_TF32_BF16X2 = 2 };
 
 rtg_status rtg_ctx_create(int32_t device, rtg_ctx** out);
 rtg_status rtg_ctx_destroy(rtg_ctx* ctx);
 /* Use an externally owned cudaStream_t (e.g. torch's current stream) instead of the context's own. */
 rtg_status rtg_ctx_set_stream(rtg_ctx* ctx, void* cuda_stream);
-/* RTG_MATH_3XTF32 (default): results within rtol 1e-5 of the reference.  RTG_MATH_TF32: rtol 2e-3. */
+/* RTG_MATH_3XTF32 (default): results within rtol 1e-5 of the reference.  RTG_MATH_TF32: rtol 2e-3.
+ * RTG_MATH_TF32_BF16X2: the same split as 3xTF32 (a = hi + lo) with hi*hi on the TF32 pipe and the two correction
+ * products lo(A)*hi(B) + hi(A)*lo(B) as ONE bf16 MMA of doubled depth: 2 tensor-core passes per product instead of 3.
+ * Worst-case error per product 2^-17 (bf16 rounding of the correction operands); also held to rtol 1e-5. */
 rtg_status rtg_ctx_set_math(rtg_ctx* ctx, int32_t mode);
 rtg_status rtg_ctx_get_math(rtg_ctx* ctx, int32_t* mode);
 rtg_status rtg_ctx_sync(rtg_ctx* ctx);

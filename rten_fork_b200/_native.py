@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "librten_gpu_prof.so" if os.environ.get("RTG_PROF
 RTG_HOST = -1
 RTG_F32, RTG_I32 = 0, 1
 RTG_MAX_DIMS = 8
-MATH_TF32, MATH_3XTF32 = 0, 1
+MATH_TF32, MATH_3XTF32, MATH_TF32_BF16X2 = 0, 1, 2
 
 STATUS_NAMES = {
     0: "Ok", 1: "IncorrectInputType", 2: "IncorrectOutputType", 3: "IncompatibleInputShapes", 4: "MissingInputs",

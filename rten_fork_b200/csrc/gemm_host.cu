@@ -60,6 +60,44 @@ rtg_status scale_buffer(Context* ctx, float* p, size_t n, float beta) {
   return RTG_OK;
 }
 
+// ---------------------------------------------------------------- B' (bf16 correction operand)
+__global__ void b_prime_kernel(uint32_t* __restrict__ out, const float* __restrict__ b, int64_t K, int64_t N,
+                               int64_t rs, int64_t cs, int64_t groups /* ceil(K/32)*4 */, int n_fastest) {
+  const int64_t total = N * groups;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    // consecutive threads walk the contiguous dimension of B
+    const int64_t n = n_fastest ? i % N : i / groups, g = n_fastest ? i / N : i % groups;
+    float x[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int64_t k = g * 8 + j;
+      x[j] = k < K ? b[k * rs + n * cs] : 0.f;
+    }
+    auto lo = [](float v) { return v - __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); };
+    uint4 hi4, lo4;
+    hi4.x = ptx::pack_bf16x2(x[0], x[1]), hi4.y = ptx::pack_bf16x2(x[2], x[3]);
+    hi4.z = ptx::pack_bf16x2(x[4], x[5]), hi4.w = ptx::pack_bf16x2(x[6], x[7]);
+    lo4.x = ptx::pack_bf16x2(lo(x[0]), lo(x[1])), lo4.y = ptx::pack_bf16x2(lo(x[2]), lo(x[3]));
+    lo4.z = ptx::pack_bf16x2(lo(x[4]), lo(x[5])), lo4.w = ptx::pack_bf16x2(lo(x[6]), lo(x[7]));
+    uint4* o = reinterpret_cast<uint4*>(out + (n * groups + g) * 8);
+    o[0] = hi4;
+    o[1] = lo4;
+  }
+}
+
+rtg_status make_b_prime(Context* ctx, MatView b, uint32_t* out) {
+  const int64_t K = b.rows, N = b.cols;
+  if (K == 0 || N == 0) return RTG_OK;
+  const int64_t groups = div_ceil(K, kBK) * 4;
+  const int64_t total = N * groups;
+  const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+  b_prime_kernel<<<blocks, 256, 0, ctx->stream>>>(out, b.p, K, N, b.rs, b.cs, groups, b.cs == 1 && b.rs != 1 ? 1 : 0);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
 // ---------------------------------------------------------------- tensor maps
 static rtg_status encode_2d(Context* ctx, CUtensorMap* map, const float* base, uint64_t inner, uint64_t outer,
                             uint64_t outer_stride_elems, uint32_t box_inner, uint32_t box_outer,
@@ -94,6 +132,19 @@ static rtg_status encode_out_3d(Context* ctx, CUtensorMap* map, const float* bas
                       (int)r, base, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)planes,
                       (unsigned long long)ld);
   return RTG_OK;
+}
+
+// B' (make_b_prime) for a launch: the caller's precomputed copy, or a pre-pass into pool scratch.  Map: [N][Kw] words,
+// box 32 x BN, 128B swizzle (a K-major tile like any other).
+static rtg_status b_prime_map(Context* ctx, const Epilogue& ep, MatView b, int bn, Scratch* tmp, CUtensorMap* map) {
+  const int64_t kw = div_ceil(b.rows, kBK) * kBK;
+  const uint32_t* bp = ep.b_prime;
+  if (!bp) {
+    RTG_TRY(tmp->alloc(ctx, static_cast<size_t>(b.cols) * kw * 4));
+    RTG_TRY(make_b_prime(ctx, b, static_cast<uint32_t*>(tmp->p)));
+    bp = static_cast<const uint32_t*>(tmp->p);
+  }
+  return encode_2d(ctx, map, reinterpret_cast<const float*>(bp), kw, b.cols, kw, kBK, bn);
 }
 
 // Can TMA address this operand in place?  The contiguous dimension must have stride 1, the base must be 16-byte
@@ -189,7 +240,10 @@ rtg_status launch_reduce(Context* ctx, const ReduceArgs& ra) {
 
 template <int A_KIND, int B_MAJOR>
 static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           GemmArgs args, int plane_rows = 0, int64_t num_planes = 0, const Epilogue* peers = nullptr) {
+                           GemmArgs args, int plane_rows = 0, int64_t num_planes = 0, const Epilogue* peers = nullptr,
+                           const CUtensorMap* mb2p = nullptr) {
+  if (mode == RTG_MATH_TF32_BF16X2 && (!mb2p || A_KIND == 3)) mode = RTG_MATH_3XTF32;  // no B' for this launch
+  const CUtensorMap& mb2 = mb2p ? *mb2p : mb;
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;
   Scratch ws, peer_maps;
@@ -266,7 +320,7 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
   }
   if (n_peers > 0 && args.n_peers == 0)
     return set_error(RTG_ERR_UNSUPPORTED_VALUE, "peer stores need a row-major, 16-byte aligned output");
-  return launch_variants<A_KIND, B_MAJOR>(ctx, bn, mode, ma, mb, md, mr, args, redp);
+  return launch_variants<A_KIND, B_MAJOR>(ctx, bn, mode, ma, mb, mb2, md, mr, args, redp);
 }
 
 // Largest tile that still fills the machine; smaller tiles when the problem has too few of them.  With `splits` the
@@ -380,8 +434,12 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
-  if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep);
-  return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep);
+  Scratch bp_tmp;
+  CUtensorMap mb2;
+  const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
+  if (m2) RTG_TRY(b_prime_map(ctx, ep, b, bn, &bp_tmp, &mb2));
+  if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep, m2 ? &mb2 : nullptr);
+  return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep, m2 ? &mb2 : nullptr);
 }
 
 // ---------------------------------------------------------------- batched GEMM (one launch for all batch entries)
@@ -558,7 +616,11 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   ctx->pending_flops = 2.0 * M * og * k_true;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.n) * g.h * g.w * g.cg + og * k_true +
                               static_cast<double>(M) * og * (a.R ? 2 : 1));
-  return dispatch<1, 0>(ctx, bn, ctx->math, ma, mb, a);
+  Scratch bp_tmp;
+  CUtensorMap mb2;
+  const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
+  if (m2) RTG_TRY(b_prime_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
+  return dispatch<1, 0>(ctx, bn, ctx->math, ma, mb, a, 0, 0, nullptr, m2 ? &mb2 : nullptr);
 }
 
 // ---------------------------------------------------------------- row-window convolution
@@ -612,7 +674,11 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
   ctx->pending_flops = 2.0 * M * og * k_true;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.n) * g.hp * g.wp * g.cp + og * k_true +
                               static_cast<double>(M) * og * (a.R ? 2 : 1));
-  return dispatch<2, 0>(ctx, bn, ctx->math, ma, mb, a, g.ow);
+  Scratch bp_tmp;
+  CUtensorMap mb2;
+  const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
+  if (m2) RTG_TRY(b_prime_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
+  return dispatch<2, 0>(ctx, bn, ctx->math, ma, mb, a, g.ow, 0, nullptr, m2 ? &mb2 : nullptr);
 }
 
 }  // namespace rtg

@@ -21,6 +21,9 @@ struct Epilogue {
   float act_lo = 0.f, act_hi = 0.f;
   // peer copies of the output (other GPUs' buffers mapped into this process, same layout as D): every tile is stored
   // to D and to each of them.  Needs a row-major, 16-byte aligned D (the TMA-store epilogue).
+  // RTG_MATH_TF32_BF16X2: the bf16 correction operand B' of a constant B, [N][ceil(K/32)*32] words written by
+  // make_b_prime at load time; NULL = computed by a pre-pass of this call
+  const uint32_t* b_prime = nullptr;
   int n_peers = 0;
   float* peer_D[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
@@ -28,6 +31,10 @@ struct Epilogue {
 // D = epilogue(A[M,K] . B[K,N]).  A and B may have any strides; operands that TMA cannot address directly (neither
 // dimension contiguous, unaligned base or pitch) are first gathered into pool scratch by a copy kernel.
 rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap, const Epilogue& ep);
+
+// B' for RTG_MATH_TF32_BF16X2: out[n][kb*32 + 8g + i] (i < 4) = bf16 pair of B[32kb + 8g + 2i, +1][n], out[..+4+i] the
+// same of lo(B) = B - trunc_tf32(B); zero beyond K.  `out` has N * ceil(K/32)*32 words.
+rtg_status make_b_prime(Context* ctx, MatView b, uint32_t* out);
 
 // Batched product in ONE launch: batch index z = z1 * n0 + z0, entry z of A at a.p + z0*a.bs0 + z1*a.bs1 (a stride of
 // 0 broadcasts the operand along that batch dimension), D contiguous [n1*n0][M][N].  The operands must be addressable
@@ -50,7 +57,7 @@ struct ConvGeom {
 };
 // wmat: [Og][kh*kw*c_blocks*32] K-major weight matrix for this group (zero padded per tap), Og output channels.
 rtg_status conv_gemm_device(Context* ctx, const float* x_nhwc, const ConvGeom& g, const float* wmat, int og,
-                            float* D, OutMap dmap, const Epilogue& ep);
+                            float* D, OutMap dmap, const Epilogue& ep);  // ep.b_prime: B' of wmat (or NULL)
 bool conv_im2col_supported(const ConvGeom& g);
 
 // Row-window convolution (few input channels): x_pad is the zero-padded [n][hp][wp][cp] image written by

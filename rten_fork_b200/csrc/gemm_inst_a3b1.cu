@@ -4,6 +4,6 @@
 
 namespace rtg {
 template rtg_status launch_variants<3, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&,
-                                            const CUtensorMap&, const CUtensorMap&, const GemmArgs&,
-                                            const ReduceArgs*);
+                                            const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                            const GemmArgs&, const ReduceArgs*);
 }  // namespace rtg

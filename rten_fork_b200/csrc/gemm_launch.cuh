@@ -31,13 +31,15 @@ rtg_status launch_reduce(Context* ctx, const ReduceArgs& ra);
 
 template <int A_KIND, int B_MAJOR>
 rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args, const ReduceArgs* red);
+                           const CUtensorMap& mb2, const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args,
+                           const ReduceArgs* red);
 
 #ifdef RTG_GEMM_INSTANTIATE
 // ---------------------------------------------------------------- launch
 template <int BN, int MODE, int A_KIND, int B_MAJOR>
-static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
-                         const CUtensorMap& mr, const GemmArgs& args, const ReduceArgs* red = nullptr) {
+static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2,
+                         const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args,
+                         const ReduceArgs* red = nullptr) {
   using Cfg = GemmCfg<BN, MODE>;
   auto kern = gemm_tcgen05_kernel<BN, MODE, A_KIND, B_MAJOR>;
   static bool configured[16] = {};  // per device
@@ -86,7 +88,7 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    RTG_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, md, mr, args));
+    RTG_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mb2, md, mr, args));
   }
   ctx->launches++;
   RTG_CUDA(cudaGetLastError());
@@ -139,7 +141,7 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
   char name[96];
   char sk[24] = "";
   if (args.splits > 1) snprintf(sk, sizeof(sk), ",splitK=%d", args.splits);
-  snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s%s>", BN, MODE ? "3xTF32" : "TF32",
+  snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s%s>", BN, MODE == 2 ? "TF32+BF16x2" : MODE ? "3xTF32" : "TF32",
            A_KIND == 3 ? "batched" : A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K", sk);
   ctx->last_kernel = name;
   return RTG_OK;
@@ -148,24 +150,28 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
 
 template <int A_KIND, int B_MAJOR>
 rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma, const CUtensorMap& mb,
-                           const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args, const ReduceArgs* redp) {
+                           const CUtensorMap& mb2, const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args,
+                           const ReduceArgs* redp) {
   if (mode == RTG_MATH_TF32) {
-    if (bn == 64) return launch<64, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args, redp);
-    if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args, redp);
-    if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args, redp);
+    if (bn == 64) return launch<64, 0, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+    if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+    if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+  } else if (mode == RTG_MATH_TF32_BF16X2 && A_KIND != 3) {  // batched products keep the three-MMA split
+    if (bn == 64) return launch<64, 2, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+    if (bn == 128) return launch<128, 2, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
   } else {
-    if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args, redp);
-    if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, md, mr, args, redp);
+    if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+    if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
   }
   return set_error(RTG_ERR_INTERNAL, "bad BN");
 }
 #else
-extern template rtg_status launch_variants<0, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
-extern template rtg_status launch_variants<0, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
-extern template rtg_status launch_variants<1, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
-extern template rtg_status launch_variants<2, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
-extern template rtg_status launch_variants<3, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
-extern template rtg_status launch_variants<3, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<0, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<0, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<1, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<2, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<3, 0>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
+extern template rtg_status launch_variants<3, 1>(Context*, int, int, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const GemmArgs&, const ReduceArgs*);
 #endif
 
 }  // namespace rtg

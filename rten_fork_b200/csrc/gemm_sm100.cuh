@@ -158,7 +158,7 @@ struct GemmCfg {
   // finished, and the TMA store of chunk i may still read its buffer while chunk i+1 is written.  With one buffer the
   // short-K layers (ResNet layer1/2 pointwise convs, K = 64..128) were bound by this chain, not by HBM.
   // 3xTF32 keeps one buffer: the pipeline stage the extra 32 KB would cost is worth more there.
-  static constexpr int kEpiBufs = MODE == 1 ? 1 : 2;
+  static constexpr int kEpiBufs = MODE != 0 ? 1 : 2;
   static constexpr int kEpiBufBytes = 4096;
   // Column bias of the whole launch (zero padded to n_tiles * BN entries), loaded once per CTA; launches with more
   // output columns than this fall back to a per-tile slice per warp at the start of the same region.
@@ -196,16 +196,16 @@ __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& b
 // epilogue warps' stall samples on the short-K layers to instruction fetch (stall_no_inst).  Everything that is not on
 // the path of a fused Conv / MatMul (+bias, +residual, Relu / Clip) into a row-major tensor now lives in these
 // functions, called through a scratch copy so that the chunk itself stays in registers on the hot path.
-__device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
+static __device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
   for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], alpha);
 }
-__device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi) {
+static __device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi) {
   for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], act, lo, hi);
 }
-__device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
+static __device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
   for (int j = 0; j < ncols; ++j) v[j] += beta * r[j * cs];
 }
-__device__ __noinline__ void epi_cold_store(const float* v, float* d, int64_t cs, int ncols) {
+static __device__ __noinline__ void epi_cold_store(const float* v, float* d, int64_t cs, int ncols) {
   for (int j = 0; j < ncols; ++j) d[j * cs] = v[j];
 }
 #define RTG_EPI_COLD(call_on_t)                  \
@@ -233,8 +233,8 @@ __device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float
 template <int BN, int MODE, int A_KIND, int B_MAJOR>
 __global__ void __launch_bounds__(GemmCfg<BN, MODE>::kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
-                    const GemmArgs args) {
+                    const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ CUtensorMap tmD,
+                    const __grid_constant__ CUtensorMap tmR, const GemmArgs args) {
   using Cfg = GemmCfg<BN, MODE>;
 #ifdef RTG_PROF
   const long long prof_entry_ = clock64();
@@ -245,7 +245,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 #endif
   constexpr int kStages = Cfg::kStages;
-  constexpr bool kChunked = MODE == 1;
+  constexpr bool kChunked = MODE != 0;
   constexpr int kTmaWarp = Cfg::kEpiWarps, kMmaWarp = Cfg::kEpiWarps + 1;
   extern __shared__ uint8_t smem_raw[];
   // 128B swizzle atoms need 1024-byte aligned tiles.
@@ -284,6 +284,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == kTmaWarp && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (MODE == 2) ptx::prefetch_tmap(&tmB2);
     if (args.flags & kFlagStagedD) ptx::prefetch_tmap(&tmD);
     if (args.flags & kFlagStagedR) ptx::prefetch_tmap(&tmR);
   }
@@ -291,7 +292,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
-      ptx::mbar_init(xf_bar(s), Cfg::kXfThreads / 32 > 0 ? Cfg::kXfThreads / 32 : 1);  // one arrival per split warp
+      // one arrival per split warp (MODE 2: the four A warps only; its B' tile arrives by TMA)
+      ptx::mbar_init(xf_bar(s), MODE == 2 ? 4 : Cfg::kXfThreads / 32 > 0 ? Cfg::kXfThreads / 32 : 1);
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
@@ -328,7 +330,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == kTmaWarp) {
     // ===================================================== TMA producer
-    if (MODE == 1) ptx::reg_dealloc<kRegsOther>();
+    if (MODE != 0) ptx::reg_dealloc<kRegsOther>();
     if (lane == 0) {
       PROF_DECL;
       int s = 0;
@@ -375,7 +377,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           uint32_t a_dst, b_dst, fa;
           const uint32_t fb = full_bar(s);
-          if (MODE == 1) {
+          if (MODE != 0) {
             PROF_WAIT(0, ptx::mbar_wait(aempty_bar(ia), pa ^ 1u));
             a_dst = smem_base + ia * kABytes;
             fa = afull_bar(ia);
@@ -390,7 +392,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const long long ti_ = clock64();
 #endif
           PROF_MARK(0, 5);  // first TMA issue
-          ptx::mbar_expect_tx(fa, MODE == 1 ? kABytes : Cfg::kRawBytes);
+          ptx::mbar_expect_tx(fa, MODE != 0 ? kABytes : Cfg::kRawBytes);
           if (A_KIND == 0) {
             ptx::tma_load_2d(a_dst, &tmA, fa, kb * kBK, m0);
           } else if (A_KIND == 3) {
@@ -409,13 +411,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             }
           }
-          if (MODE == 1) {  // the B slot (and its TMEM slot) is free once the MMAs of its previous use have completed
+          if (MODE != 0) {  // the B slot (and its TMEM slot) is free once the MMAs of its previous use have completed
             if (++ia == kAStages) {
               ia = 0;
               pa ^= 1u;
             }
             PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
-            ptx::mbar_expect_tx(fb, Cfg::kBBytes);
+            ptx::mbar_expect_tx(fb, MODE == 2 ? 2 * Cfg::kBBytes : Cfg::kBBytes);
+            // MODE 2: the bf16 correction tile B' = [bf16(B) 8 | bf16(lo(B)) 8] per group of 8 k was written to global
+            // memory once (weights: at load; otherwise by a pre-pass), K-major whatever B's own layout
+            if (MODE == 2) ptx::tma_load_2d(b_dst + Cfg::kBBytes, &tmB2, fb, kb * kBK, n0);
           }
           if (A_KIND == 3) {
             const int bz0 = z0 * args.ic.bat_b0, bz1 = z1 * args.ic.bat_b1;
@@ -446,7 +451,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp == kMmaWarp) {
     // ===================================================== MMA issuer
-    if (MODE == 1) ptx::reg_dealloc<kRegsOther>();
+    if (MODE != 0) ptx::reg_dealloc<kRegsOther>();
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::make_idesc_tf32(kBM, BN, 0, B_MAJOR);
       // K-major operands: 128B swizzle, 8-row groups 1024 B apart.  MN-major fp32 operands must use the
@@ -457,6 +462,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // descriptor words of stage 0; a stage / k-step only moves the 14-bit "address >> 4" field of the low word
       const uint64_t a_d0 = ptx::make_smem_desc(ring_base, 16, 1024);  // MODE 0 only (MODE 1 reads A from TMEM)
       const uint64_t b_d0 = ptx::make_smem_desc(ring_base + (MODE ? 0 : kABytes), b_lbo, b_sbo, b_layout);
+      // MODE 2: the bf16 correction tile B' is always K-major (written by the split warps), whatever B's own layout
+      constexpr uint32_t idesc_c = ptx::make_idesc_bf16(kBM, BN);
+      const uint64_t bc_d0 = ptx::make_smem_desc(ring_base, 16, 1024);
+      const uint32_t bc_hi = static_cast<uint32_t>(bc_d0 >> 32), bc_lo0 = static_cast<uint32_t>(bc_d0);
       const uint32_t a_hi = static_cast<uint32_t>(a_d0 >> 32), b_hi = static_cast<uint32_t>(b_d0 >> 32);
       const uint32_t a_lo0 = static_cast<uint32_t>(a_d0), b_lo0 = static_cast<uint32_t>(b_d0);
       constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4;
@@ -478,6 +487,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int kb1 = min(kb_end, kb0 + chunk_kb);
           for (int kb = kb0; kb < kb1; ++kb) {
             PROF_WAIT(1, ptx::mbar_wait(MODE ? xf_bar(s) : full_bar(s), ph));
+            if (MODE == 2) PROF_WAIT(1, ptx::mbar_wait(full_bar(s), ph));  // B and B' have landed
             ptx::tc_fence_after();
 #ifdef RTG_PROF
             const long long ti_ = clock64();
@@ -489,11 +499,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
               if (MODE == 0) {
                 ptx::mma_tf32_ss_w(d_tmem, a_lo + k * kAStep, a_hi, b_lo + k * kBStep, b_hi, idesc, acc);
-              } else {
+              } else if (MODE == 1) {
                 // lo(A) * B, A * lo(B), A * B: smallest terms first.  A planes: TMEM columns [0,32) hi, [32,64) lo
                 const uint32_t a_t = tmem_base + 2 * BN + s * Cfg::kTmemAStageCols + k * 8;
                 ptx::mma_tf32_ts_w(d_tmem, a_t + kBK, b_lo + k * kBStep, b_hi, idesc, acc);
                 ptx::mma_tf32_ts_w(d_tmem, a_t, b_lo + kBLoStep + k * kBStep, b_hi, idesc, 1);
+                ptx::mma_tf32_ts_w(d_tmem, a_t, b_lo + k * kBStep, b_hi, idesc, 1);
+              } else {
+                // MODE 2: both correction products in one bf16 MMA of depth 16 = [lo(A) 8 | hi(A) 8] x [hi(B) 8 ; lo(B) 8]
+                // (A' in TMEM columns [32,64) of the stage, B' K-major behind the raw B tile), then A * B in TF32
+                const uint32_t a_t = tmem_base + 2 * BN + s * Cfg::kTmemAStageCols + k * 8;
+                ptx::mma_f16_ts_w(d_tmem, a_t + kBK, bc_lo0 + so + kBLoStep + k * 2, bc_hi, idesc_c, acc);
                 ptx::mma_tf32_ts_w(d_tmem, a_t, b_lo + k * kBStep, b_hi, idesc, 1);
               }
             }
@@ -520,7 +536,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp < Cfg::kEpiWarps) {
     // ===================================================== epilogue
-    if (MODE == 1) ptx::reg_alloc<kRegsEpi>();
+    if (MODE != 0) ptx::reg_alloc<kRegsEpi>();
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     constexpr int kCols = Cfg::kColsPerThread;
     const int col0 = (warp >> 2) * kCols;  // first tile column this warp handles
@@ -729,7 +745,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
     }
-  } else if (MODE == 1 && warp > kMmaWarp) {
+  } else if (MODE != 0 && warp > kMmaWarp) {
     // ===================================================== 3xTF32 operand split
     // x = hi + lo with hi = x truncated to TF32 (the tensor core reads that from the raw fp32 bits by itself) and
     // lo = x - hi (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
@@ -738,6 +754,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     ptx::reg_dealloc<kRegsOther>();
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
     const int sw = t >> 5;
+    if (MODE == 1 || sw < 4) {  // MODE 2 has no B split: warps 4-5 of this role idle
     auto lo_of = [](float x) {
       return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u)) + 0x1000u;
     };
@@ -775,6 +792,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // the TMEM slot of this stage is free once the MMAs of its previous use have completed
           PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
           ptx::tc_fence_after();
+          if (MODE == 2) {
+            // A': per group of 8 k, four words of bf16 pairs of lo(A) and four of bf16(A)
+            uint32_t ap[32];
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int k0 = 8 * g + 2 * i;
+                const float x0 = __uint_as_float(hi[k0]), x1 = __uint_as_float(hi[k0 + 1]);
+                ap[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(hi[k0] & 0xFFFFE000u),
+                                                 x1 - __uint_as_float(hi[k0 + 1] & 0xFFFFE000u));
+                ap[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) lo[j] = ap[j];
+          }
           const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
           ptx::tmem_st_32x32(dst, hi);
           ptx::tmem_st_32x32(dst + kBK, lo);
@@ -801,6 +835,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
     if (t == 0) PROF_DUMP(3);
+    }
   }
 
   ptx::tc_fence_before();

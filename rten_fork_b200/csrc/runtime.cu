@@ -156,7 +156,7 @@ rtg_status rtg_ctx_set_stream(rtg_ctx* ctx, void* cuda_stream) {
 rtg_status rtg_ctx_set_math(rtg_ctx* ctx, int32_t mode) {
   Context* c = reinterpret_cast<Context*>(ctx);
   if (!c) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
-  if (mode != RTG_MATH_TF32 && mode != RTG_MATH_3XTF32) return set_error(RTG_ERR_INVALID_VALUE, "unknown math mode");
+  if (mode != RTG_MATH_TF32 && mode != RTG_MATH_3XTF32 && mode != RTG_MATH_TF32_BF16X2) return set_error(RTG_ERR_INVALID_VALUE, "unknown math mode");
   c->math = mode;
   return RTG_OK;
 }

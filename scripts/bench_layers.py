@@ -72,7 +72,7 @@ def main():
 def run_table(mode, filt, layers, B):
     ctx = R.default_context(0)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-    ctx.set_math(R.MATH_3XTF32 if mode == "3xtf32" else R.MATH_TF32)
+    ctx.set_math({"3xtf32": R.MATH_3XTF32, "tf32": R.MATH_TF32, "tf32_bf16x2": R.MATH_TF32_BF16X2}[mode])
     tot = 0.0
     for name, cin, cout, k, s, p, hw, res, groups, act in layers:
         if filt and filt not in name:
