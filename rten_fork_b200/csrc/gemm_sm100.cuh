@@ -754,67 +754,85 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     ptx::reg_dealloc<kRegsOther>();
     const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
     const int sw = t >> 5;
-    if (MODE == 1 || sw < 4) {  // MODE 2 has no B split: warps 4-5 of this role idle
     auto lo_of = [](float x) {
       return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u)) + 0x1000u;
     };
     int s = 0;
     uint32_t ph = 0;
-    int ia = 0;
-    uint32_t pa = 0;
     PROF_DECL;
-    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-      const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        const uint32_t stage = ring_base + s * Cfg::kStageBytes;  // [B raw][B lo]
-        if (sw < 4) {
-          PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
-          const int q = warp & 3;  // TMEM lane quarter this warp may write
-          const int row = q * 32 + lane;
-          const uint32_t src = smem_base + ia * kABytes + row * 128;
-          const uint32_t swz = row & 7;
-          uint32_t hi[32], lo[32];
+    if (sw < 4) {
+      // ---- A rows.  Nothing here depends on which tile a k-block belongs to, so the warp walks the CTA's k-blocks as
+      // one flat stream, software-pipelined: the tensor-memory stores of block i are in flight while block i + 1 is
+      // read from shared memory and split, and only then does the warp wait for them and release block i to the MMAs.
+      int total = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int kb_begin = (unit / num_tiles) * kb_per_split;
+        total += min(num_kb, kb_begin + kb_per_split) - kb_begin;
+      }
+      int ia = 0;
+      uint32_t pa = 0;
+      const int q = warp & 3;  // TMEM lane quarter this warp may write
+      const int row = q * 32 + lane;
+      const uint32_t swz = row & 7;
+      uint32_t hi[32], lo[32];
+      auto load_block = [&]() {
+        PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
+        const uint32_t src = smem_base + ia * kABytes + row * 128;
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 x = ptx::lds_v4(src + ((j4 ^ swz) << 4));
-            hi[4 * j4 + 0] = __float_as_uint(x.x), lo[4 * j4 + 0] = lo_of(x.x);
-            hi[4 * j4 + 1] = __float_as_uint(x.y), lo[4 * j4 + 1] = lo_of(x.y);
-            hi[4 * j4 + 2] = __float_as_uint(x.z), lo[4 * j4 + 2] = lo_of(x.z);
-            hi[4 * j4 + 3] = __float_as_uint(x.w), lo[4 * j4 + 3] = lo_of(x.w);
-          }
-          // the raw tile is in registers: hand its slot back to the TMA producer
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
-          if (++ia == kAStages) {
-            ia = 0;
-            pa ^= 1u;
-          }
-          // the TMEM slot of this stage is free once the MMAs of its previous use have completed
-          PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
-          ptx::tc_fence_after();
-          if (MODE == 2) {
-            // A': per group of 8 k, four words of bf16 pairs of lo(A) and four of bf16(A)
-            uint32_t ap[32];
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 x = ptx::lds_v4(src + ((j4 ^ swz) << 4));
+          hi[4 * j4 + 0] = __float_as_uint(x.x), hi[4 * j4 + 1] = __float_as_uint(x.y);
+          hi[4 * j4 + 2] = __float_as_uint(x.z), hi[4 * j4 + 3] = __float_as_uint(x.w);
+        }
+        // the raw tile is in registers: hand its slot back to the TMA producer
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
+        if (++ia == kAStages) {
+          ia = 0;
+          pa ^= 1u;
+        }
+        if (MODE == 2) {
+          // A': per group of 8 k, four words of bf16 pairs of lo(A) and four of bf16(A)
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+          for (int g = 0; g < 4; ++g) {
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const int k0 = 8 * g + 2 * i;
-                const float x0 = __uint_as_float(hi[k0]), x1 = __uint_as_float(hi[k0 + 1]);
-                ap[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(hi[k0] & 0xFFFFE000u),
-                                                 x1 - __uint_as_float(hi[k0 + 1] & 0xFFFFE000u));
-                ap[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
-              }
+            for (int i = 0; i < 4; ++i) {
+              const int k0 = 8 * g + 2 * i;
+              const float x0 = __uint_as_float(hi[k0]), x1 = __uint_as_float(hi[k0 + 1]);
+              lo[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(hi[k0] & 0xFFFFE000u),
+                                               x1 - __uint_as_float(hi[k0 + 1] & 0xFFFFE000u));
+              lo[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
             }
-#pragma unroll
-            for (int j = 0; j < 32; ++j) lo[j] = ap[j];
           }
-          const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
-          ptx::tmem_st_32x32(dst, hi);
-          ptx::tmem_st_32x32(dst + kBK, lo);
-          ptx::tmem_st_wait();
-          ptx::tc_fence_before();
         } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) lo[j] = lo_of(__uint_as_float(hi[j]));
+        }
+      };
+      if (total > 0) load_block();
+      for (int it = 0; it < total; ++it) {
+        // the TMEM slot of this stage is free once the MMAs of its previous use have completed
+        PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
+        ptx::tc_fence_after();
+        const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
+        ptx::tmem_st_32x32(dst, hi);
+        ptx::tmem_st_32x32(dst + kBK, lo);
+        if (it + 1 < total) load_block();
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(xf_bar(s));
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
+    } else if (MODE == 1) {
+      // ---- B lo plane (MODE 2 has no B split: its B' tile arrives by TMA and these two warps idle)
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          const uint32_t stage = ring_base + s * Cfg::kStageBytes;  // [B raw][B lo]
           PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
           constexpr int kBVecs = Cfg::kBBytes / 16;
           const uint32_t braw = stage, blo = braw + Cfg::kBBytes;
@@ -825,17 +843,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                                   __uint_as_float(lo_of(x.z)), __uint_as_float(lo_of(x.w))));
           }
           ptx::fence_proxy_async_smem();
-        }
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(xf_bar(s));
-        if (++s == kStages) {
-          s = 0;
-          ph ^= 1u;
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(xf_bar(s));
+          if (++s == kStages) {
+            s = 0;
+            ph ^= 1u;
+          }
         }
       }
     }
     if (t == 0) PROF_DUMP(3);
-    }
   }
 
   ptx::tc_fence_before();

@@ -38,7 +38,7 @@ def main():
     which = args or ["c1", "c3", "c4"]
     ctx = R.default_context(0)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-    ctx.set_math(R.MATH_3XTF32 if math == "3xtf32" else R.MATH_TF32)
+    ctx.set_math({"3xtf32": R.MATH_3XTF32, "tf32": R.MATH_TF32, "tf32_bf16x2": R.MATH_TF32_BF16X2}[math])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     if "c1" in which:
         for n in (512, 1024, 2048, 4096, 8192):

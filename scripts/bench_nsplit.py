@@ -38,7 +38,7 @@ def main():
     sizes = [int(x) for x in argv] or [2048, 4096, 8192, 16384]
     ctx = R.default_context(local_rank)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-    ctx.set_math(R.MATH_3XTF32 if math == "3xtf32" else R.MATH_TF32)
+    ctx.set_math({"3xtf32": R.MATH_3XTF32, "tf32": R.MATH_TF32, "tf32_bf16x2": R.MATH_TF32_BF16X2}[math])
 
     def timed(fn, iters):
         for _ in range(3):

@@ -37,7 +37,7 @@ def test_small_conv_model_formats(rtg, ctx, oracle, version, optimize):
     b.outputs = [y]
     m, got, want = _run_both(ctx, b, [rng.fill((2, 4, 9, 9))], optimize, version)
     assert got[0].shape == (2, 8, 4, 4)
-    expect_equal(got[0], want[0], rtol=1e-5 if ctx.math == rtg.MATH_3XTF32 else 2e-3, atol=1e-5)
+    expect_equal(got[0], want[0], rtol=2e-3 if ctx.math == rtg.MATH_TF32 else 1e-5, atol=1e-5)
     assert m.inputs[0]["name"] == "input" and m.inputs[0]["shape"] == [None, 4, 9, 9]
     assert m.num_ops == (2 if optimize else 3)  # Conv+Relu fused by the optimiser
 
