@@ -31,10 +31,13 @@ def timed(fn, steps=10, warmup=3, flush=None):
 
 
 def main():
-    args = [a for a in sys.argv[1:] if not a.startswith("--")]
-    math = "3xtf32"
-    if "--math" in sys.argv:
-        math = sys.argv[sys.argv.index("--math") + 1]
+    argv = sys.argv[1:]
+    math = "tf32_bf16x2"
+    if "--math" in argv:
+        i = argv.index("--math")
+        math = argv[i + 1]
+        del argv[i:i + 2]
+    args = [a for a in argv if not a.startswith("--")]
     which = args or ["c1", "c3", "c4"]
     ctx = R.default_context(0)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
