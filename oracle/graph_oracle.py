@@ -89,6 +89,21 @@ def run_graph(builder, inputs, outputs=None):
             y = ins[0]
             for ax in sorted(int(v) for v in ins[1]):
                 y = np.expand_dims(y, ax)
+        elif t == "Concat":  # src/ops/concat.rs
+            y = np.concatenate([x for x in ins], axis=a.get(0, 0))
+        elif t == "Slice":  # src/ops/slice.rs: NumPy slicing semantics (clamped endpoints, negative steps)
+            x = ins[0]
+            starts, ends = [int(v) for v in ins[1]], [int(v) for v in ins[2]]
+            axes = [int(v) for v in ins[3]] if len(ins) > 3 and ins[3] is not None else list(range(len(starts)))
+            steps = [int(v) for v in ins[4]] if len(ins) > 4 and ins[4] is not None else [1] * len(starts)
+            sl = [slice(None)] * x.ndim
+            for st, en, ax, sp in zip(starts, ends, axes, steps):
+                sl[ax] = slice(st, en, sp)
+            y = np.ascontiguousarray(x[tuple(sl)])
+        elif t == "Shape":
+            y = np.array(ins[0].shape, dtype=np.int32)
+        elif t == "Expand":
+            y = np.ascontiguousarray(np.broadcast_to(ins[0], np.broadcast_shapes(ins[0].shape, tuple(int(v) for v in ins[1]))))
         elif t == "Identity":
             y = ins[0].copy()
         else:

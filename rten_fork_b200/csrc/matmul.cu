@@ -42,7 +42,8 @@ rtg_status matmul_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& b
   Epilogue ep;
   if (fused) ep = *fused;
   if (K == 0) {
-    if (fused) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "fused epilogue with K == 0");
+    if (fused && (fused->bias || fused->act != ACT_NONE || fused->alpha != 1.f))
+      return set_error(RTG_ERR_UNSUPPORTED_VALUE, "fused epilogue with K == 0");
     RTG_CUDA(cudaMemsetAsync(D, 0, static_cast<size_t>(total) * 4, ctx->stream));
     return RTG_OK;
   }

@@ -366,6 +366,26 @@ rtg_status GemmOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
   return RTG_OK;
 }
 
+rtg_status MatMulOp::prepare(Context* ctx, const OpInputs& consts) {
+  release(ctx);
+  const Value* b = consts.get(1);
+  if (!b || has_perm[1] || b->t.ndim != 2 || b->t.dtype != RTG_F32 || b->t.device == RTG_HOST) return RTG_OK;
+  const int64_t K = b->t.shape[0], N = b->t.shape[1];
+  if (K == 0 || N == 0 || b->t.strides[0] < 0 || b->t.strides[1] < 0) return RTG_OK;
+  void* d = nullptr;
+  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(N) * div_ceil(K, kBK) * kBK * 4, &d));
+  b_prime = static_cast<uint32_t*>(d);
+  b_prime_from = b->t.data;
+  b_prime_dims[0] = K, b_prime_dims[1] = N, b_prime_dims[2] = b->t.strides[0], b_prime_dims[3] = b->t.strides[1];
+  return make_b_prime(ctx, MatView{static_cast<const float*>(b->t.data), K, N, b->t.strides[0], b->t.strides[1]}, b_prime);
+}
+
+void MatMulOp::release(Context* ctx) {
+  if (b_prime) ctx->pool.free(b_prime);
+  b_prime = nullptr;
+  b_prime_from = nullptr;
+}
+
 rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
   const Value *a, *b;
   RTG_TRY(in.require(0, &a));
@@ -407,6 +427,11 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     ep.act = act;
     ep.alpha = scale;
     ep.alpha_div = scale_div;
+    epp = &ep;
+  }
+  if (b_prime && tb.data == b_prime_from && tb.ndim == 2 && tb.shape[0] == b_prime_dims[0] &&
+      tb.shape[1] == b_prime_dims[1] && tb.strides[0] == b_prime_dims[2] && tb.strides[1] == b_prime_dims[3]) {
+    ep.b_prime = b_prime;
     epp = &ep;
   }
   rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);

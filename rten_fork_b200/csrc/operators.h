@@ -109,6 +109,15 @@ class MatMulOp : public Operator {
   bool fused() const { return has_bias || act != ACT_NONE || scale != 1.f || has_perm[0] || has_perm[1]; }
   const char* name() const override { return fused() ? "FusedMatMul" : "MatMul"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  // a constant 2-D right operand (linear-layer weights) gets its bf16 correction copy B' once at load (make_b_prime),
+  // the counterpart of prepack_b for RTG_MATH_TF32_BF16X2
+  rtg_status prepare(Context* ctx, const OpInputs& consts) override;
+  void release(Context* ctx) override;
+
+ private:
+  uint32_t* b_prime = nullptr;
+  const void* b_prime_from = nullptr;
+  int64_t b_prime_dims[4] = {0, 0, 0, 0};  // K, N, row stride, column stride of the operand it was made from
 };
 
 // operators_nn.cu: the remaining operators BERT-class graphs need
@@ -154,6 +163,28 @@ class BatchNormOp : public Operator {
   bool can_run_in_place() const override { return true; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
   rtg_status run_in_place(Context* ctx, Value* io, const OpInputs& rest) override;
+};
+// operators_layout.cu: index-driven copies (Concat, Slice, Shape, Expand)
+class ConcatOp : public Operator {  // src/ops/concat.rs
+ public:
+  int64_t axis = 0;
+  const char* name() const override { return "Concat"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class SliceOp : public Operator {  // src/ops/slice.rs
+ public:
+  const char* name() const override { return "Slice"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class ShapeOp : public Operator {  // src/ops/layout.rs Shape
+ public:
+  const char* name() const override { return "Shape"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class ExpandOp : public Operator {  // src/ops/layout.rs Expand
+ public:
+  const char* name() const override { return "Expand"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
 };
 class ShapeOpsOp : public Operator {  // Unsqueeze / Squeeze: metadata-only changes of a contiguous tensor
  public:

@@ -202,6 +202,16 @@ const OpRegistry& OpRegistry::with_all_ops() {
       out->reset(op);
       return RTG_OK;
     });
+    r->register_op(Op_Concat, [](const OpNodeView& n, std::unique_ptr<Operator>* out) -> rtg_status {
+      if (n.attrs_type != Attrs_ConcatAttrs || !n.attrs.valid) return attr_error("ConcatAttrs");
+      ConcatOp* op = new ConcatOp();
+      op->axis = n.attrs.scalar<int32_t>(0, 0);  // ConcatAttrs: axis:0  (src/schema.fbs:232-234)
+      out->reset(op);
+      return RTG_OK;
+    });
+    r->register_op(Op_Slice, simple<SliceOp>());
+    r->register_op(Op_Shape, simple<ShapeOp>());
+    r->register_op(Op_Expand, simple<ExpandOp>());
     r->register_op(Op_Unsqueeze, simple<ShapeOpsOp>());
     r->register_op(Op_Squeeze, simple<ShapeOpsOp>([](ShapeOpsOp* p) { p->squeeze = true; }));
     return r;

@@ -180,6 +180,10 @@ class ModelBuilder:
         return (kind + "Attrs", f)
 
     @staticmethod
+    def concat_attrs(axis=0):
+        return ("ConcatAttrs", [(0, "i32", int(axis))])
+
+    @staticmethod
     def gemm_attrs(alpha=1.0, beta=1.0, transpose_a=False, transpose_b=False):
         return ("GemmAttrs", [(0, "f32", alpha), (1, "f32", beta), (2, "bool", 1 if transpose_a else None),
                               (3, "bool", 1 if transpose_b else None)])

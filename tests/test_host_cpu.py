@@ -160,3 +160,24 @@ def test_bench_graph_flops():
 
     flops = bench.graph_flops(synth.resnet50(), 32)
     assert abs(flops / 32 / 1e9 - 8.178) < 0.01
+
+
+def test_cli_dim_specs_and_input_heuristics():
+    """rten-cli's input generation rules (rten-cli/src/main.rs:60-94, 249-267), exercised without a device."""
+    from rten_fork_b200 import cli
+
+    dims = cli._parse_dims(["dim0=4,input_ids.dim1=7", "dim1=9"])
+    assert dims == [(None, "dim0", 4), ("input_ids", "dim1", 7), (None, "dim1", 9)]
+    assert cli._resolve("input_ids", ["dim0", "dim1"], dims, quiet=True) == [4, 7]
+    assert cli._resolve("image", ["dim0", 3, "dim2"], dims, quiet=True) == [4, 3, 1]
+    with pytest.raises(SystemExit):
+        cli._parse_dims(["dim0=abc"])
+
+    class FakeModel:
+        inputs = [{"name": "input_ids", "shape": [None, 8]}, {"name": "attention_mask", "shape": [None, 8]},
+                  {"name": "pixels", "shape": [2, 3]}]
+
+    ids, mask, px = cli.generate_inputs(FakeModel(), dims, quiet=True, seed=0)
+    assert ids.dtype == np.int32 and ids.shape == (4, 8) and not ids.any()
+    assert mask.dtype == np.int32 and mask.shape == (4, 8) and (mask == 1).all()
+    assert px.dtype == np.float32 and px.shape == (2, 3) and (px >= 0).all() and (px < 1).all()

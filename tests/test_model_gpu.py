@@ -189,3 +189,48 @@ def test_fused_transpose_matmul_and_scale(rtg, ctx, oracle, math_mode, optimize,
     assert got[1].tobytes() == np.ascontiguousarray(got[0].transpose()).tobytes()
     if optimize:
         assert m.num_ops == 5  # 2 MatMuls (+3 fused transposes, Div), the second Mul, 2 Transposes
+
+
+def test_cli_runs_a_model_file(rtg, ctx, tmp_path, capsys):
+    """`python -m rten_fork_b200.cli model.rten -n 2 -t -s dim0=3`: the rten-cli flow on the GPU path."""
+    from rten_fork_b200 import cli, synth
+
+    b = synth.resnet50(image=32, width=8, blocks=(1, 1, 1, 1), classes=10, seed=0)
+    path = tmp_path / "tiny_resnet.rten"
+    path.write_bytes(b.build())
+    assert cli.main([str(path), "-n", "2", "-t", "-s", "dim0=3"]) == 0
+    out = capsys.readouterr().out
+    assert out.count("Model returned 1 outputs") == 2
+    assert "shape: [3, 10]" in out and "FusedConv" in out
+
+
+def test_shape_arithmetic_ops(rtg, ctx, oracle):
+    """Concat / Slice / Shape / Expand as BERT-class exports use them (src/ops/concat.rs, slice.rs, layout.rs): the
+    results are index-driven copies, compared bit-exactly with the oracle's evaluation of the same graph."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = oracle.XorShiftRng(1234)
+    b = ModelBuilder()
+    x = b.add_value("x", ["batch", 6, 10])
+    b.inputs = [x]
+    i32 = lambda v: np.array(v, dtype=np.int32)  # noqa: E731
+    # Slice with clamped / negative endpoints and a negative step on the last axis
+    s1 = b.op("Slice", [x, b.add_constant("st", i32([1, -8])), b.add_constant("en", i32([1000, 9])),
+                        b.add_constant("ax", i32([1, 2]))])
+    s2 = b.op("Slice", [x, b.add_constant("st2", i32([-1])), b.add_constant("en2", i32([-100])),
+                        b.add_constant("ax2", i32([2])), b.add_constant("sp2", i32([-3]))])
+    # Shape -> Slice -> Concat: the usual "[batch, -1]" target of a Reshape, computed in the graph
+    shp = b.op("Shape", [x])
+    bdim = b.op("Slice", [shp, b.add_constant("z", i32([0])), b.add_constant("o", i32([1]))])
+    target = b.op("Concat", [bdim, b.add_constant("m1", i32([-1]))], ModelBuilder.concat_attrs(0))
+    flat = b.op("Reshape", [s1, target], ("ReshapeAttrs", []))
+    cat = b.op("Concat", [x, x, b.op("Relu", [x])], ModelBuilder.concat_attrs(-1))
+    row = b.add_constant("row", rng.fill((1, 1, 10)))
+    ex = b.op("Expand", [row, shp])
+    b.outputs = [s1, s2, shp, flat, cat, ex]
+    xin = rng.fill((3, 6, 10)) - 0.5
+    m, got, want = _run_both(ctx, b, [xin])
+    assert got[0].shape == (3, 5, 7) and got[1].shape == (3, 6, 4) and got[3].shape == (3, 35)
+    assert got[4].shape == (3, 6, 30) and got[5].shape == (3, 6, 10)
+    for g, w in zip(got, want):
+        assert g.dtype == w.dtype and g.shape == w.shape and g.tobytes() == w.tobytes()
