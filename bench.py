@@ -17,6 +17,8 @@ Graph::run is sharded per GPU, no data-path collective).  Prints ONE JSON line o
 `--impl reference` times only that CPU restatement (the reference is Rust; no Rust toolchain here — DESIGN.md).
 """
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -402,7 +404,21 @@ def run_ours(args):
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
-        run_reference(a)
-    else:
-        run_ours(a)
+    # stdout carries exactly ONE JSON line: libraries that write to file descriptor 1 behind Python's back (NCCL prints
+    # its version banner there) are pointed at stderr until the line is printed
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    _buf = io.StringIO()
+    with contextlib.redirect_stdout(_buf):
+        if a.impl == "reference":
+            run_reference(a)
+        else:
+            run_ours(a)
+    sys.stdout.flush()
+    os.dup2(_real_stdout, 1)
+    lines = [l for l in _buf.getvalue().splitlines() if l.strip()]
+    for l in lines[:-1]:
+        print(l, file=sys.stderr)
+    if lines:
+        print(lines[-1], flush=True)
