@@ -151,6 +151,22 @@ rtg_status rtg_conv(rtg_ctx* ctx, const rtg_tensor* input, const rtg_tensor* wei
                     const rtg_conv_attrs* attrs, const rtg_tensor* residual_or_null, int32_t act, float act_lo,
                     float act_hi, rtg_tensor* output);
 
+/* conv_transpose() / ConvTranspose::run                           src/ops/conv.rs:377-577
+ * input NCHW (or NCW), kernel [C, O, Kh, Kw] (or [C, O, Kw]), bias [O] or NULL.  Fixed padding is [top, left, bottom,
+ * right] ([left, right] for 1-D); RTG_PAD_SAME gives out = in * stride per axis.  Errors carry the reference's strings
+ * ("Input is too small", "Strides must be > 0", "Wrong number of pad values", ...). */
+typedef struct rtg_conv_transpose_attrs {   /* struct ConvTranspose {padding, strides}  src/ops/conv.rs:547-551 */
+  int32_t pad_mode;               /* RTG_PAD_FIXED | RTG_PAD_SAME */
+  int64_t pads[4];
+  int32_t n_pads;
+  int64_t strides[2];
+  int32_t n_strides;
+} rtg_conv_transpose_attrs;
+rtg_status rtg_conv_transpose_out_shape(const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias_or_null,
+                                        const rtg_conv_transpose_attrs* attrs, int64_t* out_shape, int32_t* out_ndim);
+rtg_status rtg_conv_transpose(rtg_ctx* ctx, const rtg_tensor* input, const rtg_tensor* weight,
+                              const rtg_tensor* bias_or_null, const rtg_conv_transpose_attrs* attrs, rtg_tensor* output);
+
 /* matmul() / MatMul::run                                          src/ops/matmul.rs:119-254 */
 rtg_status rtg_matmul_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* out_shape, int32_t* out_ndim);
 rtg_status rtg_matmul(rtg_ctx* ctx, const rtg_tensor* a, const rtg_tensor* b, rtg_tensor* output);

@@ -89,6 +89,10 @@ def run_graph(builder, inputs, outputs=None):
             y = ins[0]
             for ax in sorted(int(v) for v in ins[1]):
                 y = np.expand_dims(y, ax)
+        elif t == "ConvTranspose":
+            same = a.get(1, 1) == 0
+            y = o.conv_transpose(ins[0], ins[1], ins[2] if len(ins) > 2 else None,
+                                 "same" if same else tuple(a.get(2) or (0, 0, 0, 0)), tuple(a.get(0) or (1, 1)))
         elif t == "Concat":  # src/ops/concat.rs
             y = np.concatenate([x for x in ins], axis=a.get(0, 0))
         elif t == "Slice":  # src/ops/slice.rs: NumPy slicing semantics (clamped endpoints, negative steps)

@@ -325,3 +325,82 @@ def layer_norm(x, scale, bias, axis, eps):
     if bias is not None:
         y = y + bias
     return y.astype(np.float32)
+
+
+# ---------------------------------------------------------------- ConvTranspose (test infrastructure, like the rest)
+def conv_transpose_output_size_and_padding(in_hw, k_hw, padding, strides):
+    """src/ops/conv.rs:377-439.  ``padding``: "same" or a list.  Returns ((out_h, out_w), pads) where ``pads`` is the
+    4-tuple the reference returns -- in ITS order: [top, left, bottom, right] for fixed padding but
+    [top, bottom, left, right] for "same" (:424), which conv_transpose then reads as [top, left, ...] (:511)."""
+    (in_h, in_w), (k_h, k_w), (s_h, s_w) = in_hw, k_hw, strides
+    if s_h == 0 or s_w == 0:
+        raise OracleError(5, "Strides must be > 0")
+    if in_h == 0 or in_w == 0:
+        raise OracleError(5, "Input width and height must be > 0")
+    if isinstance(padding, str):
+        out_h, out_w = in_h * s_h, in_w * s_w
+        pad_h, pad_w = (in_h - 1) * s_h + k_h - out_h, (in_w - 1) * s_w + k_w - out_w
+        if pad_h < 0 or pad_w < 0:
+            raise OracleError(5, "Input is too small")
+        return (out_h, out_w), (pad_h // 2, -(-pad_h // 2), pad_w // 2, -(-pad_w // 2))
+    if len(padding) != 4:
+        raise OracleError(5, "Wrong number of pad values")
+    t, l, b, r = padding
+    out_h, out_w = (in_h - 1) * s_h + k_h - (t + b), (in_w - 1) * s_w + k_w - (l + r)
+    if out_h < 0 or out_w < 0:
+        raise OracleError(5, "Input is too small")
+    return (out_h, out_w), (t, l, b, r)
+
+
+def conv_transpose(x, w, bias=None, padding=(0, 0, 0, 0), strides=(1, 1)):
+    """conv_transpose() (src/ops/conv.rs:441-545): per image one GemmExecutor product
+    ``kernel_mat^T [O*Kh*Kw, C] . input [C, H*W]`` followed by col2im (:329-375), whose accumulation order is bias,
+    then ky-major / kx-minor.  Input NCHW (or NCW), kernel [C, O, Kh, Kw]."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    if x.ndim == 3:
+        if w.ndim != 3:
+            raise OracleError(5, "kernel must have 3 dims (OCW)")
+        if not isinstance(padding, str):
+            if len(padding) != 2:
+                raise OracleError(5, "expected 2 pad values")
+            padding = (0, padding[0], 0, padding[1])
+        if len(strides) != 1:
+            raise OracleError(5, "expected 1 stride value")
+        n, c, wd = x.shape
+        y = conv_transpose(x.reshape(n, c, 1, wd), w.reshape(w.shape[0], w.shape[1], 1, w.shape[2]), bias, padding,
+                           (1, strides[0]))
+        return y.reshape(y.shape[0], y.shape[1], y.shape[3])
+    if x.ndim != 4:
+        raise OracleError(5, "input must have 4 dims (NCHW)")
+    if w.ndim != 4:
+        raise OracleError(5, "kernel must have 4 dims (OCHW)")
+    n, c, h, wd = x.shape
+    kc, o, kh, kw = w.shape
+    if bias is not None and np.ndim(bias) != 1:
+        raise OracleError(5, "bias must have 1 dims")
+    if c != kc:
+        raise OracleError(3, "Input channels does not match kernel input channels")
+    if len(strides) != 2:
+        raise OracleError(5, "expected 2 stride values")
+    (oh, ow), pads = conv_transpose_output_size_and_padding((h, wd), (kh, kw), padding, strides)
+    pad_t, pad_l = pads[0], pads[1]  # what col2im is handed as [top, left] (see above for "same")
+    sh, sw = strides
+    out = np.empty((n, o, oh, ow), dtype=np.float32)
+    kmat_t = w.reshape(c, o * kh * kw).T
+    for i in range(n):
+        cols = gemm(kmat_t, x[i].reshape(c, h * wd)).reshape(o, kh, kw, h, wd)
+        img = np.empty((o, oh, ow), dtype=np.float32)
+        img[...] = 0.0 if bias is None else np.asarray(bias, dtype=np.float32)[:, None, None]
+        for ky in range(kh):
+            ys = np.arange(h) * sh + ky
+            yok = (ys >= pad_t) & (ys < oh + pad_t)
+            for kx in range(kw):
+                xs = np.arange(wd) * sw + kx
+                xok = (xs >= pad_l) & (xs < ow + pad_l)
+                if not yok.any() or not xok.any():
+                    continue
+                # every (y, x) of one tap lands on a distinct output pixel, so a vectorised add keeps the order
+                img[:, (ys[yok] - pad_t)[:, None], (xs[xok] - pad_l)[None, :]] += cols[:, ky, kx][:, yok][:, :, xok]
+        out[i] = img
+    return out

@@ -54,6 +54,16 @@ class ConvAttrs(C.Structure):
     ]
 
 
+class ConvTransposeAttrs(C.Structure):
+    _fields_ = [
+        ("pad_mode", C.c_int32),
+        ("pads", C.c_int64 * 4),
+        ("n_pads", C.c_int32),
+        ("strides", C.c_int64 * 2),
+        ("n_strides", C.c_int32),
+    ]
+
+
 class PoolAttrs(C.Structure):
     _fields_ = [
         ("kernel", C.c_int64 * 2),

@@ -135,6 +135,60 @@ rtg_status rtg_conv(rtg_ctx* ctx_, const rtg_tensor* input, const rtg_tensor* we
   return finish_out(ctx, output, &o);
 }
 
+rtg_status rtg_conv_transpose_out_shape(const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias,
+                                        const rtg_conv_transpose_attrs* attrs, int64_t* out_shape, int32_t* out_ndim) {
+  if (!attrs || !out_shape || !out_ndim) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  ConvTransposePlan p;
+  RTG_TRY(conv_transpose_plan(input, weight, bias, attrs, &p));
+  out_shape[0] = p.n, out_shape[1] = p.o;
+  if (p.is_1d) {
+    out_shape[2] = p.ow;
+    *out_ndim = 3;
+  } else {
+    out_shape[2] = p.oh, out_shape[3] = p.ow;
+    *out_ndim = 4;
+  }
+  return RTG_OK;
+}
+
+rtg_status rtg_conv_transpose(rtg_ctx* ctx_, const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias,
+                              const rtg_conv_transpose_attrs* attrs, rtg_tensor* output) {
+  CTX_OR_FAIL(ctx_);
+  if (!attrs || !output) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_TRY(check_tensor(input, "input"));
+  RTG_TRY(check_tensor(weight, "kernel"));
+  if (bias) RTG_TRY(check_tensor(bias, "bias"));
+  ConvTransposePlan p;
+  RTG_TRY(conv_transpose_plan(input, weight, bias, attrs, &p));
+  int64_t oshape[4] = {p.n, p.o, p.is_1d ? p.ow : p.oh, p.ow};
+  RTG_TRY(expect_shape(output, oshape, p.is_1d ? 3 : 4));
+  Staged x, w, b, o;
+  RTG_TRY(stage_in(ctx, input, &x));
+  RTG_TRY(stage_in(ctx, weight, &w));
+  if (bias) RTG_TRY(stage_in(ctx, bias, &b));
+  RTG_TRY(stage_out(ctx, output, &o));
+  Scratch wc, bc;
+  if (!is_contiguous(w.t) || (reinterpret_cast<uintptr_t>(w.t.data) & 15) != 0) {
+    RTG_TRY(wc.alloc(ctx, static_cast<size_t>(std::max<int64_t>(numel(w.t), 1)) * 4));
+    rtg_tensor t = w.t;
+    t.data = wc.p;
+    set_contiguous_strides(t);
+    RTG_TRY(copy_view(ctx, t, w.t));
+    w.t = t;
+  }
+  if (bias && !is_contiguous(b.t)) {
+    RTG_TRY(bc.alloc(ctx, static_cast<size_t>(std::max<int64_t>(numel(b.t), 1)) * 4));
+    rtg_tensor t = b.t;
+    t.data = bc.p;
+    set_contiguous_strides(t);
+    RTG_TRY(copy_view(ctx, t, b.t));
+    b.t = t;
+  }
+  RTG_TRY(conv_transpose_forward(ctx, p, x.t, static_cast<const float*>(w.t.data),
+                                 bias ? static_cast<const float*>(b.t.data) : nullptr, o.t));
+  return finish_out(ctx, output, &o);
+}
+
 rtg_status rtg_matmul_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* out_shape, int32_t* out_ndim) {
   return matmul_out_shape(a, b, out_shape, out_ndim);
 }

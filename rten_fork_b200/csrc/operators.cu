@@ -108,6 +108,34 @@ rtg_status ConvOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
   return RTG_OK;
 }
 
+// ---------------------------------------------------------------- ConvTranspose
+rtg_status ConvTransposeOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value *x, *w;
+  RTG_TRY(in.require(0, &x));
+  RTG_TRY(in.require(1, &w));
+  const Value* b = in.get(2);
+  ConvTransposePlan p;
+  RTG_TRY(conv_transpose_plan(&x->t, &w->t, b ? &b->t : nullptr, &attrs, &p));
+  int64_t oshape[4] = {p.n, p.o, p.is_1d ? p.ow : p.oh, p.ow};
+  Value y;
+  RTG_TRY(alloc_value(ctx, RTG_F32, p.is_1d ? 3 : 4, oshape, false, &y));
+  Value wtmp, btmp;
+  rtg_tensor wv, bv = {};
+  rtg_status st = contiguous_view(ctx, *w, &wtmp, &wv);
+  if (st == RTG_OK && b) st = contiguous_view(ctx, *b, &btmp, &bv);
+  if (st == RTG_OK)
+    st = conv_transpose_forward(ctx, p, x->t, static_cast<const float*>(wv.data),
+                                b ? static_cast<const float*>(bv.data) : nullptr, y.t);
+  release_value(ctx, &wtmp);
+  release_value(ctx, &btmp);
+  if (st != RTG_OK) {
+    release_value(ctx, &y);
+    return st;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
 // ---------------------------------------------------------------- unary
 rtg_status UnaryOp::bounds(Context* ctx, const Value* lo_v, const Value* hi_v, float* lo, float* hi) const {
   *lo = act_lo, *hi = act_hi;

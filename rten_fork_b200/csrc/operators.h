@@ -24,6 +24,14 @@ class ConvOp : public Operator {
   const void* prepared_from = nullptr;
 };
 
+// struct ConvTranspose {padding, strides}  src/ops/conv.rs:547-577
+class ConvTransposeOp : public Operator {
+ public:
+  rtg_conv_transpose_attrs attrs = {};
+  const char* name() const override { return "ConvTranspose"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+
 // UnaryFloatOp blanket impl  src/ops/unary_elementwise.rs:22-63 ; Clip :335-383
 class UnaryOp : public Operator {
  public:

@@ -90,6 +90,18 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x, co
                         const float* bias_dev, const rtg_tensor* residual, int act, float act_lo, float act_hi,
                         const rtg_tensor& out);
 
+// ------------------------------------------------------------------ ConvTranspose (conv_transpose.cu)
+struct ConvTransposePlan {
+  bool is_1d = false;
+  int64_t n = 0, c = 0, h = 0, w = 0, kc = 0, o = 0, kh = 0, kw = 0, oh = 0, ow = 0, sh = 1, sw = 1;
+  int64_t pads_out[4] = {0, 0, 0, 0};  // the tuple conv_transpose_output_size_and_padding returns
+  int64_t pad_t = 0, pad_l = 0;        // what col2im uses
+};
+rtg_status conv_transpose_plan(const rtg_tensor* x, const rtg_tensor* w, const rtg_tensor* bias,
+                               const rtg_conv_transpose_attrs* a, ConvTransposePlan* p);
+rtg_status conv_transpose_forward(Context* ctx, const ConvTransposePlan& p, const rtg_tensor& x, const float* w_dev,
+                                  const float* bias_dev, const rtg_tensor& out);
+
 // ------------------------------------------------------------------ layout
 // dst (any strides) = src (any strides), same shape, f32 or i32 (4-byte elements).
 rtg_status copy_view(Context* ctx, const rtg_tensor& dst, const rtg_tensor& src);

@@ -114,6 +114,25 @@ const OpRegistry& OpRegistry::with_all_ops() {
   static OpRegistry* reg = [] {
     OpRegistry* r = new OpRegistry();
     r->register_op(Op_Conv, read_conv);
+    r->register_op(Op_ConvTranspose, [](const OpNodeView& n, std::unique_ptr<Operator>* out) -> rtg_status {
+      if (n.attrs_type != Attrs_ConvTransposeAttrs || !n.attrs.valid) return attr_error("ConvTransposeAttrs");
+      // ConvTransposeAttrs: strides:0 auto_pad:1 (default NotSet) pads:2   (src/schema.fbs:264-272, reader :459-466)
+      ConvTransposeOp* op = new ConvTransposeOp();
+      rtg_conv_transpose_attrs& a = op->attrs;
+      const uint8_t auto_pad = n.attrs.scalar<uint8_t>(1, AutoPad_NotSet);
+      fb::Vec<uint32_t> p = n.attrs.vec<uint32_t>(2), s = n.attrs.vec<uint32_t>(0);
+      if (auto_pad == AutoPad_Same) {
+        a.pad_mode = RTG_PAD_SAME;
+      } else {
+        a.pad_mode = RTG_PAD_FIXED;
+        a.n_pads = p.present ? static_cast<int32_t>(std::min<uint32_t>(p.size(), 5)) : 4;
+        for (int i = 0; i < 4; ++i) a.pads[i] = (p.present && static_cast<uint32_t>(i) < p.size()) ? p[i] : 0;
+      }
+      a.n_strides = s.present ? static_cast<int32_t>(std::min<uint32_t>(s.size(), 3)) : 2;  // default [1, 1]
+      for (int i = 0; i < 2; ++i) a.strides[i] = s.present ? (static_cast<uint32_t>(i) < s.size() ? s[i] : 1) : 1;
+      out->reset(op);
+      return RTG_OK;
+    });
     r->register_op(Op_MaxPool, [](const OpNodeView& n, std::unique_ptr<Operator>* o) -> rtg_status { return read_pool(n, o, RTG_POOL_MAX); });
     r->register_op(Op_AveragePool, [](const OpNodeView& n, std::unique_ptr<Operator>* o) -> rtg_status { return read_pool(n, o, RTG_POOL_AVG); });
     r->register_op(Op_GlobalAveragePool, simple<PoolOp>([](PoolOp* p) { p->global = true, p->kind = RTG_POOL_AVG; }));

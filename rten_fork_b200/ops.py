@@ -118,6 +118,55 @@ class Conv:
         return [conv(inputs[0], inputs[1], bias, self.padding, self.groups, self.strides, self.dilations, ctx=ctx)]
 
 
+def _conv_transpose_attrs(padding, strides):
+    a = N.ConvTransposeAttrs()
+    if isinstance(padding, str):
+        if padding.lower() != "same":
+            raise N.RtgError(5, "unknown padding mode")
+        a.pad_mode, a.n_pads = 1, 0
+    else:
+        pads = list(padding)
+        a.pad_mode, a.n_pads = 0, min(len(pads), 5)
+        for i, p in enumerate(pads[:4]):
+            a.pads[i] = int(p)
+    strides = list(strides)
+    a.n_strides = min(len(strides), 3)
+    for i, s in enumerate(strides[:2]):
+        a.strides[i] = int(s)
+    return a
+
+
+def conv_transpose(input, kernel, bias=None, padding=(0, 0, 0, 0), strides=(1, 1), *, out=None,
+                   ctx: Context | None = None):
+    """``conv_transpose(pool, input, kernel, bias, padding, strides)`` (src/ops/conv.rs:441-545): input NCHW / NCW,
+    kernel ``[C, O, Kh, Kw]`` / ``[C, O, Kw]``.  One tcgen05 GEMM over the whole batch, then the col2im gather."""
+    ctx = ctx or context_for(input)
+    a = _conv_transpose_attrs(padding, strides)
+    ti, tw = as_tensor(input), as_tensor(kernel)
+    tb = as_tensor(bias) if bias is not None else None
+    shape = (C.c_int64 * 4)()
+    nd = C.c_int32()
+    N.check(N.lib().rtg_conv_transpose_out_shape(C.byref(ti), C.byref(tw), C.byref(tb) if tb is not None else None,
+                                                 C.byref(a), shape, C.byref(nd)))
+    if out is None:
+        out = _empty_like_kind(input, shape[: nd.value])
+    to = as_tensor(out)
+    N.check(N.lib().rtg_conv_transpose(ctx.handle, C.byref(ti), C.byref(tw), C.byref(tb) if tb is not None else None,
+                                       C.byref(a), C.byref(to)))
+    return out
+
+
+def conv_transpose_output_shape(input, kernel, bias=None, padding=(0, 0, 0, 0), strides=(1, 1)):
+    a = _conv_transpose_attrs(padding, strides)
+    ti, tw = as_tensor(input), as_tensor(kernel)
+    tb = as_tensor(bias) if bias is not None else None
+    shape = (C.c_int64 * 4)()
+    nd = C.c_int32()
+    N.check(N.lib().rtg_conv_transpose_out_shape(C.byref(ti), C.byref(tw), C.byref(tb) if tb is not None else None,
+                                                 C.byref(a), shape, C.byref(nd)))
+    return tuple(shape[: nd.value])
+
+
 def matmul(a, b, *, out=None, ctx: Context | None = None):
     ctx = ctx or context_for(a)
     ta, tb = as_tensor(a), as_tensor(b)

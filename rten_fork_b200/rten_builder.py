@@ -180,6 +180,12 @@ class ModelBuilder:
         return (kind + "Attrs", f)
 
     @staticmethod
+    def conv_transpose_attrs(pads=(0, 0, 0, 0), strides=(1, 1), same=False):
+        # ConvTransposeAttrs: strides:0 auto_pad:1 (default NotSet = 1) pads:2
+        return ("ConvTransposeAttrs", [(0, "vec_u32", list(strides)), (1, "u8", 0 if same else None),
+                                       (2, "vec_u32", None if same else list(pads))])
+
+    @staticmethod
     def concat_attrs(axis=0):
         return ("ConcatAttrs", [(0, "i32", int(axis))])
 

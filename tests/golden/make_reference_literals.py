@@ -21,6 +21,36 @@ cases = {
         "no_padding": {"pads": [0, 0, 0, 0], "shape": [1, 1, 1, 1], "expected": [2.6358]},
         "with_bias": {"pads": [0, 0, 0, 0], "bias": [1.0], "shape": [1, 1, 1, 1], "expected": [3.6358]},
     },
+    # src/ops/conv.rs:1155-1290 test_conv_transpose / _padding / _1d (values from torch.nn.functional.conv_transpose2d)
+    "conv_transpose": {
+        "cite": "src/ops/conv.rs:1155-1290",
+        "tol": 1e-5,
+        "input_shape": [1, 1, 2, 2], "input": [1.0, 2.0, 3.0, 4.0],
+        "kernel_shape": [1, 1, 2, 2], "kernel": [0.1, 0.2, 0.3, 0.4],
+        "strides": [2, 2],
+        "no_padding": {"shape": [1, 1, 4, 4],
+                       "expected": [0.1, 0.2, 0.2, 0.4, 0.3, 0.4, 0.6, 0.8, 0.3, 0.6, 0.4, 0.8, 0.9, 1.2, 1.2, 1.6]},
+        "bias": 1.234,
+        "fixed_padding_1": {"pads": [1, 1, 1, 1], "shape": [1, 1, 2, 2], "expected": [0.4, 0.6, 0.6, 0.4]},
+        "same_shape": [1, 1, 4, 4],
+        "one_d": {"input_shape": [1, 1, 2], "input": [1.0, 2.0], "kernel_shape": [1, 1, 2], "kernel": [0.1, 0.2],
+                  "strides": [2], "shape": [1, 1, 4], "expected": [0.1, 0.2, 0.2, 0.4], "bias": 0.5},
+        # src/ops/conv.rs:1293-1382 test_conv_transpose_output_size_and_padding: (input, kernel, padding, strides) ->
+        # (output size, padding) or the error message; padding "same" | list
+        "size_table": [
+            {"in": [5, 5], "k": [3, 3], "pad": [0, 0, 0, 0], "s": [1, 1], "out": [7, 7], "pads": [0, 0, 0, 0]},
+            {"in": [5, 5], "k": [3, 3], "pad": [0, 0, 0, 0], "s": [3, 3], "out": [15, 15], "pads": [0, 0, 0, 0]},
+            {"in": [5, 5], "k": [3, 3], "pad": [1, 1, 1, 1], "s": [1, 1], "out": [5, 5], "pads": [1, 1, 1, 1]},
+            {"in": [5, 5], "k": [3, 3], "pad": [2, 2, 2, 2], "s": [1, 1], "out": [3, 3], "pads": [2, 2, 2, 2]},
+            {"in": [5, 5], "k": [3, 3], "pad": [1, 2, 1, 2], "s": [1, 1], "out": [5, 3], "pads": [1, 2, 1, 2]},
+            {"in": [5, 5], "k": [3, 3], "pad": "same", "s": [1, 1], "out": [5, 5], "pads": [1, 1, 1, 1]},
+            {"in": [5, 5], "k": [1, 1], "pad": "same", "s": [3, 3], "error": "Input is too small"},
+            {"in": [5, 5], "k": [3, 3], "pad": [4, 4, 4, 4], "s": [1, 1], "error": "Input is too small"},
+            {"in": [5, 5], "k": [3, 3], "pad": [0, 0, 0, 0], "s": [0, 0], "error": "Strides must be > 0"},
+            {"in": [0, 0], "k": [3, 3], "pad": [0, 0, 0, 0], "s": [1, 1], "error": "Input width and height must be > 0"},
+            {"in": [1, 1], "k": [3, 3], "pad": [0, 0], "s": [1, 1], "error": "Wrong number of pad values"},
+        ],
+    },
     # src/ops/conv.rs:922-956 test_conv_depthwise (default tolerance: rtol 1e-5, atol 1e-8)
     "conv_depthwise": {
         "cite": "src/ops/conv.rs:922-956",

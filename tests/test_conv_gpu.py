@@ -246,3 +246,85 @@ def test_conv_split_k_nhwc(rtg, ctx, oracle, math_mode, C, O, H, k, s):
     assert "splitK" in ctx.last_kernel, ctx.last_kernel
     want = oracle.unary("relu", oracle.binary("add", oracle.conv2d(x, w, b, padding=(p, p, p, p), strides=(s, s)), res))
     expect_equal(out.cpu().numpy(), want, rtol=math_mode["rtol"])
+
+
+# ------------------------------------------------------------------------------------------------ ConvTranspose
+def test_conv_transpose_golden_literals(rtg, ctx, oracle, math_mode):  # src/ops/conv.rs:1155-1290
+    from rten_fork_b200 import ops
+
+    g = GOLD["conv_transpose"]
+    x = np.array(g["input"], np.float32).reshape(g["input_shape"])
+    w = np.array(g["kernel"], np.float32).reshape(g["kernel_shape"])
+    s = tuple(g["strides"])
+    tol = max(g["tol"], math_mode["rtol"])
+    np.testing.assert_allclose(ops.conv_transpose(x, w, None, (0, 0, 0, 0), s).reshape(-1), g["no_padding"]["expected"], rtol=tol)
+    got = ops.conv_transpose(x, w, np.array([g["bias"]], np.float32), (0, 0, 0, 0), s)
+    np.testing.assert_allclose(got.reshape(-1), np.array(g["no_padding"]["expected"]) + g["bias"], rtol=tol)
+    got = ops.conv_transpose(x, w, None, tuple(g["fixed_padding_1"]["pads"]), s)
+    assert list(got.shape) == g["fixed_padding_1"]["shape"]
+    np.testing.assert_allclose(got.reshape(-1), g["fixed_padding_1"]["expected"], rtol=tol)
+    assert list(ops.conv_transpose(x, w, None, "same", s).shape) == g["same_shape"]
+    d = g["one_d"]
+    got = ops.conv_transpose(np.array(d["input"], np.float32).reshape(d["input_shape"]),
+                             np.array(d["kernel"], np.float32).reshape(d["kernel_shape"]),
+                             np.array([d["bias"]], np.float32), (0, 0), tuple(d["strides"]))
+    np.testing.assert_allclose(got.reshape(-1), np.array(d["expected"]) + d["bias"], rtol=tol)
+
+
+@pytest.mark.parametrize("shape,wshape,pads,strides", [
+    ((2, 8, 5, 7), (8, 6, 3, 3), (0, 0, 0, 0), (1, 1)),
+    ((2, 8, 5, 7), (8, 6, 3, 3), (1, 1, 1, 1), (2, 2)),
+    ((1, 32, 6, 6), (32, 20, 4, 4), (1, 1, 1, 1), (2, 2)),     # the usual 2x upsampling deconvolution
+    ((3, 5, 4, 9), (5, 7, 2, 3), (0, 1, 1, 2), (3, 2)),        # uneven padding, C % 4 != 0
+    ((2, 16, 8, 8), (16, 4, 3, 3), "same", (2, 2)),
+    ((2, 16, 8, 8), (16, 4, 5, 3), "same", (1, 1)),            # the reference's "same" quirk: left pad = ceil(pad_h / 2)
+    ((2, 6, 11), (6, 3, 4), (1, 2), (3,)),                     # 1-D
+])
+def test_conv_transpose_vs_oracle(rtg, ctx, oracle, math_mode, shape, wshape, pads, strides):
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(1234)
+    x, w, b = rng.fill(shape), rng.fill(wshape), rng.fill((wshape[1],))
+    got = ops.conv_transpose(x, w, b, pads, strides)
+    want = oracle.conv_transpose(x, w, b, pads, strides)
+    expect_equal(got, want, rtol=math_mode["rtol"])
+
+
+def test_conv_transpose_size_table_and_errors(rtg, ctx, oracle):  # src/ops/conv.rs:1293-1382, :441-505
+    from rten_fork_b200 import ops
+
+    for c in GOLD["conv_transpose"]["size_table"]:
+        x = np.zeros((1, 2, *c["in"]), np.float32)
+        w = np.zeros((2, 3, *c["k"]), np.float32)
+        if "error" in c:
+            with pytest.raises(rtg.RtgError, match=c["error"]):
+                ops.conv_transpose_output_shape(x, w, None, c["pad"], c["s"])
+        else:
+            assert ops.conv_transpose_output_shape(x, w, None, c["pad"], c["s"]) == (1, 3, *c["out"])
+    with pytest.raises(rtg.RtgError, match="Input channels does not match kernel input channels"):
+        ops.conv_transpose(np.zeros((1, 4, 3, 3), np.float32), np.zeros((5, 2, 2, 2), np.float32))
+    with pytest.raises(rtg.RtgError, match="expected 2 stride values"):
+        ops.conv_transpose(np.zeros((1, 4, 3, 3), np.float32), np.zeros((4, 2, 2, 2), np.float32), strides=(1,))
+
+
+def test_conv_transpose_in_a_model(rtg, ctx, oracle):
+    """ConvTranspose through the OpRegistry / Graph::run path (attrs from the .rten file), after a fused Conv."""
+    from rten_fork_b200.model import Model
+    from rten_fork_b200.rten_builder import ModelBuilder
+    import graph_oracle
+
+    rng = oracle.XorShiftRng(1234)
+    b = ModelBuilder()
+    x = b.add_value("x", ["batch", 4, 6, 6])
+    b.inputs = [x]
+    y = b.op("Conv", [x, b.add_constant("w0", rng.fill((8, 4, 3, 3)) - 0.5), b.add_constant("b0", rng.fill((8,)))],
+             ModelBuilder.conv_attrs((1, 1, 1, 1)))
+    y = b.op("Relu", [y])
+    y = b.op("ConvTranspose", [y, b.add_constant("w1", rng.fill((8, 5, 2, 2))), b.add_constant("b1", rng.fill((5,)))],
+             ModelBuilder.conv_transpose_attrs((0, 0, 0, 0), (2, 2)))
+    b.outputs = [y]
+    xin = rng.fill((2, 4, 6, 6))
+    got = Model.load(b.build(), ctx=ctx).run([xin])
+    want = graph_oracle.run_graph(b, [xin])
+    assert got[0].shape == (2, 5, 12, 12)
+    expect_equal(got[0], want[0], rtol=1e-5, atol=1e-5)

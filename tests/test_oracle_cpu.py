@@ -191,3 +191,33 @@ def test_graph_oracle_resnet_block(oracle):
     got = graph_oracle.run_graph(b, [xin])[0]
     want = np.maximum(oracle.conv2d(xin, b.nodes[w]["data"], None, padding=(1, 1, 1, 1)) + xin, 0)
     assert got.tobytes() == want.astype(np.float32).tobytes()
+
+
+def test_conv_transpose_oracle_matches_reference_literals():
+    """src/ops/conv.rs:1155-1382: conv_transpose2d literals (from torch), fixed / same padding, 1-D, and the
+    output-size-and-padding table with its error messages."""
+    import oracle as o
+
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_literals.json")))["conv_transpose"]
+    x = np.array(g["input"], np.float32).reshape(g["input_shape"])
+    w = np.array(g["kernel"], np.float32).reshape(g["kernel_shape"])
+    y = o.conv_transpose(x, w, None, (0, 0, 0, 0), tuple(g["strides"]))
+    assert list(y.shape) == g["no_padding"]["shape"]
+    np.testing.assert_allclose(y.reshape(-1), g["no_padding"]["expected"], rtol=g["tol"], atol=1e-8)
+    yb = o.conv_transpose(x, w, np.array([g["bias"]], np.float32), (0, 0, 0, 0), tuple(g["strides"]))
+    np.testing.assert_allclose(yb.reshape(-1), np.array(g["no_padding"]["expected"]) + g["bias"], rtol=g["tol"])
+    yp = o.conv_transpose(x, w, None, tuple(g["fixed_padding_1"]["pads"]), tuple(g["strides"]))
+    np.testing.assert_allclose(yp.reshape(-1), g["fixed_padding_1"]["expected"], rtol=g["tol"])
+    assert list(o.conv_transpose(x, w, None, "same", tuple(g["strides"])).shape) == g["same_shape"]
+    d = g["one_d"]
+    y1 = o.conv_transpose(np.array(d["input"], np.float32).reshape(d["input_shape"]),
+                          np.array(d["kernel"], np.float32).reshape(d["kernel_shape"]), None, (0, 0), tuple(d["strides"]))
+    assert list(y1.shape) == d["shape"]
+    np.testing.assert_allclose(y1.reshape(-1), d["expected"], rtol=g["tol"])
+    for c in g["size_table"]:
+        if "error" in c:
+            with pytest.raises(o.OracleError, match=c["error"]):
+                o.conv_transpose_output_size_and_padding(c["in"], c["k"], c["pad"], c["s"])
+        else:
+            out, pads = o.conv_transpose_output_size_and_padding(c["in"], c["k"], c["pad"], c["s"])
+            assert list(out) == c["out"] and list(pads) == c["pads"]
