@@ -93,6 +93,14 @@ def run_graph(builder, inputs, outputs=None):
             same = a.get(1, 1) == 0
             y = o.conv_transpose(ins[0], ins[1], ins[2] if len(ins) > 2 else None,
                                  "same" if same else tuple(a.get(2) or (0, 0, 0, 0)), tuple(a.get(0) or (1, 1)))
+        elif t == "Where":
+            y = np.ascontiguousarray(np.where(ins[0] != 0, ins[1], ins[2]))
+        elif t == "ReduceMean":  # src/ops/reduce.rs:334-353: sum / len in f32 (summation order differs: tolerance)
+            ax = a.get(0)
+            ax = tuple(int(v) for v in ax) if ax else None
+            x = ins[0].astype(np.float32)
+            cnt = x.size if ax is None else int(np.prod([x.shape[v] for v in ax]))
+            y = (x.sum(axis=ax, keepdims=bool(a.get(1)), dtype=np.float32) / np.float32(cnt)).astype(np.float32)
         elif t == "Concat":  # src/ops/concat.rs
             y = np.concatenate([x for x in ins], axis=a.get(0, 0))
         elif t == "Slice":  # src/ops/slice.rs: NumPy slicing semantics (clamped endpoints, negative steps)

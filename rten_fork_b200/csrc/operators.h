@@ -194,6 +194,18 @@ class ExpandOp : public Operator {  // src/ops/layout.rs Expand
   const char* name() const override { return "Expand"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
 };
+class WhereOp : public Operator {  // src/ops/binary_elementwise.rs where_op
+ public:
+  const char* name() const override { return "Where"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
+class ReduceMeanOp : public Operator {  // src/ops/reduce.rs reduce_mean
+ public:
+  std::vector<int64_t> axes;
+  bool has_axes = false, keep_dims = true;
+  const char* name() const override { return "ReduceMean"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
 class ShapeOpsOp : public Operator {  // Unsqueeze / Squeeze: metadata-only changes of a contiguous tensor
  public:
   bool squeeze = false;

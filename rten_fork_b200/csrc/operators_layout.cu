@@ -174,4 +174,150 @@ rtg_status ExpandOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
   return RTG_OK;
 }
 
+// ---------------------------------------------------------------- Where  (src/ops/binary_elementwise.rs:850-915)
+namespace {
+struct Strided3 {
+  int nd;
+  int64_t shape[RTG_MAX_DIMS], sc[RTG_MAX_DIMS], sx[RTG_MAX_DIMS], sy[RTG_MAX_DIMS];
+};
+__global__ void where_kernel(uint32_t* __restrict__ out, const int32_t* __restrict__ cond, const uint32_t* __restrict__ x,
+                             const uint32_t* __restrict__ y, Strided3 g, int64_t total) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    int64_t r = i, oc = 0, ox = 0, oy = 0;
+    for (int d = g.nd - 1; d >= 0; --d) {
+      const int64_t k = r % g.shape[d];
+      r /= g.shape[d];
+      oc += k * g.sc[d], ox += k * g.sx[d], oy += k * g.sy[d];
+    }
+    out[i] = cond[oc] != 0 ? x[ox] : y[oy];  // 4-byte elements of either type, copied bit for bit
+  }
+}
+
+// trailing-aligned broadcast of `shape` (ndim `nd`) against `t`; false if incompatible
+bool broadcast_into(int64_t* shape, int* nd, const rtg_tensor& t) {
+  const int n = std::max(*nd, t.ndim);
+  int64_t out[RTG_MAX_DIMS];
+  for (int i = 0; i < n; ++i) {
+    const int ia = i - (n - *nd), ib = i - (n - t.ndim);
+    const int64_t a = ia >= 0 ? shape[ia] : 1, b = ib >= 0 ? t.shape[ib] : 1;
+    if (a != b && a != 1 && b != 1) return false;
+    out[i] = a == 1 ? b : a;
+  }
+  for (int i = 0; i < n; ++i) shape[i] = out[i];
+  *nd = n;
+  return true;
+}
+void broadcast_strides(const rtg_tensor& t, int nd, int64_t* st) {
+  for (int i = 0; i < nd; ++i) {
+    const int it = i - (nd - t.ndim);
+    st[i] = (it >= 0 && t.shape[it] != 1) ? t.strides[it] : 0;
+  }
+}
+}  // namespace
+
+rtg_status WhereOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value *c, *x, *y;
+  RTG_TRY(in.require(0, &c));
+  RTG_TRY(in.require(1, &x));
+  RTG_TRY(in.require(2, &y));
+  if (c->t.dtype != RTG_I32 || x->t.dtype != y->t.dtype) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  Strided3 g;
+  g.nd = x->t.ndim;
+  for (int i = 0; i < g.nd; ++i) g.shape[i] = x->t.shape[i];
+  if (!broadcast_into(g.shape, &g.nd, y->t) || !broadcast_into(g.shape, &g.nd, c->t))
+    return set_error(RTG_ERR_INCOMPATIBLE_INPUT_SHAPES, "Cannot broadcast inputs");
+  broadcast_strides(c->t, g.nd, g.sc);
+  broadcast_strides(x->t, g.nd, g.sx);
+  broadcast_strides(y->t, g.nd, g.sy);
+  Value r;
+  RTG_TRY(alloc_value(ctx, x->t.dtype, g.nd, g.shape, false, &r));
+  const int64_t total = numel(r.t);
+  if (total > 0) {
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+    where_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<uint32_t*>(r.t.data), static_cast<const int32_t*>(c->t.data),
+                                                  static_cast<const uint32_t*>(x->t.data),
+                                                  static_cast<const uint32_t*>(y->t.data), g, total);
+    ctx->launches++;
+    if (cudaGetLastError() != cudaSuccess) {
+      release_value(ctx, &r);
+      return set_error(RTG_ERR_CUDA, "where_kernel launch failed");
+    }
+  }
+  out->push_back(r);
+  return RTG_OK;
+}
+
+// ---------------------------------------------------------------- ReduceMean  (src/ops/reduce.rs:228-353)
+namespace {
+// one warp per row of a dense [rows, len] matrix: lanes stride over the row, shuffle tree, sum / len
+__global__ void row_mean_kernel(float* __restrict__ out, const float* __restrict__ x, int64_t rows, int64_t len) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nwarps) {
+    const float* p = x + r * len;
+    float s = 0.f;
+    for (int64_t i = lane; i < len; i += 32) s += p[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[r] = __fdiv_rn(s, static_cast<float>(len));
+  }
+}
+}  // namespace
+
+rtg_status ReduceMeanOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
+  const Value* x;
+  RTG_TRY(in.require(0, &x));
+  if (x->t.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  const int nd = x->t.ndim;
+  bool red[RTG_MAX_DIMS] = {};
+  if (!has_axes || axes.empty()) {
+    for (int i = 0; i < nd; ++i) red[i] = true;
+  } else {
+    for (int64_t a : axes) {
+      int ax;
+      RTG_TRY(resolve_axis(nd, a, &ax));
+      red[ax] = true;
+    }
+  }
+  // kept dims first, reduced dims last: a dense [rows, len] matrix (gathered unless the input already has that form)
+  rtg_tensor view = x->t;
+  int64_t oshape[RTG_MAX_DIMS];
+  int k = 0, ond = 0;
+  int64_t rows = 1, len = 1;
+  for (int i = 0; i < nd; ++i)
+    if (!red[i]) view.shape[k] = x->t.shape[i], view.strides[k] = x->t.strides[i], rows *= x->t.shape[i], ++k;
+  for (int i = 0; i < nd; ++i)
+    if (red[i]) view.shape[k] = x->t.shape[i], view.strides[k] = x->t.strides[i], len *= x->t.shape[i], ++k;
+  for (int i = 0; i < nd; ++i) {
+    if (!red[i]) oshape[ond++] = x->t.shape[i];
+    else if (keep_dims) oshape[ond++] = 1;
+  }
+  if (len == 0) return set_error(RTG_ERR_INVALID_VALUE, "Cannot reduce empty tensor");
+  Value y;
+  RTG_TRY(alloc_value(ctx, RTG_F32, ond, oshape, false, &y));
+  if (rows > 0) {
+    Scratch tmp;
+    const float* src = static_cast<const float*>(x->t.data);
+    if (!is_contiguous(view)) {
+      rtg_status st = tmp.alloc(ctx, static_cast<size_t>(rows) * len * 4);
+      rtg_tensor dst = view;
+      dst.data = tmp.p;
+      set_contiguous_strides(dst);
+      if (st == RTG_OK) st = copy_view(ctx, dst, view);
+      if (st != RTG_OK) {
+        release_value(ctx, &y);
+        return st;
+      }
+      src = tmp.f32();
+    }
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(rows * 32, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+    row_mean_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<float*>(y.t.data), src, rows, len);
+    ctx->launches++;
+  }
+  out->push_back(y);
+  return RTG_OK;
+}
+
 }  // namespace rtg

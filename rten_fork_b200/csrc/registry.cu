@@ -228,6 +228,18 @@ const OpRegistry& OpRegistry::with_all_ops() {
       out->reset(op);
       return RTG_OK;
     });
+    r->register_op(Op_Where, simple<WhereOp>());
+    r->register_op(Op_ReduceMean, [](const OpNodeView& n, std::unique_ptr<Operator>* out) -> rtg_status {
+      if (n.attrs_type != Attrs_ReduceMeanAttrs || !n.attrs.valid) return attr_error("ReduceMeanAttrs");
+      // ReduceMeanAttrs: axes:0 keep_dims:1   (src/schema.fbs:387-390, reduce_axes reader src/op_registry.rs:698-712)
+      ReduceMeanOp* op = new ReduceMeanOp();
+      fb::Vec<int32_t> a = n.attrs.vec<int32_t>(0);
+      op->has_axes = a.present;
+      for (uint32_t i = 0; a.present && i < a.size(); ++i) op->axes.push_back(a[i]);
+      op->keep_dims = n.attrs.scalar<uint8_t>(1, 0) != 0;
+      out->reset(op);
+      return RTG_OK;
+    });
     r->register_op(Op_Slice, simple<SliceOp>());
     r->register_op(Op_Shape, simple<ShapeOp>());
     r->register_op(Op_Expand, simple<ExpandOp>());

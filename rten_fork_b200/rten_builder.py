@@ -186,6 +186,11 @@ class ModelBuilder:
                                        (2, "vec_u32", None if same else list(pads))])
 
     @staticmethod
+    def reduce_mean_attrs(axes=None, keep_dims=True):
+        return ("ReduceMeanAttrs", [(0, "vec_i32", None if axes is None else list(axes)),
+                                    (1, "bool", 1 if keep_dims else None)])
+
+    @staticmethod
     def concat_attrs(axis=0):
         return ("ConcatAttrs", [(0, "i32", int(axis))])
 

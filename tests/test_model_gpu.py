@@ -234,3 +234,27 @@ def test_shape_arithmetic_ops(rtg, ctx, oracle):
     assert got[4].shape == (3, 6, 30) and got[5].shape == (3, 6, 10)
     for g, w in zip(got, want):
         assert g.dtype == w.dtype and g.shape == w.shape and g.tobytes() == w.tobytes()
+
+
+def test_where_and_reduce_mean(rtg, ctx, oracle):
+    """Where (broadcast select, bit-exact) and ReduceMean (src/ops/reduce.rs: sum / len over the given axes) as a
+    mask-and-pool tail of a BERT-class export."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = oracle.XorShiftRng(1234)
+    b = ModelBuilder()
+    x = b.add_value("x", ["batch", 5, 12])
+    m = b.add_value("keep_mask", ["batch", 5, 1])
+    b.inputs = [x, m]
+    masked = b.op("Where", [m, x, b.add_constant("fill", np.array([-1.5], dtype=np.float32))])
+    mean_last = b.op("ReduceMean", [masked], ModelBuilder.reduce_mean_attrs([-1], keep_dims=True))
+    mean_mid = b.op("ReduceMean", [x], ModelBuilder.reduce_mean_attrs([1], keep_dims=False))
+    mean_all = b.op("ReduceMean", [x], ModelBuilder.reduce_mean_attrs(None, keep_dims=False))
+    b.outputs = [masked, mean_last, mean_mid, mean_all]
+    xin = rng.fill((3, 5, 12)) - 0.5
+    mask = (rng.fill((3, 5, 1)) > 0.4).astype(np.int32)
+    _m, got, want = _run_both(ctx, b, [xin, mask])
+    assert got[0].tobytes() == want[0].tobytes()
+    assert got[1].shape == (3, 5, 1) and got[2].shape == (3, 12) and got[3].shape == ()
+    for g, w in zip(got[1:], want[1:]):
+        np.testing.assert_allclose(g, w, rtol=1e-5, atol=1e-6)
