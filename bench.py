@@ -260,6 +260,24 @@ def timed_e2e_steps(torch, model, stream, x_host, out_host, flush, steps):
     return total * 1e3
 
 
+def timed_e2e_pipelined(torch, model, stream, x_hosts, out_hosts, flush, steps):
+    """K steps through Model.run_async (rtg_model_submit) with pinned host buffers, two submits in flight: every step's
+    H2D upload, graph and D2H download are inside the window, the upload of step i + 1 overlapping the graph of step i.
+    The L2 flush of each step is enqueued on the compute stream and therefore also inside the window."""
+    with torch.cuda.stream(stream):
+        stream.synchronize()
+        t0 = time.perf_counter()
+        prev = None
+        for i in range(steps):
+            flush.zero_()
+            tk = model.run_async([x_hosts[i & 1]], [out_hosts[i & 1]])
+            if prev is not None:
+                prev.wait()
+            prev = tk
+        prev.wait()
+        return (time.perf_counter() - t0) * 1e3
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -323,8 +341,18 @@ def run_ours(args):
     e2e_ms = timed_e2e_steps(torch, model, stream, x_host, out_host, flush, args.steps)
     barrier()
     e2e_ms = max_over_ranks(e2e_ms)
-    clocks = sampler.stop() if rank == 0 else None
     same = bool(torch.equal(out_host.to(out_dev.device), out_dev))
+    # the same, pipelined: what a serving loop calls (two host buffer pairs, both holding this rank's batch)
+    x_hosts = [x_host, x_host.clone().pin_memory()]
+    out_hosts = [out_host, torch.empty_like(out_host).pin_memory()]
+    timed_e2e_pipelined(torch, model, stream, x_hosts, out_hosts, flush, 3)
+    barrier()
+    e2e_pipe_ms = timed_e2e_pipelined(torch, model, stream, x_hosts, out_hosts, flush, args.steps)
+    barrier()
+    e2e_pipe_ms = max_over_ranks(e2e_pipe_ms)
+    same = same and bool(torch.equal(out_hosts[1].to(out_dev.device), out_dev)) and \
+        bool(torch.equal(out_hosts[0].to(out_dev.device), out_dev))
+    clocks = sampler.stop() if rank == 0 else None
 
     # dominant kernel: every launch of the tcgen05 contraction kernel bracketed by events on its own stream
     ctx.set_kernel_timing(True)
@@ -373,9 +401,14 @@ def run_ours(args):
                    "gflop_per_step_per_gpu": flops_step / 1e9, "parallelism": f"batch-sharded x{world}, no collective"},
         "tflops": flops_step * world * args.steps / (ms_total * 1e-3) / 1e12,
         "clocks": clocks,
-        "e2e": {"value": images / (e2e_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_ms / args.steps,
+        "e2e": {"value": images / (e2e_pipe_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_pipe_ms / args.steps,
                 "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4,
-                "matches_device_run": same},
+                "matches_device_run": same,
+                "api": "Model.run_async / rtg_model_submit, pinned host buffers, two submits in flight: each step's "
+                       "H2D, L2 flush, graph and D2H are inside the wall-clock window",
+                "one_call_at_a_time": {"value": images / (e2e_ms * 1e-3), "unit": "images/s",
+                                       "ms_per_step": e2e_ms / args.steps,
+                                       "api": "Model.run / rtg_model_run, H2D -> graph -> D2H serialised per call"}},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (all Conv / Gemm launches of a step)",
                      "achieved": tf(kt), "peak": peaks["tf32_sustained"], "unit": "TFLOP/s",

@@ -221,6 +221,16 @@ rtg_status rtg_run_output_info(const rtg_run* run, int32_t i, int64_t* shape, in
 /* Copies output i (contiguous, reference layout) to `dst` on `device` (RTG_HOST or ordinal). */
 rtg_status rtg_run_output_copy(rtg_run* run, int32_t i, void* dst, size_t dst_bytes, int32_t device);
 rtg_status rtg_run_free(rtg_run* run);
+/* Asynchronous Model::run over HOST buffers (no reference counterpart: the reference runs on the caller's thread;
+ * this is what a serving loop binds instead of rtg_model_run to keep the PCIe copies off the critical path).
+ * The inputs are uploaded on a second stream into one of two staging slots, so the upload of submit i + 1 overlaps
+ * the graph of submit i; the outputs are written to `outputs[i].data` (host; `shape` gives the capacity on entry and
+ * the actual shape on return).  All buffers must stay valid until rtg_ticket_wait, which also frees the ticket.
+ * Use pinned host memory, or the copies serialise with the caller. */
+typedef struct rtg_ticket rtg_ticket;
+rtg_status rtg_model_submit(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_tensor* outputs,
+                            int32_t n_outputs, rtg_ticket** out);
+rtg_status rtg_ticket_wait(rtg_ticket* ticket);
 /* RunOptions{timing}: per-operator device time of the last run as text   src/graph.rs:467-483, src/timing.rs */
 rtg_status rtg_model_set_timing(rtg_model* model, int32_t enabled);
 const char* rtg_model_timing_report(rtg_model* model);

@@ -8,8 +8,10 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# RTG_PROF_LIB=1 selects the developer build with per-role cycle counters (`make PROF=1`); never the default.
-LIB_PATH = os.path.join(_HERE, "librten_gpu_prof.so" if os.environ.get("RTG_PROF_LIB") == "1" else "librten_gpu.so")
+# RTG_PROF_LIB=1 selects the developer build with per-role cycle counters (`make PROF=1`), RTG_DEV_LIB=<file name> any
+# other developer build next to the package (A/B experiments); never the default.
+LIB_PATH = os.path.join(_HERE, os.environ.get("RTG_DEV_LIB") or (
+    "librten_gpu_prof.so" if os.environ.get("RTG_PROF_LIB") == "1" else "librten_gpu.so"))
 
 RTG_HOST = -1
 RTG_F32, RTG_I32 = 0, 1

@@ -4,10 +4,23 @@
 
 #include <algorithm>
 #include <map>
+#include <memory>
 
 #include "graph.h"
 
 using namespace rtg;
+
+void rtg::SubmitPipeline::release() {
+  for (Slot& sl : slots) {
+    for (void* p : sl.staging)
+      if (p) cudaFree(p);
+    if (sl.uploaded) cudaEventDestroy(sl.uploaded);
+    if (sl.consumed) cudaEventDestroy(sl.consumed);
+    sl = Slot();
+  }
+  if (upload) cudaStreamDestroy(upload);
+  upload = nullptr;
+}
 
 namespace {
 
@@ -46,6 +59,72 @@ std::string format_timing(const std::vector<TimingRecord>& recs, const DevPool& 
   return s;
 }
 
+// Model::run proper.  `host_mirror` (rtg_model_submit): the caller's host copies of `inputs`, which then point at
+// device staging buffers; small i32 inputs keep a host mirror for shape arithmetic either way.
+rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, const rtg_tensor* host_mirror, Run** out) {
+  Context* ctx = m->ctx;
+  Graph& g = m->graph;
+  if (n_inputs != static_cast<int32_t>(g.input_ids.size()))
+    return set_errorf(RTG_ERR_MISSING_INPUTS, "model expects %zu inputs, got %d", g.input_ids.size(), n_inputs);
+  std::vector<std::pair<int32_t, Value>> in;
+  auto cleanup = [&]() {
+    for (auto& kv : in) release_value(ctx, &kv.second);
+  };
+  for (int32_t i = 0; i < n_inputs; ++i) {
+    const rtg_tensor& t = inputs[i];
+    if (t.ndim < 0 || t.ndim > RTG_MAX_DIMS || (t.dtype != RTG_F32 && t.dtype != RTG_I32)) {
+      cleanup();
+      return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+    }
+    // Inputs become owned temporaries (moved into the run like the reference's owned inputs, src/graph.rs:808-824)
+    Value v;
+    rtg_status st = alloc_value(ctx, t.dtype, t.ndim, t.shape, false, &v);
+    if (st != RTG_OK) {
+      cleanup();
+      return st;
+    }
+    const int64_t n = numel(t);
+    if (n > 0) {
+      if (t.device == RTG_HOST) {
+        rtg_tensor tc = t;
+        if (!is_contiguous(tc)) {
+          release_value(ctx, &v);
+          cleanup();
+          return set_error(RTG_ERR_UNSUPPORTED_VALUE, "host model inputs must be contiguous");
+        }
+        cudaError_t e = cudaMemcpyAsync(v.t.data, t.data, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) {
+          release_value(ctx, &v);
+          cleanup();
+          return set_errorf(RTG_ERR_CUDA, "input upload failed: %s", cudaGetErrorString(e));
+        }
+        if (t.dtype == RTG_I32 && n <= 4096)
+          v.host_i32 = std::make_shared<std::vector<int32_t>>(static_cast<const int32_t*>(t.data), static_cast<const int32_t*>(t.data) + n);
+      } else {
+        if (host_mirror && t.dtype == RTG_I32 && n <= 4096) {
+          const int32_t* h = static_cast<const int32_t*>(host_mirror[i].data);
+          v.host_i32 = std::make_shared<std::vector<int32_t>>(h, h + n);
+        }
+        st = copy_view(ctx, v.t, t);
+        if (st != RTG_OK) {
+          release_value(ctx, &v);
+          cleanup();
+          return st;
+        }
+      }
+    }
+    in.emplace_back(g.input_ids[i], v);
+  }
+  std::unique_ptr<Run> run(new Run());
+  run->ctx = ctx;
+  std::vector<TimingRecord> recs;
+  rtg_status st = g.run(ctx, in, g.output_ids, &run->outputs, m->timing ? &recs : nullptr);
+  if (st != RTG_OK) return st;  // Graph::run released the inputs
+  if (m->timing) m->timing_report = format_timing(recs, ctx->pool);
+  *out = run.release();
+  return RTG_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -80,6 +159,7 @@ rtg_status rtg_model_free(rtg_model* model) {
   cudaSetDevice(m->ctx->device);
   cudaStreamSynchronize(m->ctx->stream);
   m->graph.release(m->ctx);
+  m->pipe.release();
   delete m;
   return RTG_OK;
 }
@@ -131,63 +211,130 @@ const char* rtg_model_timing_report(rtg_model* model) {
 rtg_status rtg_model_run(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_run** out) {
   Model* m = reinterpret_cast<Model*>(model);
   if (!m || !out || (n_inputs > 0 && !inputs)) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(m->ctx->device));
+  Run* run = nullptr;
+  RTG_TRY(run_inputs(m, inputs, n_inputs, nullptr, &run));
+  *out = reinterpret_cast<rtg_run*>(run);
+  return RTG_OK;
+}
+
+/* Asynchronous Model::run for host buffers (pinned memory for real overlap). */
+rtg_status rtg_model_submit(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_tensor* outputs,
+                            int32_t n_outputs, rtg_ticket** out) {
+  Model* m = reinterpret_cast<Model*>(model);
+  if (!m || !out || (n_inputs > 0 && !inputs) || (n_outputs > 0 && !outputs))
+    return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
   Context* ctx = m->ctx;
   RTG_CUDA(cudaSetDevice(ctx->device));
-  Graph& g = m->graph;
-  if (n_inputs != static_cast<int32_t>(g.input_ids.size()))
-    return set_errorf(RTG_ERR_MISSING_INPUTS, "model expects %zu inputs, got %d", g.input_ids.size(), n_inputs);
-  std::vector<std::pair<int32_t, Value>> in;
-  auto cleanup = [&]() {
-    for (auto& kv : in) release_value(ctx, &kv.second);
-  };
+  if (n_inputs != static_cast<int32_t>(m->graph.input_ids.size()))
+    return set_errorf(RTG_ERR_MISSING_INPUTS, "model expects %zu inputs, got %d", m->graph.input_ids.size(), n_inputs);
+  if (n_outputs != static_cast<int32_t>(m->graph.output_ids.size()))
+    return set_errorf(RTG_ERR_INVALID_VALUE, "model has %zu outputs, got %d buffers", m->graph.output_ids.size(), n_outputs);
   for (int32_t i = 0; i < n_inputs; ++i) {
-    const rtg_tensor& t = inputs[i];
-    if (t.ndim < 0 || t.ndim > RTG_MAX_DIMS || (t.dtype != RTG_F32 && t.dtype != RTG_I32)) {
-      cleanup();
+    rtg_tensor t = inputs[i];
+    if (t.ndim < 0 || t.ndim > RTG_MAX_DIMS || (t.dtype != RTG_F32 && t.dtype != RTG_I32))
       return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
-    }
-    // Inputs become owned temporaries (moved into the run like the reference's owned inputs, src/graph.rs:808-824)
-    Value v;
-    rtg_status st = alloc_value(ctx, t.dtype, t.ndim, t.shape, false, &v);
-    if (st != RTG_OK) {
-      cleanup();
-      return st;
-    }
-    const int64_t n = numel(t);
-    if (n > 0) {
-      if (t.device == RTG_HOST) {
-        rtg_tensor tc = t;
-        if (!is_contiguous(tc)) {
-          release_value(ctx, &v);
-          cleanup();
-          return set_error(RTG_ERR_UNSUPPORTED_VALUE, "host model inputs must be contiguous");
-        }
-        cudaError_t e = cudaMemcpyAsync(v.t.data, t.data, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, ctx->stream);
-        if (e != cudaSuccess) {
-          release_value(ctx, &v);
-          cleanup();
-          return set_errorf(RTG_ERR_CUDA, "input upload failed: %s", cudaGetErrorString(e));
-        }
-        if (t.dtype == RTG_I32 && n <= 4096)
-          v.host_i32 = std::make_shared<std::vector<int32_t>>(static_cast<const int32_t*>(t.data), static_cast<const int32_t*>(t.data) + n);
-      } else {
-        st = copy_view(ctx, v.t, t);
-        if (st != RTG_OK) {
-          release_value(ctx, &v);
-          cleanup();
-          return st;
-        }
-      }
-    }
-    in.emplace_back(g.input_ids[i], v);
+    if (t.device != RTG_HOST || !is_contiguous(t))
+      return set_error(RTG_ERR_UNSUPPORTED_VALUE, "rtg_model_submit takes contiguous host inputs");
   }
-  std::unique_ptr<Run> run(new Run());
-  run->ctx = ctx;
-  std::vector<TimingRecord> recs;
-  rtg_status st = g.run(ctx, in, g.output_ids, &run->outputs, m->timing ? &recs : nullptr);
-  if (st != RTG_OK) return st;  // Graph::run released the inputs
-  if (m->timing) m->timing_report = format_timing(recs, ctx->pool);
-  *out = reinterpret_cast<rtg_run*>(run.release());
+  for (int32_t i = 0; i < n_outputs; ++i)
+    if (outputs[i].device != RTG_HOST || !outputs[i].data)
+      return set_error(RTG_ERR_UNSUPPORTED_VALUE, "rtg_model_submit writes to host output buffers");
+  SubmitPipeline& pp = m->pipe;
+  if (!pp.upload) RTG_CUDA(cudaStreamCreateWithFlags(&pp.upload, cudaStreamNonBlocking));
+  SubmitPipeline::Slot& sl = pp.slots[pp.next++ & 1];
+  if (!sl.uploaded) {
+    RTG_CUDA(cudaEventCreateWithFlags(&sl.uploaded, cudaEventDisableTiming));
+    RTG_CUDA(cudaEventCreateWithFlags(&sl.consumed, cudaEventDisableTiming));
+  }
+  sl.staging.resize(n_inputs, nullptr);
+  sl.cap.resize(n_inputs, 0);
+  // the slot's previous contents have been copied into that run's input tensors
+  if (sl.in_use) RTG_CUDA(cudaStreamWaitEvent(pp.upload, sl.consumed, 0));
+  std::vector<rtg_tensor> dev(inputs, inputs + n_inputs);
+  for (int32_t i = 0; i < n_inputs; ++i) {
+    const size_t bytes = static_cast<size_t>(numel(inputs[i])) * 4;
+    if (bytes > sl.cap[i]) {
+      if (sl.staging[i]) {
+        RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+        RTG_CUDA(cudaFree(sl.staging[i]));
+        sl.staging[i] = nullptr, sl.cap[i] = 0;
+      }
+      RTG_CUDA(cudaMalloc(&sl.staging[i], bytes));
+      sl.cap[i] = bytes;
+    }
+    if (bytes) RTG_CUDA(cudaMemcpyAsync(sl.staging[i], inputs[i].data, bytes, cudaMemcpyHostToDevice, pp.upload));
+    dev[i].data = sl.staging[i];
+    dev[i].device = ctx->device;
+  }
+  RTG_CUDA(cudaEventRecord(sl.uploaded, pp.upload));
+  RTG_CUDA(cudaStreamWaitEvent(ctx->stream, sl.uploaded, 0));
+  Run* run = nullptr;
+  rtg_status st = run_inputs(m, dev.data(), n_inputs, inputs, &run);
+  // whatever happened, the staging reads that were enqueued are ordered before this point of the compute stream
+  RTG_CUDA(cudaEventRecord(sl.consumed, ctx->stream));
+  sl.in_use = true;
+  if (st != RTG_OK) return st;
+  std::unique_ptr<Run> guard(run);
+  auto drop = [&]() {
+    for (Value& v : run->outputs) release_value(ctx, &v);
+  };
+  for (int32_t i = 0; i < n_outputs; ++i) {
+    Value& v = run->outputs[i];
+    const size_t bytes = static_cast<size_t>(numel(v.t)) * 4;
+    const size_t have = static_cast<size_t>(numel(outputs[i])) * 4;
+    if (have < bytes) {
+      drop();
+      return set_errorf(RTG_ERR_INVALID_VALUE, "output buffer %d too small: %zu bytes for %zu", i, have, bytes);
+    }
+    outputs[i].ndim = v.t.ndim;
+    outputs[i].dtype = v.t.dtype;
+    for (int k = 0; k < v.t.ndim; ++k) outputs[i].shape[k] = v.t.shape[k];
+    set_contiguous_strides(outputs[i]);
+    if (bytes == 0) continue;
+    Scratch tmp;
+    const void* src = v.t.data;
+    if (!is_contiguous(v.t)) {
+      rtg_tensor c = v.t;
+      st = tmp.alloc(ctx, bytes);
+      if (st == RTG_OK) {
+        c.data = tmp.p;
+        set_contiguous_strides(c);
+        st = copy_view(ctx, c, v.t);
+      }
+      if (st != RTG_OK) {
+        drop();
+        return st;
+      }
+      src = tmp.p;
+    }
+    cudaError_t e = cudaMemcpyAsync(outputs[i].data, src, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e != cudaSuccess) {
+      drop();
+      return set_errorf(RTG_ERR_CUDA, "output download failed: %s", cudaGetErrorString(e));
+    }
+  }
+  drop();  // stream-ordered: the pool may hand these buffers to later work on the same stream
+  Ticket* tk = new Ticket();
+  tk->ctx = ctx;
+  cudaError_t e = cudaEventCreateWithFlags(&tk->done, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventRecord(tk->done, ctx->stream);
+  if (e != cudaSuccess) {
+    delete tk;
+    return set_errorf(RTG_ERR_CUDA, "ticket event failed: %s", cudaGetErrorString(e));
+  }
+  *out = reinterpret_cast<rtg_ticket*>(tk);
+  return RTG_OK;
+}
+
+rtg_status rtg_ticket_wait(rtg_ticket* ticket) {
+  Ticket* tk = reinterpret_cast<Ticket*>(ticket);
+  if (!tk) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(tk->ctx->device));
+  cudaError_t e = cudaEventSynchronize(tk->done);
+  cudaEventDestroy(tk->done);
+  delete tk;
+  if (e != cudaSuccess) return set_errorf(RTG_ERR_CUDA, "run failed: %s", cudaGetErrorString(e));
   return RTG_OK;
 }
 

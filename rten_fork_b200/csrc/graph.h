@@ -133,18 +133,39 @@ class Graph {
 int optimize_graph(Graph* g);
 
 // ---------------------------------------------------------------- model
+// rtg_model_submit: host inputs are uploaded on a second stream into one of two staging slots, so the upload of run
+// i + 1 overlaps the graph of run i; outputs go back to the caller's host buffers on the compute stream.
+struct SubmitPipeline {
+  struct Slot {
+    std::vector<void*> staging;   // one device buffer per graph input
+    std::vector<size_t> cap;
+    cudaEvent_t uploaded = nullptr, consumed = nullptr;
+    bool in_use = false;          // `consumed` has been recorded at least once
+  };
+  cudaStream_t upload = nullptr;
+  Slot slots[2];
+  uint64_t next = 0;
+  void release();
+};
+
 struct Model {
   Context* ctx = nullptr;
   Graph graph;
   bool timing = false;
   std::string timing_report;
   std::vector<std::string> name_store;
+  SubmitPipeline pipe;
 };
 rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimize, Model** out);
 
 struct Run {
   Context* ctx = nullptr;
   std::vector<Value> outputs;
+};
+
+struct Ticket {  // one rtg_model_submit in flight
+  Context* ctx = nullptr;
+  cudaEvent_t done = nullptr;
 };
 
 }  // namespace rtg

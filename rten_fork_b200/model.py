@@ -11,6 +11,31 @@ from . import _native as N
 from .context import Context, as_tensor, default_context
 
 
+class Ticket:
+    """One Model.run_async in flight."""
+
+    def __init__(self, handle, out, odescs, keep):
+        self._h, self._out, self._odescs, self._keep = handle, out, odescs, keep
+
+    def wait(self):
+        if self._h is not None:
+            h, self._h = self._h, None
+            N.check(N.lib().rtg_ticket_wait(h))
+        res = []
+        for o, d in zip(self._out, self._odescs):
+            shp = tuple(d.shape[k] for k in range(d.ndim))
+            n = int(np.prod(shp)) if shp else 1
+            res.append(o.reshape(-1)[:n].reshape(shp))
+        return res
+
+    def __del__(self):
+        try:
+            if self._h is not None:
+                N.lib().rtg_ticket_wait(self._h)
+        except Exception:
+            pass
+
+
 class Model:
     def __init__(self, handle, ctx: Context):
         self._h, self.ctx = handle, ctx
@@ -111,6 +136,19 @@ class Model:
             return results
         finally:
             N.lib().rtg_run_free(run)
+
+    def run_async(self, inputs, out):
+        """rtg_model_submit: asynchronous run over host buffers.  ``inputs`` are contiguous host arrays (numpy, or
+        pinned torch CPU tensors for real copy / compute overlap), ``out`` one host buffer per graph output with at
+        least the output's size.  Returns a Ticket; ``ticket.wait()`` blocks until the outputs are in ``out`` and
+        returns them shaped like the results.  Two submits may be in flight: the upload of the second overlaps the
+        graph of the first."""
+        keep = list(inputs) + list(out)
+        descs = (N.Tensor * len(inputs))(*[as_tensor(x) for x in inputs])
+        odescs = (N.Tensor * len(out))(*[as_tensor(o) for o in out])
+        tk = C.c_void_p()
+        N.check(N.lib().rtg_model_submit(self._h, descs, C.c_int32(len(inputs)), odescs, C.c_int32(len(out)), C.byref(tk)))
+        return Ticket(tk, out, odescs, keep)
 
     def run_one(self, x, out=None):
         """Model::run_one (src/model.rs:620-637): single input, single output."""

@@ -157,3 +157,37 @@ def test_gemm_split_k(rtg, ctx, oracle, math_mode, m, n, k):
     expect_equal(got, oracle.gemm(a, b, alpha=0.5, beta=2.0, bias=bias, out=c0.copy()), rtol=math_mode["rtol"])
     again = _run(rtg, ctx, a, b, alpha=0.5, beta=2.0, bias=bias, out=c0.copy())
     assert again.tobytes() == got.tobytes()
+
+
+@pytest.mark.parametrize("mode", ["3xtf32", "tf32_bf16x2", "tf32"])
+def test_contraction_reruns_are_bit_identical(rtg, ctx, mode):
+    """The kernel is deterministic (fixed accumulation order, split-K planes added in split order), so a result that
+    differs between reruns is a pipeline race (a stage overwritten or read early).  Back-to-back launches with a small
+    unrelated GEMM in between exercise the programmatic-dependent-launch overlap too (scripts/stress_race.py is the
+    long version)."""
+    import torch
+    from rten_fork_b200 import ops
+
+    ctx.set_math({"3xtf32": rtg.MATH_3XTF32, "tf32": rtg.MATH_TF32, "tf32_bf16x2": rtg.MATH_TF32_BF16X2}[mode])
+    try:
+        torch.manual_seed(0)
+        cl = torch.channels_last
+        cases = []
+        for (B, C, O, H, k) in [(4, 512, 512, 7, 3), (32, 256, 128, 56, 1), (32, 128, 128, 28, 3)]:
+            x = (torch.rand((B, C, H, H), device="cuda") - 0.4).contiguous(memory_format=cl)
+            w, b = torch.rand((O, C, k, k), device="cuda") - 0.5, torch.rand((O,), device="cuda")
+            r = torch.rand((B, O, H, H), device="cuda").contiguous(memory_format=cl)
+            p = k // 2
+            cases.append(lambda x=x, w=w, b=b, p=p, r=r: ops.conv(x, w, b, padding=(p, p, p, p), groups=1, strides=(1, 1),
+                                                                 residual=r, activation="relu", out_nhwc=True, ctx=ctx))
+        a, bm = torch.rand((2048, 512), device="cuda") - 0.5, torch.rand((512, 2048), device="cuda") - 0.5
+        cases.append(lambda: ops.matmul(a, bm, ctx=ctx))
+        sa, sb = torch.rand((64, 64), device="cuda"), torch.rand((64, 64), device="cuda")
+        for fn in cases:
+            ref = fn().clone()
+            for i in range(40):
+                if i % 3 == 0:
+                    ops.matmul(sa, sb, ctx=ctx)
+                assert torch.equal(fn(), ref), f"rerun {i} differs ({ctx.last_kernel})"
+    finally:
+        ctx.set_math(rtg.MATH_3XTF32)

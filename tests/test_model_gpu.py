@@ -258,3 +258,35 @@ def test_where_and_reduce_mean(rtg, ctx, oracle):
     assert got[1].shape == (3, 5, 1) and got[2].shape == (3, 12) and got[3].shape == ()
     for g, w in zip(got[1:], want[1:]):
         np.testing.assert_allclose(g, w, rtol=1e-5, atol=1e-6)
+
+
+def test_run_async_pipelined_matches_run(rtg, ctx):
+    """rtg_model_submit / rtg_ticket_wait: host inputs uploaded on a second stream into two staging slots, outputs
+    written to the caller's host buffers; results must equal the synchronous Model.run bit for bit, whatever the number
+    of submits in flight, and changing batch sizes must regrow the staging buffers."""
+    import torch
+    from rten_fork_b200 import synth
+
+    b = synth.resnet50(image=32, width=8, blocks=(1, 1, 1, 1), classes=10, seed=0)
+    model = rtg.Model.load(b.build(), ctx=ctx)
+    gen = torch.Generator().manual_seed(7)
+    xs = [torch.rand((n, 3, 32, 32), generator=gen).pin_memory() for n in (4, 4, 2, 8, 4, 4)]
+    want = [model.run([x.numpy()])[0] for x in xs]
+    outs = [torch.empty((8, 10)).pin_memory() for _ in xs]
+    tickets = []
+    got = []
+    for x, o in zip(xs, outs):
+        tickets.append(model.run_async([x], [o]))
+        if len(tickets) == 2:  # two in flight
+            got.append(tickets.pop(0).wait()[0])
+    while tickets:
+        got.append(tickets.pop(0).wait()[0])
+    for g, w in zip(got, want):
+        assert tuple(g.shape) == w.shape
+        np.testing.assert_array_equal(g.numpy(), w)
+    # numpy (pageable) buffers work too, and a too-small output buffer is an error, not an overrun
+    o = np.empty((4, 10), np.float32)
+    np.testing.assert_array_equal(model.run_async([xs[0].numpy()], [o]).wait()[0], want[0])
+    with pytest.raises(rtg.RtgError, match="too small"):
+        model.run_async([xs[3].numpy()], [np.empty((4, 10), np.float32)])
+    np.testing.assert_array_equal(model.run_async([xs[1].numpy()], [o]).wait()[0], want[1])
