@@ -160,7 +160,7 @@ def test_gemm_split_k(rtg, ctx, oracle, math_mode, m, n, k):
 
 
 @pytest.mark.parametrize("mode", ["3xtf32", "tf32_bf16x2", "tf32"])
-def test_contraction_reruns_are_bit_identical(rtg, ctx, mode):
+def test_contraction_reruns_are_bit_identical(rtg, mode):
     """The kernel is deterministic (fixed accumulation order, split-K planes added in split order), so a result that
     differs between reruns is a pipeline race (a stage overwritten or read early).  Back-to-back launches with a small
     unrelated GEMM in between exercise the programmatic-dependent-launch overlap too (scripts/stress_race.py is the
@@ -168,6 +168,9 @@ def test_contraction_reruns_are_bit_identical(rtg, ctx, mode):
     import torch
     from rten_fork_b200 import ops
 
+    # a context on torch's stream: the comparisons (torch kernels) and the launches under test are stream-ordered
+    ctx = rtg.Context(0)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_math({"3xtf32": rtg.MATH_3XTF32, "tf32": rtg.MATH_TF32, "tf32_bf16x2": rtg.MATH_TF32_BF16X2}[mode])
     try:
         torch.manual_seed(0)
@@ -190,4 +193,5 @@ def test_contraction_reruns_are_bit_identical(rtg, ctx, mode):
                     ops.matmul(sa, sb, ctx=ctx)
                 assert torch.equal(fn(), ref), f"rerun {i} differs ({ctx.last_kernel})"
     finally:
-        ctx.set_math(rtg.MATH_3XTF32)
+        torch.cuda.synchronize()
+        ctx.close()
