@@ -777,6 +777,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t hi[32], lo[32];
       auto load_block = [&]() {
         PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
+#ifdef RTG_PROF
+        const long long tl_ = clock64();
+#endif
         const uint32_t src = smem_base + ia * kABytes + row * 128;
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
@@ -808,6 +811,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) lo[j] = lo_of(__uint_as_float(hi[j]));
         }
+#ifdef RTG_PROF
+        prof_acc_[3] += clock64() - tl_;  // LDS + split arithmetic of one block
+#endif
       };
       if (total > 0) load_block();
       for (int it = 0; it < total; ++it) {
@@ -818,7 +824,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::tmem_st_32x32(dst, hi);
         ptx::tmem_st_32x32(dst + kBK, lo);
         if (it + 1 < total) load_block();
-        ptx::tmem_st_wait();
+        PROF_WAIT(2, ptx::tmem_st_wait());
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(xf_bar(s));
