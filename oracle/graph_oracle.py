@@ -24,6 +24,61 @@ def _padding(a, auto_field, pads_field):
     return tuple(p) if p is not None else (0, 0, 0, 0)
 
 
+def einsum(equation, ins):
+    """src/ops/einsum.rs: terms folded left to right (einsum_path); each pairwise step permutes the operands to
+    [batch.., M.., K..] x [batch.., K.., N..], multiplies them with the oracle's MatMul (reference GEMM kernel and
+    accumulation order) and permutes the product into the requested label order (einsum_matmul)."""
+    eq = "".join(equation.split())
+    lhs, _, rhs = eq.partition("->")
+    terms = lhs.split(",")
+    if "->" not in eq:
+        letters = "".join(terms)
+        rhs = "".join(sorted(c for c in set(letters) if letters.count(c) == 1))
+    sizes = {}
+    for t, x in zip(terms, ins):
+        for c, n in zip(t, x.shape):
+            sizes[c] = n
+
+    def view(term, x, order):
+        x = np.asarray(x, np.float32)
+        have = [c for c in order if c in term]
+        x = np.transpose(x, [term.index(c) for c in have])
+        shape = [sizes[c] if c in term else 1 for c in order]
+        return np.broadcast_to(x.reshape(shape), [sizes[c] for c in order])
+
+    def contract(ta, a, tb, b, out):
+        batch = [c for c in out if c in ta and c in tb]
+        ms = [c for c in out if c in ta and c not in tb]
+        ns = [c for c in out if c in tb and c not in ta]
+        ks = []
+        for c in ta + tb:
+            if c not in out and c not in ks:
+                ks.append(c)
+        prod = lambda ls: int(np.prod([sizes[c] for c in ls])) if ls else 1  # noqa: E731
+        a3 = np.ascontiguousarray(view(ta, a, batch + ms + ks)).reshape(prod(batch), prod(ms), prod(ks))
+        b3 = np.ascontiguousarray(view(tb, b, batch + ks + ns)).reshape(prod(batch), prod(ks), prod(ns))
+        p = o.matmul(a3, b3).reshape([sizes[c] for c in batch + ms + ns])
+        order = batch + ms + ns
+        return np.array(np.transpose(p, [order.index(c) for c in out]), order="C")
+
+    if len(terms) == 1:
+        return np.array(view(terms[0], ins[0], list(rhs)), order="C")
+    cur_t, cur = terms[0], ins[0]
+    for i in range(1, len(terms)):
+        if i + 1 < len(terms):
+            later = set(rhs).union(*terms[i + 1:])
+            step = []
+            for c in cur_t + terms[i]:
+                if c in later and c not in step:
+                    step.append(c)
+            step = "".join(step)
+        else:
+            step = rhs
+        cur = contract(cur_t, cur, terms[i], ins[i], step)
+        cur_t = step
+    return cur
+
+
 def run_graph(builder, inputs, outputs=None):
     """``inputs``: arrays in graph-input order.  Returns the graph outputs (or the requested node ids)."""
     vals = {}
@@ -72,6 +127,8 @@ def run_graph(builder, inputs, outputs=None):
         elif t == "Gemm":
             y = o.gemm_op(ins[0], ins[1], ins[2] if len(ins) > 2 else None, a.get(0, 0.0), a.get(1, 0.0),
                           bool(a.get(2)), bool(a.get(3)))
+        elif t == "Einsum":
+            y = einsum(a[0], ins)
         elif t == "MatMul":
             y = o.matmul(np.ascontiguousarray(ins[0]), np.ascontiguousarray(ins[1]))
         elif t == "Transpose":

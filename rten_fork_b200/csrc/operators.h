@@ -206,6 +206,12 @@ class ReduceMeanOp : public Operator {  // src/ops/reduce.rs reduce_mean
   const char* name() const override { return "ReduceMean"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
 };
+class EinsumOp : public Operator {  // src/ops/einsum.rs; einsum.cu
+ public:
+  std::string equation;
+  const char* name() const override { return "Einsum"; }
+  rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+};
 class ShapeOpsOp : public Operator {  // Unsqueeze / Squeeze: metadata-only changes of a contiguous tensor
  public:
   bool squeeze = false;

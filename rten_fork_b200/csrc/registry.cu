@@ -240,6 +240,13 @@ const OpRegistry& OpRegistry::with_all_ops() {
       out->reset(op);
       return RTG_OK;
     });
+    r->register_op(Op_Einsum, [](const OpNodeView& n, std::unique_ptr<Operator>* out) -> rtg_status {
+      if (n.attrs_type != Attrs_EinsumAttrs || !n.attrs.valid) return attr_error("EinsumAttrs");
+      EinsumOp* op = new EinsumOp();  // EinsumAttrs: equation:0   (src/schema.fbs:274-276)
+      op->equation = n.attrs.str(0);
+      out->reset(op);
+      return RTG_OK;
+    });
     r->register_op(Op_Slice, simple<SliceOp>());
     r->register_op(Op_Shape, simple<ShapeOp>());
     r->register_op(Op_Expand, simple<ExpandOp>());

@@ -191,6 +191,10 @@ class ModelBuilder:
                                     (1, "bool", 1 if keep_dims else None)])
 
     @staticmethod
+    def einsum_attrs(equation):
+        return ("EinsumAttrs", [(0, "str", str(equation))])
+
+    @staticmethod
     def concat_attrs(axis=0):
         return ("ConcatAttrs", [(0, "i32", int(axis))])
 
@@ -244,6 +248,8 @@ class ModelBuilder:
                             continue
                         if kind.startswith("vec_"):
                             enc.append((fid, "offset", fb.vector(kind[4:], val)))
+                        elif kind == "str":
+                            enc.append((fid, "offset", fb.string(val)))
                         else:
                             enc.append((fid, kind, val))
                     attrs_h, attrs_id = fb.table(enc), ATTR_ID[tname]

@@ -290,3 +290,55 @@ def test_run_async_pipelined_matches_run(rtg, ctx):
     with pytest.raises(rtg.RtgError, match="too small"):
         model.run_async([xs[3].numpy()], [np.empty((4, 10), np.float32)])
     np.testing.assert_array_equal(model.run_async([xs[1].numpy()], [o]).wait()[0], want[1])
+
+
+EINSUM_CASES = [  # the equation forms of the reference's tests (src/ops/einsum.rs:740-960) plus an attention pair
+    ("ij->ji", [(3, 5)]), ("ij,jk->ik", [(3, 5), (5, 4)]), ("ij,jk", [(3, 5), (5, 4)]), ("ji,kj->ik", [(5, 3), (4, 5)]),
+    ("ij,jk->ki", [(3, 5), (5, 4)]), ("bhwc,hkc->bhwk", [(2, 3, 4, 6), (3, 5, 6)]), ("i,i->", [(7,), (7,)]),
+    ("ij,j->i", [(3, 5), (5,)]), ("j,jk->k", [(5,), (5, 4)]), ("ij,ij->", [(3, 5), (3, 5)]), ("ij,j->", [(3, 5), (5,)]),
+    ("i,j->ij", [(3,), (4,)]), ("bhqd,bhkd->bhqk", [(2, 12, 128, 64), (2, 12, 128, 64)]),
+    ("bhqk,bhkd->bqhd", [(2, 4, 16, 16), (2, 4, 16, 32)]), ("ab,bc,cd,de->ea", [(2, 3), (3, 4), (4, 5), (5, 6)]),
+    (" i j , j k -> i k ", [(3, 5), (5, 4)]),
+]
+
+
+@pytest.mark.parametrize("eq,shapes", EINSUM_CASES, ids=[c[0].strip().replace(" ", "") + f"#{i}" for i, c in enumerate(EINSUM_CASES)])
+def test_einsum(rtg, ctx, oracle, math_mode, eq, shapes):
+    """Einsum (src/ops/einsum.rs) lowered to permute -> batched MatMul on the contraction kernel -> permute, against
+    the oracle's evaluation of the same lowering."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = oracle.XorShiftRng(1234)
+    b = ModelBuilder()
+    ins = [b.add_value(f"x{i}", list(s)) for i, s in enumerate(shapes)]
+    b.inputs = ins
+    b.outputs = [b.op("Einsum", ins, ModelBuilder.einsum_attrs(eq))]
+    xs = [rng.fill(s) - 0.5 for s in shapes]
+    _m, got, want = _run_both(ctx, b, xs)
+    assert got[0].shape == want[0].shape
+    np.testing.assert_allclose(got[0], want[0], rtol=math_mode["rtol"] * 10, atol=math_mode["rtol"])
+
+
+def test_einsum_errors(rtg, ctx):
+    """OpError strings of EinsumExpr::parse / einsum() (src/ops/einsum.rs:27-93,151-203), and the forms this path
+    does not build fail loudly."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    def run(eq, shapes):
+        b = ModelBuilder()
+        ins = [b.add_value(f"x{i}", list(s)) for i, s in enumerate(shapes)]
+        b.inputs = ins
+        b.outputs = [b.op("Einsum", ins, ModelBuilder.einsum_attrs(eq))]
+        m = rtg.Model.load(b.build(), ctx=ctx)
+        return m.run([np.zeros(s, np.float32) for s in shapes])
+
+    for eq, shapes, msg in [("->ij", [(2, 2)], "Einsum equation must have at least one term"),
+                            ("iJ,jk->ik", [(2, 2), (2, 2)], "Input term is invalid"),
+                            ("ij,jk->ik", [(2, 2)], "Number of terms in Einsum equation does not match input tensor count"),
+                            ("ijk,jk->ik", [(2, 2), (2, 2)], "Einsum term dimension count does not match input tensor"),
+                            ("ij,jk->ik", [(2, 3), (4, 2)], "do not match"),
+                            ("ii->i", [(2, 2)], "not supported on this path"),
+                            ("...ij,...jk->...ik", [(2, 2, 2), (2, 2, 2)], "not supported on this path"),
+                            ("ij->i", [(2, 2)], "not supported on this path")]:
+        with pytest.raises(rtg.RtgError, match=msg):
+            run(eq, shapes)

@@ -221,3 +221,23 @@ def test_conv_transpose_oracle_matches_reference_literals():
         else:
             out, pads = o.conv_transpose_output_size_and_padding(c["in"], c["k"], c["pad"], c["s"])
             assert list(out) == c["out"] and list(pads) == c["pads"]
+
+
+def test_einsum_oracle_against_float64():
+    """The Einsum restatement (permute -> MatMul -> permute, left-to-right folding) against numpy's float64 einsum on
+    the equation forms the reference's tests use (src/ops/einsum.rs:740-960)."""
+    import graph_oracle
+
+    rng = np.random.default_rng(0)
+    f = lambda *s: rng.standard_normal(s).astype(np.float32)  # noqa: E731
+    cases = [("ij->ji", [f(3, 5)]), ("ij,jk->ik", [f(3, 5), f(5, 4)]), ("ij,jk", [f(3, 5), f(5, 4)]),
+             ("ji,kj->ik", [f(5, 3), f(4, 5)]), ("ij,jk->ki", [f(3, 5), f(5, 4)]),
+             ("bhwc,hkc->bhwk", [f(2, 3, 4, 6), f(3, 5, 6)]), ("i,i->", [f(7), f(7)]), ("ij,j->i", [f(3, 5), f(5)]),
+             ("j,jk->k", [f(5), f(5, 4)]), ("ij,ij->", [f(3, 5), f(3, 5)]), ("ij,j->", [f(3, 5), f(5)]),
+             ("i,j->ij", [f(3), f(4)]), ("bhqd,bhkd->bhqk", [f(2, 3, 4, 8), f(2, 3, 5, 8)]),
+             ("ab,bc,cd,de->ea", [f(2, 3), f(3, 4), f(4, 5), f(5, 6)])]
+    for eq, xs in cases:
+        want = np.einsum(eq, *[x.astype(np.float64) for x in xs])
+        got = graph_oracle.einsum(eq, xs)
+        assert got.shape == want.shape, eq
+        np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-5, err_msg=eq)
