@@ -452,7 +452,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == kMmaWarp) {
     // ===================================================== MMA issuer
     if (MODE != 0) ptx::reg_dealloc<kRegsOther>();
-    if (lane == 0) {
+    // The whole warp walks the loop (uniform control flow: stage / descriptor arithmetic stays in uniform registers and
+    // the waits are not behind a divergent branch); one elected lane issues the MMAs and their commits.
+    {
       constexpr uint32_t idesc = ptx::make_idesc_tf32(kBM, BN, 0, B_MAJOR);
       // K-major operands: 128B swizzle, 8-row groups 1024 B apart.  MN-major fp32 operands must use the
       // 128B-swizzle-with-32B-atoms layout: 4 k-rows (512 B) per atom, 32-column chunks 4096 B apart.
@@ -494,6 +496,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #endif
             PROF_MARK(1, 5);  // first operands ready
             const uint32_t a_lo = a_lo0 + so, b_lo = b_lo0 + so;
+            if (ptx::elect_one()) {
 #pragma unroll
             for (int k = 0; k < kBK / 8; ++k) {
               const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
@@ -514,6 +517,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             }
             ptx::mma_commit(empty_bar(s));
+            }
 #ifdef RTG_PROF
             prof_acc_[2] += clock64() - ti_;
 #endif
@@ -524,7 +528,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               ph ^= 1u;
             }
           }
-          ptx::mma_commit(tfull_bar(as));
+          if (ptx::elect_one()) ptx::mma_commit(tfull_bar(as));
           PROF_MARK_LAST(1, 6);  // last accumulator commit
           if (++as == 2) {
             as = 0;
@@ -532,7 +536,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
-      PROF_DUMP(1);
+      if (lane == 0) PROF_DUMP(1);
     }
   } else if (warp < Cfg::kEpiWarps) {
     // ===================================================== epilogue
