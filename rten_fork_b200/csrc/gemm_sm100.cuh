@@ -331,7 +331,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == kTmaWarp) {
     // ===================================================== TMA producer
     if (MODE != 0) ptx::reg_dealloc<kRegsOther>();
-    if (lane == 0) {
+    // Like the MMA warp, the whole warp walks the loop and an elected lane issues: tile coordinates, ring slots and
+    // phases are warp-uniform values.
+    {
       PROF_DECL;
       int s = 0;
       uint32_t ph = 0;
@@ -392,17 +394,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const long long ti_ = clock64();
 #endif
           PROF_MARK(0, 5);  // first TMA issue
-          ptx::mbar_expect_tx(fa, MODE != 0 ? kABytes : Cfg::kRawBytes);
-          if (A_KIND == 0) {
-            ptx::tma_load_2d(a_dst, &tmA, fa, kb * kBK, m0);
-          } else if (A_KIND == 3) {
-            ptx::tma_load_4d(a_dst, &tmA, fa, kb * kBK, m0, z0 * args.ic.bat_a0, z1 * args.ic.bat_a1);
-          } else if (A_KIND == 2) {
-            // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
-            ptx::tma_load_4d(a_dst, &tmA, fa, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
-          } else {
-            ptx::tma_load_im2col_4d(a_dst, &tmA, fa, ic_c_off + cb * kBK, pix_w, pix_h, pix_n,
-                                    static_cast<uint16_t>(tap_x * ic_dil_w), static_cast<uint16_t>(tap_y * ic_dil_h));
+          const bool leader = ptx::elect_one() != 0;
+          if (leader) {
+            ptx::mbar_expect_tx(fa, MODE != 0 ? kABytes : Cfg::kRawBytes);
+            if (A_KIND == 0) {
+              ptx::tma_load_2d(a_dst, &tmA, fa, kb * kBK, m0);
+            } else if (A_KIND == 3) {
+              ptx::tma_load_4d(a_dst, &tmA, fa, kb * kBK, m0, z0 * args.ic.bat_a0, z1 * args.ic.bat_a1);
+            } else if (A_KIND == 2) {
+              // {window floats, output column, padded input row, image}: columns past ow are zero-filled by TMA
+              ptx::tma_load_4d(a_dst, &tmA, fa, 0, pix_w, pix_h + kb * ic_dil_h, pix_n);
+            } else {
+              ptx::tma_load_im2col_4d(a_dst, &tmA, fa, ic_c_off + cb * kBK, pix_w, pix_h, pix_n,
+                                      static_cast<uint16_t>(tap_x * ic_dil_w), static_cast<uint16_t>(tap_y * ic_dil_h));
+            }
+          }
+          if (A_KIND == 1) {
             if (++cb == ic_c_blocks) {
               cb = 0;
               if (++tap_x == ic_kw) {
@@ -417,12 +424,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               pa ^= 1u;
             }
             PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
-            ptx::mbar_expect_tx(fb, MODE == 2 ? 2 * Cfg::kBBytes : Cfg::kBBytes);
-            // MODE 2: the bf16 correction tile B' = [bf16(B) 8 | bf16(lo(B)) 8] per group of 8 k was written to global
-            // memory once (weights: at load; otherwise by a pre-pass), K-major whatever B's own layout
-            if (MODE == 2) ptx::tma_load_2d(b_dst + Cfg::kBBytes, &tmB2, fb, kb * kBK, n0);
+            if (leader) {
+              ptx::mbar_expect_tx(fb, MODE == 2 ? 2 * Cfg::kBBytes : Cfg::kBBytes);
+              // MODE 2: the bf16 correction tile B' = [bf16(B) 8 | bf16(lo(B)) 8] per group of 8 k was written to
+              // global memory once (weights: at load; otherwise by a pre-pass), K-major whatever B's own layout
+              if (MODE == 2) ptx::tma_load_2d(b_dst + Cfg::kBBytes, &tmB2, fb, kb * kBK, n0);
+            }
           }
-          if (A_KIND == 3) {
+          if (!leader) {
+            // only the elected lane issues the B loads
+          } else if (A_KIND == 3) {
             const int bz0 = z0 * args.ic.bat_b0, bz1 = z1 * args.ic.bat_b1;
             if (B_MAJOR == 0) {
               ptx::tma_load_4d(b_dst, &tmB, fb, kb * kBK, n0, bz0, bz1);
@@ -447,7 +458,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
-      PROF_DUMP(0);
+      if (lane == 0) PROF_DUMP(0);
     }
   } else if (warp == kMmaWarp) {
     // ===================================================== MMA issuer
