@@ -169,12 +169,16 @@ struct GemmCfg {
   static constexpr int kStagesSmem = (kMaxSmem - kARingBytes) / kStageBytes;
   static constexpr int kStagesTmem = MODE ? (512 - 2 * BN) / kTmemAStageCols : 8;  // accumulators take 2 * BN columns
   static constexpr int kStagesRaw = kStagesSmem < kStagesTmem ? kStagesSmem : kStagesTmem;
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  // MODE 2: even, so that a stage is always served by the same one of the two split warps of a lane quarter
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : MODE == 2 ? (kStagesRaw & ~1) : kStagesRaw;
   static constexpr int kSmemBytes = kARingBytes + kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
   // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
   // and 6 split warps so that the operand split keeps up with the tensor core.
   static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
-  static constexpr int kXfThreads = MODE ? 192 : 0;
+  // MODE 2 has no B split.  One warp's operand-split loop (wait -> LDS -> split -> tcgen05.st -> wait::st -> arrive) takes
+  // ~640 busy cycles per k-block against ~480 for the MMAs, so two warps per TMEM lane quarter take alternate blocks:
+  // 8 split warps, plus 2 idle warps because ptxas sizes the launch register file for whole warpgroups (640 threads x 96).
+  static constexpr int kXfThreads = MODE == 2 ? 320 : MODE ? 192 : 0;
   static constexpr int kThreads = (kEpiWarps + 2) * 32 + kXfThreads;
   static constexpr int kTmemCols = MODE ? 512 : (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
 };
@@ -325,7 +329,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // MODE 1: 512 threads start with 128 registers each.  An epilogue thread carries BN/2 running sums plus a 32-column
   // chunk and spilled at that size; the TMA / MMA / operand-split warpgroups need fewer, so every role branch starts
   // by re-balancing the register file: 8 x 32 x kRegsEpi + 8 x 32 x kRegsOther = 64 K.
-  constexpr int kRegsEpi = 152, kRegsOther = 104;
+  // MODE 2 (20 warps x 96 at launch = 61440): 8 x 32 x 144 + 12 x 32 x 64 = 61440.  setmaxnreg is a warpgroup-wide
+  // instruction: the four warps of a group (8-11: TMA, MMA, split 0-1; 12-15: split 2-5; 16-19: split 6-7, idle) must
+  // ask for the same count.
+  constexpr int kRegsEpi = MODE == 2 ? 144 : 152, kRegsOther = MODE == 2 ? 64 : 104;
   const bool bias_table = args.bias_mode == BIAS_COL && n_tiles * BN <= Cfg::kBiasTable;
 
   if (warp == kTmaWarp) {
@@ -759,6 +766,80 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0 && lane == 0) {
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
+    }
+  } else if (MODE == 2 && warp > kMmaWarp) {
+    // ===================================================== TF32 + bf16 operand split (A only)
+    // Thread = one row of the A tile.  Per group of 8 k the row goes to tensor memory as its raw bits (the TF32 MMA
+    // truncates them itself) and as A' = four words of bf16 pairs of lo(A) = A - trunc_tf32(A) plus four of bf16(A).
+    ptx::reg_dealloc<kRegsOther>();
+    const int sw = warp - (kMmaWarp + 1);
+    if (sw < 8) {
+      PROF_DECL;
+      int total = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int kb_begin = (unit / num_tiles) * kb_per_split;
+        total += min(num_kb, kb_begin + kb_per_split) - kb_begin;
+      }
+      const int first = sw >> 2;  // the two warps of a lane quarter take alternate blocks of the CTA's flat k-block stream
+      const int q = warp & 3;     // TMEM lane quarter this warp may write
+      const int row = q * 32 + lane;
+      const uint32_t swz = row & 7;
+      int ia = first % kAStages, s = first % kStages;
+      uint32_t pa = 0, ph = 0;
+      static_assert(MODE != 2 || kStages % 2 == 0, "a pipeline stage must always be served by the same one of the two warps");
+      for (int it = first; it < total; it += 2) {
+        // The A ring has 3 slots, so this warp only sees every other phase of a slot's barriers and a parity wait
+        // alone could be satisfied by the phase before the one it wants.  The slot's previous round (served by the
+        // other warp of the quarter) has to be over first: its `aempty` phase cannot run ahead of this warp.
+        PROF_WAIT(0, ptx::mbar_wait_parked(aempty_bar(ia), pa ^ 1u));
+        PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
+        const uint32_t src = smem_base + ia * kABytes + row * 128;
+        // the TMEM slot of this stage is free once the MMAs of its previous use have completed
+        PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
+        ptx::tc_fence_after();
+        const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r[16], w[16];
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 x = ptx::lds_v4(src + (((4 * h + j4) ^ swz) << 4));
+            r[4 * j4 + 0] = __float_as_uint(x.x), r[4 * j4 + 1] = __float_as_uint(x.y);
+            r[4 * j4 + 2] = __float_as_uint(x.z), r[4 * j4 + 3] = __float_as_uint(x.w);
+          }
+          ptx::tmem_st_32x16(dst + 16 * h, r);
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int k0 = 8 * g + 2 * i;
+              const float x0 = __uint_as_float(r[k0]), x1 = __uint_as_float(r[k0 + 1]);
+              w[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(r[k0] & 0xFFFFE000u),
+                                              x1 - __uint_as_float(r[k0 + 1] & 0xFFFFE000u));
+              w[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
+            }
+          }
+          ptx::tmem_st_32x16(dst + kBK + 16 * h, w);
+        }
+        // the raw tile has been read: hand its slot back to the TMA producer
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
+        PROF_WAIT(2, ptx::tmem_st_wait());
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(xf_bar(s));
+        ia += 2;
+        if (ia >= kAStages) {
+          ia -= kAStages;
+          pa ^= 1u;
+        }
+        s += 2;
+        if (s >= kStages) {
+          s -= kStages;
+          ph ^= 1u;
+        }
+      }
+      if (sw == 0 && lane == 0) PROF_DUMP(3);
     }
   } else if (MODE != 0 && warp > kMmaWarp) {
     // ===================================================== 3xTF32 operand split
