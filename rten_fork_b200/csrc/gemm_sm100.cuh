@@ -170,7 +170,7 @@ struct GemmCfg {
   static constexpr int kStagesTmem = MODE ? (512 - 2 * BN) / kTmemAStageCols : 8;  // accumulators take 2 * BN columns
   static constexpr int kStagesRaw = kStagesSmem < kStagesTmem ? kStagesSmem : kStagesTmem;
   // MODE 2: even, so that a stage is always served by the same one of the two split warps of a lane quarter
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : MODE == 2 ? (kStagesRaw & ~1) : kStagesRaw;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : MODE != 0 ? (kStagesRaw & ~1) : kStagesRaw;
   static constexpr int kSmemBytes = kARingBytes + kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
   // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
   // and 6 split warps so that the operand split keeps up with the tensor core.
@@ -178,7 +178,7 @@ struct GemmCfg {
   // MODE 2 has no B split.  One warp's operand-split loop (wait -> LDS -> split -> tcgen05.st -> wait::st -> arrive) takes
   // ~640 busy cycles per k-block against ~480 for the MMAs, so two warps per TMEM lane quarter take alternate blocks:
   // 8 split warps, plus 2 idle warps because ptxas sizes the launch register file for whole warpgroups (640 threads x 96).
-  static constexpr int kXfThreads = MODE == 2 ? 320 : MODE ? 192 : 0;
+  static constexpr int kXfThreads = MODE ? 320 : 0;
   static constexpr int kThreads = (kEpiWarps + 2) * 32 + kXfThreads;
   static constexpr int kTmemCols = MODE ? 512 : (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
 };
@@ -297,7 +297,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
       // one arrival per split warp (MODE 2: the four A warps only; its B' tile arrives by TMA)
-      ptx::mbar_init(xf_bar(s), MODE == 2 ? 4 : Cfg::kXfThreads / 32 > 0 ? Cfg::kXfThreads / 32 : 1);
+      ptx::mbar_init(xf_bar(s), MODE == 2 ? 4 : 6);  // A-split warps of the four lane quarters (+ 2 B-lo warps)
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
@@ -332,7 +332,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // MODE 2 (20 warps x 96 at launch = 61440): 8 x 32 x 144 + 12 x 32 x 64 = 61440.  setmaxnreg is a warpgroup-wide
   // instruction: the four warps of a group (8-11: TMA, MMA, split 0-1; 12-15: split 2-5; 16-19: split 6-7, idle) must
   // ask for the same count.
-  constexpr int kRegsEpi = MODE == 2 ? 144 : 152, kRegsOther = MODE == 2 ? 64 : 104;
+  constexpr int kRegsEpi = 144, kRegsOther = 64;
   const bool bias_table = args.bias_mode == BIAS_COL && n_tiles * BN <= Cfg::kBiasTable;
 
   if (warp == kTmaWarp) {
@@ -767,10 +767,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
     }
-  } else if (MODE == 2 && warp > kMmaWarp) {
-    // ===================================================== TF32 + bf16 operand split (A only)
-    // Thread = one row of the A tile.  Per group of 8 k the row goes to tensor memory as its raw bits (the TF32 MMA
-    // truncates them itself) and as A' = four words of bf16 pairs of lo(A) = A - trunc_tf32(A) plus four of bf16(A).
+  } else if (MODE != 0 && warp > kMmaWarp) {
+    // ===================================================== operand split (fp32-accurate modes)
+    // x = hi + lo with hi = x truncated to TF32 (the tensor core reads that from the raw fp32 bits by itself) and
+    // lo = x - hi (exact in fp32).  Thread = one row of the A tile; per block the row goes to the stage's tensor-memory
+    // slot as its raw bits plus, MODE 1: lo rounded to nearest TF32 (+ half an ulp, the tensor core drops the low 13
+    // bits); MODE 2: A' = per group of 8 k four words of bf16 pairs of lo(A) and four of bf16(A).
+    // MODE 1 only: warps 8-9 of the role write the lo plane of B next to the raw B tile.
+    auto lo_of = [](float x) {
+      return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u)) + 0x1000u;
+    };
     ptx::reg_dealloc<kRegsOther>();
     const int sw = warp - (kMmaWarp + 1);
     if (sw < 8) {
@@ -786,7 +792,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t swz = row & 7;
       int ia = first % kAStages, s = first % kStages;
       uint32_t pa = 0, ph = 0;
-      static_assert(MODE != 2 || kStages % 2 == 0, "a pipeline stage must always be served by the same one of the two warps");
+      static_assert(MODE == 0 || kStages % 2 == 0, "a pipeline stage must always be served by the same one of the two warps");
       for (int it = first; it < total; it += 2) {
         // The A ring has 3 slots, so this warp only sees every other phase of a slot's barriers and a parity wait
         // alone could be satisfied by the phase before the one it wants.  The slot's previous round (served by the
@@ -808,16 +814,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             r[4 * j4 + 2] = __float_as_uint(x.z), r[4 * j4 + 3] = __float_as_uint(x.w);
           }
           ptx::tmem_st_32x16(dst + 16 * h, r);
+          if (MODE == 2) {
 #pragma unroll
-          for (int g = 0; g < 2; ++g) {
+            for (int g = 0; g < 2; ++g) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int k0 = 8 * g + 2 * i;
-              const float x0 = __uint_as_float(r[k0]), x1 = __uint_as_float(r[k0 + 1]);
-              w[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(r[k0] & 0xFFFFE000u),
-                                              x1 - __uint_as_float(r[k0 + 1] & 0xFFFFE000u));
-              w[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
+              for (int i = 0; i < 4; ++i) {
+                const int k0 = 8 * g + 2 * i;
+                const float x0 = __uint_as_float(r[k0]), x1 = __uint_as_float(r[k0 + 1]);
+                w[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(r[k0] & 0xFFFFE000u),
+                                                x1 - __uint_as_float(r[k0 + 1] & 0xFFFFE000u));
+                w[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
+              }
             }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = lo_of(__uint_as_float(r[j]));
           }
           ptx::tmem_st_32x16(dst + kBK + 16 * h, w);
         }
@@ -840,106 +851,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       if (sw == 0 && lane == 0) PROF_DUMP(3);
-    }
-  } else if (MODE != 0 && warp > kMmaWarp) {
-    // ===================================================== 3xTF32 operand split
-    // x = hi + lo with hi = x truncated to TF32 (the tensor core reads that from the raw fp32 bits by itself) and
-    // lo = x - hi (exact in fp32) rounded to nearest TF32: + half an ulp, the tensor core drops the low 13 bits.
-    // Warps 0-3 of this role own the A tile, one row per thread: the row goes to tensor memory as a hi plane (raw
-    // bits) and a lo plane, from where the MMAs read it.  Warps 4-5 write the lo plane of B next to the raw B tile.
-    ptx::reg_dealloc<kRegsOther>();
-    const int t = threadIdx.x - (Cfg::kEpiWarps + 2) * 32;
-    const int sw = t >> 5;
-    auto lo_of = [](float x) {
-      return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u)) + 0x1000u;
-    };
-    int s = 0;
-    uint32_t ph = 0;
-    PROF_DECL;
-    if (sw < 4) {
-      // ---- A rows.  Nothing here depends on which tile a k-block belongs to, so the warp walks the CTA's k-blocks as
-      // one flat stream, software-pipelined: the tensor-memory stores of block i are in flight while block i + 1 is
-      // read from shared memory and split, and only then does the warp wait for them and release block i to the MMAs.
-      int total = 0;
-      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const int kb_begin = (unit / num_tiles) * kb_per_split;
-        total += min(num_kb, kb_begin + kb_per_split) - kb_begin;
-      }
-      int ia = 0;
-      uint32_t pa = 0;
-      const int q = warp & 3;  // TMEM lane quarter this warp may write
-      const int row = q * 32 + lane;
-      const uint32_t swz = row & 7;
-      uint32_t hi[32], lo[32];
-      auto load_block = [&]() {
-        PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
-#ifdef RTG_PROF
-        const long long tl_ = clock64();
-#endif
-        const uint32_t src = smem_base + ia * kABytes + row * 128;
-#pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 x = ptx::lds_v4(src + ((j4 ^ swz) << 4));
-          hi[4 * j4 + 0] = __float_as_uint(x.x), hi[4 * j4 + 1] = __float_as_uint(x.y);
-          hi[4 * j4 + 2] = __float_as_uint(x.z), hi[4 * j4 + 3] = __float_as_uint(x.w);
-        }
-        // the raw tile is in registers: hand its slot back to the TMA producer
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
-        if (++ia == kAStages) {
-          ia = 0;
-          pa ^= 1u;
-        }
-        if (MODE == 2) {
-          // A': per group of 8 k, four words of bf16 pairs of lo(A) and four of bf16(A)
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int k0 = 8 * g + 2 * i;
-              const float x0 = __uint_as_float(hi[k0]), x1 = __uint_as_float(hi[k0 + 1]);
-              lo[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(hi[k0] & 0xFFFFE000u),
-                                               x1 - __uint_as_float(hi[k0 + 1] & 0xFFFFE000u));
-              lo[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
-            }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) lo[j] = lo_of(__uint_as_float(hi[j]));
-        }
-#ifdef RTG_PROF
-        prof_acc_[3] += clock64() - tl_;  // LDS + split arithmetic of one block
-#endif
-      };
-      if (total > 0) load_block();
-      for (int it = 0; it < total; ++it) {
-        // the TMEM slot of this stage is free once the MMAs of its previous use have completed
-        PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
-        ptx::tc_fence_after();
-        const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
-        ptx::tmem_st_32x32(dst, hi);
-        ptx::tmem_st_32x32(dst + kBK, lo);
-        if (it + 1 < total) load_block();
-        PROF_WAIT(2, ptx::tmem_st_wait());
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(xf_bar(s));
-        if (++s == kStages) {
-          s = 0;
-          ph ^= 1u;
-        }
-      }
     } else if (MODE == 1) {
       // ---- B lo plane (MODE 2 has no B split: its B' tile arrives by TMA and these two warps idle)
+      const int t = threadIdx.x - (kMmaWarp + 1 + 8) * 32;  // 0..63
+      int s = 0;
+      uint32_t ph = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
         const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           const uint32_t stage = ring_base + s * Cfg::kStageBytes;  // [B raw][B lo]
-          PROF_WAIT(0, ptx::mbar_wait_parked(full_bar(s), ph));
+          ptx::mbar_wait_parked(full_bar(s), ph);
           constexpr int kBVecs = Cfg::kBBytes / 16;
           const uint32_t braw = stage, blo = braw + Cfg::kBBytes;
 #pragma unroll 4
-          for (int i = t - 128; i < kBVecs; i += 64) {
+          for (int i = t; i < kBVecs; i += 64) {
             const float4 x = ptx::lds_v4(braw + i * 16);
             ptx::sts_v4(blo + i * 16, make_float4(__uint_as_float(lo_of(x.x)), __uint_as_float(lo_of(x.y)),
                                                   __uint_as_float(lo_of(x.z)), __uint_as_float(lo_of(x.w))));
@@ -954,7 +879,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
-    if (t == 0) PROF_DUMP(3);
   }
 
   ptx::tc_fence_before();
