@@ -103,6 +103,26 @@ rtg_status rtg_gemm(rtg_ctx* ctx, int32_t device, float* out, size_t out_len, si
                     size_t m, size_t k, ptrdiff_t a_rs, ptrdiff_t a_cs, const float* b, size_t b_rows, size_t n,
                     ptrdiff_t b_rs, ptrdiff_t b_cs, float alpha, float beta, const float* bias, size_t bias_len);
 
+/* Split-K GEMM that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arithmetic as rtg_gemm's split-K path (partial sums of `splits` K ranges in scratch planes, folded in split
+ * order by the reduction pass together with alpha / beta / bias[m]); the scratch is a file-scope device array of
+ * RTG_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit, instead of the context pool.
+ *   - all pointers are DEVICE pointers on the context's device; a is a dense row-major [m, k], b a dense row-major
+ *     [k, n]; a, b and out 16-byte aligned, k, n and out_row_stride multiples of 4 (so that no operand needs a gathered
+ *     copy); k must be long enough to split (two 32-deep blocks in TF32 mode, more than 128 otherwise).
+ *   - splits: 0 = the library's choice (at least 2), else the requested number of K ranges.
+ *   - the call needs  splits * m * n * 4  bytes (+ n * ceil32(k) * 4 in RTG_MATH_TF32_BF16X2): anything beyond
+ *     RTG_STATIC_SCRATCH_BYTES fails with RTG_ERR_UNSUPPORTED_VALUE and a message naming both numbers.
+ *   - no cudaMalloc / cudaFree / pool call; fails if per-launch kernel timing (rtg_ctx_set_kernel_timing) is on.
+ *   - ALL calls on a GPU share the one array (it keeps the last call's contents; nothing in it has to start at zero,
+ *     every element is written before it is read): calls that overlap on the GPU — two streams, two contexts of one
+ *     device — race.  Calls on one stream are ordered and safe. */
+#define RTG_STATIC_SCRATCH_BYTES (16u << 20)
+rtg_status rtg_gemm_static_scratch(rtg_ctx* ctx, float* out, size_t out_len, size_t out_row_stride, const float* a,
+                                   size_t m, size_t k, const float* b, size_t n, float alpha, float beta,
+                                   const float* bias, int32_t splits);
+
 /* N-split GEMM across GPUs (BASELINE.json configs[4]).  The reference has no multi-device path: this is
  * the exchange step the split adds after GemmExecutor::gemm (src/gemm.rs:448-542), fused into the GEMM epilogue.
  * Every rank owns a peer-visible row-major [m, n_total] result buffer (rtg_symm_alloc; the 64-byte handle is sent to the

@@ -86,6 +86,21 @@ extern "C" rtg_status rtg_gemm(rtg_ctx* ctx_, int32_t device, float* out, size_t
   return RTG_OK;
 }
 
+// ---------------------------------------------------------------- split-K GEMM on static scratch (allocates nothing)
+extern "C" rtg_status rtg_gemm_static_scratch(rtg_ctx* ctx_, float* out, size_t out_len, size_t out_row_stride,
+                                              const float* a, size_t m, size_t k, const float* b, size_t n, float alpha,
+                                              float beta, const float* bias, int32_t splits) {
+  Context* ctx = reinterpret_cast<Context*>(ctx_);
+  if (!ctx) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
+  if (!out || !a || !b) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  if (m == 0 || n == 0) return RTG_OK;
+  if (out_row_stride < n || (m - 1) * out_row_stride + n > out_len)
+    return set_error(RTG_ERR_PANIC, "Output buffer should be large enough");
+  RTG_CUDA(cudaSetDevice(ctx->device));
+  return gemm_splitk_static(ctx, a, static_cast<int64_t>(m), static_cast<int64_t>(k), b, static_cast<int64_t>(n), out,
+                            static_cast<int64_t>(out_row_stride), alpha, beta, bias, splits);
+}
+
 // ---------------------------------------------------------------- N-split GEMM with peer stores
 extern "C" rtg_status rtg_symm_alloc(rtg_ctx* ctx_, size_t bytes, void** dptr, uint8_t handle[RTG_SYMM_HANDLE_BYTES]) {
   Context* ctx = reinterpret_cast<Context*>(ctx_);

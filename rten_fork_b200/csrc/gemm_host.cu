@@ -681,4 +681,107 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
   return dispatch<2, 0>(ctx, bn, ctx->math, ma, mb, a, g.ow, 0, nullptr, m2 ? &mb2 : nullptr);
 }
 
+// ---------------------------------------------------------------- split-K GEMM on static scratch (no allocation)
+// rtg_gemm_static_scratch (include/rten_gpu.h): the split-K form of the contraction for callers that may not allocate
+// (CUDA graph capture, tight serving loops).  Its scratch — the {N, M, splits} partial-sum planes that
+// splitk_reduce_kernel folds, preceded by the bf16 correction operand B' in RTG_MATH_TF32_BF16X2 — lives in this
+// file-scope device array instead of the context pool.  Every GPU that loads the library holds it until exit; all calls
+// share it, so calls that overlap on the GPU (two streams, two contexts of one device) race.  Nothing in it has to
+// start at zero: every plane element and every B' word is written by this call before it is read (TMA stores cover the
+// whole {N, M, splits} box, make_b_prime zero-fills beyond K).
+static __device__ __align__(256) float g_static_scratch[RTG_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+// The array's name is a host-side stand-in in host code, not a device address: resolve it once per device, with that
+// device current.
+static rtg_status static_scratch_base(Context* ctx, float** out) {
+  static float* base[64] = {};
+  static std::mutex mu;
+  if (ctx->device < 0 || ctx->device >= 64) return set_error(RTG_ERR_INVALID_VALUE, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!base[ctx->device]) {
+    RTG_CUDA(cudaSetDevice(ctx->device));
+    float* p = nullptr;
+    RTG_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch));
+    if (!p) return set_error(RTG_ERR_CUDA, "cudaGetSymbolAddress returned NULL for the static scratch array");
+    base[ctx->device] = p;
+  }
+  *out = base[ctx->device];
+  return RTG_OK;
+}
+
+rtg_status gemm_splitk_static(Context* ctx, const float* a, int64_t M, int64_t K, const float* b, int64_t N, float* D,
+                              int64_t ldd, float alpha, float beta, const float* bias, int splits_req) {
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "GEMM dims exceed i32");
+  auto aligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!aligned(a) || !aligned(b) || !aligned(D) || K % 4 != 0 || N % 4 != 0 || ldd % 4 != 0 || ldd < N)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE,
+                     "rtg_gemm_static_scratch: a, b and out must be 16-byte aligned dense row-major matrices with "
+                     "k, n and out_row_stride multiples of 4 (nothing may need a gathered copy)");
+  if (ctx->ktiming)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "rtg_gemm_static_scratch: per-launch kernel timing creates events; disable it");
+  const int64_t num_kb = div_ceil(K, kBK);
+  if (num_kb < 2) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "rtg_gemm_static_scratch: k must span at least two 32-deep blocks");
+  int mode = ctx->math;
+  int splits = 1;
+  const int bn = choose_bn(ctx, M, N, num_kb, 1, &splits);
+  if (splits_req > 0) splits = splits_req;
+  if (splits < 2) splits = 2;  // this entry point is the split-K form: at least two partial planes
+  int kbs = static_cast<int>(div_ceil(num_kb, splits));
+  if (mode != RTG_MATH_TF32) kbs = static_cast<int>(div_ceil(kbs, kChunkKb)) * kChunkKb;  // whole accumulation chunks
+  splits = static_cast<int>(div_ceil(num_kb, kbs));
+  if (splits < 2)
+    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "rtg_gemm_static_scratch: k is too short to split (needs more than 128 in the fp32-accurate modes)");
+
+  // scratch layout: [B' (TF32+BF16x2 only)][splits planes of M x N partial sums]
+  const int64_t kw = num_kb * kBK;
+  const size_t bprime_bytes = mode == RTG_MATH_TF32_BF16X2 ? static_cast<size_t>(N) * kw * 4 : 0;
+  const size_t bprime_pad = (bprime_bytes + 255) & ~static_cast<size_t>(255);
+  const int64_t plane = N * M;
+  const size_t need = bprime_pad + static_cast<size_t>(plane) * splits * sizeof(float);
+  if (need > RTG_STATIC_SCRATCH_BYTES)
+    return set_errorf(RTG_ERR_UNSUPPORTED_VALUE,
+                      "rtg_gemm_static_scratch: m=%lld n=%lld k=%lld with %d splits needs %zu bytes of scratch, the static "
+                      "buffer holds %zu (RTG_STATIC_SCRATCH_BYTES); use rtg_gemm",
+                      (long long)M, (long long)N, (long long)K, splits, need, static_cast<size_t>(RTG_STATIC_SCRATCH_BYTES));
+  float* base = nullptr;
+  RTG_TRY(static_scratch_base(ctx, &base));
+  uint32_t* bprime = reinterpret_cast<uint32_t*>(base);
+  float* ws = reinterpret_cast<float*>(reinterpret_cast<char*>(base) + bprime_pad);
+
+  CUtensorMap ma, mb, mb2, md;
+  RTG_TRY(encode_2d(ctx, &ma, a, K, M, K, kBK, kBM));
+  RTG_TRY(encode_2d(ctx, &mb, b, N, K, N, 32, kBK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B));  // row-major [K][N]: MN-major B
+  mb2 = mb;
+  if (mode == RTG_MATH_TF32_BF16X2) {
+    RTG_TRY(make_b_prime(ctx, MatView{b, K, N, N, 1}, bprime));
+    RTG_TRY(encode_2d(ctx, &mb2, reinterpret_cast<const float*>(bprime), kw, N, kw, kBK, bn));
+  }
+  RTG_TRY(encode_out_3d(ctx, &md, ws, N, M, splits, N));
+
+  GemmArgs g = {};
+  g.M = static_cast<int>(M), g.N = static_cast<int>(N), g.K = static_cast<int>(K);
+  g.num_kb = static_cast<int>(num_kb);
+  g.alpha = 1.f, g.beta = 0.f;  // the kernel only accumulates; the reduction pass applies the epilogue
+  g.bias_mode = BIAS_NONE;
+  g.D = ws;
+  g.dmap = OutMap{N, 0, 0, 0};
+  g.act = ACT_NONE;
+  g.flags = kFlagStagedD;
+  g.splits = splits, g.kb_per_split = kbs;
+
+  ReduceArgs red = {};
+  red.ws = ws, red.plane = plane, red.ws_ld = N;
+  red.splits = splits, red.M = g.M, red.N = g.N;
+  red.alpha = alpha, red.beta = beta;
+  red.bias_mode = bias ? BIAS_ROW : BIAS_NONE, red.bias = bias;
+  red.R = beta != 0.f ? D : nullptr, red.r_ld = ldd;
+  red.D = D, red.d_ld = ldd;
+  red.act = ACT_NONE;
+  red.vec_d = 1, red.vec_r = red.R ? 1 : 0;
+  ctx->pending_flops = 2.0 * g.M * g.N * g.K;
+  ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
+                              static_cast<double>(g.M) * g.N * (red.R ? 2 : 1));
+  return launch_variants<0, 1>(ctx, bn, mode, ma, mb, mb2, md, ma, g, &red);
+}
+
 }  // namespace rtg

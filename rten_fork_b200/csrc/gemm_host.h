@@ -72,6 +72,11 @@ struct WindowGeom {
 rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const WindowGeom& g, const float* wmat, int og,
                                    float* D, OutMap dmap, const Epilogue& ep);
 
+// Split-K GEMM whose scratch (partial-sum planes, B') is a file-scope device array: allocates nothing (gemm_host.cu).
+// a [M,K] and b [K,N] dense row-major device matrices, D row-major with row stride ldd; bias per row or NULL.
+rtg_status gemm_splitk_static(Context* ctx, const float* a, int64_t M, int64_t K, const float* b, int64_t N, float* D,
+                              int64_t ldd, float alpha, float beta, const float* bias, int splits_req);
+
 // dst[r*dst_ld + c] = src[r*rs + c*cs]
 rtg_status copy_strided_2d(Context* ctx, float* dst, int64_t dst_ld, const float* src, int64_t rows, int64_t cols,
                            int64_t rs, int64_t cs);

@@ -72,6 +72,23 @@ class GemmExecutor:
             C.c_float(alpha), C.c_float(beta), C.c_void_p(pbias), C.c_size_t(blen)))
         return out
 
+    def gemm_static_scratch(self, out, out_row_stride, a, b, alpha=1.0, beta=0.0, bias=None, splits=0):
+        """``rtg_gemm_static_scratch``: split-K GEMM over device tensors whose scratch is the library's static device
+        array (no allocation of any kind).  ``a`` / ``b`` dense row-major CUDA tensors, ``out`` a flat CUDA buffer."""
+        for t in (a, b, out) + ((bias,) if bias is not None else ()):
+            if not (hasattr(t, "is_cuda") and t.is_cuda and t.is_contiguous()):
+                raise N.RtgError(5, "gemm_static_scratch takes contiguous CUDA tensors")
+        m, k = a.shape
+        kb, n = b.shape
+        if k != kb:
+            raise N.RtgError(50, "Columns of matrix `a` must match rows of matrix `b`")
+        N.check(N.lib().rtg_gemm_static_scratch(
+            self.ctx.handle, C.c_void_p(out.data_ptr()), C.c_size_t(out.numel()), C.c_size_t(out_row_stride),
+            C.c_void_p(a.data_ptr()), C.c_size_t(m), C.c_size_t(k), C.c_void_p(b.data_ptr()), C.c_size_t(n),
+            C.c_float(alpha), C.c_float(beta), C.c_void_p(bias.data_ptr() if bias is not None else None),
+            C.c_int32(splits)))
+        return out
+
     def gemm(self, out, out_row_stride, a, b, alpha=1.0, beta=0.0):
         return self.gemm_bias(out, out_row_stride, a, b, alpha, beta, None)
 

@@ -1,0 +1,293 @@
+// Developer probe (not part of the library): issue / pipe rates of tcgen05.mma on this GPU, the numbers the contraction
+// kernel's main loop is designed around.  One CTA (or one 2-CTA cluster) per launch, one issuing thread, operands are
+// whatever is in shared / tensor memory.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I rten_fork_b200/csrc scripts/mma_probe.cu -o scripts/mma_probe
+#include "sm100_ptx.cuh"
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <vector>
+
+using namespace rtg;
+
+#define CK(x)                                                                        \
+  do {                                                                               \
+    cudaError_t e_ = (x);                                                            \
+    if (e_ != cudaSuccess) {                                                         \
+      printf("%s failed: %s\n", #x, cudaGetErrorString(e_));                         \
+      exit(1);                                                                       \
+    }                                                                                \
+  } while (0)
+
+enum Form { SS_TF32 = 0, TS_TF32 = 1, TS_F16 = 2, ALT_TS = 3, GRP_TS = 4, SS_F16 = 5 };
+
+__device__ __forceinline__ void mma2_tf32_ts(uint32_t d, uint32_t a_t, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d), "r"(a_t), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void mma2_f16_ts(uint32_t d, uint32_t a_t, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d), "r"(a_t), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void mma2_tf32_ss(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void mma_f16_ss(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void commit2(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void issue1(int form, int i, uint32_t d, uint32_t a_t, uint64_t adesc, uint64_t bdesc,
+                                       uint32_t id_tf32, uint32_t id_bf16) {
+  const uint32_t bl = static_cast<uint32_t>(bdesc), bh = static_cast<uint32_t>(bdesc >> 32);
+  const uint32_t al = static_cast<uint32_t>(adesc), ah = static_cast<uint32_t>(adesc >> 32);
+  const uint32_t ks = (i & 3) * 2;  // walk the four k-steps of a 128-byte row
+  switch (form) {
+    case SS_TF32: ptx::mma_tf32_ss_w(d, al + ks, ah, bl + ks, bh, id_tf32, 1); break;
+    case TS_TF32: ptx::mma_tf32_ts_w(d, a_t + (i & 3) * 8, bl + ks, bh, id_tf32, 1); break;
+    case TS_F16: ptx::mma_f16_ts_w(d, a_t + (i & 3) * 8, bl + ks, bh, id_bf16, 1); break;
+    case ALT_TS:
+      if (i & 1) ptx::mma_tf32_ts_w(d, a_t + (i & 3) * 8, bl + ks, bh, id_tf32, 1);
+      else ptx::mma_f16_ts_w(d, a_t + 32 + (i & 3) * 8, bl + 1024 + ks, bh, id_bf16, 1);
+      break;
+    case GRP_TS:
+      if (i & 4) ptx::mma_tf32_ts_w(d, a_t + (i & 3) * 8, bl + ks, bh, id_tf32, 1);
+      else ptx::mma_f16_ts_w(d, a_t + 32 + (i & 3) * 8, bl + 1024 + ks, bh, id_bf16, 1);
+      break;
+    case SS_F16: mma_f16_ss(d, adesc + ks, bdesc + ks, id_bf16, 1); break;
+  }
+}
+
+// mode 0: throughput of a chain of `reps` MMAs; mode 1: clock after every issue (queue depth); mode 2: pipeline skeleton
+// (a producer warp arrives on `full`, the MMA thread waits `nwait` barriers, issues `per_round` MMAs, commits `empty`)
+template <int N>
+__global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, int per_round, int nwait, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + 160 * 1024;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) ptx::sts_f32(base + i * 4, 1.0f);
+  constexpr int S = 4;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2 * S + 2; ++s) ptx::mbar_init(bars + 8 * s, 1);
+    for (int s = 0; s < S; ++s) ptx::mbar_init(bars + 8 * (2 * S + 2 + s), 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc(ptx::smem_u32(&tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tm = tmem_slot;
+  const uint32_t id_tf32 = ptx::make_idesc_tf32(128, N, 0, 0), id_bf16 = ptx::make_idesc_bf16(128, N);
+  const uint64_t adesc = ptx::make_smem_desc(base, 16, 1024);
+  const uint64_t bdesc = ptx::make_smem_desc(base + 32 * 1024, 16, 1024);
+  const uint32_t done = bars;  // barrier 0
+  auto full = [&](int s) { return bars + 8 * (1 + s); };
+  auto empty = [&](int s) { return bars + 8 * (1 + S + s); };
+  auto full2 = [&](int s) { return bars + 8 * (2 * S + 2 + s); };
+  if (mode == 2 && warp == 1) {  // producer skeleton
+    int s = 0;
+    uint32_t ph = 0;
+    const int rounds = reps / per_round;
+    for (int r = 0; r < rounds; ++r) {
+      ptx::mbar_wait(empty(s), ph ^ 1u);
+      if (lane == 0) {
+        ptx::mbar_arrive(full(s));
+        ptx::mbar_arrive(full2(s));
+      }
+      __syncwarp();
+      if (++s == S) s = 0, ph ^= 1u;
+    }
+  }
+  if (warp == 0) {
+    const uint32_t d = tm, a_t = tm + 256;
+    if (mode == 0) {
+      long long t0 = 0, t1 = 0;
+      for (int pass = 0; pass < 2; ++pass) {  // pass 0 warms up
+        __syncwarp();
+        t0 = clock64();
+        if (ptx::elect_one()) {
+          for (int i = 0; i < reps; ++i) issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          ptx::mma_commit(done);
+        }
+        __syncwarp();
+        ptx::mbar_wait(done, pass & 1);
+        t1 = clock64();
+      }
+      if (lane == 0) out[0] = t1 - t0;
+    } else if (mode == 1) {
+      if (lane == 0) {
+        const long long t0 = clock64();
+        for (int i = 0; i < reps && i < 64; ++i) {
+          issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          out[1 + i] = clock64() - t0;
+        }
+        ptx::mma_commit(done);
+        ptx::mbar_wait(done, 0);
+        out[0] = clock64() - t0;
+      }
+    } else {
+      int s = 0;
+      uint32_t ph = 0;
+      const int rounds = reps / per_round;
+      __syncwarp();
+      const long long t0 = clock64();
+      for (int r = 0; r < rounds; ++r) {
+        ptx::mbar_wait(full(s), ph);
+        if (nwait > 1) ptx::mbar_wait(full2(s), ph);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          for (int i = 0; i < per_round; ++i) issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          ptx::mma_commit(empty(s));
+        }
+        __syncwarp();
+        if (++s == S) s = 0, ph ^= 1u;
+      }
+      if (ptx::elect_one()) ptx::mma_commit(done);
+      __syncwarp();
+      ptx::mbar_wait(done, 0);
+      if (lane == 0) out[0] = clock64() - t0;
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tm, 512);
+  }
+}
+
+// 2-CTA pair: M = 256 (128 rows per CTA), each CTA holds N/2 columns of B.  The leader CTA's thread issues.
+template <int N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int form, int reps, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + 160 * 1024;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) ptx::sts_f32(base + i * 4, 1.0f);
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bars, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(ptx::smem_u32(&tmem_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  ptx::tc_fence_after();
+  const uint32_t tm = tmem_slot;
+  const uint32_t id_tf32 = ptx::make_idesc_tf32(256, N, 0, 0), id_bf16 = ptx::make_idesc_bf16(256, N);
+  const uint64_t adesc = ptx::make_smem_desc(base, 16, 1024);
+  const uint64_t bdesc = ptx::make_smem_desc(base + 32 * 1024, 16, 1024);
+  if (rank == 0 && warp == 0) {
+    const uint32_t d = tm, a_t = tm + 256;
+    long long t0 = 0, t1 = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      __syncwarp();
+      t0 = clock64();
+      if (ptx::elect_one()) {
+        for (int i = 0; i < reps; ++i) {
+          const uint32_t ks = (i & 3) * 2;
+          if (form == TS_TF32) mma2_tf32_ts(d, a_t + (i & 3) * 8, bdesc + ks, id_tf32, 1);
+          else if (form == TS_F16) mma2_f16_ts(d, a_t + (i & 3) * 8, bdesc + ks, id_bf16, 1);
+          else if (form == ALT_TS) {
+            if (i & 1) mma2_tf32_ts(d, a_t + (i & 3) * 8, bdesc + ks, id_tf32, 1);
+            else mma2_f16_ts(d, a_t + 32 + (i & 3) * 8, bdesc + 1024 + ks, id_bf16, 1);
+          } else mma2_tf32_ss(d, adesc + ks, bdesc + ks, id_tf32, 1);
+        }
+        commit2(bars);
+      }
+      __syncwarp();
+      ptx::mbar_wait(bars, pass & 1);
+      t1 = clock64();
+    }
+    if (lane == 0) out[0] = t1 - t0;
+  }
+  ptx::tc_fence_before();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(512) : "memory");
+  }
+}
+
+static const char* kFormName[] = {"SS tf32", "TS tf32", "TS bf16", "alt TS bf16/tf32", "4 bf16 + 4 tf32 TS", "SS bf16"};
+constexpr int kSmem = 160 * 1024 + 1024 + 256;
+
+template <int N>
+static void run1(long long* dout, int form, int mode, int reps, int per_round, int nwait) {
+  CK(cudaFuncSetAttribute(probe1<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  CK(cudaMemset(dout, 0, 80 * 8));
+  probe1<N><<<1, 128, kSmem>>>(form, mode, reps, per_round, nwait, dout);
+  CK(cudaDeviceSynchronize());
+  long long h[80];
+  CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
+  if (mode == 0) {
+    printf("N=%3d %-20s chain of %d: %6.1f cycles / MMA\n", N, kFormName[form], reps, double(h[0]) / reps);
+  } else if (mode == 1) {
+    printf("N=%3d %-20s issue clocks:", N, kFormName[form]);
+    for (int i = 0; i < 24; ++i) printf(" %lld", h[1 + i]);
+    printf(" ... total %lld\n", h[0]);
+  } else {
+    printf("N=%3d %-20s pipeline skeleton: %2d MMAs / round, %d wait(s): %7.1f cycles / round (%5.1f / MMA)\n", N,
+           kFormName[form], per_round, nwait, double(h[0]) / (reps / per_round), double(h[0]) / reps);
+  }
+}
+
+template <int N>
+static void run2(long long* dout, int form, int reps) {
+  CK(cudaFuncSetAttribute(probe2<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  CK(cudaMemset(dout, 0, 80 * 8));
+  probe2<N><<<2, 128, kSmem>>>(form, reps, dout);
+  CK(cudaDeviceSynchronize());
+  long long h[1];
+  CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
+  printf("2-CTA M=256 N=%3d %-20s chain of %d: %6.1f cycles / MMA\n", N, kFormName[form], reps, double(h[0]) / reps);
+}
+
+int main() {
+  long long* dout;
+  CK(cudaMalloc(&dout, 80 * 8));
+  const int reps = 512;
+  for (int form : {SS_TF32, TS_TF32, TS_F16, ALT_TS, GRP_TS, SS_F16}) {
+    run1<64>(dout, form, 0, reps, 0, 0);
+    run1<128>(dout, form, 0, reps, 0, 0);
+    if (form != ALT_TS && form != GRP_TS) run1<256>(dout, form, 0, reps, 0, 0);
+  }
+  for (int form : {SS_TF32, TS_TF32, ALT_TS}) run1<128>(dout, form, 1, 64, 0, 0);
+  for (int form : {SS_TF32, ALT_TS, GRP_TS})
+    for (int per_round : {4, 8, 16, 32})
+      for (int nwait : {1, 2}) run1<128>(dout, form, 2, 1024, per_round, nwait);
+  run1<256>(dout, SS_TF32, 2, 1024, 4, 1);
+  run1<256>(dout, SS_TF32, 2, 1024, 8, 1);
+  for (int form : {SS_TF32, TS_TF32, TS_F16, ALT_TS}) {
+    run2<64>(dout, form, reps);
+    run2<128>(dout, form, reps);
+    run2<256>(dout, form, reps);
+  }
+  printf("probe done\n");
+  return 0;
+}
