@@ -102,20 +102,19 @@ bool conv_window_supported(const ConvPlan& p) {
 }
 
 // ---------------------------------------------------------------- weights
-// B' of the prepared K-major weight matrix [o][k] (row pitch k): computed once here, so that RTG_MATH_TF32_BF16X2 launches
-// load it by TMA instead of splitting the weights again in every CTA.
-static rtg_status prepare_wprime(Context* ctx, ConvWeights* out, int64_t o, int64_t k) {
-  const int64_t kw = div_ceil(k, kBK) * kBK;
+// Packed copy (BPack) of the prepared K-major weight matrix [o][k] (row pitch k): computed once here, so that
+// RTG_MATH_TF32_BF16X2 launches load both of its planes by TMA instead of splitting the weights again in every CTA.
+static rtg_status prepare_wpack(Context* ctx, ConvWeights* out, int64_t o, int64_t k) {
+  const int64_t ld = b_pack_ld(k);
   void* d = nullptr;
-  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(o) * kw * 4, &d));
-  out->wprime = static_cast<uint32_t*>(d);
-  out->wprime_ld = kw;
-  return make_b_prime(ctx, MatView{out->wmat, k, o, 1, k}, out->wprime);
+  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(o) * ld * 4 * 2, &d));
+  out->wpack = BPack{static_cast<const float*>(d), ld, o * ld};
+  return make_b_pack(ctx, MatView{out->wmat, k, o, 1, k}, static_cast<float*>(d), o * ld);
 }
 
 rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out) {
   out->wmat = nullptr;
-  out->wprime = nullptr;
+  out->wpack = BPack{};
   out->direct = false;
   out->window = false;
   const int khw = static_cast<int>(p.kh * p.kw);
@@ -136,7 +135,7 @@ rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_
     out->wmat = const_cast<float*>(w_dev);  // [O][C] is already the K-major B operand
     out->direct = true;
     out->kpt = static_cast<int>(p.c);
-    return prepare_wprime(ctx, out, p.o, p.c);
+    return prepare_wpack(ctx, out, p.o, p.c);
   }
   if (conv_window_supported(p)) {
     const int cp = static_cast<int>(div_ceil(p.c, 4) * 4);
@@ -152,7 +151,7 @@ rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_
     out->wmat = static_cast<float*>(d);
     out->kpt = kBK;
     out->window = true;
-    return prepare_wprime(ctx, out, p.o, p.kh * kBK);
+    return prepare_wpack(ctx, out, p.o, p.kh * kBK);
   }
   const int kpt = static_cast<int>(div_ceil(p.cg, kBK) * kBK);
   const int64_t total = p.o * khw * kpt;
@@ -165,14 +164,14 @@ rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_
   RTG_CUDA(cudaGetLastError());
   out->wmat = static_cast<float*>(d);
   out->kpt = kpt;
-  return prepare_wprime(ctx, out, p.o, static_cast<int64_t>(khw) * kpt);
+  return prepare_wpack(ctx, out, p.o, static_cast<int64_t>(khw) * kpt);
 }
 
 void conv_release_weights(Context* ctx, ConvWeights* w) {
   if (w->wmat && !w->direct) ctx->pool.free(w->wmat);
-  if (w->wprime) ctx->pool.free(w->wprime);
+  if (w->wpack.p) ctx->pool.free(const_cast<float*>(w->wpack.p));
   w->wmat = nullptr;
-  w->wprime = nullptr;
+  w->wpack = BPack{};
 }
 
 // ---------------------------------------------------------------- forward
@@ -350,7 +349,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
       }
       WindowGeom wg = {N, hp, wp, cpw, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
                        static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.dil_h), C};
-      ep.b_prime = w.wprime;
+      ep.b_pack = w.wpack;
       RTG_TRY(conv_window_gemm_device(ctx, x_pad.f32(), wg, w.wmat, O, static_cast<float*>(out.data), dm, ep));
       if (need_out_tmp) RTG_TRY(copy_view(ctx, out_final, out));
       return RTG_OK;
@@ -385,7 +384,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
       float* D = static_cast<float*>(out.data);
       if (w.direct) {
         // pointwise: A = activations [M, C] (pitch cp), B = W [O][C]
-        ep.b_prime = w.wprime;
+        ep.b_pack = w.wpack;
         RTG_TRY(gemm_device(ctx, MatView{xp, M, C, cp, 1}, MatView{w.wmat, C, O, 1, C}, D, dm, ep));
         continue;
       }
@@ -396,9 +395,10 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
                      static_cast<int>(p.pads[1]), static_cast<int>(p.pads[2]), static_cast<int>(p.pads[3]),
                      static_cast<int>(p.dil_h), static_cast<int>(p.dil_w)};
       if (conv_im2col_supported(cg)) {
-        ep.b_prime = w.wprime ? w.wprime + static_cast<int64_t>(g) * OG * w.wprime_ld : nullptr;
+        ep.b_pack = w.wpack;  // rows [g * OG, +OG) of both planes
+        if (ep.b_pack.p) ep.b_pack.p += static_cast<int64_t>(g) * OG * w.wpack.ld;
         RTG_TRY(conv_gemm_device(ctx, xp, cg, wg, OG, D, dm, ep));
-        ep.b_prime = nullptr;
+        ep.b_pack = BPack{};
       } else {
         // outside the TMA im2col limits: materialise the patch matrix, then a plain GEMM
         Scratch cols;

@@ -60,39 +60,45 @@ rtg_status scale_buffer(Context* ctx, float* p, size_t n, float beta) {
   return RTG_OK;
 }
 
-// ---------------------------------------------------------------- B' (bf16 correction operand)
-__global__ void b_prime_kernel(uint32_t* __restrict__ out, const float* __restrict__ b, int64_t K, int64_t N,
-                               int64_t rs, int64_t cs, int64_t groups /* ceil(K/32)*4 */, int n_fastest) {
+// ---------------------------------------------------------------- packed B operand of RTG_MATH_TF32_BF16X2 (BPack)
+__global__ void b_pack_kernel(float* __restrict__ out_hi, uint32_t* __restrict__ out_prime, const float* __restrict__ b,
+                              int64_t K, int64_t N, int64_t rs, int64_t cs, int64_t groups /* ceil(K/32)*4 */,
+                              int n_fastest) {
   const int64_t total = N * groups;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     // consecutive threads walk the contiguous dimension of B
     const int64_t n = n_fastest ? i % N : i / groups, g = n_fastest ? i / N : i % groups;
-    float x[8];
+    float hi[8], lo[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int64_t k = g * 8 + j;
-      x[j] = k < K ? b[k * rs + n * cs] : 0.f;
+      const float x = k < K ? b[k * rs + n * cs] : 0.f;
+      hi[j] = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);  // round to nearest TF32
+      lo[j] = x - hi[j];                                                        // exact in fp32
     }
-    auto lo = [](float v) { return v - __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); };
+    float4* oh = reinterpret_cast<float4*>(out_hi + (n * groups + g) * 8);
+    oh[0] = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    oh[1] = make_float4(hi[4], hi[5], hi[6], hi[7]);
     uint4 hi4, lo4;
-    hi4.x = ptx::pack_bf16x2(x[0], x[1]), hi4.y = ptx::pack_bf16x2(x[2], x[3]);
-    hi4.z = ptx::pack_bf16x2(x[4], x[5]), hi4.w = ptx::pack_bf16x2(x[6], x[7]);
-    lo4.x = ptx::pack_bf16x2(lo(x[0]), lo(x[1])), lo4.y = ptx::pack_bf16x2(lo(x[2]), lo(x[3]));
-    lo4.z = ptx::pack_bf16x2(lo(x[4]), lo(x[5])), lo4.w = ptx::pack_bf16x2(lo(x[6]), lo(x[7]));
-    uint4* o = reinterpret_cast<uint4*>(out + (n * groups + g) * 8);
+    hi4.x = ptx::pack_bf16x2(hi[0], hi[1]), hi4.y = ptx::pack_bf16x2(hi[2], hi[3]);
+    hi4.z = ptx::pack_bf16x2(hi[4], hi[5]), hi4.w = ptx::pack_bf16x2(hi[6], hi[7]);
+    lo4.x = ptx::pack_bf16x2(lo[0], lo[1]), lo4.y = ptx::pack_bf16x2(lo[2], lo[3]);
+    lo4.z = ptx::pack_bf16x2(lo[4], lo[5]), lo4.w = ptx::pack_bf16x2(lo[6], lo[7]);
+    uint4* o = reinterpret_cast<uint4*>(out_prime + (n * groups + g) * 8);
     o[0] = hi4;
     o[1] = lo4;
   }
 }
 
-rtg_status make_b_prime(Context* ctx, MatView b, uint32_t* out) {
+rtg_status make_b_pack(Context* ctx, MatView b, float* out, int64_t plane) {
   const int64_t K = b.rows, N = b.cols;
   if (K == 0 || N == 0) return RTG_OK;
   const int64_t groups = div_ceil(K, kBK) * 4;
   const int64_t total = N * groups;
   const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 16));
-  b_prime_kernel<<<blocks, 256, 0, ctx->stream>>>(out, b.p, K, N, b.rs, b.cs, groups, b.cs == 1 && b.rs != 1 ? 1 : 0);
+  b_pack_kernel<<<blocks, 256, 0, ctx->stream>>>(out, reinterpret_cast<uint32_t*>(out + plane), b.p, K, N, b.rs, b.cs,
+                                                 groups, b.cs == 1 && b.rs != 1 ? 1 : 0);
   ctx->launches++;
   RTG_CUDA(cudaGetLastError());
   return RTG_OK;
@@ -134,17 +140,28 @@ static rtg_status encode_out_3d(Context* ctx, CUtensorMap* map, const float* bas
   return RTG_OK;
 }
 
-// B' (make_b_prime) for a launch: the caller's precomputed copy, or a pre-pass into pool scratch.  Map: [N][Kw] words,
-// box 32 x BN, 128B swizzle (a K-major tile like any other).
-static rtg_status b_prime_map(Context* ctx, const Epilogue& ep, MatView b, int bn, Scratch* tmp, CUtensorMap* map) {
-  const int64_t kw = div_ceil(b.rows, kBK) * kBK;
-  const uint32_t* bp = ep.b_prime;
-  if (!bp) {
-    RTG_TRY(tmp->alloc(ctx, static_cast<size_t>(b.cols) * kw * 4));
-    RTG_TRY(make_b_prime(ctx, b, static_cast<uint32_t*>(tmp->p)));
-    bp = static_cast<const uint32_t*>(tmp->p);
+// Packed B operand for a launch: the caller's precomputed copy, or a pre-pass into pool scratch.  Map: {K, N, 2 planes},
+// box 32 x BN x 2, 128B swizzle: one load fills a stage's [B hi][B'] tiles.
+static rtg_status b_pack_map(Context* ctx, const Epilogue& ep, MatView b, int bn, Scratch* tmp, CUtensorMap* map) {
+  BPack bp = ep.b_pack;
+  if (!bp.p) {
+    bp.ld = b_pack_ld(b.rows);
+    bp.plane = b.cols * bp.ld;
+    RTG_TRY(tmp->alloc(ctx, static_cast<size_t>(bp.plane) * 2 * 4));
+    RTG_TRY(make_b_pack(ctx, b, tmp->f32(), bp.plane));
+    bp.p = tmp->f32();
   }
-  return encode_2d(ctx, map, reinterpret_cast<const float*>(bp), kw, b.cols, kw, kBK, bn);
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(bp.ld), static_cast<cuuint64_t>(b.cols), 2};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(bp.ld) * 4, static_cast<cuuint64_t>(bp.plane) * 4};
+  cuuint32_t box[3] = {kBK, static_cast<cuuint32_t>(bn), 2};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(bp.p), dims, strides, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (packed B) failed (%d): base %p dims [%lld,%lld,2] plane %lld",
+                      (int)r, bp.p, (long long)bp.ld, (long long)b.cols, (long long)bp.plane);
+  return RTG_OK;
 }
 
 // Can TMA address this operand in place?  The contiguous dimension must have stride 1, the base must be 16-byte
@@ -387,9 +404,12 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
     RTG_TRY(copy_strided_2d(ctx, a_tmp.f32(), Kp, a.p, M, K, a.rs, a.cs));
     a = MatView{a_tmp.f32(), M, K, Kp, 1};
   }
-  // --- legalise B: either [N][K] K-major (b.rs == 1) or [K][N] MN-major (b.cs == 1)
-  int b_major;
-  if (direct_ok(b.p, b.rs, b.cs, N)) {
+  // --- legalise B: either [N][K] K-major (b.rs == 1) or [K][N] MN-major (b.cs == 1).  RTG_MATH_TF32_BF16X2 reads B
+  // only through its packed K-major copy (make_b_pack gathers any strides), so B itself needs no legal layout there.
+  const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
+  int b_major = 0;
+  if (m2) {
+  } else if (direct_ok(b.p, b.rs, b.cs, N)) {
     b_major = 0;
     if (N == 1) b.cs = Kp;
   } else if (direct_ok(b.p, b.cs, b.rs, K)) {
@@ -408,7 +428,9 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   int splits = 1;
   const int bn = choose_bn(ctx, M, N, div_ceil(K, kBK), 1, dmap.hw > 0 ? nullptr : &splits);
   RTG_TRY(encode_2d(ctx, &ma, a.p, K, M, a.rs, kBK, kBM));
-  if (b_major == 0)
+  if (m2)
+    mb = ma;  // unused by the kernel in this mode; any valid map
+  else if (b_major == 0)
     RTG_TRY(encode_2d(ctx, &mb, b.p, K, N, b.cs, kBK, bn));
   else
     RTG_TRY(encode_2d(ctx, &mb, b.p, N, K, b.rs, 32, kBK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B));
@@ -436,8 +458,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
   Scratch bp_tmp;
   CUtensorMap mb2;
-  const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
-  if (m2) RTG_TRY(b_prime_map(ctx, ep, b, bn, &bp_tmp, &mb2));
+  if (m2) RTG_TRY(b_pack_map(ctx, ep, b, bn, &bp_tmp, &mb2));
   if (b_major == 0) return dispatch<0, 0>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep, m2 ? &mb2 : nullptr);
   return dispatch<0, 1>(ctx, bn, ctx->math, ma, mb, g, 0, 0, &ep, m2 ? &mb2 : nullptr);
 }
@@ -619,7 +640,7 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   Scratch bp_tmp;
   CUtensorMap mb2;
   const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
-  if (m2) RTG_TRY(b_prime_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
+  if (m2) RTG_TRY(b_pack_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
   return dispatch<1, 0>(ctx, bn, ctx->math, ma, mb, a, 0, 0, nullptr, m2 ? &mb2 : nullptr);
 }
 
@@ -677,7 +698,7 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
   Scratch bp_tmp;
   CUtensorMap mb2;
   const bool m2 = ctx->math == RTG_MATH_TF32_BF16X2;
-  if (m2) RTG_TRY(b_prime_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
+  if (m2) RTG_TRY(b_pack_map(ctx, ep, MatView{wmat, Kmat, og, 1, Kmat}, bn, &bp_tmp, &mb2));
   return dispatch<2, 0>(ctx, bn, ctx->math, ma, mb, a, g.ow, 0, nullptr, m2 ? &mb2 : nullptr);
 }
 
@@ -688,7 +709,7 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
 // file-scope device array instead of the context pool.  Every GPU that loads the library holds it until exit; all calls
 // share it, so calls that overlap on the GPU (two streams, two contexts of one device) race.  Nothing in it has to
 // start at zero: every plane element and every B' word is written by this call before it is read (TMA stores cover the
-// whole {N, M, splits} box, make_b_prime zero-fills beyond K).
+// whole {N, M, splits} box, make_b_pack zero-fills beyond K).
 static __device__ __align__(256) float g_static_scratch[RTG_STATIC_SCRATCH_BYTES / sizeof(float)];
 
 // The array's name is a host-side stand-in in host code, not a device address: resolve it once per device, with that
@@ -734,7 +755,7 @@ rtg_status gemm_splitk_static(Context* ctx, const float* a, int64_t M, int64_t K
 
   // scratch layout: [B' (TF32+BF16x2 only)][splits planes of M x N partial sums]
   const int64_t kw = num_kb * kBK;
-  const size_t bprime_bytes = mode == RTG_MATH_TF32_BF16X2 ? static_cast<size_t>(N) * kw * 4 : 0;
+  const size_t bprime_bytes = mode == RTG_MATH_TF32_BF16X2 ? static_cast<size_t>(N) * kw * 4 * 2 : 0;  // two planes
   const size_t bprime_pad = (bprime_bytes + 255) & ~static_cast<size_t>(255);
   const int64_t plane = N * M;
   const size_t need = bprime_pad + static_cast<size_t>(plane) * splits * sizeof(float);
@@ -753,8 +774,10 @@ rtg_status gemm_splitk_static(Context* ctx, const float* a, int64_t M, int64_t K
   RTG_TRY(encode_2d(ctx, &mb, b, N, K, N, 32, kBK, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B));  // row-major [K][N]: MN-major B
   mb2 = mb;
   if (mode == RTG_MATH_TF32_BF16X2) {
-    RTG_TRY(make_b_prime(ctx, MatView{b, K, N, N, 1}, bprime));
-    RTG_TRY(encode_2d(ctx, &mb2, reinterpret_cast<const float*>(bprime), kw, N, kw, kBK, bn));
+    Epilogue pk;
+    pk.b_pack = BPack{reinterpret_cast<const float*>(bprime), kw, N * kw};
+    RTG_TRY(make_b_pack(ctx, MatView{b, K, N, N, 1}, reinterpret_cast<float*>(bprime), N * kw));
+    RTG_TRY(b_pack_map(ctx, pk, MatView{b, K, N, N, 1}, bn, nullptr, &mb2));
   }
   RTG_TRY(encode_out_3d(ctx, &md, ws, N, M, splits, N));
 
@@ -781,6 +804,7 @@ rtg_status gemm_splitk_static(Context* ctx, const float* a, int64_t M, int64_t K
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (red.R ? 2 : 1));
+  if (mode == RTG_MATH_TF32_BF16X2) return launch_variants<0, 0>(ctx, bn, mode, ma, mb, mb2, md, ma, g, &red);
   return launch_variants<0, 1>(ctx, bn, mode, ma, mb, mb2, md, ma, g, &red);
 }
 

@@ -10,6 +10,15 @@ struct MatView {      // [rows, cols] f32 matrix view on the device, element str
   int64_t rows, cols, rs, cs;
 };
 
+// Packed B operand of RTG_MATH_TF32_BF16X2: two K-major planes of [N][ld] 32-bit words (ld = ceil(K/32)*32, zero beyond
+// K), `plane` words apart.  Plane 0: B rounded to nearest TF32 (the hi*hi MMA reads it; the tensor core's own
+// truncation is then exact).  Plane 1: the bf16 correction operand B': per group of 8 k, four words of bf16 pairs of
+// hi(B) followed by four of lo(B) = B - hi(B).  One 3-D TMA box {32, BN, 2} loads both tiles of a k-block.
+struct BPack {
+  const float* p = nullptr;
+  int64_t ld = 0, plane = 0;
+};
+
 struct Epilogue {
   float alpha = 1.f, beta = 0.f;
   bool alpha_div = false;     // D = acc / alpha instead of acc * alpha (fused MatMul -> Div by a scalar)
@@ -21,9 +30,9 @@ struct Epilogue {
   float act_lo = 0.f, act_hi = 0.f;
   // peer copies of the output (other GPUs' buffers mapped into this process, same layout as D): every tile is stored
   // to D and to each of them.  Needs a row-major, 16-byte aligned D (the TMA-store epilogue).
-  // RTG_MATH_TF32_BF16X2: the bf16 correction operand B' of a constant B, [N][ceil(K/32)*32] words written by
-  // make_b_prime at load time; NULL = computed by a pre-pass of this call
-  const uint32_t* b_prime = nullptr;
+  // RTG_MATH_TF32_BF16X2: the packed B operand of a constant B, written by make_b_pack at load time; p == NULL =
+  // computed by a pre-pass of this call
+  BPack b_pack;
   int n_peers = 0;
   float* peer_D[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
@@ -32,9 +41,10 @@ struct Epilogue {
 // dimension contiguous, unaligned base or pitch) are first gathered into pool scratch by a copy kernel.
 rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap, const Epilogue& ep);
 
-// B' for RTG_MATH_TF32_BF16X2: out[n][kb*32 + 8g + i] (i < 4) = bf16 pair of B[32kb + 8g + 2i, +1][n], out[..+4+i] the
-// same of lo(B) = B - trunc_tf32(B); zero beyond K.  `out` has N * ceil(K/32)*32 words.
-rtg_status make_b_prime(Context* ctx, MatView b, uint32_t* out);
+// Writes the packed B operand (BPack) of b [K, N] (any strides): plane 0 at out, plane 1 at out + plane.  Needs
+// 2 planes of N * ceil(K/32)*32 words.
+rtg_status make_b_pack(Context* ctx, MatView b, float* out, int64_t plane);
+inline int64_t b_pack_ld(int64_t k) { return (k + 31) / 32 * 32; }
 
 // Batched product in ONE launch: batch index z = z1 * n0 + z0, entry z of A at a.p + z0*a.bs0 + z1*a.bs1 (a stride of
 // 0 broadcasts the operand along that batch dimension), D contiguous [n1*n0][M][N].  The operands must be addressable
@@ -57,7 +67,7 @@ struct ConvGeom {
 };
 // wmat: [Og][kh*kw*c_blocks*32] K-major weight matrix for this group (zero padded per tap), Og output channels.
 rtg_status conv_gemm_device(Context* ctx, const float* x_nhwc, const ConvGeom& g, const float* wmat, int og,
-                            float* D, OutMap dmap, const Epilogue& ep);  // ep.b_prime: B' of wmat (or NULL)
+                            float* D, OutMap dmap, const Epilogue& ep);  // ep.b_pack: packed wmat (or empty)
 bool conv_im2col_supported(const ConvGeom& g);
 
 // Row-window convolution (few input channels): x_pad is the zero-padded [n][hp][wp][cp] image written by

@@ -157,8 +157,13 @@ rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma
     if (bn == 128) return launch<128, 0, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
     if (bn == 256) return launch<256, 0, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
   } else if (mode == RTG_MATH_TF32_BF16X2 && A_KIND != 3) {  // batched products keep the three-MMA split
-    if (bn == 64) return launch<64, 2, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
-    if (bn == 128) return launch<128, 2, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
+    // this mode reads B through its packed K-major copy: there is no MN-major variant
+    if constexpr (B_MAJOR == 0) {
+      if (bn == 64) return launch<64, 2, A_KIND, 0>(ctx, ma, mb, mb2, md, mr, args, redp);
+      if (bn == 128) return launch<128, 2, A_KIND, 0>(ctx, ma, mb, mb2, md, mr, args, redp);
+    } else {
+      return set_error(RTG_ERR_INTERNAL, "TF32+BF16x2 launches take the packed (K-major) B operand");
+    }
   } else {
     if (bn == 64) return launch<64, 1, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);
     if (bn == 128) return launch<128, 1, A_KIND, B_MAJOR>(ctx, ma, mb, mb2, md, mr, args, redp);

@@ -124,6 +124,7 @@ struct GemmArgs {
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
 constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
 constexpr int kFlagStagedR = 4;  // residual arrives by TMA load into the same staging buffer (needs kFlagStagedD)
+constexpr int kFlagDebugNoB = 32, kFlagDebugNoA = 64, kFlagDebugNoSplit = 128, kFlagDebugNoDrain = 256;  // (debug) MODE 2: skip the B / A TMA stream (timing experiments)
 constexpr int kFlagAlphaDiv = 16;  // alpha is a divisor: D = acc / alpha (8 is the debug "no staging" switch)
 
 constexpr int kBM = 128;
@@ -143,7 +144,7 @@ struct GemmCfg {
   // run, and sits in its own short ring of kAStages slots; a pipeline stage proper is [B raw][B lo] plus its TMEM slot.
   // That buys a fourth stage at BN = 128 (sixth at BN = 64) in the same shared memory; this mode is bound by the
   // TMA -> split -> tcgen05.st -> MMA chain, i.e. by how many k-blocks are in flight.
-  static constexpr int kAStages = MODE ? 3 : 0;
+  static constexpr int kAStages = MODE ? (BN <= 64 ? 5 : 3) : 0;
   static constexpr int kStageBytes = MODE ? 2 * kBBytes : kRawBytes;
   static constexpr int kARingBytes = kAStages * kABytes;
   static constexpr int kTmemAStageCols = 2 * kBK;  // hi plane + lo plane, one 32-bit column per k
@@ -402,7 +403,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #endif
           PROF_MARK(0, 5);  // first TMA issue
           const bool leader = ptx::elect_one() != 0;
-          if (leader) {
+          if (leader && MODE == 2 && (args.flags & kFlagDebugNoA)) {  // (debug, wrong results) timing without the A stream
+            ptx::mbar_arrive(fa);
+          } else if (leader) {
             ptx::mbar_expect_tx(fa, MODE != 0 ? kABytes : Cfg::kRawBytes);
             if (A_KIND == 0) {
               ptx::tma_load_2d(a_dst, &tmA, fa, kb * kBK, m0);
@@ -430,13 +433,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               ia = 0;
               pa ^= 1u;
             }
+            if (MODE == 2) continue;  // the B stream has its own producer warp (below)
             PROF_WAIT(0, ptx::mbar_wait(empty_bar(s), ph ^ 1u));
-            if (leader) {
-              ptx::mbar_expect_tx(fb, MODE == 2 ? 2 * Cfg::kBBytes : Cfg::kBBytes);
-              // MODE 2: the bf16 correction tile B' = [bf16(B) 8 | bf16(lo(B)) 8] per group of 8 k was written to
-              // global memory once (weights: at load; otherwise by a pre-pass), K-major whatever B's own layout
-              if (MODE == 2) ptx::tma_load_2d(b_dst + Cfg::kBBytes, &tmB2, fb, kb * kBK, n0);
-            }
+            if (leader) ptx::mbar_expect_tx(fb, Cfg::kBBytes);
           }
           if (!leader) {
             // only the elected lane issues the B loads
@@ -731,6 +730,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
           PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
           ptx::tc_fence_after();
+          if (!(args.flags & kFlagDebugNoDrain) || kb0 == kb_begin)  // (debug, wrong results) skip the chunk drains
 #pragma unroll
           for (int c0 = 0; c0 < kCols; c0 += 32) {
             float v[32];
@@ -766,6 +766,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0 && lane == 0) {
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
+    }
+  } else if (MODE == 2 && warp == kMmaWarp + 9) {
+    // ===================================================== B producer (MODE 2)
+    // One 3-D TMA load per k-block brings both planes of the packed B operand (make_b_pack: plane 0 = B rounded to
+    // TF32, plane 1 = the bf16 correction operand B', both K-major) into the stage: [B hi][B'].  Its own warp, so that
+    // the A stream (warp kTmaWarp) and the B stream do not queue behind each other's waits and issue latencies.
+    ptx::reg_dealloc<kRegsOther>();
+    int s = 0;
+    uint32_t ph = 0;
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      const int split = unit / num_tiles, tile = unit - split * num_tiles;
+      const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+      const int n0 = (tile % n_tiles) * BN;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+        if (ptx::elect_one()) {
+          if (args.flags & kFlagDebugNoB) {  // (debug, wrong results) timing without the B stream
+            ptx::mbar_arrive(full_bar(s));
+          } else {
+            ptx::mbar_expect_tx(full_bar(s), 2 * Cfg::kBBytes);
+            ptx::tma_load_3d(ring_base + s * Cfg::kStageBytes, &tmB2, full_bar(s), kb * kBK, n0, 0);
+          }
+        }
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
     }
   } else if (MODE != 0 && warp > kMmaWarp) {
     // ===================================================== operand split (fp32-accurate modes)
@@ -804,6 +832,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
         ptx::tc_fence_after();
         const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
+        if (!(args.flags & kFlagDebugNoSplit))  // (debug, wrong results) handshakes only
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t r[16], w[16];
@@ -813,20 +842,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             r[4 * j4 + 0] = __float_as_uint(x.x), r[4 * j4 + 1] = __float_as_uint(x.y);
             r[4 * j4 + 2] = __float_as_uint(x.z), r[4 * j4 + 3] = __float_as_uint(x.w);
           }
-          ptx::tmem_st_32x16(dst + 16 * h, r);
           if (MODE == 2) {
+            // hi = x rounded to nearest TF32 (|lo| <= 2^-12 |x|, half of what truncation leaves), written explicitly:
+            // the tensor core would truncate the raw bits.  A' = [bf16(lo) x8 | bf16(x) x8] per group of 8 k.
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 const int k0 = 8 * g + 2 * i;
                 const float x0 = __uint_as_float(r[k0]), x1 = __uint_as_float(r[k0 + 1]);
-                w[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(r[k0] & 0xFFFFE000u),
-                                                x1 - __uint_as_float(r[k0 + 1] & 0xFFFFE000u));
+                const uint32_t h0 = (r[k0] + 0x1000u) & 0xFFFFE000u, h1 = (r[k0 + 1] + 0x1000u) & 0xFFFFE000u;
+                w[8 * g + i] = ptx::pack_bf16x2(x0 - __uint_as_float(h0), x1 - __uint_as_float(h1));
                 w[8 * g + 4 + i] = ptx::pack_bf16x2(x0, x1);
+                r[k0] = h0, r[k0 + 1] = h1;
               }
             }
+            ptx::tmem_st_32x16(dst + 16 * h, r);
           } else {
+            ptx::tmem_st_32x16(dst + 16 * h, r);
 #pragma unroll
             for (int j = 0; j < 16; ++j) w[j] = lo_of(__uint_as_float(r[j]));
           }

@@ -401,17 +401,19 @@ rtg_status MatMulOp::prepare(Context* ctx, const OpInputs& consts) {
   const int64_t K = b->t.shape[0], N = b->t.shape[1];
   if (K == 0 || N == 0 || b->t.strides[0] < 0 || b->t.strides[1] < 0) return RTG_OK;
   void* d = nullptr;
-  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(N) * div_ceil(K, kBK) * kBK * 4, &d));
-  b_prime = static_cast<uint32_t*>(d);
-  b_prime_from = b->t.data;
-  b_prime_dims[0] = K, b_prime_dims[1] = N, b_prime_dims[2] = b->t.strides[0], b_prime_dims[3] = b->t.strides[1];
-  return make_b_prime(ctx, MatView{static_cast<const float*>(b->t.data), K, N, b->t.strides[0], b->t.strides[1]}, b_prime);
+  const int64_t ld = b_pack_ld(K);
+  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(N) * ld * 4 * 2, &d));
+  b_pack = BPack{static_cast<const float*>(d), ld, N * ld};
+  b_pack_from = b->t.data;
+  b_pack_dims[0] = K, b_pack_dims[1] = N, b_pack_dims[2] = b->t.strides[0], b_pack_dims[3] = b->t.strides[1];
+  return make_b_pack(ctx, MatView{static_cast<const float*>(b->t.data), K, N, b->t.strides[0], b->t.strides[1]},
+                     static_cast<float*>(d), N * ld);
 }
 
 void MatMulOp::release(Context* ctx) {
-  if (b_prime) ctx->pool.free(b_prime);
-  b_prime = nullptr;
-  b_prime_from = nullptr;
+  if (b_pack.p) ctx->pool.free(const_cast<float*>(b_pack.p));
+  b_pack = BPack{};
+  b_pack_from = nullptr;
 }
 
 rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
@@ -457,9 +459,9 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     ep.alpha_div = scale_div;
     epp = &ep;
   }
-  if (b_prime && tb.data == b_prime_from && tb.ndim == 2 && tb.shape[0] == b_prime_dims[0] &&
-      tb.shape[1] == b_prime_dims[1] && tb.strides[0] == b_prime_dims[2] && tb.strides[1] == b_prime_dims[3]) {
-    ep.b_prime = b_prime;
+  if (b_pack.p && tb.data == b_pack_from && tb.ndim == 2 && tb.shape[0] == b_pack_dims[0] &&
+      tb.shape[1] == b_pack_dims[1] && tb.strides[0] == b_pack_dims[2] && tb.strides[1] == b_pack_dims[3]) {
+    ep.b_pack = b_pack;
     epp = &ep;
   }
   rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);

@@ -117,15 +117,15 @@ class MatMulOp : public Operator {
   bool fused() const { return has_bias || act != ACT_NONE || scale != 1.f || has_perm[0] || has_perm[1]; }
   const char* name() const override { return fused() ? "FusedMatMul" : "MatMul"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
-  // a constant 2-D right operand (linear-layer weights) gets its bf16 correction copy B' once at load (make_b_prime),
+  // a constant 2-D right operand (linear-layer weights) gets its packed copy (BPack) once at load (make_b_pack),
   // the counterpart of prepack_b for RTG_MATH_TF32_BF16X2
   rtg_status prepare(Context* ctx, const OpInputs& consts) override;
   void release(Context* ctx) override;
 
  private:
-  uint32_t* b_prime = nullptr;
-  const void* b_prime_from = nullptr;
-  int64_t b_prime_dims[4] = {0, 0, 0, 0};  // K, N, row stride, column stride of the operand it was made from
+  BPack b_pack;
+  const void* b_pack_from = nullptr;
+  int64_t b_pack_dims[4] = {0, 0, 0, 0};  // K, N, row stride, column stride of the operand it was made from
 };
 
 // operators_nn.cu: the remaining operators BERT-class graphs need

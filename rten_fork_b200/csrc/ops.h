@@ -76,9 +76,9 @@ struct ConvWeights {
   int kpt = 0;               // c_blocks*32
   bool direct = false;       // pointwise with C % 4 == 0: the OIHW tensor already is the K-major matrix
   bool window = false;       // row-window path (few input channels): wmat is [O][Kh][32]
-  // bf16 correction operand of wmat for RTG_MATH_TF32_BF16X2 (make_b_prime), same row pitch as wmat rounded up to 32
-  uint32_t* wprime = nullptr;
-  int64_t wprime_ld = 0;
+  // packed copy of wmat for RTG_MATH_TF32_BF16X2 (make_b_pack): two planes [O][wpack.ld], row pitch = wmat's rounded up
+  // to 32
+  BPack wpack;
 };
 bool conv_window_supported(const ConvPlan& p);
 rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out);

@@ -19,7 +19,7 @@ using namespace rtg;
     }                                                                                \
   } while (0)
 
-enum Form { SS_TF32 = 0, TS_TF32 = 1, TS_F16 = 2, ALT_TS = 3, GRP_TS = 4, SS_F16 = 5 };
+enum Form { SS_TF32 = 0, TS_TF32 = 1, TS_F16 = 2, ALT_TS = 3, GRP_TS = 4, SS_F16 = 5, DUAL_TS_TF32 = 6, DUAL_ALT = 7, DUAL_SS_TF32 = 8, QUAD_TS_TF32 = 9 };
 
 __device__ __forceinline__ void mma2_tf32_ts(uint32_t d, uint32_t a_t, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
@@ -49,8 +49,9 @@ __device__ __forceinline__ void commit2(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-__device__ __forceinline__ void issue1(int form, int i, uint32_t d, uint32_t a_t, uint64_t adesc, uint64_t bdesc,
-                                       uint32_t id_tf32, uint32_t id_bf16) {
+template <int form>
+__device__ __forceinline__ void issue1(int i, uint32_t d, uint32_t a_t, uint64_t adesc, uint64_t bdesc,
+                                       uint32_t id_tf32, uint32_t id_bf16, uint32_t dn = 128) {
   const uint32_t bl = static_cast<uint32_t>(bdesc), bh = static_cast<uint32_t>(bdesc >> 32);
   const uint32_t al = static_cast<uint32_t>(adesc), ah = static_cast<uint32_t>(adesc >> 32);
   const uint32_t ks = (i & 3) * 2;  // walk the four k-steps of a 128-byte row
@@ -67,13 +68,21 @@ __device__ __forceinline__ void issue1(int form, int i, uint32_t d, uint32_t a_t
       else ptx::mma_f16_ts_w(d, a_t + 32 + (i & 3) * 8, bl + 1024 + ks, bh, id_bf16, 1);
       break;
     case SS_F16: mma_f16_ss(d, adesc + ks, bdesc + ks, id_bf16, 1); break;
+    // independent accumulators, interleaved (dn = columns per accumulator)
+    case DUAL_TS_TF32: ptx::mma_tf32_ts_w(d + (i & 1) * dn, a_t + ((i >> 1) & 3) * 8, bl + ks, bh, id_tf32, 1); break;
+    case DUAL_SS_TF32: ptx::mma_tf32_ss_w(d + (i & 1) * dn, al + ks, ah, bl + ks, bh, id_tf32, 1); break;
+    case QUAD_TS_TF32: ptx::mma_tf32_ts_w(d + (i & 3) * dn, a_t + ((i >> 2) & 3) * 8, bl + ks, bh, id_tf32, 1); break;
+    case DUAL_ALT:  // TF32 hi*hi into accumulator 0, bf16 corrections into accumulator 1
+      if (i & 1) ptx::mma_tf32_ts_w(d, a_t + ((i >> 1) & 3) * 8, bl + ks, bh, id_tf32, 1);
+      else ptx::mma_f16_ts_w(d + dn, a_t + 32 + ((i >> 1) & 3) * 8, bl + 1024 + ks, bh, id_bf16, 1);
+      break;
   }
 }
 
 // mode 0: throughput of a chain of `reps` MMAs; mode 1: clock after every issue (queue depth); mode 2: pipeline skeleton
 // (a producer warp arrives on `full`, the MMA thread waits `nwait` barriers, issues `per_round` MMAs, commits `empty`)
-template <int N>
-__global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, int per_round, int nwait, long long* out) {
+template <int N, int form>
+__global__ void __launch_bounds__(128, 1) probe1(int mode, int reps, int per_round, int nwait, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = base + 160 * 1024;
@@ -124,7 +133,7 @@ __global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, i
         __syncwarp();
         t0 = clock64();
         if (ptx::elect_one()) {
-          for (int i = 0; i < reps; ++i) issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          _Pragma("unroll 8") for (int i = 0; i < reps; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
           ptx::mma_commit(done);
         }
         __syncwarp();
@@ -136,7 +145,7 @@ __global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, i
       if (lane == 0) {
         const long long t0 = clock64();
         for (int i = 0; i < reps && i < 64; ++i) {
-          issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
           out[1 + i] = clock64() - t0;
         }
         ptx::mma_commit(done);
@@ -154,7 +163,7 @@ __global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, i
         if (nwait > 1) ptx::mbar_wait(full2(s), ph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          for (int i = 0; i < per_round; ++i) issue1(form, i, d, a_t, adesc, bdesc, id_tf32, id_bf16);
+          _Pragma("unroll 8") for (int i = 0; i < per_round; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
           ptx::mma_commit(empty(s));
         }
         __syncwarp();
@@ -175,8 +184,8 @@ __global__ void __launch_bounds__(128, 1) probe1(int form, int mode, int reps, i
 }
 
 // 2-CTA pair: M = 256 (128 rows per CTA), each CTA holds N/2 columns of B.  The leader CTA's thread issues.
-template <int N>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int form, int reps, long long* out) {
+template <int N, int form>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int reps, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = base + 160 * 1024;
@@ -209,6 +218,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int f
       __syncwarp();
       t0 = clock64();
       if (ptx::elect_one()) {
+_Pragma("unroll 8")
         for (int i = 0; i < reps; ++i) {
           const uint32_t ks = (i & 3) * 2;
           if (form == TS_TF32) mma2_tf32_ts(d, a_t + (i & 3) * 8, bdesc + ks, id_tf32, 1);
@@ -234,14 +244,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int f
   }
 }
 
-static const char* kFormName[] = {"SS tf32", "TS tf32", "TS bf16", "alt TS bf16/tf32", "4 bf16 + 4 tf32 TS", "SS bf16"};
+static const char* kFormName[] = {"SS tf32", "TS tf32", "TS bf16", "alt TS bf16/tf32", "4 bf16 + 4 tf32 TS", "SS bf16", "TS tf32, 2 accs", "bf16->acc1 tf32->acc0", "SS tf32, 2 accs", "TS tf32, 4 accs"};
 constexpr int kSmem = 160 * 1024 + 1024 + 256;
 
-template <int N>
-static void run1(long long* dout, int form, int mode, int reps, int per_round, int nwait) {
-  CK(cudaFuncSetAttribute(probe1<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+template <int N, int form>
+static void run1f(long long* dout, int mode, int reps, int per_round, int nwait) {
+  CK(cudaFuncSetAttribute(probe1<N, form>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   CK(cudaMemset(dout, 0, 80 * 8));
-  probe1<N><<<1, 128, kSmem>>>(form, mode, reps, per_round, nwait, dout);
+  probe1<N, form><<<1, 128, kSmem>>>(mode, reps, per_round, nwait, dout);
   CK(cudaDeviceSynchronize());
   long long h[80];
   CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
@@ -258,10 +268,30 @@ static void run1(long long* dout, int form, int mode, int reps, int per_round, i
 }
 
 template <int N>
+static void run1(long long* dout, int form, int mode, int reps, int per_round, int nwait) {
+  switch (form) {
+    case 0: run1f<N, 0>(dout, mode, reps, per_round, nwait); break;
+    case 1: run1f<N, 1>(dout, mode, reps, per_round, nwait); break;
+    case 2: run1f<N, 2>(dout, mode, reps, per_round, nwait); break;
+    case 3: run1f<N, 3>(dout, mode, reps, per_round, nwait); break;
+    case 4: run1f<N, 4>(dout, mode, reps, per_round, nwait); break;
+    case 5: run1f<N, 5>(dout, mode, reps, per_round, nwait); break;
+    case 6: run1f<N, 6>(dout, mode, reps, per_round, nwait); break;
+    case 7: run1f<N, 7>(dout, mode, reps, per_round, nwait); break;
+    case 8: run1f<N, 8>(dout, mode, reps, per_round, nwait); break;
+    case 9: run1f<N, 9>(dout, mode, reps, per_round, nwait); break;
+  }
+}
+
+template <int N>
 static void run2(long long* dout, int form, int reps) {
-  CK(cudaFuncSetAttribute(probe2<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   CK(cudaMemset(dout, 0, 80 * 8));
-  probe2<N><<<2, 128, kSmem>>>(form, reps, dout);
+  switch (form) {
+    case 0: CK(cudaFuncSetAttribute(probe2<N, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)); probe2<N, 0><<<2, 128, kSmem>>>(reps, dout); break;
+    case 1: CK(cudaFuncSetAttribute(probe2<N, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)); probe2<N, 1><<<2, 128, kSmem>>>(reps, dout); break;
+    case 2: CK(cudaFuncSetAttribute(probe2<N, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)); probe2<N, 2><<<2, 128, kSmem>>>(reps, dout); break;
+    case 3: CK(cudaFuncSetAttribute(probe2<N, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)); probe2<N, 3><<<2, 128, kSmem>>>(reps, dout); break;
+  }
   CK(cudaDeviceSynchronize());
   long long h[1];
   CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
@@ -277,7 +307,16 @@ int main() {
     run1<128>(dout, form, 0, reps, 0, 0);
     if (form != ALT_TS && form != GRP_TS) run1<256>(dout, form, 0, reps, 0, 0);
   }
-  for (int form : {SS_TF32, TS_TF32, ALT_TS}) run1<128>(dout, form, 1, 64, 0, 0);
+  for (int form : {DUAL_TS_TF32, DUAL_ALT, DUAL_SS_TF32}) {
+    run1<64>(dout, form, 0, reps, 0, 0);
+    run1<128>(dout, form, 0, reps, 0, 0);
+  }
+  run1<64>(dout, QUAD_TS_TF32, 0, reps, 0, 0);
+  run1<32>(dout, QUAD_TS_TF32, 0, reps, 0, 0);
+  run1<32>(dout, TS_TF32, 0, reps, 0, 0);
+  run1<192>(dout, TS_TF32, 0, reps, 0, 0);
+  for (int per_round : {4, 8, 16}) run1<128>(dout, DUAL_ALT, 2, 1024, per_round, 1);
+  for (int form : {SS_TF32, TS_TF32, ALT_TS, DUAL_ALT}) run1<128>(dout, form, 1, 64, 0, 0);
   for (int form : {SS_TF32, ALT_TS, GRP_TS})
     for (int per_round : {4, 8, 16, 32})
       for (int nwait : {1, 2}) run1<128>(dout, form, 2, 1024, per_round, nwait);

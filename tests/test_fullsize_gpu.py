@@ -4,9 +4,10 @@ at batch 64 x seq 128, and the square GEMM sweep above 1024 (plus the K = 16384 
 against the oracle (graphs) or float64 (single GEMMs), in all three math modes.
 
 Tolerances.  Single contractions are held to the reference's own rule (rten-tensor/src/test_util.rs:44-61:
-|x - y| <= 1e-8 + 1e-5 |y|; TF32 mode: the stated 2e-3).  Early post-ReLU activations of a graph (one to three
-contractions deep) are held to that rule per element plus an absolute floor of 2e-6 of the tensor's scale (elements
-that are small sums of large terms: the oracle itself sums in fp32 in another order).  Values 50 layers deep are
+|x - y| <= 1e-8 + 1e-5 |y|; TF32 mode: the stated 2e-3).  Early post-ReLU activations of a graph are held to that
+rule per element, once per contraction between the input and the value (relu1: one, layer1.0.relu3: four), plus an
+absolute floor of 2e-6 of the tensor's scale per contraction (elements that are small sums of large terms: the oracle
+itself sums in fp32 in another order).  Values 50 layers deep are
 compared against the scale of the tensor at 20x the mode's rtol, like the reduced-size graph tests: two correct fp32
 evaluations of a 53-convolution network differ by more than 1e-5 per element, and the reference has no test that says
 otherwise (its model tests compare single operators, src/ops/conv.rs:677-702, src/gemm.rs:1185-1238).
@@ -33,7 +34,10 @@ def _case(key, make):
     return _cache[key]
 
 
-def _check_graph(got, want, names, strict, math_mode):
+def _check_graph(got, want, names, depth, math_mode):
+    """`depth`: name -> number of contractions between the graph input and that value, for the values held to the
+    per-element rule: every contraction may contribute the mode's rtol once (and an absolute floor of 2e-6 of the
+    tensor's scale for elements that are small sums of large terms); the rest are compared against the scale."""
     rtol = math_mode["rtol"]
     report = []
     for g, w, name in zip(got, want, names):
@@ -41,9 +45,10 @@ def _check_graph(got, want, names, strict, math_mode):
         scale = float(np.abs(w).max())
         err = np.abs(g.astype(np.float64) - w.astype(np.float64))
         report.append(f"{name}: max err {err.max():.3e} (scale {scale:.3e}, rel-to-scale {err.max() / scale:.2e})")
-        if name in strict:
-            bad = err > rtol * np.abs(w) + 2e-6 * scale * (rtol / 1e-5)
-            assert not bad.any(), f"{name}: {bad.sum()} of {bad.size} elements outside rtol {rtol}; " + "; ".join(report)
+        if name in depth:
+            d = depth[name]
+            bad = err > d * (rtol * np.abs(w) + 2e-6 * scale * (rtol / 1e-5))
+            assert not bad.any(), f"{name}: {bad.sum()} of {bad.size} elements outside {d} x rtol {rtol}; " + "; ".join(report)
         else:
             assert err.max() <= 20 * rtol * scale, "; ".join(report)
     print("\n".join(report))
@@ -54,7 +59,7 @@ def _resnet50_b32(oracle):
     from rten_fork_b200 import synth
 
     b = synth.resnet50(image=224, classes=1000, seed=0)   # bench.py's graph
-    names = ["layer1.0.relu3", "layer2.0.relu3", "layer3.0.relu3", "layer4.2.relu3", "fc"]
+    names = ["relu1", "layer1.0.relu3", "layer2.0.relu3", "layer3.0.relu3", "layer4.2.relu3", "fc"]
     b.outputs = [_node_output(b, n) for n in names]
     x = oracle.XorShiftRng(1234).fill((32, 3, 224, 224))
     return b, names, x, graph_oracle.run_graph(b, [x])
@@ -72,7 +77,7 @@ def test_resnet50_b32_full_size(rtg, ctx, oracle, math_mode):
     finally:
         m.close()
     assert got[-1].shape == (32, 1000)
-    _check_graph(got, want, names, {"layer1.0.relu3"}, math_mode)
+    _check_graph(got, want, names, {"relu1": 1, "layer1.0.relu3": 4}, math_mode)
 
 
 def _mobilenet_b64(oracle):
@@ -96,7 +101,7 @@ def test_mobilenet_v2_b64_full_size(rtg, ctx, oracle, math_mode):
         got = m.run([x])
     finally:
         m.close()
-    _check_graph(got, want, names, {"features.0.relu6"}, math_mode)
+    _check_graph(got, want, names, {"features.0.relu6": 1}, math_mode)
 
 
 def _bert_layer(oracle):
@@ -124,7 +129,7 @@ def test_bert_base_layer_b64_s128(rtg, ctx, oracle, math_mode):
         got = m.run(ins)
     finally:
         m.close()
-    _check_graph(got, want, names, set(), math_mode)
+    _check_graph(got, want, names, {}, math_mode)
 
 
 def _f64_case(m, n, k):
