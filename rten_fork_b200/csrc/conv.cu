@@ -349,7 +349,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
       }
       WindowGeom wg = {N, hp, wp, cpw, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
                        static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.dil_h), C};
-      ep.b_pack = w.wpack;
+      ep.b_pack = w.wpack, ep.b_pack_const = w.persistent;
       RTG_TRY(conv_window_gemm_device(ctx, x_pad.f32(), wg, w.wmat, O, static_cast<float*>(out.data), dm, ep));
       if (need_out_tmp) RTG_TRY(copy_view(ctx, out_final, out));
       return RTG_OK;
@@ -384,7 +384,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
       float* D = static_cast<float*>(out.data);
       if (w.direct) {
         // pointwise: A = activations [M, C] (pitch cp), B = W [O][C]
-        ep.b_pack = w.wpack;
+        ep.b_pack = w.wpack, ep.b_pack_const = w.persistent;
         RTG_TRY(gemm_device(ctx, MatView{xp, M, C, cp, 1}, MatView{w.wmat, C, O, 1, C}, D, dm, ep));
         continue;
       }
@@ -395,7 +395,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
                      static_cast<int>(p.pads[1]), static_cast<int>(p.pads[2]), static_cast<int>(p.pads[3]),
                      static_cast<int>(p.dil_h), static_cast<int>(p.dil_w)};
       if (conv_im2col_supported(cg)) {
-        ep.b_pack = w.wpack;  // rows [g * OG, +OG) of both planes
+        ep.b_pack = w.wpack, ep.b_pack_const = w.persistent;  // rows [g * OG, +OG) of both planes
         if (ep.b_pack.p) ep.b_pack.p += static_cast<int64_t>(g) * OG * w.wpack.ld;
         RTG_TRY(conv_gemm_device(ctx, xp, cg, wg, OG, D, dm, ep));
         ep.b_pack = BPack{};

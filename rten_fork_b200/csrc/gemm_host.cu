@@ -451,7 +451,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   g.act = ep.act;
   g.act_lo = ep.act_lo;
   g.act_hi = ep.act_hi;
-  g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0);
+  g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0) | (ep.b_pack.p && ep.b_pack_const ? kFlagBConst : 0);
   g.splits = splits;
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
@@ -617,7 +617,7 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   a.act = ep.act;
   a.act_lo = ep.act_lo;
   a.act_hi = ep.act_hi;
-  a.flags = debug_flags();
+  a.flags = debug_flags() | (ep.b_pack.p && ep.b_pack_const ? kFlagBConst : 0);
   a.splits = splits;
   a.ic.ow = g.ow;
   a.ic.oh = g.oh;
@@ -684,7 +684,7 @@ rtg_status conv_window_gemm_device(Context* ctx, const float* x_pad, const Windo
   a.act = ep.act;
   a.act_lo = ep.act_lo;
   a.act_hi = ep.act_hi;
-  a.flags = debug_flags();
+  a.flags = debug_flags() | (ep.b_pack.p && ep.b_pack_const ? kFlagBConst : 0);
   a.ic.ow = g.ow;
   a.ic.oh = g.oh;
   a.ic.stride_h = g.stride_h;

@@ -33,6 +33,7 @@ struct Epilogue {
   // RTG_MATH_TF32_BF16X2: the packed B operand of a constant B, written by make_b_pack at load time; p == NULL =
   // computed by a pre-pass of this call
   BPack b_pack;
+  bool b_pack_const = false;  // b_pack was written at load time (not by an earlier launch of this call): loads of it need no stream dependency
   int n_peers = 0;
   float* peer_D[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };

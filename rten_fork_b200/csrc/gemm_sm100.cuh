@@ -124,7 +124,8 @@ struct GemmArgs {
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
 constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
 constexpr int kFlagStagedR = 4;  // residual arrives by TMA load into the same staging buffer (needs kFlagStagedD)
-constexpr int kFlagDebugNoB = 32, kFlagDebugNoA = 64, kFlagDebugNoSplit = 128, kFlagDebugNoDrain = 256;  // (debug) MODE 2: skip the B / A TMA stream (timing experiments)
+constexpr int kFlagDebugNoB = 32, kFlagDebugNoA = 64;
+constexpr int kFlagBConst = 512;   // the packed B operand was written at load time: nothing in this stream produces it  // (debug) MODE 2: skip the B / A TMA stream (timing experiments)
 constexpr int kFlagAlphaDiv = 16;  // alpha is a divisor: D = acc / alpha (8 is the debug "no staging" switch)
 
 constexpr int kBM = 128;
@@ -325,8 +326,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // while the previous kernel in the stream drains.  From here on global memory is read and written: wait for the
   // predecessor's results (and its last reads of buffers this launch overwrites), then let the successor start its
   // own prologue early.  Both are no-ops when the launch did not ask for programmatic serialisation.
-  ptx::grid_dependency_wait();
-  ptx::grid_launch_dependents();
+  // The B producer of a launch whose B operand is a load-time constant (weights) skips the wait: its first kStages
+  // loads overlap the previous kernel's tail.
+  if (!(MODE == 2 && warp == kMmaWarp + 9 && (args.flags & kFlagBConst))) {
+    ptx::grid_dependency_wait();
+    ptx::grid_launch_dependents();
+  }
   // MODE 1: 512 threads start with 128 registers each.  An epilogue thread carries BN/2 running sums plus a 32-column
   // chunk and spilled at that size; the TMA / MMA / operand-split warpgroups need fewer, so every role branch starts
   // by re-balancing the register file: 8 x 32 x kRegsEpi + 8 x 32 x kRegsOther = 64 K.
@@ -730,7 +735,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
           PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
           ptx::tc_fence_after();
-          if (!(args.flags & kFlagDebugNoDrain) || kb0 == kb_begin)  // (debug, wrong results) skip the chunk drains
 #pragma unroll
           for (int c0 = 0; c0 < kCols; c0 += 32) {
             float v[32];
@@ -762,7 +766,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
-    PROF_WAIT(3, if (staged_d && lane == 0) ptx::bulk_wait<0>());  // stores complete before shared memory goes away
+    // the stores must have READ their staging buffers before shared memory goes away; their global writes complete with
+    // the grid (a dependent launch waits for that in griddepcontrol.wait)
+    PROF_WAIT(3, if (staged_d && lane == 0) ptx::bulk_wait_read<0>());
     if (warp == 0 && lane == 0) {
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
@@ -832,7 +838,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
         ptx::tc_fence_after();
         const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
-        if (!(args.flags & kFlagDebugNoSplit))  // (debug, wrong results) handshakes only
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t r[16], w[16];

@@ -58,6 +58,7 @@ rtg_status ConvOp::prepare(Context* ctx, const OpInputs& consts) {
   if (partial_plan(w->t, &p) != RTG_OK) return RTG_OK;  // run() reports the real error
   RTG_TRY(conv_prepare_weights(ctx, p, static_cast<const float*>(w->t.data), &weights));
   prepared = true;
+  weights.persistent = true;
   prepared_pointwise = p.pointwise;
   prepared_depthwise = p.depthwise;
   prepared_from = w->t.data;
@@ -461,7 +462,7 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
   }
   if (b_pack.p && tb.data == b_pack_from && tb.ndim == 2 && tb.shape[0] == b_pack_dims[0] &&
       tb.shape[1] == b_pack_dims[1] && tb.strides[0] == b_pack_dims[2] && tb.strides[1] == b_pack_dims[3]) {
-    ep.b_pack = b_pack;
+    ep.b_pack = b_pack, ep.b_pack_const = true;
     epp = &ep;
   }
   rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);

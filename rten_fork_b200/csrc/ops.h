@@ -79,6 +79,7 @@ struct ConvWeights {
   // packed copy of wmat for RTG_MATH_TF32_BF16X2 (make_b_pack): two planes [O][wpack.ld], row pitch = wmat's rounded up
   // to 32
   BPack wpack;
+  bool persistent = false;   // prepared at load time (Operator::prepare), not by the call that uses it
 };
 bool conv_window_supported(const ConvPlan& p);
 rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_dev, ConvWeights* out);

@@ -74,6 +74,7 @@ def run_table(mode, filt, layers, B):
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_math({"3xtf32": R.MATH_3XTF32, "tf32": R.MATH_TF32, "tf32_bf16x2": R.MATH_TF32_BF16X2}[mode])
     tot = 0.0
+    tot_chain = 0.0
     for name, cin, cout, k, s, p, hw, res, groups, act in layers:
         if filt and filt not in name:
             continue
@@ -106,9 +107,20 @@ def run_table(mode, filt, layers, B):
                   "bytes": nbytes * n}
         us = kt["ms"] / kt["launches"] * 1e3
         tot += us
+        # steady state inside a stream: 20 launches back to back between ONE pair of events (what Graph::run sees:
+        # programmatic dependent launch overlaps each prologue with the previous tail, no event between launches)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            ops.conv(x, w, b, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        chain = e0.elapsed_time(e1) / 20 * 1e3
+        tot_chain += chain
         print(f"{name:24s} {us:8.1f} us  {kt['flops'] / kt['launches'] / us / 1e6:7.1f} TF/s  "
-              f"{kt['bytes'] / kt['launches'] / us / 1e3:7.1f} GB/s  {ctx.last_kernel}")
-    print(f"sum {tot:.1f} us")
+              f"{kt['bytes'] / kt['launches'] / us / 1e3:7.1f} GB/s  chained {chain:6.1f} us  {ctx.last_kernel}")
+    print(f"sum {tot:.1f} us, chained {tot_chain:.1f} us")
 
 
 if __name__ == "__main__":
