@@ -241,6 +241,29 @@ rtg_status rtg_run_output_info(const rtg_run* run, int32_t i, int64_t* shape, in
 /* Copies output i (contiguous, reference layout) to `dst` on `device` (RTG_HOST or ordinal). */
 rtg_status rtg_run_output_copy(rtg_run* run, int32_t i, void* dst, size_t dst_bytes, int32_t device);
 rtg_status rtg_run_free(rtg_run* run);
+/* Model::run proper: inputs and outputs addressed by node id                    src/model.rs:580-592
+ * (rtg_model_run above is run with the graph's own input / output lists).  Any value node may be requested, e.g. an
+ * intermediate activation; ids must be unique ("Inputs are not unique" / "Outputs are not unique"). */
+rtg_status rtg_model_run_ids(rtg_model* model, const int32_t* input_ids, const rtg_tensor* inputs, int32_t n_inputs,
+                             const int32_t* output_ids, int32_t n_outputs, rtg_run** out);
+/* Model::partial_run / Graph::partial_run                                      src/model.rs:639-646, src/graph.rs:1147-1235
+ * Runs with an incomplete set of inputs: every operator of the plan whose inputs are available is evaluated; the run's
+ * outputs are the leaves of that sub-plan (requested outputs, or values feeding operators that could not run).
+ * rtg_run_output_node gives the node id of each; pass them to rtg_model_run_ids later with the remaining inputs. */
+rtg_status rtg_model_partial_run(rtg_model* model, const int32_t* input_ids, const rtg_tensor* inputs, int32_t n_inputs,
+                                 const int32_t* output_ids, int32_t n_outputs, rtg_run** out);
+rtg_status rtg_run_output_node(const rtg_run* run, int32_t i, int32_t* node_id);
+/* Model::find_node, input_ids, output_ids                                      src/model.rs:525-553 */
+rtg_status rtg_model_find_node(const rtg_model* model, const char* name, int32_t* id);
+rtg_status rtg_model_input_id(const rtg_model* model, int32_t i, int32_t* id);
+rtg_status rtg_model_output_id(const rtg_model* model, int32_t i, int32_t* id);
+/* Graph::get_node / get_source_node                                            src/graph.rs:560-600
+ * kind: 0 operator, 1 constant, 2 value.  rtg_model_source_op: the operator producing value `value_id` after the
+ * load-time optimiser (GraphOptimizer, src/optimize.rs:286-297) ran: its operator name ("Silu", "Gelu",
+ * "LayerNormalization", "FusedMatMul", ...) and its node name. */
+rtg_status rtg_model_node_kind(const rtg_model* model, int32_t id, int32_t* kind);
+rtg_status rtg_model_source_op(const rtg_model* model, int32_t value_id, const char** op_name, const char** node_name);
+
 /* Asynchronous Model::run over HOST buffers (no reference counterpart: the reference runs on the caller's thread;
  * this is what a serving loop binds instead of rtg_model_run to keep the PCIe copies off the critical path).
  * The inputs are uploaded on a second stream into one of two staging slots, so the upload of submit i + 1 overlaps

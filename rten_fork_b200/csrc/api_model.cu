@@ -61,11 +61,27 @@ std::string format_timing(const std::vector<TimingRecord>& recs, const DevPool& 
 
 // Model::run proper.  `host_mirror` (rtg_model_submit): the caller's host copies of `inputs`, which then point at
 // device staging buffers; small i32 inputs keep a host mirror for shape arithmetic either way.
-rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, const rtg_tensor* host_mirror, Run** out) {
+// `input_ids` / `output_ids`: node ids (Model::run addresses values by id, src/model.rs:580-592); NULL = the graph's
+// own input / output lists in order.  `partial`: Model::partial_run (src/model.rs:639-646).
+rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, const rtg_tensor* host_mirror, Run** out,
+                      const int32_t* input_ids = nullptr, const int32_t* output_ids = nullptr, int32_t n_outputs = 0,
+                      bool partial = false) {
   Context* ctx = m->ctx;
   Graph& g = m->graph;
-  if (n_inputs != static_cast<int32_t>(g.input_ids.size()))
+  if (!input_ids && n_inputs != static_cast<int32_t>(g.input_ids.size()))
     return set_errorf(RTG_ERR_MISSING_INPUTS, "model expects %zu inputs, got %d", g.input_ids.size(), n_inputs);
+  const int32_t n_nodes = static_cast<int32_t>(g.nodes.size());
+  for (int32_t i = 0; input_ids && i < n_inputs; ++i) {
+    if (input_ids[i] < 0 || input_ids[i] >= n_nodes) return set_error(RTG_ERR_INVALID_VALUE, "Input node ID is invalid");
+    for (int32_t k = 0; k < i; ++k)
+      if (input_ids[k] == input_ids[i]) return set_error(RTG_ERR_INVALID_VALUE, "Inputs are not unique");  // RunError::PlanningError
+  }
+  std::vector<int32_t> outs_req = output_ids ? std::vector<int32_t>(output_ids, output_ids + n_outputs) : g.output_ids;
+  for (size_t i = 0; i < outs_req.size(); ++i) {
+    if (outs_req[i] < 0 || outs_req[i] >= n_nodes) return set_error(RTG_ERR_INVALID_VALUE, "Output node ID is invalid");
+    for (size_t k = 0; k < i; ++k)
+      if (outs_req[k] == outs_req[i]) return set_error(RTG_ERR_INVALID_VALUE, "Outputs are not unique");
+  }
   std::vector<std::pair<int32_t, Value>> in;
   auto cleanup = [&]() {
     for (auto& kv : in) release_value(ctx, &kv.second);
@@ -113,13 +129,25 @@ rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, cons
         }
       }
     }
-    in.emplace_back(g.input_ids[i], v);
+    in.emplace_back(input_ids ? input_ids[i] : g.input_ids[i], v);
   }
   std::unique_ptr<Run> run(new Run());
   run->ctx = ctx;
   std::vector<TimingRecord> recs;
-  rtg_status st = g.run(ctx, in, g.output_ids, &run->outputs, m->timing ? &recs : nullptr);
+  if (partial) {
+    std::vector<std::pair<int32_t, Value>> leaves;
+    rtg_status st = g.partial_run(ctx, in, outs_req, &leaves);
+    if (st != RTG_OK) return st;
+    for (auto& kv : leaves) {
+      run->node_ids.push_back(kv.first);
+      run->outputs.push_back(kv.second);
+    }
+    *out = run.release();
+    return RTG_OK;
+  }
+  rtg_status st = g.run(ctx, in, outs_req, &run->outputs, m->timing ? &recs : nullptr);
   if (st != RTG_OK) return st;  // Graph::run released the inputs
+  run->node_ids = outs_req;
   if (m->timing) m->timing_report = format_timing(recs, ctx->pool);
   *out = run.release();
   return RTG_OK;
@@ -215,6 +243,88 @@ rtg_status rtg_model_run(rtg_model* model, const rtg_tensor* inputs, int32_t n_i
   Run* run = nullptr;
   RTG_TRY(run_inputs(m, inputs, n_inputs, nullptr, &run));
   *out = reinterpret_cast<rtg_run*>(run);
+  return RTG_OK;
+}
+
+rtg_status rtg_model_run_ids(rtg_model* model, const int32_t* input_ids, const rtg_tensor* inputs, int32_t n_inputs,
+                             const int32_t* output_ids, int32_t n_outputs, rtg_run** out) {
+  Model* m = reinterpret_cast<Model*>(model);
+  if (!m || !out || (n_inputs > 0 && (!inputs || !input_ids)) || (n_outputs > 0 && !output_ids))
+    return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(m->ctx->device));
+  static const int32_t none = 0;
+  Run* run = nullptr;
+  RTG_TRY(run_inputs(m, inputs, n_inputs, nullptr, &run, input_ids ? input_ids : &none, output_ids ? output_ids : &none,
+                     n_outputs, false));
+  *out = reinterpret_cast<rtg_run*>(run);
+  return RTG_OK;
+}
+
+rtg_status rtg_model_partial_run(rtg_model* model, const int32_t* input_ids, const rtg_tensor* inputs, int32_t n_inputs,
+                                 const int32_t* output_ids, int32_t n_outputs, rtg_run** out) {
+  Model* m = reinterpret_cast<Model*>(model);
+  if (!m || !out || (n_inputs > 0 && (!inputs || !input_ids)) || (n_outputs > 0 && !output_ids))
+    return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_CUDA(cudaSetDevice(m->ctx->device));
+  static const int32_t none = 0;
+  Run* run = nullptr;
+  RTG_TRY(run_inputs(m, inputs, n_inputs, nullptr, &run, input_ids ? input_ids : &none, output_ids ? output_ids : &none,
+                     n_outputs, true));
+  *out = reinterpret_cast<rtg_run*>(run);
+  return RTG_OK;
+}
+
+rtg_status rtg_run_output_node(const rtg_run* run, int32_t i, int32_t* node_id) {
+  const Run* r = reinterpret_cast<const Run*>(run);
+  if (!r || !node_id || i < 0 || i >= static_cast<int32_t>(r->node_ids.size()))
+    return set_error(RTG_ERR_INVALID_VALUE, "output index out of range");
+  *node_id = r->node_ids[i];
+  return RTG_OK;
+}
+
+rtg_status rtg_model_find_node(const rtg_model* model, const char* name, int32_t* id) {
+  const Model* m = reinterpret_cast<const Model*>(model);
+  if (!m || !name || !id) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  for (size_t i = 0; i < m->graph.nodes.size(); ++i)
+    if (m->graph.nodes[i].name == name) {
+      *id = static_cast<int32_t>(i);
+      return RTG_OK;
+    }
+  return set_errorf(RTG_ERR_INVALID_VALUE, "node \"%s\" not found", name);
+}
+
+rtg_status rtg_model_input_id(const rtg_model* model, int32_t i, int32_t* id) {
+  const Model* m = reinterpret_cast<const Model*>(model);
+  if (!m || !id || i < 0 || i >= static_cast<int32_t>(m->graph.input_ids.size()))
+    return set_error(RTG_ERR_INVALID_VALUE, "input index out of range");
+  *id = m->graph.input_ids[i];
+  return RTG_OK;
+}
+
+rtg_status rtg_model_output_id(const rtg_model* model, int32_t i, int32_t* id) {
+  const Model* m = reinterpret_cast<const Model*>(model);
+  if (!m || !id || i < 0 || i >= static_cast<int32_t>(m->graph.output_ids.size()))
+    return set_error(RTG_ERR_INVALID_VALUE, "output index out of range");
+  *id = m->graph.output_ids[i];
+  return RTG_OK;
+}
+
+rtg_status rtg_model_node_kind(const rtg_model* model, int32_t id, int32_t* kind) {
+  const Model* m = reinterpret_cast<const Model*>(model);
+  if (!m || !kind || id < 0 || id >= static_cast<int32_t>(m->graph.nodes.size()))
+    return set_error(RTG_ERR_INVALID_VALUE, "node id out of range");
+  *kind = static_cast<int32_t>(m->graph.nodes[id].kind);
+  return RTG_OK;
+}
+
+rtg_status rtg_model_source_op(const rtg_model* model, int32_t value_id, const char** op_name, const char** node_name) {
+  const Model* m = reinterpret_cast<const Model*>(model);
+  if (!m || value_id < 0 || value_id >= static_cast<int32_t>(m->graph.nodes.size()))
+    return set_error(RTG_ERR_INVALID_VALUE, "node id out of range");
+  const int32_t src = m->graph.source_node(value_id);
+  if (src < 0) return set_error(RTG_ERR_INVALID_VALUE, "value has no source operator");
+  if (op_name) *op_name = m->graph.nodes[src].op->name();
+  if (node_name) *node_name = m->graph.nodes[src].name.c_str();
   return RTG_OK;
 }
 

@@ -90,8 +90,17 @@ void Graph::release(Context* ctx) {
 }
 
 // Depth-first from the requested outputs; an operator is scheduled once all of its inputs are resolved.
+int32_t Graph::source_node(int32_t id) const {
+  const int32_t n = static_cast<int32_t>(nodes.size());
+  for (int32_t i = 0; i < n; ++i)
+    if (nodes[i].kind == NodeKind::Operator)
+      for (int32_t o : nodes[i].outputs)
+        if (o == id) return i;
+  return -1;
+}
+
 rtg_status Graph::create_plan(const std::vector<int32_t>& inputs, const std::vector<int32_t>& outputs,
-                              std::vector<int32_t>* plan) const {
+                              std::vector<int32_t>* plan, bool allow_missing) const {
   plan->clear();
   const int32_t n = static_cast<int32_t>(nodes.size());
   std::vector<int32_t> producer(nodes.size(), -1);  // value node id -> operator node id
@@ -114,8 +123,10 @@ rtg_status Graph::create_plan(const std::vector<int32_t>& inputs, const std::vec
   for (int32_t out : outputs) {
     if (out < 0 || out >= n) return set_error(RTG_ERR_INVALID_VALUE, "Output node ID is invalid");
     if (resolved[out]) continue;
-    if (producer[out] < 0)
+    if (producer[out] < 0) {
+      if (allow_missing) continue;
       return set_errorf(RTG_ERR_INVALID_VALUE, "Missing input \"%s\" for op \"<output>\"", nodes[out].name.c_str());
+    }
     std::vector<Frame> stack;
     stack.push_back(Frame{producer[out], 0});
     while (!stack.empty()) {
@@ -130,9 +141,11 @@ rtg_status Graph::create_plan(const std::vector<int32_t>& inputs, const std::vec
         const int32_t in = op.inputs[f.next++];
         if (in < 0 || resolved[in]) continue;
         if (in >= n) return set_error(RTG_ERR_INVALID_VALUE, "operator input id out of range");
-        if (producer[in] < 0)
+        if (producer[in] < 0) {
+          if (allow_missing) continue;  // a value nobody can provide: prune_plan drops what depends on it
           return set_errorf(RTG_ERR_INVALID_VALUE, "Missing input \"%s\" for op \"%s\"", nodes[in].name.c_str(),
                             op.name.c_str());
+        }
         if (!scheduled[producer[in]]) {
           stack.push_back(Frame{producer[in], 0});
           descended = true;
@@ -161,13 +174,94 @@ rtg_status Graph::run(Context* ctx, const std::vector<std::pair<int32_t, Value>>
                       std::vector<TimingRecord>* timing) {
   std::vector<int32_t> in_ids;
   for (auto& kv : inputs) in_ids.push_back(kv.first);
-  // get_cached_plan (src/graph.rs:768-795): re-plan only when the input / output ids change
-  if (cached_plan_.empty() || in_ids != cached_inputs_ || outputs != cached_outputs_) {
-    RTG_TRY(create_plan(in_ids, outputs, &cached_plan_));
-    cached_inputs_ = in_ids;
-    cached_outputs_ = outputs;
+  const int32_t nn = static_cast<int32_t>(nodes.size());
+  for (int32_t o : outputs)
+    if (o < 0 || o >= nn) {
+      for (auto& kv : inputs) {
+        Value v = kv.second;
+        release_value(ctx, &v);
+      }
+      return set_error(RTG_ERR_INVALID_VALUE, "Output node ID is invalid");
+    }
+  // get_cached_plan (src/graph.rs:768-795): re-plan only when the input / output ids change.  The cache is shared by
+  // concurrent runs: it is read and replaced under the mutex, the plan itself is immutable once published.
+  std::shared_ptr<const std::vector<int32_t>> plan_ptr;
+  {
+    std::lock_guard<std::mutex> lock(plan_mu_);
+    if (!cached_plan_ || in_ids != cached_inputs_ || outputs != cached_outputs_) {
+      auto fresh = std::make_shared<std::vector<int32_t>>();
+      rtg_status st = create_plan(in_ids, outputs, fresh.get());
+      if (st != RTG_OK) {
+        for (auto& kv : inputs) {
+          Value v = kv.second;
+          release_value(ctx, &v);
+        }
+        return st;
+      }
+      cached_plan_ = fresh;
+      cached_inputs_ = in_ids;
+      cached_outputs_ = outputs;
+    }
+    plan_ptr = cached_plan_;
   }
-  const std::vector<int32_t>& plan = cached_plan_;
+  return run_plan(ctx, inputs, *plan_ptr, outputs, results, timing);
+}
+
+void Graph::prune_plan(const std::vector<int32_t>& plan, const std::vector<int32_t>& inputs,
+                       const std::vector<int32_t>& outputs, std::vector<int32_t>* pruned,
+                       std::vector<int32_t>* leaves) const {
+  std::vector<char> resolved(nodes.size(), 0), feeds_pruned(nodes.size(), 0);
+  for (size_t i = 0; i < nodes.size(); ++i)
+    if (nodes[i].kind == NodeKind::Constant) resolved[i] = 1;
+  for (int32_t i : inputs) resolved[i] = 1;
+  std::vector<int32_t> candidates;
+  for (int32_t op_id : plan) {
+    const Node& op = nodes[op_id];
+    bool all = true;
+    for (int32_t in : op.inputs)
+      if (in >= 0 && !resolved[in]) all = false;
+    if (!all) {  // every operator here is deterministic (Operator::is_deterministic, src/ops/mod.rs:850-861)
+      for (int32_t in : op.inputs)
+        if (in >= 0 && resolved[in]) feeds_pruned[in] = 1;
+      continue;
+    }
+    for (int32_t o : op.outputs)
+      if (o >= 0) {
+        resolved[o] = 1;
+        candidates.push_back(o);
+      }
+    pruned->push_back(op_id);
+  }
+  for (int32_t c : candidates)
+    if (feeds_pruned[c] || std::find(outputs.begin(), outputs.end(), c) != outputs.end()) leaves->push_back(c);
+}
+
+rtg_status Graph::partial_run(Context* ctx, const std::vector<std::pair<int32_t, Value>>& inputs,
+                              const std::vector<int32_t>& outputs, std::vector<std::pair<int32_t, Value>>* leaves) {
+  leaves->clear();
+  auto drop_inputs = [&]() {
+    for (auto& kv : inputs) {
+      Value v = kv.second;
+      release_value(ctx, &v);
+    }
+  };
+  std::vector<int32_t> in_ids, plan, pruned, leaf_ids;
+  for (auto& kv : inputs) in_ids.push_back(kv.first);
+  rtg_status st = create_plan(in_ids, outputs, &plan, /*allow_missing=*/true);
+  if (st != RTG_OK) {
+    drop_inputs();
+    return st;
+  }
+  prune_plan(plan, in_ids, outputs, &pruned, &leaf_ids);
+  std::vector<Value> vals;
+  RTG_TRY(run_plan(ctx, inputs, pruned, leaf_ids, &vals, nullptr));
+  for (size_t i = 0; i < leaf_ids.size(); ++i) leaves->emplace_back(leaf_ids[i], vals[i]);
+  return RTG_OK;
+}
+
+rtg_status Graph::run_plan(Context* ctx, const std::vector<std::pair<int32_t, Value>>& inputs,
+                           const std::vector<int32_t>& plan, const std::vector<int32_t>& outputs,
+                           std::vector<Value>* results, std::vector<TimingRecord>* timing) {
   const size_t n = nodes.size();
 
   // values produced during this run (operator outputs and owned inputs)
@@ -314,6 +408,51 @@ rtg_status Graph::run(Context* ctx, const std::vector<std::pair<int32_t, Value>>
   for (size_t i = 0; i < n; ++i)
     if (live[i]) release_value(ctx, &temp[i]);
   return RTG_OK;
+}
+
+rtg_status propagate_constants(Context* ctx, Graph* g, int* replaced) {
+  *replaced = 0;
+  std::vector<std::pair<int32_t, Value>> leaves;
+  RTG_TRY(g->partial_run(ctx, {}, g->output_ids, &leaves));
+  rtg_status st = RTG_OK;
+  for (auto& kv : leaves) {
+    Value v = kv.second;
+    if (st == RTG_OK && !is_contiguous(v.t)) {  // constants are stored in the reference layout
+      Value c;
+      st = alloc_value(ctx, v.t.dtype, v.t.ndim, v.t.shape, false, &c);
+      if (st == RTG_OK) st = copy_view(ctx, c.t, v.t);
+      if (st == RTG_OK) {
+        c.host_i32 = v.host_i32, c.host_f32 = v.host_f32;
+        release_value(ctx, &v);
+        v = c;
+      } else {
+        release_value(ctx, &c);
+      }
+    }
+    const int64_t cnt = numel(v.t);
+    if (st == RTG_OK && cnt > 0 && cnt <= 4096) {  // host mirror, like the constants of the file (make_constant)
+      if (v.t.dtype == RTG_I32 && !v.host_i32) {
+        std::vector<int64_t> tmp;
+        st = host_ints(ctx, v, &tmp);
+        if (st == RTG_OK) v.host_i32 = std::make_shared<std::vector<int32_t>>(tmp.begin(), tmp.end());
+      } else if (v.t.dtype == RTG_F32 && !v.host_f32) {
+        std::vector<float> tmp;
+        st = host_floats(ctx, v, &tmp);
+        if (st == RTG_OK) v.host_f32 = std::make_shared<std::vector<float>>(tmp);
+      }
+    }
+    if (st != RTG_OK) {
+      release_value(ctx, &v);
+      continue;
+    }
+    // The value node becomes the constant (node ids stay stable; the reference adds a node and rewires,
+    // GraphMutator::replace_value).  Its producer is never planned again: constants are resolved from the start.
+    Node& nd = g->nodes[kv.first];
+    nd.kind = NodeKind::Constant;
+    nd.constant = v;
+    ++*replaced;
+  }
+  return st;
 }
 
 }  // namespace rtg

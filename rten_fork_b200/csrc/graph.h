@@ -7,6 +7,7 @@
 #pragma once
 #include <functional>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -117,17 +118,39 @@ class Graph {
   std::vector<int32_t> input_ids, output_ids;
 
   // Graph::run (src/graph.rs:733-1073): plan (cached), then execute with refcounts, in-place selection and pool reuse.
+  // `inputs` / `outputs` address values by node id (Model::run, src/model.rs:580-592).
   rtg_status run(Context* ctx, const std::vector<std::pair<int32_t, Value>>& inputs, const std::vector<int32_t>& outputs,
                  std::vector<Value>* results, std::vector<TimingRecord>* timing);
+  // Graph::partial_run (src/graph.rs:1147-1183): with an incomplete set of inputs, evaluates every operator of the
+  // plan whose inputs are available and returns the leaves of that sub-plan (values that are requested outputs or
+  // feed operators that could not run) as (node id, value).
+  rtg_status partial_run(Context* ctx, const std::vector<std::pair<int32_t, Value>>& inputs,
+                         const std::vector<int32_t>& outputs, std::vector<std::pair<int32_t, Value>>* leaves);
   // create_plan (src/graph.rs:1256-1346): operator node ids in execution order for the requested outputs.
+  // `allow_missing`: PlanOptions::allow_missing_inputs — unresolvable values are tolerated (partial_run prunes).
   rtg_status create_plan(const std::vector<int32_t>& inputs, const std::vector<int32_t>& outputs,
-                         std::vector<int32_t>* plan) const;
+                         std::vector<int32_t>* plan, bool allow_missing = false) const;
+  // The operator producing value `id`, or -1 (Graph::get_source_node).
+  int32_t source_node(int32_t id) const;
   int num_operators() const;
   void release(Context* ctx);
 
  private:
-  std::vector<int32_t> cached_inputs_, cached_outputs_, cached_plan_;
+  rtg_status run_plan(Context* ctx, const std::vector<std::pair<int32_t, Value>>& inputs,
+                      const std::vector<int32_t>& plan, const std::vector<int32_t>& outputs, std::vector<Value>* results,
+                      std::vector<TimingRecord>* timing);
+  // prune_plan (src/graph.rs:1185-1235)
+  void prune_plan(const std::vector<int32_t>& plan, const std::vector<int32_t>& inputs,
+                  const std::vector<int32_t>& outputs, std::vector<int32_t>* pruned, std::vector<int32_t>* leaves) const;
+  // get_cached_plan (src/graph.rs:513,768-795): concurrent runs on one model are allowed, the cache is behind a mutex
+  std::mutex plan_mu_;
+  std::vector<int32_t> cached_inputs_, cached_outputs_;
+  std::shared_ptr<const std::vector<int32_t>> cached_plan_;
 };
+
+// GraphOptimizer::propagate_constants (src/optimize.rs:301-327): a partial run with no inputs evaluates everything that
+// depends only on constants; those values become constant nodes.  Returns how many values were replaced.
+rtg_status propagate_constants(Context* ctx, Graph* g, int* replaced);
 
 // GPU-side GraphOptimizer (src/optimize.rs:286-297 plus the new epilogue fusions); returns how many nodes it fused.
 int optimize_graph(Graph* g);
@@ -161,6 +184,7 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
 struct Run {
   Context* ctx = nullptr;
   std::vector<Value> outputs;
+  std::vector<int32_t> node_ids;  // the value node each output belongs to (the leaves, for a partial run)
 };
 
 struct Ticket {  // one rtg_model_submit in flight

@@ -162,7 +162,17 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
   }
   RTG_CUDA(cudaStreamSynchronize(ctx->stream));  // constants are uploaded from the caller's buffer
 
-  if (optimize) optimize_graph(&model->graph);
+  if (optimize) {
+    // GraphOptimizer::optimize (src/optimize.rs:286-297): constant propagation first, then the fusions
+    int replaced = 0;
+    rtg_status st = propagate_constants(ctx, &model->graph, &replaced);
+    if (st != RTG_OK) {
+      std::string msg = rtg_last_error();
+      model->graph.release(ctx);
+      return set_errorf(st, "optimization failed: %s", msg.c_str());  // ModelLoadError::OptimizeError
+    }
+    optimize_graph(&model->graph);
+  }
 
   // Let operators pre-arrange constant operands (weights) once.
   Graph& g = model->graph;
@@ -222,6 +232,13 @@ int optimize_graph(Graph* g) {
     const float v = (*c.constant.host_f32)[0];
     return fabsf(v - want) <= 1e-6f * fabsf(want);
   };
+  auto scalar_value = [&](int32_t id, float* v) {
+    if (id < 0) return false;
+    const Node& c = g->nodes[id];
+    if (c.kind != NodeKind::Constant || !c.constant.host_f32 || c.constant.host_f32->size() != 1) return false;
+    *v = (*c.constant.host_f32)[0];
+    return true;
+  };
   auto bin_node = [&](int32_t value, int op) -> Node* {  // the binary operator of kind `op` producing `value`
     if (value < 0 || producer[value] < 0 || dead[producer[value]]) return nullptr;
     Node& nd = g->nodes[producer[value]];
@@ -262,6 +279,129 @@ int optimize_graph(Graph* g) {
   }
   if (fused) rebuild();
 
+  // ---- Silu: x * Sigmoid(x)  =>  Silu(x)      (GraphOptimizer::fuse_silu, src/optimize.rs:379-399).  The reference has
+  //      no serialised Silu operator: this fusion is the only way one comes to exist.  Same arithmetic as the pair
+  //      (x * sigmoid(x), rten-vecmath/src/exp.rs:194-197), so fused and unfused results are bit-identical.
+  {
+    int sf = 0;
+    for (int32_t i = 0; i < n; ++i) {
+      Node& mul = g->nodes[i];
+      if (mul.kind != NodeKind::Operator || dead[i]) continue;
+      BinaryOp* mb = dynamic_cast<BinaryOp*>(mul.op.get());
+      if (!mb || mb->op != RTG_BIN_MUL || mul.inputs.size() != 2 || mul.outputs.size() != 1) continue;
+      for (int side = 0; side < 2; ++side) {
+        const int32_t x = mul.inputs[side], s_val = mul.inputs[1 - side];
+        if (x < 0 || s_val < 0 || producer[s_val] < 0 || dead[producer[s_val]]) continue;
+        Node& sig = g->nodes[producer[s_val]];
+        UnaryOp* su = dynamic_cast<UnaryOp*>(sig.op.get());
+        if (!su || su->act != ACT_SIGMOID || sig.inputs.size() != 1 || sig.inputs[0] != x) continue;
+        if (uses[s_val] == 1) dead[producer[s_val]] = 1;  // otherwise the Sigmoid stays for its other consumers
+        mul.op.reset(new UnaryOp(ACT_SILU, "Silu"));
+        mul.inputs.assign(1, x);
+        ++sf;
+        break;
+      }
+    }
+    if (sf) rebuild();
+    fused += sf;
+  }
+
+  // ---- LayerNormalization spelled out as primitives      (GraphOptimizer::fuse_layer_norm, src/optimize.rs:427-513)
+  //        c = x - ReduceMean(x, axes=[-1])
+  //        n = c / Sqrt(epsilon + ReduceMean(Pow(c, 2), axes=[-1]))
+  //        y = n * scale + bias                 (scale, bias, epsilon constants)
+  //      => LayerNormalization{axis = -1, epsilon}(x, scale, bias), matched from the final Add backwards like the
+  //      reference's three patterns.  One pass over x instead of nine.
+  {
+    auto is_const = [&](int32_t id) { return id >= 0 && g->nodes[id].kind == NodeKind::Constant; };
+    auto unary_node = [&](int32_t value, int act) -> Node* {
+      if (value < 0 || producer[value] < 0 || dead[producer[value]]) return nullptr;
+      Node& nd = g->nodes[producer[value]];
+      UnaryOp* u = dynamic_cast<UnaryOp*>(nd.op.get());
+      return (u && u->act == act && nd.inputs.size() >= 1 && nd.outputs.size() == 1) ? &nd : nullptr;
+    };
+    // a ReduceMean over the last axis given as -1 (attribute or constant input), the only form the reference fuses
+    auto mean_last_axis = [&](int32_t value) -> Node* {
+      if (value < 0 || producer[value] < 0 || dead[producer[value]]) return nullptr;
+      Node& nd = g->nodes[producer[value]];
+      ReduceMeanOp* r = dynamic_cast<ReduceMeanOp*>(nd.op.get());
+      if (!r || nd.inputs.empty() || nd.outputs.size() != 1) return nullptr;
+      if (r->has_axes) return (r->axes.size() == 1 && r->axes[0] == -1) ? &nd : nullptr;
+      if (nd.inputs.size() > 1 && is_const(nd.inputs[1])) {
+        const Value& ax = g->nodes[nd.inputs[1]].constant;
+        if (ax.host_i32 && ax.host_i32->size() == 1 && (*ax.host_i32)[0] == -1) return &nd;
+      }
+      return nullptr;
+    };
+    int lf = 0;
+    for (int32_t i = 0; i < n; ++i) {
+      Node& fin = g->nodes[i];
+      if (fin.kind != NodeKind::Operator || dead[i]) continue;
+      BinaryOp* fb_ = dynamic_cast<BinaryOp*>(fin.op.get());
+      if (!fb_ || fb_->op != RTG_BIN_ADD || fin.inputs.size() != 2 || fin.outputs.size() != 1) continue;
+      bool done = false;
+      for (int a_side = 0; a_side < 2 && !done; ++a_side) {           // (n * scale) + bias, either operand order
+        const int32_t bias = fin.inputs[a_side], m_val = fin.inputs[1 - a_side];
+        if (!is_const(bias)) continue;
+        Node* mul = bin_node(m_val, RTG_BIN_MUL);
+        if (!mul) continue;
+        for (int m_side = 0; m_side < 2 && !done; ++m_side) {
+          const int32_t scale = mul->inputs[m_side], n_val = mul->inputs[1 - m_side];
+          if (!is_const(scale)) continue;
+          Node* div = bin_node(n_val, RTG_BIN_DIV);                    // c / Sqrt(...)
+          if (!div) continue;
+          const int32_t c_val = div->inputs[0];
+          Node* sq = unary_node(div->inputs[1], ACT_SQRT);
+          if (!sq) continue;
+          Node* add_eps = bin_node(sq->inputs[0], RTG_BIN_ADD);        // epsilon + ReduceMean(...), either order
+          if (!add_eps) continue;
+          for (int e_side = 0; e_side < 2 && !done; ++e_side) {
+            const int32_t eps_id = add_eps->inputs[e_side], var_val = add_eps->inputs[1 - e_side];
+            float eps = 0.f;
+            if (!scalar_value(eps_id, &eps)) continue;
+            Node* var_mean = mean_last_axis(var_val);
+            if (!var_mean) continue;
+            Node* pw = bin_node(var_mean->inputs[0], RTG_BIN_POW);     // Pow(c, 2)
+            if (!pw || pw->inputs[0] != c_val || !scalar_const(pw->inputs[1], 2.f)) continue;
+            Node* sub = bin_node(c_val, RTG_BIN_SUB);                  // x - ReduceMean(x)
+            if (!sub) continue;
+            const int32_t x = sub->inputs[0];
+            Node* ctr_mean = mean_last_axis(sub->inputs[1]);
+            if (!ctr_mean || ctr_mean->inputs[0] != x) continue;
+            LayerNormOp* ln = new LayerNormOp();
+            ln->axis = -1;
+            ln->epsilon = eps;
+            fin.op.reset(ln);
+            fin.inputs = {x, scale, bias};
+            ++lf;
+            done = true;
+          }
+        }
+      }
+    }
+    if (lf) {
+      // operators that only fed the fused expression die (the planner would never schedule them anyway)
+      rebuild();
+      bool changed = true;
+      while (changed) {
+        changed = false;
+        for (int32_t i = 0; i < n; ++i) {
+          Node& nd = g->nodes[i];
+          if (nd.kind != NodeKind::Operator || dead[i] || nd.outputs.empty()) continue;
+          bool used = false;
+          for (int32_t o : nd.outputs)
+            if (o >= 0 && uses[o] > 0) used = true;
+          if (!used) {
+            dead[i] = 1;
+            changed = true;
+          }
+        }
+        if (changed) rebuild();
+      }
+    }
+    fused += lf;
+  }
+
   // ---- Transpose -> MatMul  =>  FusedTranspose(MatMul): the permuted view feeds the TMA maps directly
   //      (GraphOptimizer::fuse_transpose, src/optimize.rs:333-377)
   {
@@ -288,13 +428,6 @@ int optimize_graph(Graph* g) {
     if (tf) rebuild();
     fused += tf;
   }
-  auto scalar_value = [&](int32_t id, float* v) {
-    if (id < 0) return false;
-    const Node& c = g->nodes[id];
-    if (c.kind != NodeKind::Constant || !c.constant.host_f32 || c.constant.host_f32->size() != 1) return false;
-    *v = (*c.constant.host_f32)[0];
-    return true;
-  };
   auto single_consumer = [&](int32_t value) -> int32_t {
     if (value < 0 || uses[value] != 1 || consumers[value].size() != 1) return -1;
     return consumers[value][0];
@@ -397,7 +530,7 @@ int optimize_graph(Graph* g) {
       int act;
       float lo, hi;
       if (an.outputs.size() == 1 && act_of(an, &act, &lo, &hi) &&
-          (act == ACT_RELU || act == ACT_CLIP || act == ACT_GELU || act == ACT_SIGMOID || act == ACT_TANH)) {
+          (act == ACT_RELU || act == ACT_CLIP || act == ACT_GELU || act == ACT_SIGMOID || act == ACT_TANH || act == ACT_SILU)) {
         if (conv) conv->act = act, conv->act_lo = lo, conv->act_hi = hi;
         else if (act != ACT_CLIP) mm->act = act;
         if (conv || act != ACT_CLIP) {

@@ -80,6 +80,17 @@ rtg_status ConvOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
   ConvPlan p;
   RTG_TRY(conv_plan(&x->t, &w->t, b ? &b->t : nullptr, &attrs, &p));
   int64_t oshape[4] = {p.n, p.o, p.is_1d ? p.ow : p.oh, p.ow};
+  // The load-time fusion Conv -> Add (-> activation) is only an epilogue when the other Add operand has exactly the
+  // convolution's output shape and the layer is not depthwise (whose kernel has no residual input).  Anything else —
+  // a broadcast operand such as [N, C, 1, 1], a depthwise layer — runs as the reference does: convolution, then the
+  // Add operator with numpy broadcasting, then the activation.
+  bool unfused_tail = false;
+  if (res) {
+    const int ond = p.is_1d ? 3 : 4;
+    bool same = res->t.ndim == ond && res->t.dtype == RTG_F32;
+    for (int i = 0; i < ond && same; ++i) same = res->t.shape[i] == oshape[i];
+    unfused_tail = !same || p.depthwise;
+  }
   Value y;
   RTG_TRY(alloc_value(ctx, RTG_F32, p.is_1d ? 3 : 4, oshape, !p.is_1d, &y));
   Value wtmp, btmp;
@@ -96,11 +107,23 @@ rtg_status ConvOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
     cw = &local;
   }
   if (st == RTG_OK)
-    st = conv_forward(ctx, p, x->t, *cw, b ? static_cast<const float*>(bv.data) : nullptr, res ? &res->t : nullptr,
-                      act, act_lo, act_hi, y.t);
+    st = conv_forward(ctx, p, x->t, *cw, b ? static_cast<const float*>(bv.data) : nullptr,
+                      (res && !unfused_tail) ? &res->t : nullptr, unfused_tail ? ACT_NONE : act, act_lo, act_hi, y.t);
   if (!use_prepared) conv_release_weights(ctx, &local);
   release_value(ctx, &wtmp);
   release_value(ctx, &btmp);
+  if (st == RTG_OK && unfused_tail) {
+    BinaryOp add(RTG_BIN_ADD, "Add");
+    OpInputs ain;
+    ain.v = {&y, res};
+    std::vector<Value> sum;
+    st = add.run(ctx, ain, &sum);
+    if (st == RTG_OK) {
+      release_value(ctx, &y);
+      y = sum[0];
+      if (act != ACT_NONE) st = unary_forward(ctx, act, y.t, act_lo, act_hi, y.t);
+    }
+  }
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;
@@ -187,11 +210,66 @@ rtg_status BinaryOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
   const Value *a, *b;
   RTG_TRY(in.require(0, &a));
   RTG_TRY(in.require(1, &b));
-  if (a->t.dtype != RTG_F32 || b->t.dtype != RTG_F32)
-    return set_error(RTG_ERR_UNSUPPORTED_VALUE, "integer binary operators are not implemented on the GPU path");
+  if (a->t.dtype != b->t.dtype) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
   int64_t shape[RTG_MAX_DIMS];
   int32_t nd;
   RTG_TRY(binary_out_shape(&a->t, &b->t, shape, &nd));
+  if (a->t.dtype == RTG_I32) {
+    // i32 operands are shape arithmetic (the reference's operators are generic over f32 / i32,
+    // src/ops/binary_elementwise.rs:395-560): small tensors, evaluated on their host mirrors and re-uploaded with one.
+    int64_t total = 1;
+    for (int i = 0; i < nd; ++i) total *= shape[i];
+    if (total > 4096 || op == RTG_BIN_POW)
+      return set_error(RTG_ERR_UNSUPPORTED_VALUE, "integer binary operators are implemented for shape-sized tensors only");
+    std::vector<int64_t> av, bv;
+    RTG_TRY(host_ints(ctx, *a, &av));
+    RTG_TRY(host_ints(ctx, *b, &bv));
+    auto res = std::make_shared<std::vector<int32_t>>(static_cast<size_t>(total));
+    int64_t idx[RTG_MAX_DIMS] = {0};
+    for (int64_t e = 0; e < total; ++e) {
+      int64_t ia = 0, ib = 0, sa = 1, sb = 1;  // broadcast source offsets (right-aligned shapes, contiguous mirrors)
+      for (int d = nd - 1; d >= 0; --d) {
+        const int da = d - (nd - a->t.ndim), db = d - (nd - b->t.ndim);
+        if (da >= 0) {
+          if (a->t.shape[da] != 1) ia += idx[d] * sa;
+          sa *= a->t.shape[da];
+        }
+        if (db >= 0) {
+          if (b->t.shape[db] != 1) ib += idx[d] * sb;
+          sb *= b->t.shape[db];
+        }
+      }
+      const int32_t x = static_cast<int32_t>(av[ia]), y = static_cast<int32_t>(bv[ib]);
+      int32_t r = 0;
+      switch (op) {
+        case RTG_BIN_ADD: r = static_cast<int32_t>(static_cast<uint32_t>(x) + static_cast<uint32_t>(y)); break;
+        case RTG_BIN_SUB: r = static_cast<int32_t>(static_cast<uint32_t>(x) - static_cast<uint32_t>(y)); break;
+        case RTG_BIN_MUL: r = static_cast<int32_t>(static_cast<uint32_t>(x) * static_cast<uint32_t>(y)); break;
+        case RTG_BIN_DIV:
+          if (y == 0) return set_error(RTG_ERR_INVALID_VALUE, "integer division by zero");
+          r = (x == INT32_MIN && y == -1) ? INT32_MIN : x / y;
+          break;
+      }
+      (*res)[e] = r;
+      for (int d = nd - 1; d >= 0; --d) {
+        if (++idx[d] < shape[d]) break;
+        idx[d] = 0;
+      }
+    }
+    Value yv;
+    RTG_TRY(alloc_value(ctx, RTG_I32, nd, shape, false, &yv));
+    if (total > 0) {
+      cudaError_t e = cudaMemcpyAsync(yv.t.data, res->data(), static_cast<size_t>(total) * 4, cudaMemcpyHostToDevice, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // `res` may not outlive the copy otherwise
+      if (e != cudaSuccess) {
+        release_value(ctx, &yv);
+        return set_errorf(RTG_ERR_CUDA, "upload failed: %s", cudaGetErrorString(e));
+      }
+    }
+    yv.host_i32 = res;
+    out->push_back(yv);
+    return RTG_OK;
+  }
   // keep the NHWC layout of a full-size operand
   bool nhwc = false;
   if (nd == 4) {
@@ -444,18 +522,21 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
   RTG_TRY(alloc_value(ctx, RTG_F32, nd, shape, false, &y));
   Epilogue ep;
   const Epilogue* epp = nullptr;
-  if (has_bias) {
-    // fused `MatMul -> Add(bias[N])` (+ activation): bias per output column
-    const Value* bias = in.get(2);
-    if (!bias || numel(bias->t) != shape[nd - 1] || !is_contiguous(bias->t)) {
-      release_value(ctx, &y);
-      return set_error(RTG_ERR_INTERNAL, "fused MatMul bias must be a dense vector of length N");
-    }
+  // fused `MatMul -> Add(constant vector)` (+ activation) is a per-column bias only when the vector has exactly N
+  // entries; any other 1-D constant (e.g. shape [1]) is an ordinary broadcast Add, run after the product as the
+  // reference does
+  const Value* bias = has_bias ? in.get(2) : nullptr;
+  if (has_bias && !bias) {
+    release_value(ctx, &y);
+    return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
+  }
+  const bool bias_tail = bias && !(bias->t.dtype == RTG_F32 && numel(bias->t) == shape[nd - 1] && is_contiguous(bias->t));
+  if (bias && !bias_tail) {
     ep.bias = static_cast<const float*>(bias->t.data);
     ep.bias_mode = BIAS_COL;
   }
-  if (has_bias || act != ACT_NONE || scale != 1.f) {
-    ep.act = act;
+  if ((bias && !bias_tail) || (!bias_tail && act != ACT_NONE) || scale != 1.f) {
+    ep.act = bias_tail ? ACT_NONE : act;
     ep.alpha = scale;
     ep.alpha_div = scale_div;
     epp = &ep;
@@ -466,6 +547,18 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     epp = &ep;
   }
   rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);
+  if (st == RTG_OK && bias_tail) {
+    BinaryOp add(RTG_BIN_ADD, "Add");
+    OpInputs ain;
+    ain.v = {&y, bias};
+    std::vector<Value> sum;
+    st = add.run(ctx, ain, &sum);
+    if (st == RTG_OK) {
+      release_value(ctx, &y);
+      y = sum[0];
+      if (act != ACT_NONE) st = unary_forward(ctx, act, y.t, 0.f, 0.f, y.t);
+    }
+  }
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;

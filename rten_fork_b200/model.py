@@ -102,9 +102,55 @@ class Model:
         N.lib().rtg_model_timing_report.restype = C.c_char_p
         return N.lib().rtg_model_timing_report(self._h).decode()
 
-    # -- Model::run: inputs in graph-input order; returns numpy arrays (or fills ``out`` buffers)
-    def run(self, inputs, out=None):
-        descs = (N.Tensor * len(inputs))()
+    # -- node lookup (Model::find_node / input_ids / output_ids, src/model.rs:525-553; Graph::get_source_node)
+    def find_node(self, name: str) -> int:
+        i = C.c_int32()
+        N.check(N.lib().rtg_model_find_node(self._h, name.encode(), C.byref(i)))
+        return i.value
+
+    @property
+    def input_ids(self):
+        n, i = C.c_int32(), C.c_int32()
+        N.check(N.lib().rtg_model_num_inputs(self._h, C.byref(n)))
+        ids = []
+        for k in range(n.value):
+            N.check(N.lib().rtg_model_input_id(self._h, C.c_int32(k), C.byref(i)))
+            ids.append(i.value)
+        return ids
+
+    @property
+    def output_ids(self):
+        n, i = C.c_int32(), C.c_int32()
+        N.check(N.lib().rtg_model_num_outputs(self._h, C.byref(n)))
+        ids = []
+        for k in range(n.value):
+            N.check(N.lib().rtg_model_output_id(self._h, C.c_int32(k), C.byref(i)))
+            ids.append(i.value)
+        return ids
+
+    def node_kind(self, node_id: int) -> str:
+        k = C.c_int32()
+        N.check(N.lib().rtg_model_node_kind(self._h, C.c_int32(node_id), C.byref(k)))
+        return ("operator", "constant", "value")[k.value]
+
+    def source_op(self, value_id: int):
+        """(operator name, node name) of the operator producing ``value_id`` after the load-time optimiser."""
+        op, node = C.c_char_p(), C.c_char_p()
+        N.check(N.lib().rtg_model_source_op(self._h, C.c_int32(value_id), C.byref(op), C.byref(node)))
+        return (op.value or b"").decode(), (node.value or b"").decode()
+
+    # -- Model::run: inputs in graph-input order (a list), or addressed by node id like the reference
+    #    (``inputs`` a list of (node id, array) pairs / a dict, ``outputs`` a list of node ids); returns numpy arrays (or
+    #    fills ``out`` buffers).  ``partial=True``: Model::partial_run, returns a list of (node id, array) leaves.
+    def run(self, inputs, out=None, outputs=None, partial=False):
+        by_id = isinstance(inputs, dict) or (len(inputs) > 0 and isinstance(inputs[0], tuple)) or outputs is not None \
+            or partial
+        ids = None
+        if by_id:
+            pairs = list(inputs.items()) if isinstance(inputs, dict) else list(inputs)
+            ids = [int(k) for k, _ in pairs]
+            inputs = [v for _, v in pairs]
+        descs = (N.Tensor * max(1, len(inputs)))()
         keep = []
         for i, x in enumerate(inputs):
             if isinstance(x, np.ndarray) and not x.flags.c_contiguous:
@@ -112,7 +158,14 @@ class Model:
             keep.append(x)
             descs[i] = as_tensor(x)
         run = C.c_void_p()
-        N.check(N.lib().rtg_model_run(self._h, descs, C.c_int32(len(inputs)), C.byref(run)))
+        if by_id:
+            outs = list(self.output_ids if outputs is None else outputs)
+            id_arr = (C.c_int32 * max(1, len(ids)))(*ids)
+            out_arr = (C.c_int32 * max(1, len(outs)))(*outs)
+            fn = N.lib().rtg_model_partial_run if partial else N.lib().rtg_model_run_ids
+            N.check(fn(self._h, id_arr, descs, C.c_int32(len(ids)), out_arr, C.c_int32(len(outs)), C.byref(run)))
+        else:
+            N.check(N.lib().rtg_model_run(self._h, descs, C.c_int32(len(inputs)), C.byref(run)))
         try:
             n = C.c_int32()
             N.check(N.lib().rtg_run_num_outputs(run, C.byref(n)))
@@ -132,7 +185,12 @@ class Model:
                     ptr, nbytes = dst.data_ptr(), dst.numel() * dst.element_size()
                     dev = dst.device.index if dst.is_cuda else N.RTG_HOST
                 N.check(N.lib().rtg_run_output_copy(run, C.c_int32(i), C.c_void_p(ptr), C.c_size_t(nbytes), C.c_int32(dev)))
-                results.append(dst)
+                if partial:
+                    nid = C.c_int32()
+                    N.check(N.lib().rtg_run_output_node(run, C.c_int32(i), C.byref(nid)))
+                    results.append((nid.value, dst))
+                else:
+                    results.append(dst)
             return results
         finally:
             N.lib().rtg_run_free(run)
@@ -149,6 +207,10 @@ class Model:
         tk = C.c_void_p()
         N.check(N.lib().rtg_model_submit(self._h, descs, C.c_int32(len(inputs)), odescs, C.c_int32(len(out)), C.byref(tk)))
         return Ticket(tk, out, odescs, keep)
+
+    def partial_run(self, inputs, outputs=None):
+        """Model::partial_run (src/model.rs:639-646): list of (node id, value) leaves."""
+        return self.run(inputs, outputs=outputs, partial=True)
 
     def run_one(self, x, out=None):
         """Model::run_one (src/model.rs:620-637): single input, single output."""
