@@ -3,6 +3,7 @@
 #include "gemm_launch.cuh"
 #include <vector>
 
+#include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -343,6 +344,24 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
 // Largest tile that still fills the machine; smaller tiles when the problem has too few of them.  With `splits` the
 // choice is joint over (BN, split-K factor): layers whose tile count is a poor fit for 148 SMs (98 or 196 tiles)
 // divide K so that the work units fill whole waves; the price is one pass over the partial sums (L2 resident).
+// Rasterisation of the output tiles (GemmArgs::group_m): when the output has many tiles in both directions, walk them
+// in groups of group_m m-tiles so that the tiles in flight share operand panels in L2.  A tile of A costs 16 KB per
+// k-block, a tile of B (and B') 16 KB per 128 columns: the traffic of num_sms tiles in flight is minimal near
+// group_m = sqrt(num_sms * b_bytes / a_bytes).
+static int choose_group_m(Context* ctx, int64_t M, int64_t N, int bn) {
+  static const int forced = []() {
+    const char* e = getenv("RTG_GROUP_M");  // developer switch: 0 disables, n forces
+    return e ? atoi(e) : -1;
+  }();
+  const int64_t m_tiles = div_ceil(M, kBM), n_tiles = div_ceil(N, bn);
+  if (forced >= 0) return forced;
+  if (n_tiles < 4 || m_tiles < 8) return 0;  // one of the operands is re-used by (almost) every tile in flight anyway
+  const double ratio = bn >= 256 ? 2.0 : (bn >= 128 ? (ctx->math == RTG_MATH_TF32 ? 1.0 : 2.0) : 1.0);
+  int gm = static_cast<int>(sqrt(static_cast<double>(ctx->num_sms) * ratio) + 0.5);
+  gm = std::max(4, std::min<int>(gm, static_cast<int>(m_tiles)));
+  return gm;
+}
+
 static int choose_bn(Context* ctx, int64_t M, int64_t N, int64_t num_kb, int64_t batch = 1, int* splits = nullptr) {
   // Cycle model fitted to the per-role counters of the PROF build (profiles/): the MMA thread needs
   // max(64, BN/2) cycles per 128 x BN x 8 instruction (64 is the dispatch floor, so BN = 64 runs the tensor pipe at
@@ -453,6 +472,7 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   g.act_hi = ep.act_hi;
   g.flags = debug_flags() | (ep.alpha_div ? kFlagAlphaDiv : 0) | (ep.b_pack.p && ep.b_pack_const ? kFlagBConst : 0);
   g.splits = splits;
+  g.group_m = choose_group_m(ctx, M, N, bn);
   ctx->pending_flops = 2.0 * g.M * g.N * g.K;
   ctx->pending_bytes = 4.0 * (static_cast<double>(g.M) * g.K + static_cast<double>(g.K) * g.N +
                               static_cast<double>(g.M) * g.N * (g.R ? 2 : 1));
@@ -619,6 +639,7 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
   a.act_hi = ep.act_hi;
   a.flags = debug_flags() | (ep.b_pack.p && ep.b_pack_const ? kFlagBConst : 0);
   a.splits = splits;
+  a.group_m = choose_group_m(ctx, M, og, bn);
   a.ic.ow = g.ow;
   a.ic.oh = g.oh;
   a.ic.stride_w = g.stride_w;

@@ -75,6 +75,7 @@ struct GemmArgs {
   // and leaves its raw partial sums in plane `split` of a {N, M, splits} workspace (tmD); splitk_reduce_kernel adds
   // the planes in a fixed order and applies the epilogue.  Used when a layer has too few output tiles for 148 SMs.
   int32_t splits, kb_per_split;
+  int32_t group_m;  // > 0: tiles are walked in groups of group_m m-tiles (L2 reuse for large GEMMs), A_KIND 0 / 1 only
   // N-split GEMM over several GPUs: every finished chunk is also stored (TMA, NVLink) into the same window of each
   // peer's output buffer, so the "all-gather" of the column blocks happens tile by tile inside the GEMM.  The maps
   // live in global memory (host-encoded, copied before the launch).
@@ -281,6 +282,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                   : A_KIND == 3 ? args.ic.bat_count * m_tiles_1 : m_tiles_1;
   const int n_tiles = (args.N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
+  // Tile index -> (m-tile, n-tile).  Plain order is n fastest.  With args.group_m > 0 (large GEMMs) tiles are walked
+  // in groups of group_m m-tiles, m fastest inside a group: the ~148 tiles in flight then cover a group_m x
+  // (148 / group_m) block of the output and share that many A row panels and B column panels in L2, instead of
+  // 2 row panels and every column panel (at 16384^3 the plain order re-reads all of B from HBM for every other m-tile).
+  const int group_m = args.group_m;
+  auto tile_mn = [&](int tile, int& mt, int& nt) {
+    if (group_m <= 0) {
+      mt = tile / n_tiles;
+      nt = tile - mt * n_tiles;
+    } else {
+      const int per_group = group_m * n_tiles;
+      const int g = tile / per_group, r = tile - g * per_group;
+      const int gm = min(group_m, m_tiles - g * group_m);  // rows of the (last, partial) group
+      nt = r / gm;
+      mt = g * group_m + (r - nt * gm);
+    }
+  };
   const int num_kb = args.num_kb;
   const int chunk_kb = kChunked ? kChunkKb : num_kb;  // k-blocks per TMEM accumulation chunk
   const int splits = args.splits > 1 ? args.splits : 1;
@@ -357,19 +375,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
         const int split = unit / num_tiles, tile = unit - split * num_tiles;
         const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
-        int m0 = (tile / n_tiles) * kBM;
-        const int n0 = (tile % n_tiles) * BN;
+        int tmt, tnt;
+        tile_mn(tile, tmt, tnt);
+        int m0 = tmt * kBM;
+        const int n0 = tnt * BN;
         int pix_w = 0, pix_h = 0, pix_n = 0;
         int z0 = 0, z1 = 0;
         if (A_KIND == 3) {
-          const int z = (tile / n_tiles) / m_tiles_1;
-          m0 = ((tile / n_tiles) - z * m_tiles_1) * kBM;
+          const int z = tmt / m_tiles_1;
+          m0 = (tmt - z * m_tiles_1) * kBM;
           z1 = z / args.ic.bat_n0;
           z0 = z - z1 * args.ic.bat_n0;
         }
         if (A_KIND == 2) {
-          const int rowidx = (tile / n_tiles) / args.ic.win_tpr;
-          pix_w = ((tile / n_tiles) % args.ic.win_tpr) * kBM;  // first output column of the tile
+          const int rowidx = tmt / args.ic.win_tpr;
+          pix_w = (tmt % args.ic.win_tpr) * kBM;  // first output column of the tile
           pix_n = rowidx / args.ic.oh;
           pix_h = (rowidx - pix_n * args.ic.oh) * args.ic.stride_h;
         }
@@ -583,22 +603,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int split = unit / num_tiles, tile = unit - split * num_tiles;
       const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
-      const int n0 = (tile % n_tiles) * BN;
+      int tmt, tnt;
+      tile_mn(tile, tmt, tnt);
+      const int n0 = tnt * BN;
       // store coordinates of this warp's 32 rows: (st_r, st_z) in the {columns, rows, planes} view of D / R
       int m, st_r, st_z = 0;
       bool row_ok;
       if (A_KIND == 2) {
-        st_z = (tile / n_tiles) / args.ic.win_tpr;
-        st_r = ((tile / n_tiles) % args.ic.win_tpr) * kBM + q * 32;
+        st_z = tmt / args.ic.win_tpr;
+        st_r = (tmt % args.ic.win_tpr) * kBM + q * 32;
         m = st_z * args.ic.ow + st_r + lane;
         row_ok = st_r + lane < args.ic.ow;
       } else if (A_KIND == 3) {
-        st_z = (tile / n_tiles) / m_tiles_1;
-        st_r = ((tile / n_tiles) - st_z * m_tiles_1) * kBM + q * 32;
+        st_z = tmt / m_tiles_1;
+        st_r = (tmt - st_z * m_tiles_1) * kBM + q * 32;
         m = st_z * args.M + st_r + lane;
         row_ok = st_r + lane < args.M;
       } else {
-        st_r = (tile / n_tiles) * kBM + q * 32;
+        st_r = tmt * kBM + q * 32;
         st_z = split;  // split-K: plane of the partial-sum workspace (0 otherwise)
         m = st_r + lane;
         row_ok = m < args.M;
@@ -784,7 +806,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int split = unit / num_tiles, tile = unit - split * num_tiles;
       const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
-      const int n0 = (tile % n_tiles) * BN;
+      int tmt, tnt;
+      tile_mn(tile, tmt, tnt);
+      const int n0 = tnt * BN;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
         ptx::mbar_wait(empty_bar(s), ph ^ 1u);
         if (ptx::elect_one()) {

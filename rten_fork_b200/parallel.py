@@ -61,11 +61,11 @@ def gather_outputs(local, total_rows: int, group=None):
     return torch.cat([p[: hi - lo] for p, (lo, hi) in zip(parts, rows)], dim=0)
 
 
-def gemm_nsplit(a, b, group=None, local_gemm=None, align: int = 128):
+def gemm_nsplit(a, b, group=None, local_gemm=None, align: int = 128, ctx=None):
     """``A @ B`` with B's columns split over the ranks of ``group`` and the result gathered on every rank.
 
     ``a``: [M, K], ``b``: [K, N] torch tensors on this rank's device.  ``local_gemm(a, b_block) -> [M, n_r]`` defaults
-    to the tcgen05 GEMM of this package (CUDA tensors); the CPU tests pass a stand-in so that only the partition /
+    to the tcgen05 GEMM of this package on context ``ctx`` (CUDA tensors); the CPU tests pass a stand-in so that only the partition /
     gather logic is exercised.  The gather is ONE all-gather of equal-sized padded blocks (NCCL needs equal sizes);
     the padding columns are dropped when the blocks are laid side by side.
     """
@@ -78,10 +78,16 @@ def gemm_nsplit(a, b, group=None, local_gemm=None, align: int = 128):
     lo, hi = blocks[rank]
     if local_gemm is None:
         from . import ops
+        from .context import default_context
+
+        # the contraction must be ordered with the torch work around it (the copy into `mine`, the all-gather): run it
+        # on torch's current stream, not on the context's own
+        ctx = ctx or default_context(a.device.index)
+        ctx.set_stream(torch.cuda.current_stream(a.device).cuda_stream)
 
         def local_gemm(x, y):
             out = torch.empty((x.shape[0], y.shape[1]), dtype=torch.float32, device=x.device)
-            return ops.matmul(x, y, out=out)
+            return ops.matmul(x, y, out=out, ctx=ctx)
 
     width = max(h - l for l, h in blocks)
     mine = torch.zeros((m, width), dtype=torch.float32, device=a.device)
@@ -140,10 +146,19 @@ class SymmetricMatrix:
             self._opened.append(peer.value)
         self.tensor = torch.as_tensor(_DevicePtrView(self._local, (m, n)), device=torch.device("cuda", self.ctx.device))
         self._flag = torch.zeros(1, dtype=torch.int32, device=self.tensor.device)
+        self._written = False   # a fused product has been stored into the buffers since the last leading fence
+
+    def bind_stream(self):
+        """The context launches on ITS stream; the fences (NCCL all-reduces) and the caller's reads of ``tensor`` run on
+        torch's current stream.  Binding the context to that stream orders all three."""
+        import torch
+
+        self.ctx.set_stream(torch.cuda.current_stream(self.tensor.device).cuda_stream)
 
     def fence(self):
         """Stream-ordered cross-rank barrier: once it has run on this rank's stream, every rank's GEMM (and with it
-        every peer store into this rank's buffer) has completed.  One 4-byte all-reduce; no host synchronisation."""
+        every peer store into this rank's buffer) has completed.  One 4-byte all-reduce; no host synchronisation.
+        Only orders work on torch's current stream: ``gemm_nsplit_fused`` binds the context to it first."""
         import torch.distributed as dist
 
         dist.all_reduce(self._flag, group=self.group)
@@ -170,7 +185,8 @@ def gemm_nsplit_fused(a, b, out: SymmetricMatrix, align: int = 128, fence: bool 
     """``A @ B`` with B's columns split over the ranks, the gather fused into the GEMM epilogue: rank r multiplies A by
     its column block and every finished tile is stored by TMA into columns ``[lo, hi)`` of ALL ranks' ``out`` buffers
     (its own through HBM, the peers' over NVLink), so no all-gather runs afterwards — only ``out.fence()``, a 4-byte
-    all-reduce that orders the ranks.  ``a``: [M, K], ``b``: [K, N] CUDA tensors (any strides).  Returns the local
+    all-reduce that orders the ranks (and a second one in front when the same buffers are stored into again).  The
+    context is bound to torch's current stream, so the product, the fences and the caller's reads are stream-ordered.  ``a``: [M, K], ``b``: [K, N] CUDA tensors (any strides).  Returns the local
     ``[M, N]`` tensor of ``out`` (complete once the fence has run on the stream).
 
     ``gemm_nsplit`` (local GEMM, then one NCCL all-gather and a strided copy) is the baseline this replaces."""
@@ -182,6 +198,13 @@ def gemm_nsplit_fused(a, b, out: SymmetricMatrix, align: int = 128, fence: bool 
     n = b.shape[1]
     if (m, n) != (out.m, out.n):
         raise N.RtgError(3, "output buffer shape does not match the product")
+    out.bind_stream()
+    if out._written:
+        # Re-use of the buffers: a fast rank's peer stores of this product must not land in a buffer a slower rank is
+        # still reading from the previous one.  A leading fence makes every rank's stream reach this point (all of its
+        # earlier reads are ordered before it) before any rank stores again.
+        out.fence()
+    out._written = True
     lo, hi = column_blocks(n, out.world, align)[out.rank]
     if hi > lo:
         bb = b[:, lo:hi]
