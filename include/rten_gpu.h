@@ -274,6 +274,14 @@ typedef struct rtg_ticket rtg_ticket;
 rtg_status rtg_model_submit(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_tensor* outputs,
                             int32_t n_outputs, rtg_ticket** out);
 rtg_status rtg_ticket_wait(rtg_ticket* ticket);
+/* CUDA-graph replay of the cached plan (no reference counterpart: it replaces the per-operator dispatch loop of
+ * run_plan, src/graph.rs:883-1051, whose cost on a GPU is launch latency).  On by default: the first run of a
+ * (node ids, input shapes, math mode) key executes eagerly, the second is stream-captured, later runs replay one
+ * cudaGraphLaunch.  Graphs that need a host round trip while running (shape tensors computed on the device and read
+ * back) stay on the eager path.  Environment: RTEN_GPU_GRAPH=0 turns it off for every model.
+ * rtg_model_graph_replays: how many runs of this model were replays (diagnostics / tests). */
+rtg_status rtg_model_set_graph_capture(rtg_model* model, int32_t enabled);
+rtg_status rtg_model_graph_replays(rtg_model* model, uint64_t* replays);
 /* RunOptions{timing}: per-operator device time of the last run as text   src/graph.rs:467-483, src/timing.rs */
 rtg_status rtg_model_set_timing(rtg_model* model, int32_t enabled);
 const char* rtg_model_timing_report(rtg_model* model);

@@ -1,6 +1,7 @@
 // C ABI: Model::load / load_file / run and RunOptions timing (reference: src/model.rs:214-263,580-646,
 // src/graph.rs:467-483,1053-1135, src/timing.rs).
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <map>
@@ -22,7 +23,155 @@ void rtg::SubmitPipeline::release() {
   upload = nullptr;
 }
 
+void rtg::Model::release_captured() {
+  for (auto& c : captured) {
+    if (c->exec) {
+      cudaGraphExecDestroy(c->exec);
+      ctx->pool.pinned_addresses--;
+    }
+    for (Value& v : c->in_bufs) release_value(ctx, &v);
+    for (Value& v : c->outs) release_value(ctx, &v);
+  }
+  captured.clear();
+}
+
 namespace {
+
+bool graph_capture_default() {
+  static const bool on = []() {
+    const char* e = getenv("RTEN_GPU_GRAPH");
+    return !e || atoi(e) != 0;
+  }();
+  return on;
+}
+
+// Copies one caller input (host or device, any strides for device tensors) into a device value of the same shape.
+rtg_status copy_input(Context* ctx, const rtg_tensor& t, const Value& dst) {
+  const int64_t n = numel(t);
+  if (n == 0) return RTG_OK;
+  if (t.device == RTG_HOST) {
+    rtg_tensor tc = t;
+    if (!is_contiguous(tc)) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "host model inputs must be contiguous");
+    RTG_CUDA(cudaMemcpyAsync(dst.t.data, t.data, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    return RTG_OK;
+  }
+  return copy_view(ctx, dst.t, t);
+}
+
+// The outputs of a replay live in buffers the next replay overwrites: the run handle gets its own copies (same
+// strides, so an NHWC-strided result stays one).
+rtg_status copy_outputs(Context* ctx, const CapturedPlan& cp, Run* run) {
+  for (const Value& src : cp.outs) {
+    Value dst;
+    RTG_TRY(alloc_value(ctx, src.t.dtype, src.t.ndim, src.t.shape, false, &dst));
+    for (int k = 0; k < src.t.ndim; ++k) dst.t.strides[k] = src.t.strides[k];
+    const int64_t n = numel(src.t);
+    if (n > 0) {
+      cudaError_t e = cudaMemcpyAsync(dst.t.data, src.t.data, static_cast<size_t>(n) * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+      if (e != cudaSuccess) {
+        release_value(ctx, &dst);
+        return set_errorf(RTG_ERR_CUDA, "output copy failed: %s", cudaGetErrorString(e));
+      }
+    }
+    dst.host_i32 = src.host_i32, dst.host_f32 = src.host_f32;
+    run->outputs.push_back(dst);
+  }
+  return RTG_OK;
+}
+
+// Replays (or first captures) the plan for this key.  Returns RTG_OK with *handled = false when the caller should run
+// eagerly (first run of a key, capture not possible, timing on).
+rtg_status run_captured(Model* m, const rtg_tensor* inputs, int32_t n_inputs, const std::vector<int32_t>& in_ids,
+                        const std::vector<int32_t>& outs_req, Run* run, bool* handled) {
+  *handled = false;
+  Context* ctx = m->ctx;
+  if (!m->graph_capture || !graph_capture_default() || m->timing || ctx->ktiming) return RTG_OK;
+  std::lock_guard<std::mutex> lock(m->cap_mu);
+  CapturedPlan* cp = nullptr;
+  for (auto& c : m->captured) {
+    if (c->math != ctx->math || c->in_ids != in_ids || c->out_ids != outs_req) continue;
+    bool same = true;
+    for (int32_t i = 0; i < n_inputs && same; ++i) {
+      same = c->in_desc[i].dtype == inputs[i].dtype && c->in_desc[i].ndim == inputs[i].ndim;
+      for (int k = 0; k < inputs[i].ndim && same; ++k) same = c->in_desc[i].shape[k] == inputs[i].shape[k];
+    }
+    if (same) {
+      cp = c.get();
+      break;
+    }
+  }
+  if (!cp) {
+    if (m->captured.size() >= 8) return RTG_OK;  // a model run at many shapes: keep the eager path for the rest
+    m->captured.emplace_back(new CapturedPlan());
+    cp = m->captured.back().get();
+    cp->in_ids = in_ids, cp->out_ids = outs_req, cp->math = ctx->math;
+    cp->in_desc.assign(inputs, inputs + n_inputs);
+  }
+  if (cp->failed) return RTG_OK;
+  if (!cp->exec) {
+    if (cp->seen++ < 1) return RTG_OK;  // first run: eager
+    // ---- capture
+    rtg_status st = RTG_OK;
+    for (int32_t i = 0; i < n_inputs && st == RTG_OK; ++i) {
+      Value v;
+      st = alloc_value(ctx, inputs[i].dtype, inputs[i].ndim, inputs[i].shape, false, &v);
+      if (st == RTG_OK) cp->in_bufs.push_back(v);
+    }
+    for (int32_t i = 0; i < n_inputs && st == RTG_OK; ++i) st = copy_input(ctx, inputs[i], cp->in_bufs[i]);
+    auto give_up = [&](rtg_status why) {
+      for (Value& v : cp->in_bufs) release_value(ctx, &v);
+      for (Value& v : cp->outs) release_value(ctx, &v);
+      cp->in_bufs.clear();
+      cp->outs.clear();
+      cp->failed = true;
+      cudaGetLastError();
+      (void)why;
+      return RTG_OK;  // the caller runs eagerly
+    };
+    if (st != RTG_OK) return give_up(st);
+    if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) return give_up(RTG_ERR_CUDA);
+    std::vector<std::pair<int32_t, Value>> in;
+    for (int32_t i = 0; i < n_inputs; ++i) {
+      Value v = cp->in_bufs[i];
+      v.owned = false;  // the captured kernels read the persistent buffers; nothing may recycle or overwrite them
+      in.emplace_back(in_ids[i], v);
+    }
+    const uint64_t l0 = ctx->launches;
+    std::vector<Value> outs;
+    st = m->graph.run(ctx, in, outs_req, &outs, nullptr);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+    if (st != RTG_OK || ce != cudaSuccess || !graph) {
+      // an operator needed a host round trip (or failed): not capturable; nothing was executed
+      if (graph) cudaGraphDestroy(graph);
+      for (Value& v : outs) release_value(ctx, &v);
+      ctx->launches = l0;
+      return give_up(st);
+    }
+    cp->launches = ctx->launches - l0;
+    ctx->launches = l0;
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) {
+      for (Value& v : outs) release_value(ctx, &v);
+      return give_up(RTG_ERR_CUDA);
+    }
+    // outputs that are views of something else (constants, requested twice) were copied by Graph::run: all owned
+    cp->outs = outs;
+    cp->exec = exec;
+    ctx->pool.pinned_addresses++;
+  } else {
+    for (int32_t i = 0; i < n_inputs; ++i) RTG_TRY(copy_input(ctx, inputs[i], cp->in_bufs[i]));
+  }
+  RTG_CUDA(cudaGraphLaunch(cp->exec, ctx->stream));
+  ctx->launches += cp->launches;
+  m->replays++;
+  RTG_TRY(copy_outputs(ctx, *cp, run));
+  run->node_ids = outs_req;
+  *handled = true;
+  return RTG_OK;
+}
 
 rtg_status node_info(const Model* m, int32_t id, const char** name, int64_t* shape, int32_t* ndim, int32_t* dtype) {
   const Node& nd = m->graph.nodes[id];
@@ -81,6 +230,25 @@ rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, cons
     if (outs_req[i] < 0 || outs_req[i] >= n_nodes) return set_error(RTG_ERR_INVALID_VALUE, "Output node ID is invalid");
     for (size_t k = 0; k < i; ++k)
       if (outs_req[k] == outs_req[i]) return set_error(RTG_ERR_INVALID_VALUE, "Outputs are not unique");
+  }
+  for (int32_t i = 0; i < n_inputs; ++i)
+    if (inputs[i].ndim < 0 || inputs[i].ndim > RTG_MAX_DIMS || (inputs[i].dtype != RTG_F32 && inputs[i].dtype != RTG_I32))
+      return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  if (!partial) {
+    std::vector<int32_t> in_ids_v(n_inputs);
+    for (int32_t i = 0; i < n_inputs; ++i) in_ids_v[i] = input_ids ? input_ids[i] : g.input_ids[i];
+    std::unique_ptr<Run> crun(new Run());
+    crun->ctx = ctx;
+    bool handled = false;
+    rtg_status cst = run_captured(m, inputs, n_inputs, in_ids_v, outs_req, crun.get(), &handled);
+    if (cst != RTG_OK) {
+      for (Value& v : crun->outputs) release_value(ctx, &v);
+      return cst;
+    }
+    if (handled) {
+      *out = crun.release();
+      return RTG_OK;
+    }
   }
   std::vector<std::pair<int32_t, Value>> in;
   auto cleanup = [&]() {
@@ -186,6 +354,7 @@ rtg_status rtg_model_free(rtg_model* model) {
   if (!m) return RTG_OK;
   cudaSetDevice(m->ctx->device);
   cudaStreamSynchronize(m->ctx->stream);
+  m->release_captured();
   m->graph.release(m->ctx);
   m->pipe.release();
   delete m;
@@ -223,6 +392,20 @@ rtg_status rtg_model_output_info(const rtg_model* model, int32_t i, const char**
   if (!m || i < 0 || i >= static_cast<int32_t>(m->graph.output_ids.size()))
     return set_error(RTG_ERR_INVALID_VALUE, "output index out of range");
   return node_info(m, m->graph.output_ids[i], name, shape, ndim, dtype);
+}
+
+rtg_status rtg_model_set_graph_capture(rtg_model* model, int32_t enabled) {
+  Model* m = reinterpret_cast<Model*>(model);
+  if (!m) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  std::lock_guard<std::mutex> lock(m->cap_mu);
+  m->graph_capture = enabled != 0;
+  return RTG_OK;
+}
+rtg_status rtg_model_graph_replays(rtg_model* model, uint64_t* replays) {
+  Model* m = reinterpret_cast<Model*>(model);
+  if (!m || !replays) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  *replays = m->replays;
+  return RTG_OK;
 }
 
 rtg_status rtg_model_set_timing(rtg_model* model, int32_t enabled) {

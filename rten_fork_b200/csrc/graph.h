@@ -171,6 +171,23 @@ struct SubmitPipeline {
   void release();
 };
 
+// One cached plan captured as a CUDA graph (the loop it replaces is run_plan, src/graph.rs:883-1051).
+// Key: the input / output node ids, the input shapes and the math mode.  The first run with a key executes eagerly
+// (it sizes the pool and lets operators settle their caches); the second is stream-captured, instantiated and then
+// replayed by every later run: ~70 launches and their tensor-map encodes become one cudaGraphLaunch.  Tensor maps are
+// kernel parameters, so they are baked into the graph together with the pool addresses of every temporary.
+struct CapturedPlan {
+  std::vector<int32_t> in_ids, out_ids;
+  std::vector<rtg_tensor> in_desc;   // dtype / ndim / shape per input
+  int math = 0;
+  int seen = 0;                      // eager runs so far
+  bool failed = false;               // capture was tried and this graph cannot be captured (host round trips)
+  cudaGraphExec_t exec = nullptr;
+  std::vector<Value> in_bufs;        // persistent device inputs the captured kernels read
+  std::vector<Value> outs;           // outputs of the captured run; every replay overwrites them
+  uint64_t launches = 0;             // kernels in the graph (Context::launches advances by this per replay)
+};
+
 struct Model {
   Context* ctx = nullptr;
   Graph graph;
@@ -178,6 +195,12 @@ struct Model {
   std::string timing_report;
   std::vector<std::string> name_store;
   SubmitPipeline pipe;
+  // CUDA-graph replay of cached plans.  RTEN_GPU_GRAPH=0 (or rtg_model_set_graph_capture) turns it off.
+  bool graph_capture = true;
+  std::mutex cap_mu;                 // replays share the captured buffers: one at a time per model
+  std::vector<std::unique_ptr<CapturedPlan>> captured;
+  uint64_t replays = 0;
+  void release_captured();
 };
 rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimize, Model** out);
 

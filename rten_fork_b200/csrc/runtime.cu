@@ -40,6 +40,7 @@ rtg_status DevPool::alloc(size_t bytes, void** out) {
   auto it = free_.lower_bound(bytes);
   if (it != free_.end() && it->first <= bytes * 4 + (1 << 20)) {
     *out = it->second;
+    capacity_[it->second].pooled = false;
     free_.erase(it);
     hit_count++;
     return RTG_OK;
@@ -47,6 +48,11 @@ rtg_status DevPool::alloc(size_t bytes, void** out) {
   size_t cap = (bytes + 511) & ~size_t(511);
   void* p = nullptr;
   cudaError_t e = cudaMalloc(&p, cap);
+  if (e != cudaSuccess && pinned_addresses > 0) {
+    cudaGetLastError();
+    return set_errorf(RTG_ERR_CUDA, "cudaMalloc(%zu) failed: %s (pooled buffers are pinned by captured graphs)", cap,
+                      cudaGetErrorString(e));
+  }
   if (e != cudaSuccess) {
     // Give pooled memory back to the driver and retry once.
     for (auto& kv : free_) {
@@ -59,7 +65,7 @@ rtg_status DevPool::alloc(size_t bytes, void** out) {
     e = cudaMalloc(&p, cap);
     if (e != cudaSuccess) return set_errorf(RTG_ERR_CUDA, "cudaMalloc(%zu) failed: %s", cap, cudaGetErrorString(e));
   }
-  capacity_[p] = cap;
+  capacity_[p] = Slot{cap, false};
   bytes_reserved += cap;
   *out = p;
   return RTG_OK;
@@ -69,7 +75,9 @@ rtg_status DevPool::free(void* p) {
   if (!p) return RTG_OK;
   auto it = capacity_.find(p);
   if (it == capacity_.end()) return set_error(RTG_ERR_INVALID_VALUE, "pointer was not allocated from this pool");
-  free_.emplace(it->second, p);
+  if (it->second.pooled) return set_error(RTG_ERR_INVALID_VALUE, "pointer was already returned to the pool (double free)");
+  it->second.pooled = true;
+  free_.emplace(it->second.cap, p);
   return RTG_OK;
 }
 

@@ -43,10 +43,17 @@ class DevPool {
   uint64_t alloc_count = 0, hit_count = 0;
   size_t len() const { return free_.size(); }
   size_t bytes_reserved = 0;
+  // > 0 while captured CUDA graphs reference addresses of this pool (Model graph capture): pooled buffers are then
+  // never given back to the driver, their addresses are baked into the graphs
+  int pinned_addresses = 0;
 
  private:
-  std::multimap<size_t, void*> free_;            // capacity -> buffer
-  std::unordered_map<void*, size_t> capacity_;   // every live or pooled buffer
+  struct Slot {
+    size_t cap;
+    bool pooled;  // sitting in free_ (a second free of the same pointer is an error, not a silent double entry)
+  };
+  std::multimap<size_t, void*> free_;          // capacity -> buffer
+  std::unordered_map<void*, Slot> capacity_;   // every live or pooled buffer
 };
 
 // ---------------------------------------------------------------- context

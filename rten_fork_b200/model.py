@@ -94,6 +94,16 @@ class Model:
         N.check(N.lib().rtg_model_num_ops(self._h, C.byref(n)))
         return n.value
 
+    # -- CUDA-graph replay of the cached plan (rtg_model_set_graph_capture / rtg_model_graph_replays)
+    def set_graph_capture(self, enabled: bool):
+        N.check(N.lib().rtg_model_set_graph_capture(self._h, C.c_int32(bool(enabled))))
+
+    @property
+    def graph_replays(self) -> int:
+        n = C.c_uint64()
+        N.check(N.lib().rtg_model_graph_replays(self._h, C.byref(n)))
+        return n.value
+
     # -- RunOptions {timing} (src/graph.rs:467-483)
     def set_timing(self, enabled: bool):
         N.check(N.lib().rtg_model_set_timing(self._h, C.c_int32(bool(enabled))))

@@ -342,3 +342,73 @@ def test_einsum_errors(rtg, ctx):
                             ("ij->i", [(2, 2)], "not supported on this path")]:
         with pytest.raises(rtg.RtgError, match=msg):
             run(eq, shapes)
+
+
+def test_cached_plan_replays_as_a_cuda_graph(rtg, oracle):
+    """The second run of a (shapes, math mode) key is stream-captured and later runs replay one CUDA graph: results are
+    bit-identical to the eager run, follow the input values, and a new batch size gets its own capture."""
+    from rten_fork_b200 import synth
+    from rten_fork_b200.model import Model
+
+    c = rtg.Context(0)
+    c.set_math(rtg.MATH_TF32_BF16X2)
+    b = synth.resnet50(image=32, width=8, blocks=(1, 1, 1, 1), classes=10, seed=5)
+    m = Model.load(b.build(), ctx=c)
+    rng = oracle.XorShiftRng(3)
+    x1, x2 = rng.fill((4, 3, 32, 32)), rng.fill((4, 3, 32, 32))
+    eager = m.run([x1])[0]                    # first run of the key: eager
+    assert m.graph_replays == 0
+    l0 = c.launch_count
+    captured = m.run([x1])[0]                 # second: captured, instantiated, launched
+    assert m.graph_replays == 1
+    per_run = c.launch_count - l0
+    assert per_run > 10                       # the launch counter advances by the kernels inside the graph
+    replay = m.run([x1])[0]
+    assert m.graph_replays == 2 and c.launch_count - l0 == 2 * per_run
+    assert eager.tobytes() == captured.tobytes() == replay.tobytes()
+    other = m.run([x2])[0]                    # replays read the new input
+    assert other.tobytes() != replay.tobytes()
+    m.set_graph_capture(False)
+    assert m.run([x2])[0].tobytes() == other.tobytes() and m.graph_replays == 3
+    m.set_graph_capture(True)
+    y8 = m.run([rng.fill((8, 3, 32, 32))])[0]  # another batch size: its own key, eager first
+    assert y8.shape == (8, 10) and m.graph_replays == 3
+    assert m.run([x1])[0].tobytes() == eager.tobytes() and m.graph_replays == 4
+    # asynchronous submits replay too
+    import torch
+
+    xh, oh = torch.from_numpy(x1).pin_memory(), torch.empty((4, 10)).pin_memory()
+    m.run_async([xh], [oh]).wait()
+    assert oh.numpy().tobytes() == eager.tobytes() and m.graph_replays == 5
+    m.close()
+    c.close()
+
+
+def test_graph_with_host_round_trip_stays_eager(rtg, oracle):
+    """A graph that reads a device-computed shape back on the host (Shape -> Gather -> ... -> Reshape) cannot be
+    captured: it keeps running eagerly and correctly."""
+    from rten_fork_b200.model import Model
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    b = ModelBuilder()
+    x = b.add_value("x", ["n", 6])
+    b.inputs = [x]
+    y = b.op("Relu", [x], name="relu")
+    # the new shape arrives as a graph INPUT that lives on the device: Reshape has to read it back
+    shp = b.add_value("shape", [2])
+    b.inputs.append(shp)
+    y = b.op("Reshape", [y, shp], ("ReshapeAttrs", []), name="reshape")
+    b.outputs = [y]
+    c = rtg.Context(0)
+    m = Model.load(b.build(), ctx=c)
+    import torch
+
+    xin = oracle.XorShiftRng(9).fill((4, 6)) - 0.5
+    sh = torch.tensor([3, 8], dtype=torch.int32, device="cuda")   # a device tensor: no host mirror
+    xs = torch.from_numpy(xin).cuda()
+    for _ in range(3):
+        got = m.run([xs, sh])[0]
+        assert got.shape == (3, 8) and got.tobytes() == np.maximum(xin, 0).reshape(3, 8).tobytes()
+    assert m.graph_replays == 0
+    m.close()
+    c.close()
