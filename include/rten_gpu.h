@@ -171,6 +171,23 @@ rtg_status rtg_conv(rtg_ctx* ctx, const rtg_tensor* input, const rtg_tensor* wei
                     const rtg_conv_attrs* attrs, const rtg_tensor* residual_or_null, int32_t act, float act_lo,
                     float act_hi, rtg_tensor* output);
 
+/* VirtualIm2Col and the layouts around it                          src/ops/conv/im2col.rs:75-260, src/ops/conv.rs:212-271
+ * The reference gathers the patch matrix on demand with i32 offset tables and a zero-fill mask; here TMA's im2col mode
+ * does it in hardware, with three software layout kernels around it.  This entry point writes what those kernels build
+ * to a HOST buffer so that it can be compared bit for bit with the reference's tables (every element is a copy or 0):
+ *   kind 0  patch matrix of `group`: [n][oh*ow][kh*kw*kpt], kpt = ceil32(C/groups), column (ky*kw + kx)*kpt + c
+ *           (the software gather the convolution falls back to outside TMA's im2col limits)
+ *   kind 1  zero-padded NHWC image of the few-channel (row-window) path: [n][hp][wp][ceil4(C)]
+ *   kind 2  NHWC copy [n][h*w][ceil4(C)]        kind 3  kind 2 converted back to dense NCHW [n][c][h][w]
+ * out_dims receives 4 extents.  RTG_DEBUG_FORCE_IM2COL_FALLBACK (rtg_ctx_set_debug_flags) makes rtg_conv itself take the
+ * software gather, whose contraction result must equal the TMA path's bit for bit. */
+rtg_status rtg_conv_patches(rtg_ctx* ctx, int32_t kind, const rtg_tensor* input, const rtg_tensor* weight,
+                            const rtg_conv_attrs* attrs, int32_t group, float* out_host, size_t out_floats,
+                            int64_t* out_dims);
+#define RTG_DEBUG_FORCE_IM2COL_FALLBACK (1 << 16)
+/* Developer / test switches of a context (no reference counterpart). */
+rtg_status rtg_ctx_set_debug_flags(rtg_ctx* ctx, int32_t flags);
+
 /* conv_transpose() / ConvTranspose::run                           src/ops/conv.rs:377-577
  * input NCHW (or NCW), kernel [C, O, Kh, Kw] (or [C, O, Kw]), bias [O] or NULL.  Fixed padding is [top, left, bottom,
  * right] ([left, right] for 1-D); RTG_PAD_SAME gives out = in * stride per axis.  Errors carry the reference's strings

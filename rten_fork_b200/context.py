@@ -9,6 +9,9 @@ import numpy as np
 from . import _native as N
 
 
+FORCE_IM2COL_FALLBACK = 1 << 16
+
+
 class Context:
     """Owns one ``rtg_ctx``.  Mirrors what a run of the reference owns implicitly: a TensorPool
     (src/tensor_pool.rs:103-199) plus, new here, the CUDA stream and device weight cache."""
@@ -47,6 +50,10 @@ class Context:
 
     def set_stream(self, cuda_stream: int):
         N.check(N.lib().rtg_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def set_debug_flags(self, flags: int):
+        """Developer / test switches (``rtg_ctx_set_debug_flags``), e.g. ``FORCE_IM2COL_FALLBACK``."""
+        N.check(N.lib().rtg_ctx_set_debug_flags(self._h, C.c_int32(flags)))
 
     def sync(self):
         N.check(N.lib().rtg_ctx_sync(self._h))

@@ -135,6 +135,26 @@ rtg_status rtg_conv(rtg_ctx* ctx_, const rtg_tensor* input, const rtg_tensor* we
   return finish_out(ctx, output, &o);
 }
 
+rtg_status rtg_conv_patches(rtg_ctx* ctx_, int32_t kind, const rtg_tensor* input, const rtg_tensor* weight,
+                            const rtg_conv_attrs* attrs, int32_t group, float* out_host, size_t out_floats,
+                            int64_t* out_dims) {
+  CTX_OR_FAIL(ctx_);
+  if (!attrs || !out_host || !out_dims) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");
+  RTG_TRY(check_tensor(input, "input"));
+  RTG_TRY(check_tensor(weight, "kernel"));
+  ConvPlan p;
+  RTG_TRY(conv_plan(input, weight, nullptr, attrs, &p));
+  Staged x;
+  RTG_TRY(stage_in(ctx, input, &x));
+  Scratch d;
+  RTG_TRY(d.alloc(ctx, std::max<size_t>(out_floats, 1) * 4));
+  RTG_TRY(conv_patches(ctx, kind, p, x.t, group, d.f32(), out_floats, out_dims));
+  const size_t n = static_cast<size_t>(out_dims[0] * out_dims[1] * out_dims[2] * out_dims[3]);
+  if (n > 0) RTG_CUDA(cudaMemcpyAsync(out_host, d.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  RTG_CUDA(cudaStreamSynchronize(ctx->stream));
+  return RTG_OK;
+}
+
 rtg_status rtg_conv_transpose_out_shape(const rtg_tensor* input, const rtg_tensor* weight, const rtg_tensor* bias,
                                         const rtg_conv_transpose_attrs* attrs, int64_t* out_shape, int32_t* out_ndim) {
   if (!attrs || !out_shape || !out_ndim) return set_error(RTG_ERR_INVALID_VALUE, "NULL argument");

@@ -137,7 +137,7 @@ rtg_status conv_prepare_weights(Context* ctx, const ConvPlan& p, const float* w_
     out->kpt = static_cast<int>(p.c);
     return prepare_wpack(ctx, out, p.o, p.c);
   }
-  if (conv_window_supported(p)) {
+  if (conv_window_supported(p) && !(ctx->debug_flags & kForceIm2colFallback)) {
     const int cp = static_cast<int>(div_ceil(p.c, 4) * 4);
     const int64_t total = p.o * p.kh * kBK;
     void* d = nullptr;
@@ -394,7 +394,7 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
                      static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.pads[0]),
                      static_cast<int>(p.pads[1]), static_cast<int>(p.pads[2]), static_cast<int>(p.pads[3]),
                      static_cast<int>(p.dil_h), static_cast<int>(p.dil_w)};
-      if (conv_im2col_supported(cg)) {
+      if (conv_im2col_supported(cg) && !(ctx->debug_flags & kForceIm2colFallback)) {
         ep.b_pack = w.wpack, ep.b_pack_const = w.persistent;  // rows [g * OG, +OG) of both planes
         if (ep.b_pack.p) ep.b_pack.p += static_cast<int64_t>(g) * OG * w.wpack.ld;
         RTG_TRY(conv_gemm_device(ctx, xp, cg, wg, OG, D, dm, ep));
@@ -415,6 +415,77 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
     }
   }
   if (need_out_tmp) RTG_TRY(copy_view(ctx, out_final, out));
+  return RTG_OK;
+}
+
+rtg_status conv_patches(Context* ctx, int kind, const ConvPlan& p, const rtg_tensor& x_in, int group, float* dst,
+                        size_t dst_floats, int64_t dims[4]) {
+  rtg_tensor x = x_in;
+  if (x.ndim == 3) {  // 1-D convolution: H = 1
+    x.ndim = 4;
+    x.shape[3] = x.shape[2], x.strides[3] = x.strides[2];
+    x.shape[2] = 1, x.strides[2] = x.shape[3] * x.strides[3];
+  }
+  const int N = static_cast<int>(p.n), C = static_cast<int>(p.c), H = static_cast<int>(p.h), W = static_cast<int>(p.w);
+  const int OH = static_cast<int>(p.oh), OW = static_cast<int>(p.ow), CG = static_cast<int>(p.cg);
+  if (group < 0 || group >= p.groups) return set_error(RTG_ERR_INVALID_VALUE, "group out of range");
+  Scratch x_cont;
+  if (!is_nhwc_dense(x) && !plane_collapsible(x)) {
+    RTG_TRY(x_cont.alloc(ctx, static_cast<size_t>(numel(x)) * 4));
+    rtg_tensor xc = x;
+    xc.data = x_cont.p;
+    set_contiguous_strides(xc);
+    RTG_TRY(copy_view(ctx, xc, x));
+    x = xc;
+  }
+  auto need = [&](int64_t a, int64_t b, int64_t c, int64_t d) {
+    dims[0] = a, dims[1] = b, dims[2] = c, dims[3] = d;
+    return static_cast<size_t>(a * b * c * d) <= dst_floats
+               ? RTG_OK
+               : set_error(RTG_ERR_INVALID_VALUE, "destination buffer too small");
+  };
+  const int cp = static_cast<int>(div_ceil(C, 4) * 4);
+  if (kind == 1) {
+    const int hp = H + static_cast<int>(p.pads[0] + p.pads[2]);
+    const int wp = std::max(W + static_cast<int>(p.pads[1] + p.pads[3]), (OW - 1) * static_cast<int>(p.stride_w) + kBK / cp);
+    RTG_TRY(need(N, hp, wp, cp));
+    const int64_t pixels = static_cast<int64_t>(N) * hp * wp;
+    if (pixels == 0) return RTG_OK;
+    const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(pixels, 256), static_cast<int64_t>(ctx->num_sms) * 16));
+    pad_to_window_layout_kernel<<<blocks, 256, 0, ctx->stream>>>(dst, static_cast<const float*>(x.data), N, C, H, W, cp,
+                                                                 hp, wp, static_cast<int>(p.pads[0]),
+                                                                 static_cast<int>(p.pads[1]), x.strides[0], x.strides[1],
+                                                                 x.strides[2], x.strides[3]);
+    ctx->launches++;
+    RTG_CUDA(cudaGetLastError());
+    return RTG_OK;
+  }
+  if (kind == 2) {
+    RTG_TRY(need(N, H * W, cp, 1));
+    return to_nhwc(ctx, x, 0, C, cp, dst);
+  }
+  Scratch nhwc;
+  RTG_TRY(nhwc.alloc(ctx, static_cast<size_t>(std::max<int64_t>(1, static_cast<int64_t>(N) * H * W * cp)) * 4));
+  RTG_TRY(to_nhwc(ctx, x, 0, C, cp, nhwc.f32()));
+  if (kind == 3) {
+    RTG_TRY(need(N, C, H, W));
+    rtg_tensor o = x;
+    o.data = dst;
+    set_contiguous_strides(o);
+    return from_nhwc(ctx, nhwc.f32(), C, cp, o, 0);
+  }
+  if (kind != 0) return set_error(RTG_ERR_INVALID_VALUE, "unknown patch kind");
+  const int kpt = static_cast<int>(div_ceil(CG, kBK) * kBK);
+  const int64_t kmat = p.kh * p.kw * kpt, M = static_cast<int64_t>(N) * OH * OW;
+  RTG_TRY(need(N, static_cast<int64_t>(OH) * OW, kmat, 1));
+  if (M * kmat == 0) return RTG_OK;
+  Im2colGeom ig = {N, H, W, cp, group * CG, CG, static_cast<int>(p.kh), static_cast<int>(p.kw), OH, OW,
+                   static_cast<int>(p.stride_h), static_cast<int>(p.stride_w), static_cast<int>(p.pads[0]),
+                   static_cast<int>(p.pads[1]), static_cast<int>(p.dil_h), static_cast<int>(p.dil_w), kpt};
+  const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(M * kmat, 256), static_cast<int64_t>(ctx->num_sms) * 32));
+  im2col_nhwc_kernel<<<blocks, 256, 0, ctx->stream>>>(dst, nhwc.f32(), ig);
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
   return RTG_OK;
 }
 

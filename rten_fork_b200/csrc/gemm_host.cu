@@ -172,7 +172,7 @@ static bool direct_ok(const float* p, int64_t inner_stride, int64_t outer_stride
   return outer_count == 1 || (outer_stride > 0 && outer_stride % 4 == 0);
 }
 
-static int debug_flags() {
+static int env_debug_flags() {
   static int f = -1;
   if (f < 0) {
     const char* e = getenv("RTG_DEBUG_FLAGS");
@@ -180,6 +180,7 @@ static int debug_flags() {
   }
   return f;
 }
+#define debug_flags() (env_debug_flags() | (ctx->debug_flags & 0xFFFF))
 
 // ---------------------------------------------------------------- split-K reduction
 // Adds the partial-sum planes of a split-K launch in split order (fixed, so repeated runs are bit-identical) and

@@ -91,6 +91,19 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x, co
                         const float* bias_dev, const rtg_tensor* residual, int act, float act_lo, float act_hi,
                         const rtg_tensor& out);
 
+// The index-driven layouts the convolution path builds before it contracts, written to `dst` (device) for inspection:
+// VirtualIm2Col (src/ops/conv/im2col.rs:75-260) and the layout changes around it.  All are pure gathers: every element
+// is a copy of an input element or a zero, so they are compared bit for bit with the oracle's offset tables.
+//   kind 0  patch matrix of `group`: [n][oh*ow][kh*kw*kpt], kpt = ceil32(C/groups); column (ky*kw + kx)*kpt + c
+//           (im2col_nhwc_kernel over the NHWC copy: the software gather used outside TMA's im2col limits)
+//   kind 1  zero-padded NHWC image of the row-window path: [n][hp][wp][cp]   (pad_to_window_layout_kernel)
+//   kind 2  NHWC copy: [n][h*w][cp], cp = ceil4(C)                            (nchw_to_nhwc_kernel)
+//   kind 3  kind 2 converted back to dense NCHW: [n][c][h][w]                  (nhwc_to_nchw_kernel)
+// `dims` receives the shape written (4 entries).
+constexpr int kForceIm2colFallback = 1 << 16;  // Context::debug_flags: conv_forward never uses TMA im2col / row windows
+rtg_status conv_patches(Context* ctx, int kind, const ConvPlan& p, const rtg_tensor& x, int group, float* dst,
+                        size_t dst_floats, int64_t dims[4]);
+
 // ------------------------------------------------------------------ ConvTranspose (conv_transpose.cu)
 struct ConvTransposePlan {
   bool is_1d = false;

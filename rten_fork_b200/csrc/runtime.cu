@@ -135,6 +135,13 @@ rtg_status rtg_ctx_create(int32_t device, rtg_ctx** out) {
   return RTG_OK;
 }
 
+rtg_status rtg_ctx_set_debug_flags(rtg_ctx* ctx, int32_t flags) {
+  Context* c = reinterpret_cast<Context*>(ctx);
+  if (!c) return set_error(RTG_ERR_INVALID_VALUE, "ctx is NULL");
+  c->debug_flags = flags;
+  return RTG_OK;
+}
+
 rtg_status rtg_ctx_destroy(rtg_ctx* ctx) {
   Context* c = reinterpret_cast<Context*>(ctx);
   if (!c) return RTG_OK;

@@ -76,6 +76,7 @@ struct Context {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   int math = RTG_MATH_3XTF32;
+  int debug_flags = 0;  // rtg_ctx_set_debug_flags (developer / test switches), OR-ed with RTG_DEBUG_FLAGS
   DevPool pool;
   uint64_t launches = 0;
   std::string last_kernel;

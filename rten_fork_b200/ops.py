@@ -103,6 +103,42 @@ def conv(input, kernel, bias=None, padding=(0, 0, 0, 0), groups=1, strides=(1, 1
     return out
 
 
+PATCH_KINDS = {"im2col": 0, "window": 1, "nhwc": 2, "nchw_round_trip": 3}
+
+
+def conv_patches(kind, input, kernel, padding=(0, 0, 0, 0), groups=1, strides=(1, 1), dilations=(1, 1), group=0,
+                 ctx: Context | None = None):
+    """``rtg_conv_patches``: the index-driven layouts the convolution path builds (the software counterpart of
+    ``VirtualIm2Col``, src/ops/conv/im2col.rs:75-260), as a host array, for bit-exact comparison with the oracle."""
+    ctx = ctx or context_for(input)
+    a = _conv_attrs(padding, groups, strides, dilations)
+    ti, tw = as_tensor(input), as_tensor(kernel)
+    shape = (C.c_int64 * 4)()
+    nd = C.c_int32()
+    N.check(N.lib().rtg_conv_out_shape(C.byref(ti), C.byref(tw), None, C.byref(a), shape, C.byref(nd)))
+    n, c = input.shape[0], input.shape[1]
+    spatial = 1
+    for d in input.shape[2:]:
+        spatial *= d
+    out_pix = 1
+    for d in list(shape)[2: nd.value]:
+        out_pix *= d
+    kh, kw = (kernel.shape[2], kernel.shape[3]) if kernel.ndim == 4 else (1, kernel.shape[2])
+    cap = max(n * out_pix * kh * kw * ((c // groups + 31) // 32 * 32),          # patch matrix
+              n * ((c + 3) // 4 * 4) * (spatial + 64) * 4 + 4096, 16)            # padded image (generous)
+    pw = 0
+    if kind == "window":
+        pads = [0, 0, 0, 0] if isinstance(padding, str) else list(padding)
+        cap = max(cap, n * ((c + 3) // 4 * 4) * (input.shape[2] + 64) * (input.shape[3] * 2 + 64 + 8 * 32))
+    buf = np.empty(cap, dtype=np.float32)
+    dims = (C.c_int64 * 4)()
+    N.check(N.lib().rtg_conv_patches(ctx.handle, C.c_int32(PATCH_KINDS[kind]), C.byref(ti), C.byref(tw), C.byref(a),
+                                     C.c_int32(group), buf.ctypes.data_as(C.c_void_p), C.c_size_t(cap), dims))
+    shp = tuple(int(d) for d in dims)
+    cnt = int(np.prod(shp))
+    return buf[:cnt].reshape(shp).copy()
+
+
 class Conv:
     """``struct Conv {groups, dilations, padding, strides}`` + ``Operator::run`` (src/ops/conv.rs:282-311)."""
 
