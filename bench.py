@@ -170,21 +170,57 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------- CPU restatement arm
-def cpu_resnet(builder, seconds, batch_cap=BATCH, steps=None, warmup=1):
-    """Times the oracle's CPU evaluation of the same ResNet-50 graph (same weights) with every host thread.
-    Returns (images/s, threads, sample description, ms per step, batch)."""
+def physical_cores():
+    """The reference sizes its thread pool to the PHYSICAL cores (num_cpus::get_physical, src/threading.rs:41-63),
+    RTEN_NUM_THREADS overriding it."""
+    env = os.environ.get("RTEN_NUM_THREADS")
+    if env and env.isdigit() and int(env) >= 1:
+        return int(env)
+    try:
+        import psutil
+
+        n = psutil.cpu_count(logical=False)
+        if n:
+            return int(n)
+    except Exception:
+        pass
+    return os.cpu_count() or 1
+
+
+def host_avx2_peak_gflops(threads):
+    """cores x 2 FMA ports x 8 lanes x 2 flop x clock, the bound the reference quotes for its kernel
+    (src/gemm.rs:1871-1886); clock = the highest 'cpu MHz' the kernel reports right now."""
+    mhz = 0.0
+    try:
+        for l in open("/proc/cpuinfo"):
+            if l.lower().startswith("cpu mhz"):
+                mhz = max(mhz, float(l.split(":")[1]))
+    except Exception:
+        pass
+    return threads * 2 * 8 * 2 * mhz / 1e3 if mhz else None, mhz
+
+
+def cpu_resnet(builder, seconds, batch_cap=BATCH, steps=None, warmup=1, extras=False):
+    """Times the oracle's CPU evaluation of the same ResNet-50 graph (same weights) the way the reference would run
+    it: thread pool = physical cores (src/threading.rs:44), operator outputs from a buffer pool and Relu / Add in place
+    (src/graph.rs:897-931, src/tensor_pool.rs) — `graph_oracle.run_graph(reuse=True)`.
+    Returns (images/s, threads, sample description, ms per step, batch, extra lines)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import graph_oracle
     import oracle as o
 
     o.build()
-    threads = o.num_threads()
+    logical = o.num_threads()
+    threads = max(1, min(physical_cores(), logical))
+    o.set_num_threads(threads)
     rng = o.XorShiftRng(1234)
+    pool = graph_oracle._Pool()
+    run = lambda x: graph_oracle.run_graph(builder, [x], reuse=True, pool=pool)  # noqa: E731
     # calibrate on 2 images so that the bounded sample fits the budget
     x2 = rng.fill((2, 3, IMAGE, IMAGE))
-    graph_oracle.run_graph(builder, [x2])
+    run(x2)
     t0 = time.perf_counter()
-    graph_oracle.run_graph(builder, [x2])
+    run(x2)
     per_img = (time.perf_counter() - t0) / 2
     if steps is None:
         batch = int(max(1, min(batch_cap, seconds / 3 / per_img)))
@@ -193,14 +229,91 @@ def cpu_resnet(builder, seconds, batch_cap=BATCH, steps=None, warmup=1):
         batch = int(max(1, min(batch_cap, seconds / (steps + warmup) / per_img)))
     x = rng.fill((batch, 3, IMAGE, IMAGE))
     for _ in range(warmup):
-        graph_oracle.run_graph(builder, [x])
+        run(x)
     t0 = time.perf_counter()
     for _ in range(steps):
-        graph_oracle.run_graph(builder, [x])
+        run(x)
     dt = time.perf_counter() - t0
+    ips = batch * steps / dt
     sample = (f"ResNet-50 full graph, batch {batch} x {steps} steps ({warmup} warm-up), CPU restatement of the reference "
-              f"(AVX2 6x16 kernel, reference blocking), {threads} threads")
-    return batch * steps / dt, threads, sample, dt / steps * 1e3, batch
+              f"(AVX2 6x16 kernel, reference blocking, pooled buffers + in-place Relu/Add), {threads} threads = physical "
+              f"cores ({logical} logical)")
+    more = {}
+    if extras:
+        gflop_img = FLOP_PER_IMAGE / 1e9 if FLOP_PER_IMAGE else 8.178
+        peak, mhz = host_avx2_peak_gflops(threads)
+        more["gflops"] = ips * gflop_img
+        if peak:
+            more["fraction_of_avx2_fma_peak"] = ips * gflop_img / peak
+            more["avx2_fma_peak_gflops"] = peak
+            more["cpu_mhz"] = mhz
+        # one thread (1 image), all logical CPUs, and a torch / oneDNN context line: informational
+        o.set_num_threads(1)
+        p1 = graph_oracle._Pool()
+        x1 = rng.fill((1, 3, IMAGE, IMAGE))
+        graph_oracle.run_graph(builder, [x1], reuse=True, pool=p1)
+        t0 = time.perf_counter()
+        graph_oracle.run_graph(builder, [x1], reuse=True, pool=p1)
+        more["one_thread_images_per_s"] = 1.0 / (time.perf_counter() - t0)
+        if logical != threads:
+            o.set_num_threads(logical)
+            run(x)
+            t0 = time.perf_counter()
+            run(x)
+            more["all_logical_cpus_images_per_s"] = batch / (time.perf_counter() - t0)
+        o.set_num_threads(threads)
+        try:
+            more["torch_cpu_context_images_per_s"] = torch_cpu_resnet(builder, x, threads)
+        except Exception as exc:  # context only
+            more["torch_cpu_context_error"] = str(exc)[:100]
+    return ips, threads, sample, dt / steps * 1e3, batch, more
+
+
+def torch_cpu_resnet(builder, x, threads):
+    """Context line only: the same graph through torch's CPU kernels (oneDNN), same thread count."""
+    import torch
+    import torch.nn.functional as F
+
+    torch.set_num_threads(threads)
+    consts = {i: torch.from_numpy(nd["data"]) for i, nd in enumerate(builder.nodes) if nd["kind"] == "const"}
+
+    def run(inp):
+        vals = dict(consts)
+        vals[builder.inputs[0]] = inp
+        for nd in builder.nodes:
+            if nd["kind"] != "op":
+                continue
+            a = {fid: val for fid, _k, val in nd["attrs"][1]} if nd["attrs"] else {}
+            ins = [vals[i] if i is not None and i >= 0 else None for i in nd["inputs"]]
+            t = nd["type"]
+            if t == "Conv":
+                pads = a.get(1) or (0, 0, 0, 0)
+                y = F.conv2d(ins[0], ins[1], ins[2], stride=tuple(a.get(3) or (1, 1)), padding=(pads[0], pads[1]),
+                             groups=a.get(2, 1))
+            elif t == "Relu":
+                y = F.relu(ins[0])
+            elif t == "Add":
+                y = ins[0] + ins[1]
+            elif t == "MaxPool":
+                pads = a.get(2) or (0, 0, 0, 0)
+                y = F.max_pool2d(ins[0], tuple(a[0]), tuple(a.get(3) or (1, 1)), (pads[0], pads[1]))
+            elif t == "GlobalAveragePool":
+                y = ins[0].mean((2, 3), keepdim=True)
+            elif t == "Flatten":
+                y = ins[0].flatten(1)
+            elif t == "Gemm":
+                y = F.linear(ins[0], ins[1], ins[2])
+            else:
+                raise NotImplementedError(t)
+            vals[nd["outputs"][0]] = y
+        return vals[builder.outputs[0]]
+
+    xt = torch.from_numpy(x)
+    with torch.no_grad():
+        run(xt)
+        t0 = time.perf_counter()
+        run(xt)
+        return x.shape[0] / (time.perf_counter() - t0)
 
 
 def run_reference(args):
@@ -210,13 +323,16 @@ def run_reference(args):
     from rten_fork_b200 import synth
 
     builder = synth.resnet50(image=IMAGE, classes=CLASSES, seed=0)
-    ips, threads, sample, ms, batch = cpu_resnet(builder, seconds=150.0, steps=args.steps, warmup=max(1, min(args.warmup, 3)))
+    global FLOP_PER_IMAGE
+    FLOP_PER_IMAGE = graph_flops(builder, 1)
+    ips, threads, sample, ms, batch, more = cpu_resnet(builder, seconds=150.0, steps=args.steps,
+                                                       warmup=max(1, min(args.warmup, 3)), extras=True)
     line = {
         "impl": "reference", "metric": "resnet50_b32_images_per_sec", "value": ips, "unit": "images/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "ResNet-50 .rten, random-init weights, batch 32 3x224x224", "sample_batch": batch},
-        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": dict({"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample}, **more),
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -591,8 +707,11 @@ def run_ours(args):
     line.update(parity)
     line.update(extras)
     if world == 1 and not args.no_cpu_baseline:
-        ips, threads, sample, _ms, _b = cpu_resnet(builder, seconds=args.cpu_seconds)
-        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample}
+        global FLOP_PER_IMAGE
+        FLOP_PER_IMAGE = flops_step / args.batch
+        ips, threads, sample, _ms, _b, more = cpu_resnet(builder, seconds=args.cpu_seconds, extras=True)
+        line["cpu_baseline"] = dict({"value": ips, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
+                                    **more)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

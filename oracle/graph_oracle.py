@@ -79,23 +79,77 @@ def einsum(equation, ins):
     return cur
 
 
-def run_graph(builder, inputs, outputs=None):
-    """``inputs``: arrays in graph-input order.  Returns the graph outputs (or the requested node ids)."""
+class _Pool:
+    """TensorPool (src/tensor_pool.rs:103-199) for the timed CPU baseline: operator outputs come from buffers of dead
+    values (best fit by size) instead of fresh allocations, which on the CPU cost a page fault per 4 KiB."""
+
+    def __init__(self):
+        self.free = []
+
+    def alloc(self, shape):
+        n = int(np.prod(shape))
+        best = -1
+        for i, b in enumerate(self.free):
+            if b.size >= n and (best < 0 or b.size < self.free[best].size):
+                best = i
+        if best >= 0:
+            return self.free.pop(best)[:n].reshape(shape)
+        return np.empty(shape, dtype=np.float32)
+
+    def add(self, arr):
+        base = arr
+        while isinstance(base.base, np.ndarray):
+            base = base.base
+        if base.dtype == np.float32 and base.flags.c_contiguous and base.flags.owndata:
+            self.free.append(base.reshape(-1))
+
+
+def run_graph(builder, inputs, outputs=None, reuse=False, pool=None):
+    """``inputs``: arrays in graph-input order.  Returns the graph outputs (or the requested node ids).
+
+    ``reuse``: execute like Graph::run_plan does (src/graph.rs:883-1051): values are reference counted, Relu / Clip /
+    Add run in place on temporaries nobody else reads (src/graph.rs:897-931), dead temporaries go back to a pool that
+    later convolutions allocate from.  Results are identical; only the timed CPU baseline uses it (pass the same
+    ``pool`` to consecutive steps to keep its buffers)."""
     vals = {}
     for nid, x in zip(builder.inputs, inputs):
         vals[nid] = np.asarray(x)
     for i, nd in enumerate(builder.nodes):
         if nd["kind"] == "const":
             vals[i] = nd["data"]
+    ids = outputs if outputs is not None else builder.outputs
+    refs, temp = {}, set()
+    if reuse:
+        pool = pool if pool is not None else _Pool()
+        for nd in builder.nodes:
+            if nd["kind"] == "op":
+                for i in nd["inputs"]:
+                    if i is not None and i >= 0:
+                        refs[i] = refs.get(i, 0) + 1
+        for i in ids:
+            refs[i] = refs.get(i, 0) + 1
     for nd in builder.nodes:
         if nd["kind"] != "op":
             continue
         ins = [vals[i] if i is not None and i >= 0 else None for i in nd["inputs"]]
         a = _attrs(nd)
         t = nd["type"]
+        # in place: the first input is an owned temporary with no other reader
+        inplace = reuse and nd["inputs"] and nd["inputs"][0] in temp and refs.get(nd["inputs"][0], 0) == 1
         if t == "Conv":
             y = o.conv2d(ins[0], ins[1], ins[2] if len(ins) > 2 else None, padding=_padding(a, 0, 1),
-                         groups=a.get(2, 1), strides=tuple(a.get(3) or (1, 1)), dilations=tuple(a.get(4) or (1, 1)))
+                         groups=a.get(2, 1), strides=tuple(a.get(3) or (1, 1)), dilations=tuple(a.get(4) or (1, 1)),
+                         alloc=pool.alloc if reuse else None)
+        elif reuse and t in ("Relu", "Gelu", "Sigmoid", "Erf"):
+            y = o.unary(t.lower(), ins[0], in_place=inplace)
+        elif reuse and t == "Add" and ins[0].dtype == np.float32 and ins[1].dtype == np.float32:
+            # commutative: the executor may pick either operand as the in-place one (src/graph.rs:905-925)
+            if inplace:
+                y = o.binary("add", ins[0], ins[1], in_place=True)
+            elif nd["inputs"][1] in temp and refs.get(nd["inputs"][1], 0) == 1 and ins[1].shape == ins[0].shape:
+                y = o.binary("add", ins[1], ins[0], in_place=True)
+            else:
+                y = o.binary("add", ins[0], ins[1])
         elif t in ("Relu", "Gelu", "Sigmoid", "Erf"):
             y = o.unary(t.lower(), ins[0])
         elif t == "Sqrt":
@@ -177,6 +231,15 @@ def run_graph(builder, inputs, outputs=None):
             y = ins[0].copy()
         else:
             raise NotImplementedError(t)
-        vals[nd["outputs"][0]] = y
-    ids = outputs if outputs is not None else builder.outputs
+        out_id = nd["outputs"][0]
+        vals[out_id] = y
+        if reuse:
+            temp.add(out_id)
+            for i in nd["inputs"]:
+                if i is None or i < 0:
+                    continue
+                refs[i] -= 1
+                if refs[i] == 0 and i in temp and not any(np.shares_memory(vals[i], vals[k]) for k in (out_id,)):
+                    pool.add(vals[i])
+                    del vals[i]
     return [vals[i] for i in ids]

@@ -161,8 +161,10 @@ def conv_out_size(in_hw, k_hw, strides, padding, dilations=(1, 1)):
     return oh.value, ow.value, list(fixed)
 
 
-def conv2d(x, w, bias=None, padding=(0, 0, 0, 0), groups=1, strides=(1, 1), dilations=(1, 1), kernel=KERNEL_AUTO):
-    """conv() for NCHW / OIHW inputs, including the 1-D lift (src/ops/conv.rs:98-139)."""
+def conv2d(x, w, bias=None, padding=(0, 0, 0, 0), groups=1, strides=(1, 1), dilations=(1, 1), kernel=KERNEL_AUTO,
+           alloc=None):
+    """conv() for NCHW / OIHW inputs, including the 1-D lift (src/ops/conv.rs:98-139).  ``alloc(shape)`` supplies
+    the output buffer (the reference allocates it from its TensorPool, src/ops/conv.rs:212-220)."""
     x = np.ascontiguousarray(x, dtype=np.float32)
     w = np.ascontiguousarray(w, dtype=np.float32)
     if x.ndim == 3:
@@ -194,7 +196,7 @@ def conv2d(x, w, bias=None, padding=(0, 0, 0, 0), groups=1, strides=(1, 1), dila
     args = [C.c_int(kernel), _fp(x), _sz(x.shape), _fp(w), _sz(w.shape), _fp(b), C.c_size_t(0 if b is None else b.size),
             C.c_int(same), pads, C.c_size_t(groups), _sz(strides), _sz(dilations)]
     _check(lib().orc_conv2d(*args, None, oshape))
-    out = np.empty(tuple(oshape), dtype=np.float32)
+    out = alloc(tuple(oshape)) if alloc is not None else np.empty(tuple(oshape), dtype=np.float32)
     _check(lib().orc_conv2d(*args, _fp(out), oshape))
     return out
 
@@ -220,9 +222,10 @@ def im2col(image, k_hw, pads, strides, dilations=(1, 1), panel_width=16, pack=Tr
             "packed": out}
 
 
-def unary(op, x, lo=-np.inf, hi=np.inf):
+def unary(op, x, lo=-np.inf, hi=np.inf, in_place=False):
+    """``in_place``: write into ``x`` (UnaryFloatOp::run_in_place, src/ops/unary_elementwise.rs:39-63)."""
     x = np.ascontiguousarray(x, dtype=np.float32)
-    out = np.empty_like(x)
+    out = x if in_place and x.flags.writeable else np.empty_like(x)
     lo = np.float32(np.finfo(np.float32).min if lo is None or lo == -np.inf else lo)
     hi = np.float32(np.finfo(np.float32).max if hi is None or hi == np.inf else hi)
     lib().orc_unary(C.c_int(UNARY[op]), _fp(x), _fp(out), C.c_size_t(x.size), C.c_float(lo), C.c_float(hi))
@@ -233,7 +236,9 @@ def vm_scalar(name, x):
     return lib().orc_vm_scalar({"exp": 0, "sigmoid": 1, "erf": 2, "gelu": 3}[name], C.c_float(x))
 
 
-def binary(op, a, b):
+def binary(op, a, b, in_place=False):
+    """``in_place``: write into ``a`` when it already has the output shape (binary_op_in_place,
+    src/ops/binary_elementwise.rs:261-322)."""
     a = np.ascontiguousarray(a, dtype=np.float32)
     b = np.ascontiguousarray(b, dtype=np.float32)
     oshape = _sz([0] * 8)
@@ -242,7 +247,8 @@ def binary(op, a, b):
                           C.c_size_t(b.ndim), None, oshape, C.byref(ond))
     if rc != 0:
         raise OracleError(3, "Cannot broadcast inputs to same shape")
-    out = np.empty(tuple(oshape[:ond.value]), dtype=np.float32)
+    oshp = tuple(oshape[:ond.value])
+    out = a if in_place and a.shape == oshp and a.flags.writeable else np.empty(oshp, dtype=np.float32)
     lib().orc_binary(C.c_int(BINARY[op]), _fp(a), _sz(a.shape), C.c_size_t(a.ndim), _fp(b), _sz(b.shape),
                      C.c_size_t(b.ndim), _fp(out), oshape, C.byref(ond))
     return out

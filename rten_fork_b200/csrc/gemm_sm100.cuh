@@ -7,16 +7,29 @@
 // step of the reference (src/gemm/packing.rs:20-186) has no equivalent here: TMA writes 128B-swizzled K-major (or
 // MN-major) tiles straight into shared memory in the layout the tensor core's matrix descriptors read.
 //
-// Roles (one CTA per SM, 128 x BN output tile per step, BK = 32 floats = one 128-byte swizzle row):
-//   warps 0..E-1  epilogue       (tcgen05.ld -> alpha/beta/bias/activation -> global stores; warp w may only read
-//                                 TMEM lanes 32(w%4)..+31, so these are the first warps; E = 4, or 8 in MODE 1
-//                                 where warps 4-7 take the upper half of the tile's columns)
-//   warp E        TMA producer   (tiled 2-D loads, or im2col-mode loads over an NHWC activation tensor)
-//   warp E+1      MMA issuer     (one thread: tcgen05.mma.kind::tf32, accumulators in TMEM, double-buffered)
-//                                 + TMEM allocation
-//   warps E+2..   3xTF32 split   (MODE 1 only, 6 warps: write lo = x - tf32(x) planes next to the raw tiles)
+// Roles (one persistent CTA per SM, 128 x BN output tile per work unit, BK = 32 floats = one 128-byte swizzle row).
+// MODE 0 runs 10 warps (320 threads), the fp32-accurate modes 20 warps (640 threads, setmaxnreg 144 / 64):
+//   warps 0-7     epilogue        tcgen05.ld -> alpha / bias / residual / activation -> swizzled staging -> TMA store.
+//                                 Warp w may only touch TMEM lanes 32(w%4)..+31; warps 4-7 take the upper half of the
+//                                 tile's columns.  MODE 1/2: also fold every 4-k-block accumulation chunk into fp32
+//                                 running sums (round-to-nearest adds)
+//   warp 8        TMA producer    the whole warp walks the loop, an elected lane issues.  MODE 0: A and B tiles of a
+//                                 stage; MODE 1: raw A tiles (own 3-slot ring) and raw B tiles; MODE 2: raw A tiles
+//                                 only (tiled, im2col-mode, row-window or batched maps)
+//   warp 9        MMA issuer      whole warp walks the loop, an elected lane issues tcgen05.mma + commits; TMEM
+//                                 allocation; accumulators double-buffered in TMEM
+//   warps 10-17   operand split   (MODE 1/2) two warps per TMEM lane quarter on alternate k-blocks: one A row per
+//                                 thread -> hi plane + lo plane (MODE 1) / hi plane (round to nearest TF32) + bf16
+//                                 A' plane (MODE 2) into the stage's tensor-memory slot with tcgen05.st
+//   warps 18-19   MODE 1: write the lo plane of B next to the raw B tile in shared memory.
+//                 MODE 2: warp 18 is the B producer (ONE 3-D TMA load per k-block brings the packed B operand:
+//                 [B rounded to TF32][B']; it does not wait for the previous grid when B is a load-time constant);
+//                 warp 19 idles (ptxas sizes the register file for whole warpgroups)
 //
 // MODE 0 (TF32):   one MMA per k-step on the raw fp32 bits (the tensor core keeps the top 19 bits).
+// MODE 2 (TF32 + bf16 correction): hi = x rounded to nearest TF32 on BOTH operands (A by the split warps, B at pack
+//                  time), lo = x - hi (exact); acc += bf16[lo_A | A] . bf16[hi_B ; lo_B] (one kind::f16 MMA of depth 16
+//                  per 8 k) + hi_A * hi_B (one kind::tf32 MMA).  Per-product error <= 2^-18 + 2^-19.
 // MODE 1 (3xTF32): hi = raw (the tensor core truncates to the top 19 bits itself; verified on B200),
 //                  lo = rna_tf32(x - trunc19(x));
 //                  acc += lo_A*hi_B + hi_A*lo_B + hi_A*hi_B.
@@ -175,8 +188,7 @@ struct GemmCfg {
   // MODE 2: even, so that a stage is always served by the same one of the two split warps of a lane quarter
   static constexpr int kStages = kStagesRaw > 8 ? 8 : MODE != 0 ? (kStagesRaw & ~1) : kStagesRaw;
   static constexpr int kSmemBytes = kARingBytes + kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 512 /*barriers*/;
-  // MODE 1 runs 16 warps (128 registers each): 8 epilogue warps so that a thread carries only BN/2 running sums,
-  // and 6 split warps so that the operand split keeps up with the tensor core.
+  // Eight epilogue warps: a thread carries only BN/2 running sums in the fp32-accurate modes.
   static constexpr int kColsPerThread = BN / (kEpiWarps / 4);
   // MODE 2 has no B split.  One warp's operand-split loop (wait -> LDS -> split -> tcgen05.st -> wait::st -> arrive) takes
   // ~640 busy cycles per k-block against ~480 for the MMAs, so two warps per TMEM lane quarter take alternate blocks:
