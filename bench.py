@@ -449,6 +449,42 @@ def gemm_section(torch, R, ops, ctx, stream, modes, peak_tf32):
                 if n == 1024:
                     out["c1_1024"][name] = rec
             del a, b, c
+        # the memory-bound M <= 8 path (gemv kernels): bench_gemm's 1 x 4096 x 512 case in both B layouts
+        # (src/gemm.rs:1790-1838) and the ResNet classifier head at batch 1 / 8, against the measured HBM copy rate
+        hbm = load_peaks()["hbm_gbs"]
+        out["gemv"] = {"unit": "GB/s", "peak": hbm, "cases": {}}
+        ctx.set_math(list(modes.values())[0])
+        for name, (m, n, k, tb) in {"1x4096x512": (1, 4096, 512, False), "1x4096x512_transposed_b": (1, 4096, 512, True),
+                                    "fc_1x1000x2048": (1, 1000, 2048, True), "fc_8x1000x2048": (8, 1000, 2048, True),
+                                    "1x16384x4096": (1, 16384, 4096, False)}.items():
+            a = torch.rand((m, k), device=dev, generator=gen)
+            b = torch.rand((n, k), device=dev, generator=gen).t() if tb else torch.rand((k, n), device=dev, generator=gen)
+            c = torch.empty((m, n), device=dev)
+            for _ in range(3):
+                ops.matmul(a, b, out=c, ctx=ctx)
+            try:
+                g = torch.cuda.CUDAGraph()
+                iters = 200
+                with torch.cuda.graph(g, stream=stream):
+                    for _ in range(iters):
+                        ops.matmul(a, b, out=c, ctx=ctx)
+                g.replay()
+                stream.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                g.replay()
+                e1.record(stream)
+                stream.synchronize()
+                us = e0.elapsed_time(e1) / iters * 1e3
+                by = 4.0 * (k * n + m * k + m * n)
+                out["gemv"]["cases"][name] = {"us": round(us, 2), "gbs": round(by / us / 1e3, 1),
+                                              "frac": round(by / us / 1e3 / hbm, 3), "kernel": ctx.last_kernel,
+                                              "note": "200 calls replayed from one CUDA graph; operands L2-resident "
+                                                      "when they fit (8 MB), so small cases can exceed the HBM rate"}
+                del g
+            except Exception as exc:
+                out["gemv"]["cases"][name] = {"error": str(exc)[:120]}
+                torch.cuda.synchronize()
     return out
 
 

@@ -412,6 +412,12 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
   const int64_t M = a.rows, K = a.cols, N = b.cols;
   if (M == 0 || N == 0) return RTG_OK;
   if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "GEMM dims exceed i32");
+  // --- very few rows: memory-bound, one pass over B on the CUDA cores (src/gemm.rs:651-704 gemv)
+  static const bool gemv_on = []() {
+    const char* e = getenv("RTG_GEMV");  // developer switch: 0 keeps M <= 8 on the tensor path
+    return !e || atoi(e) != 0;
+  }();
+  if (gemv_on && K > 0 && gemv_supported(a, b, dmap, ep)) return gemv_device(ctx, a, b, D, dmap, ep);
 
   // --- legalise A: K-major rows with 16-byte aligned base and pitch
   Scratch a_tmp, b_tmp;

@@ -47,6 +47,11 @@ rtg_status gemm_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
 rtg_status make_b_pack(Context* ctx, MatView b, float* out, int64_t plane);
 inline int64_t b_pack_ld(int64_t k) { return (k + 31) / 32 * 32; }
 
+// M <= 8 (the reference's gemv case, src/gemm.rs:651-704, and batch-1..8 classifier heads): one pass over B at HBM
+// speed on the CUDA cores (gemv.cu).  gemm_device takes this path when gemv_supported says so.
+bool gemv_supported(const MatView& a, const MatView& b, const OutMap& dmap, const Epilogue& ep);
+rtg_status gemv_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap, const Epilogue& ep);
+
 // Batched product in ONE launch: batch index z = z1 * n0 + z0, entry z of A at a.p + z0*a.bs0 + z1*a.bs1 (a stride of
 // 0 broadcasts the operand along that batch dimension), D contiguous [n1*n0][M][N].  The operands must be addressable
 // by TMA in place (gemm_batched_supported); callers fall back to one gemm_device per entry otherwise.
