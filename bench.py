@@ -681,6 +681,32 @@ def run_ours(args):
             extras["small_batch"] = small
         ctx.set_math(math)
 
+    # strong scaling of ONE call: a batch of 32 host images through rtg_sharded_model_run over all N GPUs of this box
+    # (rank 0's process drives them: a context, worker thread and weight replica per GPU; the other ranks wait)
+    if not args.no_extras and world > 1:
+        barrier()
+        if rank == 0:
+            try:
+                sm = R.ShardedModel(builder.build(), list(range(world)), math=math)
+                xs_h = x_host.numpy()
+                os_h = np.empty((args.batch, CLASSES), np.float32)
+                for _ in range(4):
+                    sm.run([xs_h], [os_h])
+                t0 = time.perf_counter()
+                reps = max(args.steps, 10)
+                for _ in range(reps):
+                    sm.run([xs_h], [os_h])
+                dt = (time.perf_counter() - t0) / reps
+                extras["strong"] = {"gpus": world, "batch": args.batch, "ms_per_call": dt * 1e3,
+                                    "images_per_s": args.batch / dt,
+                                    "matches_one_gpu": bool(np.allclose(os_h, out_dev.cpu().numpy(), rtol=1e-3, atol=1e-2)),
+                                    "api": "rtg_sharded_model_run: pageable host input -> dim-0 chunks on N GPUs of one "
+                                           "process -> host output; wall clock, copies inside"}
+                sm.close()
+            except Exception as exc:
+                extras["strong"] = {"error": str(exc)[:200]}
+        barrier()
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

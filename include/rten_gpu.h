@@ -281,6 +281,23 @@ rtg_status rtg_model_output_id(const rtg_model* model, int32_t i, int32_t* id);
 rtg_status rtg_model_node_kind(const rtg_model* model, int32_t id, int32_t* kind);
 rtg_status rtg_model_source_op(const rtg_model* model, int32_t value_id, const char** op_name, const char** node_name);
 
+/* Batch-sharded Model::run inside one process (the reference's advice for scaling is the same:
+ * "use Rayon to execute the model on separate chunks in parallel", docs/performance.md:137-139).  The model is loaded
+ * once per device of `devices` (weights replicated; a device may be named twice: two contexts on one GPU); a run splits
+ * dim 0 of every (host, contiguous) input into contiguous chunks — the first batch % g shards take one item more —, runs
+ * them concurrently (one host thread, stream and device pool per shard) and writes every shard's rows into the
+ * caller's host output buffers ([batch, ...] contiguous).  There is no collective.  Loading fails with
+ * RTG_ERR_UNSUPPORTED_VALUE when an operator of the graph is not known to keep batch items independent (a Reshape that
+ * folds the batch, a Transpose that moves it, reductions over dim 0, activation x activation MatMul ...); a failed
+ * shard fails the whole run. */
+typedef struct rtg_sharded_model rtg_sharded_model;
+rtg_status rtg_sharded_model_load(const int32_t* devices, int32_t n_devices, int32_t math, const void* data, size_t len,
+                                  int32_t optimize, rtg_sharded_model** out);
+rtg_status rtg_sharded_model_num_shards(const rtg_sharded_model* model, int32_t* n);
+rtg_status rtg_sharded_model_run(rtg_sharded_model* model, const rtg_tensor* inputs, int32_t n_inputs,
+                                 rtg_tensor* outputs, int32_t n_outputs);
+rtg_status rtg_sharded_model_free(rtg_sharded_model* model);
+
 /* Asynchronous Model::run over HOST buffers (no reference counterpart: the reference runs on the caller's thread;
  * this is what a serving loop binds instead of rtg_model_run to keep the PCIe copies off the critical path).
  * The inputs are uploaded on a second stream into one of two staging slots, so the upload of submit i + 1 overlaps

@@ -7,5 +7,5 @@ from ._native import MATH_3XTF32, MATH_TF32, MATH_TF32_BF16X2, RtgError  # noqa:
 from .context import Context, default_context  # noqa: F401
 from .gemm import GemmExecutor, gemm  # noqa: F401
 from . import ops, synth  # noqa: F401
-from .model import Model  # noqa: F401
+from .model import Model, ShardedModel  # noqa: F401
 from .rten_builder import ModelBuilder  # noqa: F401

@@ -225,3 +225,37 @@ class Model:
     def run_one(self, x, out=None):
         """Model::run_one (src/model.rs:620-637): single input, single output."""
         return self.run([x], None if out is None else [out])[0]
+
+
+class ShardedModel:
+    """``rtg_sharded_model_*``: one ``run`` over a batch, split along dim 0 over several GPUs of this process (one
+    context + worker thread + weight replica per entry of ``devices``; a device may appear twice).  No collective; the
+    graph must be separable by batch item, which is checked at load (``RtgError`` UnsupportedValue otherwise)."""
+
+    def __init__(self, data: bytes, devices, math: int = N.MATH_3XTF32, optimize: bool = True):
+        devs = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+        h = C.c_void_p()
+        buf = (C.c_char * len(data)).from_buffer_copy(data)
+        N.check(N.lib().rtg_sharded_model_load(devs, C.c_int32(len(devices)), C.c_int32(math), buf, C.c_size_t(len(data)),
+                                               C.c_int32(bool(optimize)), C.byref(h)))
+        self._h, self.devices = h, list(devices)
+
+    def run(self, inputs, out):
+        """``inputs``: contiguous host arrays [batch, ...]; ``out``: one contiguous host buffer [batch, ...] per graph
+        output (numpy, or pinned torch CPU tensors).  Returns ``out``."""
+        keep = [np.ascontiguousarray(x) if isinstance(x, np.ndarray) else x for x in inputs]
+        descs = (N.Tensor * len(keep))(*[as_tensor(x) for x in keep])
+        odescs = (N.Tensor * len(out))(*[as_tensor(o) for o in out])
+        N.check(N.lib().rtg_sharded_model_run(self._h, descs, C.c_int32(len(keep)), odescs, C.c_int32(len(out))))
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().rtg_sharded_model_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
