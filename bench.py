@@ -685,6 +685,10 @@ def run_ours(args):
     # (rank 0's process drives them: a context, worker thread and weight replica per GPU; the other ranks wait)
     if not args.no_extras and world > 1:
         barrier()
+        # the other ranks must wait on the HOST: an NCCL barrier would spin a kernel on their GPUs, which are shards here
+        store = dist.distributed_c10d._get_default_store()
+        if rank != 0:
+            store.wait(["strong_done"])
         if rank == 0:
             try:
                 sm = R.ShardedModel(builder.build(), list(range(world)), math=math)
@@ -699,12 +703,14 @@ def run_ours(args):
                 dt = (time.perf_counter() - t0) / reps
                 extras["strong"] = {"gpus": world, "batch": args.batch, "ms_per_call": dt * 1e3,
                                     "images_per_s": args.batch / dt,
-                                    "matches_one_gpu": bool(np.allclose(os_h, out_dev.cpu().numpy(), rtol=1e-3, atol=1e-2)),
+                                    "matches_one_gpu": bool(np.abs(os_h - out_dev.cpu().numpy()).max()
+                                                            <= 2e-4 * np.abs(os_h).max()),
                                     "api": "rtg_sharded_model_run: pageable host input -> dim-0 chunks on N GPUs of one "
                                            "process -> host output; wall clock, copies inside"}
                 sm.close()
             except Exception as exc:
                 extras["strong"] = {"error": str(exc)[:200]}
+            store.set("strong_done", "1")
         barrier()
 
     if rank != 0:
