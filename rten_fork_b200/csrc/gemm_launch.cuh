@@ -107,7 +107,7 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     static const char* slots[4][4] = {{"wait_empty", "issue", "-", "-"},
                                       {"wait_tempty", "wait_full", "issue", "-"},
                                       {"wait_tfull", "wait_resid", "wait_stread", "wait_stdone"},
-                                      {"wait_afull", "wait_empty", "wait_tmem_st", "lds_and_split"}};
+                                      {"wait_afull", "wait_empty", "st_wait_and_arrive", "lds_and_split"}};
     fprintf(stderr, "[prof] BN=%d mode=%d akind=%d grid=%d M=%d N=%d kb=%d:", BN, MODE, A_KIND, grid, args.M, args.N,
             args.num_kb);
     for (int r = 0; r < 4; ++r) {

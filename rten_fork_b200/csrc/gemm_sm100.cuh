@@ -107,6 +107,14 @@ struct GemmArgs {
     stmt;                              \
     prof_acc_[slot] += clock64() - t_; \
   } while (0)
+// contiguous timeline: every PROF_LINE(slot) charges the time since the previous stamp to `slot`
+#define PROF_LINE_DECL long long tl_ = clock64()
+#define PROF_LINE(slot)               \
+  do {                                \
+    const long long u_ = clock64();   \
+    prof_acc_[slot] += u_ - tl_;      \
+    tl_ = u_;                         \
+  } while (0)
 #define PROF_MARK(role, slot)                                                                                     \
   do {                                                                                                            \
     if (args.prof) {                                                                                              \
@@ -130,6 +138,8 @@ struct GemmArgs {
 #else
 #define PROF_DECL
 #define PROF_WAIT(slot, stmt) stmt
+#define PROF_LINE_DECL
+#define PROF_LINE(slot)
 #define PROF_DUMP(role)
 #define PROF_MARK(role, slot)
 #define PROF_MARK_LAST(role, slot)
@@ -863,16 +873,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int ia = first % kAStages, s = first % kStages;
       uint32_t pa = 0, ph = 0;
       static_assert(MODE == 0 || kStages % 2 == 0, "a pipeline stage must always be served by the same one of the two warps");
+      PROF_LINE_DECL;
       for (int it = first; it < total; it += 2) {
         // The A ring has 3 slots, so this warp only sees every other phase of a slot's barriers and a parity wait
         // alone could be satisfied by the phase before the one it wants.  The slot's previous round (served by the
         // other warp of the quarter) has to be over first: its `aempty` phase cannot run ahead of this warp.
-        PROF_WAIT(0, ptx::mbar_wait_parked(aempty_bar(ia), pa ^ 1u));
-        PROF_WAIT(0, ptx::mbar_wait_parked(afull_bar(ia), pa));
+        ptx::mbar_wait_parked(aempty_bar(ia), pa ^ 1u);
+        ptx::mbar_wait_parked(afull_bar(ia), pa);
+        PROF_LINE(0);
         const uint32_t src = smem_base + ia * kABytes + row * 128;
         // the TMEM slot of this stage is free once the MMAs of its previous use have completed
-        PROF_WAIT(1, ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u));
+        ptx::mbar_wait_parked(empty_bar(s), ph ^ 1u);
         ptx::tc_fence_after();
+        PROF_LINE(1);
         const uint32_t dst = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 2 * BN + s * Cfg::kTmemAStageCols;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -906,13 +919,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           ptx::tmem_st_32x16(dst + kBK + 16 * h, w);
         }
+        PROF_LINE(3);
         // the raw tile has been read: hand its slot back to the TMA producer
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(aempty_bar(ia));
-        PROF_WAIT(2, ptx::tmem_st_wait());
+        ptx::tmem_st_wait();
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(xf_bar(s));
+        PROF_LINE(2);
         ia += 2;
         if (ia >= kAStages) {
           ia -= kAStages;

@@ -6,6 +6,7 @@
 
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <vector>
 
 using namespace rtg;
@@ -89,10 +90,10 @@ __global__ void __launch_bounds__(128, 1) probe1(int mode, int reps, int per_rou
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) ptx::sts_f32(base + i * 4, 1.0f);
-  constexpr int S = 4;
+  const int S = (mode == 6 && nwait == 0) ? 8 : 4;
+  constexpr int SMAX = 8;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2 * S + 2; ++s) ptx::mbar_init(bars + 8 * s, 1);
-    for (int s = 0; s < S; ++s) ptx::mbar_init(bars + 8 * (2 * S + 2 + s), 1);
+    for (int s = 0; s < 3 * SMAX + 2; ++s) ptx::mbar_init(bars + 8 * s, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 0) {
@@ -109,9 +110,9 @@ __global__ void __launch_bounds__(128, 1) probe1(int mode, int reps, int per_rou
   const uint64_t bdesc = ptx::make_smem_desc(base + 32 * 1024, 16, 1024);
   const uint32_t done = bars;  // barrier 0
   auto full = [&](int s) { return bars + 8 * (1 + s); };
-  auto empty = [&](int s) { return bars + 8 * (1 + S + s); };
-  auto full2 = [&](int s) { return bars + 8 * (2 * S + 2 + s); };
-  if (mode == 2 && warp == 1) {  // producer skeleton
+  auto empty = [&](int s) { return bars + 8 * (1 + SMAX + s); };
+  auto full2 = [&](int s) { return bars + 8 * (2 * SMAX + 2 + s); };
+  if ((mode == 2 || mode == 3 || mode == 4 || mode == 6) && warp == 1) {  // producer skeleton
     int s = 0;
     uint32_t ph = 0;
     const int rounds = reps / per_round;
@@ -152,6 +153,107 @@ __global__ void __launch_bounds__(128, 1) probe1(int mode, int reps, int per_rou
         ptx::mbar_wait(done, 0);
         out[0] = clock64() - t0;
       }
+    } else if (mode == 3) {  // skeleton with per-phase clocks: wait / fence / issue / commit
+      int s = 0;
+      uint32_t ph = 0;
+      const int rounds = reps / per_round;
+      long long tw = 0, tf = 0, ti = 0, tc = 0;
+      __syncwarp();
+      const long long t0 = clock64();
+      long long t = t0;
+      for (int r = 0; r < rounds; ++r) {
+        ptx::mbar_wait(full(s), ph);
+        if (nwait > 1) ptx::mbar_wait(full2(s), ph);
+        long long u = clock64(); tw += u - t; t = u;
+        ptx::tc_fence_after();
+        u = clock64(); tf += u - t; t = u;
+        if (ptx::elect_one()) {
+          _Pragma("unroll 8") for (int i = 0; i < per_round; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
+        }
+        u = clock64(); ti += u - t; t = u;
+        if (ptx::elect_one()) ptx::mma_commit(empty(s));
+        __syncwarp();
+        u = clock64(); tc += u - t; t = u;
+        if (++s == S) s = 0, ph ^= 1u;
+      }
+      if (ptx::elect_one()) ptx::mma_commit(done);
+      __syncwarp();
+      ptx::mbar_wait(done, 0);
+      if (lane == 0) out[0] = clock64() - t0, out[1] = tw, out[2] = tf, out[3] = ti, out[4] = tc;
+    } else if (mode == 6) {  // variants: nwait 0: 8 stages; 1: a shared-memory load between commit and wait; 2: plain arrive, no commit
+      int s = 0;
+      uint32_t ph = 0;
+      const int rounds = reps / per_round;
+      long long tw = 0, tf = 0, ti = 0, tc = 0, tl = 0;
+      float sink = 0.f;
+      __syncwarp();
+      const long long t0 = clock64();
+      long long t = t0;
+      for (int r = 0; r < rounds; ++r) {
+        long long u;
+        if (nwait == 1) {
+          sink += ptx::lds_f32(base + lane * 4);
+          if (sink == 12345.f) printf("x");
+          u = clock64(); tl += u - t; t = u;
+        }
+        ptx::mbar_wait(full(s), ph);
+        u = clock64(); tw += u - t; t = u;
+        ptx::tc_fence_after();
+        u = clock64(); tf += u - t; t = u;
+        if (ptx::elect_one()) {
+          _Pragma("unroll 8") for (int i = 0; i < per_round; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
+        }
+        u = clock64(); ti += u - t; t = u;
+        if (nwait == 2) {
+          if (ptx::elect_one()) ptx::mbar_arrive(empty(s));
+        } else {
+          if (ptx::elect_one()) ptx::mma_commit(empty(s));
+        }
+        __syncwarp();
+        u = clock64(); tc += u - t; t = u;
+        if (++s == S) s = 0, ph ^= 1u;
+      }
+      if (ptx::elect_one()) ptx::mma_commit(done);
+      __syncwarp();
+      ptx::mbar_wait(done, 0);
+      if (lane == 0) out[0] = clock64() - t0, out[1] = tw, out[2] = tf, out[3] = ti, out[4] = tc, out[5] = tl;
+    } else if (mode == 4) {  // one thread runs the whole loop (no elect / syncwarp per round)
+      const int rounds = reps / per_round;
+      __syncwarp();
+      const long long t0 = clock64();
+      if (lane == 0) {
+        int s = 0;
+        uint32_t ph = 0;
+        for (int r = 0; r < rounds; ++r) {
+          ptx::mbar_wait(full(s), ph);
+          if (nwait > 1) ptx::mbar_wait(full2(s), ph);
+          ptx::tc_fence_after();
+          _Pragma("unroll 8") for (int i = 0; i < per_round; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
+          ptx::mma_commit(empty(s));
+          if (++s == S) s = 0, ph ^= 1u;
+        }
+        ptx::mma_commit(done);
+      }
+      __syncwarp();
+      ptx::mbar_wait(done, 0);
+      if (lane == 0) out[0] = clock64() - t0;
+    } else if (mode == 5) {  // no producer round trip: issue + commit only (what the commits cost by themselves)
+      const int rounds = reps / per_round;
+      __syncwarp();
+      const long long t0 = clock64();
+      int s = 0;
+      for (int r = 0; r < rounds; ++r) {
+        if (ptx::elect_one()) {
+          _Pragma("unroll 8") for (int i = 0; i < per_round; ++i) issue1<form>(i, d, a_t, adesc, bdesc, id_tf32, id_bf16, N);
+          if (nwait > 0) ptx::mma_commit(full2(s));  // nobody waits on it
+        }
+        __syncwarp();
+        if (++s == S) s = 0;
+      }
+      if (ptx::elect_one()) ptx::mma_commit(done);
+      __syncwarp();
+      ptx::mbar_wait(done, 0);
+      if (lane == 0) out[0] = clock64() - t0;
     } else {
       int s = 0;
       uint32_t ph = 0;
@@ -261,10 +363,90 @@ static void run1f(long long* dout, int mode, int reps, int per_round, int nwait)
     printf("N=%3d %-20s issue clocks:", N, kFormName[form]);
     for (int i = 0; i < 24; ++i) printf(" %lld", h[1 + i]);
     printf(" ... total %lld\n", h[0]);
+  } else if (mode == 6) {
+    const double r = reps / per_round;
+    printf("N=%3d %-20s variant %d (%s): %2d MMAs / round: %7.1f cycles / round = lds %.1f + wait %.1f + fence %.1f + issue %.1f + commit %.1f\n",
+           N, kFormName[form], nwait, nwait == 0 ? "8 stages" : nwait == 1 ? "lds before wait" : "plain arrive, no commit", per_round,
+           h[0] / r, h[5] / r, h[1] / r, h[2] / r, h[3] / r, h[4] / r);
+  } else if (mode == 3) {
+    const double r = reps / per_round;
+    printf("N=%3d %-20s skeleton phases: %2d MMAs / round, %d wait(s): %7.1f cycles / round = wait %.1f + fence %.1f + issue %.1f + commit %.1f\n",
+           N, kFormName[form], per_round, nwait, h[0] / r, h[1] / r, h[2] / r, h[3] / r, h[4] / r);
   } else {
-    printf("N=%3d %-20s pipeline skeleton: %2d MMAs / round, %d wait(s): %7.1f cycles / round (%5.1f / MMA)\n", N,
-           kFormName[form], per_round, nwait, double(h[0]) / (reps / per_round), double(h[0]) / reps);
+    printf("N=%3d %-20s %s: %2d MMAs / round, %d wait(s): %7.1f cycles / round (%5.1f / MMA)\n", N, kFormName[form],
+           mode == 4 ? "one-thread skeleton" : mode == 5 ? "issue + commit only" : "pipeline skeleton", per_round, nwait,
+           double(h[0]) / (reps / per_round), double(h[0]) / reps);
   }
+}
+
+
+// TMEM store throughput: the warps in `mask` each issue `reps` tcgen05.st.32x32b.x16 (2 KB each) into their lane quarter,
+// optionally while one thread keeps the tensor pipe busy with TS-form MMAs (mma != 0).
+__global__ void __launch_bounds__(320, 1) probe_st(int mask, int reps, int mma, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + 160 * 1024;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) ptx::sts_f32(base + i * 4, 1.0f);
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bars, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) {
+    ptx::tmem_alloc(ptx::smem_u32(&tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tm = tmem_slot;
+  if (warp < 8 && ((mask >> warp) & 1)) {
+    uint32_t r[16];
+    for (int j = 0; j < 16; ++j) r[j] = lane * 16 + j;
+    const uint32_t dst = tm + (static_cast<uint32_t>((warp & 3) * 32) << 16) + 256 + (warp >> 2) * 64;
+    long long t0 = 0, t1 = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      __syncwarp();
+      t0 = clock64();
+#pragma unroll 4
+      for (int i = 0; i < reps; ++i) ptx::tmem_st_32x16(dst + (i & 3) * 16, r);
+      t1 = clock64();
+      ptx::tmem_st_wait();
+    }
+    const long long t2 = clock64();
+    if (lane == 0) out[warp * 2] = t1 - t0, out[warp * 2 + 1] = t2 - t0;
+  } else if (warp == 8 && mma) {
+    const uint32_t id_tf32 = ptx::make_idesc_tf32(128, 128, 0, 0);
+    const uint64_t bdesc = ptx::make_smem_desc(base + 32 * 1024, 16, 1024);
+    if (ptx::elect_one()) {
+      for (int i = 0; i < mma; ++i)
+        ptx::mma_tf32_ts_w(tm, tm + 448 + (i & 3) * 8, static_cast<uint32_t>(bdesc) + (i & 3) * 2, static_cast<uint32_t>(bdesc >> 32), id_tf32, 1);
+      ptx::mma_commit(bars);
+    }
+    __syncwarp();
+    ptx::mbar_wait(bars, 0);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tm, 512);
+  }
+}
+
+static void run_st(long long* dout, int mask, int reps, int mma) {
+  CK(cudaFuncSetAttribute(probe_st, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  CK(cudaMemset(dout, 0, 80 * 8));
+  probe_st<<<1, 320, kSmem>>>(mask, reps, mma, dout);
+  CK(cudaDeviceSynchronize());
+  long long h[16];
+  CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
+  printf("tcgen05.st.32x32b.x16 warps 0x%02x%s:", mask, mma ? " + MMA chain" : "");
+  for (int w = 0; w < 8; ++w)
+    if ((mask >> w) & 1) printf("  w%d %.1f issue / %.1f done", w, double(h[2 * w]) / reps, double(h[2 * w + 1]) / reps);
+  printf("  cycles per store\n");
 }
 
 template <int N>
@@ -298,10 +480,38 @@ static void run2(long long* dout, int form, int reps) {
   printf("2-CTA M=256 N=%3d %-20s chain of %d: %6.1f cycles / MMA\n", N, kFormName[form], reps, double(h[0]) / reps);
 }
 
-int main() {
+int main(int argc, char** argv) {
   long long* dout;
   CK(cudaMalloc(&dout, 80 * 8));
   const int reps = 512;
+  if (argc > 1 && !strcmp(argv[1], "st")) {
+    for (int mma : {0, 4096})
+      for (int mask : {0x01, 0x11, 0x03, 0x0f, 0xff}) run_st(dout, mask, 256, mma);
+    printf("probe done\n");
+    return 0;
+  }
+  if (argc > 1 && !strcmp(argv[1], "round")) {  // where a round's fixed cost goes
+    for (int per_round : {8, 16}) {
+      for (int nwait : {1, 2}) {
+        run1<64>(dout, ALT_TS, 2, 1024, per_round, nwait);
+        run1<64>(dout, ALT_TS, 3, 1024, per_round, nwait);
+        run1<64>(dout, ALT_TS, 4, 1024, per_round, nwait);
+        run1<128>(dout, ALT_TS, 2, 1024, per_round, nwait);
+        run1<128>(dout, ALT_TS, 3, 1024, per_round, nwait);
+        run1<128>(dout, ALT_TS, 4, 1024, per_round, nwait);
+      }
+      run1<64>(dout, ALT_TS, 5, 1024, per_round, 0);
+      run1<64>(dout, ALT_TS, 5, 1024, per_round, 1);
+      run1<128>(dout, ALT_TS, 5, 1024, per_round, 0);
+      run1<128>(dout, ALT_TS, 5, 1024, per_round, 1);
+    }
+    for (int v : {0, 1, 2}) {
+      run1<64>(dout, ALT_TS, 6, 1024, 8, v);
+      run1<128>(dout, ALT_TS, 6, 1024, 8, v);
+    }
+    printf("probe done\n");
+    return 0;
+  }
   for (int form : {SS_TF32, TS_TF32, TS_F16, ALT_TS, GRP_TS, SS_F16}) {
     run1<64>(dout, form, 0, reps, 0, 0);
     run1<128>(dout, form, 0, reps, 0, 0);
@@ -320,6 +530,9 @@ int main() {
   for (int form : {SS_TF32, ALT_TS, GRP_TS})
     for (int per_round : {4, 8, 16, 32})
       for (int nwait : {1, 2}) run1<128>(dout, form, 2, 1024, per_round, nwait);
+  for (int form : {TS_TF32, ALT_TS}) run1<64>(dout, form, 1, 64, 0, 0);
+  for (int per_round : {4, 8, 16, 32})
+    for (int nwait : {1, 2}) run1<64>(dout, ALT_TS, 2, 1024, per_round, nwait);
   run1<256>(dout, SS_TF32, 2, 1024, 4, 1);
   run1<256>(dout, SS_TF32, 2, 1024, 8, 1);
   for (int form : {SS_TF32, TS_TF32, TS_F16, ALT_TS}) {
