@@ -3,6 +3,7 @@
 // the tcgen05 kernel with TMA im2col loads over NHWC activations (pixels are GEMM rows, output channels GEMM columns,
 // batch folded into M); depthwise runs as a direct CUDA-core kernel.
 #include "conv_kernels.cuh"
+#include "depthwise_tma.cuh"
 #include "ops.h"
 
 namespace rtg {
@@ -209,6 +210,79 @@ rtg_status from_nhwc(Context* ctx, const float* src, int c, int cp, const rtg_te
 
 }  // namespace
 
+// Tile shape of the TMA-staged depthwise kernel: 128 threads = (TW / 4 strips) x (CB / 4 channel vectors).  Picks the
+// shape that wastes the fewest threads on channels beyond C and columns beyond OW, then cuts the rows into bands so
+// that there are several CTAs per SM.
+static rtg_status launch_depthwise3x3_tma(Context* ctx, float* out, const float* x, const float* wt, const float* bias,
+                                          const DwGeom& g) {
+  const int stride = g.stride_h;
+  int best_tw = 0;
+  double best_waste = 1e30;
+  for (int tw = 64; tw >= 8; tw >>= 1) {
+    const int cb = (kDwThreads / (tw / kDwTX)) * 4;
+    const double waste = (static_cast<double>(div_ceil(g.c, cb)) * cb / g.c) * (static_cast<double>(div_ceil(g.ow, tw)) * tw / g.ow);
+    if (waste < best_waste - 1e-9) best_waste = waste, best_tw = tw;
+  }
+  DwTile t = {};
+  t.tw = best_tw;
+  t.cvs = kDwThreads / (t.tw / kDwTX);
+  const int cb = t.cvs * 4;
+  t.iwb = (t.tw - 1) * stride + 3;
+  t.box_bytes = t.iwb * cb * 4;
+  t.row_bytes = static_cast<int>(div_ceil(t.box_bytes, 128) * 128);
+  t.ch_blocks = static_cast<int>(div_ceil(g.c, cb));
+  t.bands = static_cast<int>(div_ceil(g.ow, t.tw));
+  const int64_t columns = static_cast<int64_t>(g.n) * t.ch_blocks * t.bands;
+  // row bands: ~8 jobs per SM, at least 4 output rows each (a band re-reads 2 / STRIDE halo rows, mostly from L2)
+  const int64_t want = std::max<int64_t>(1, div_ceil(static_cast<int64_t>(ctx->num_sms) * 8, columns));
+  t.rows_per_job = static_cast<int>(std::max<int64_t>(std::min<int64_t>(4, g.oh), div_ceil(g.oh, want)));
+  t.row_bands = static_cast<int>(div_ceil(g.oh, t.rows_per_job));
+  const int64_t jobs = columns * t.row_bands;
+  if (jobs > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "depthwise convolution: too many tiles");
+
+  CUtensorMap map;
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(g.c), static_cast<cuuint64_t>(g.w), static_cast<cuuint64_t>(g.h),
+                        static_cast<cuuint64_t>(g.n)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(g.cp_in) * 4, static_cast<cuuint64_t>(g.w) * g.cp_in * 4,
+                           static_cast<cuuint64_t>(g.h) * g.w * g.cp_in * 4};
+  cuuint32_t box[4] = {static_cast<cuuint32_t>(cb), static_cast<cuuint32_t>(t.iwb), 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = ctx->encode_tiled(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(x), dims, strides, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (depthwise input) failed (%d): dims [%d,%d,%d,%d] box [%d,%d]",
+                      (int)r, g.c, g.w, g.h, g.n, cb, t.iwb);
+  const int smem = kDwRing * t.row_bytes;
+  const int ac = g.act == ACT_NONE ? 0 : g.act == ACT_RELU ? 1 : g.act == ACT_CLIP ? 2 : 3;
+  using Kern = void (*)(const CUtensorMap, float*, const float*, const float*, const DwGeom, const DwTile);
+#define RTG_DW_ROW(S, A) {depthwise3x3_tma_kernel<S, A, 8>, depthwise3x3_tma_kernel<S, A, 16>, depthwise3x3_tma_kernel<S, A, 32>, depthwise3x3_tma_kernel<S, A, 64>}
+  static const Kern kerns[2][4][4] = {{RTG_DW_ROW(1, 0), RTG_DW_ROW(1, 1), RTG_DW_ROW(1, 2), RTG_DW_ROW(1, 3)},
+                                      {RTG_DW_ROW(2, 0), RTG_DW_ROW(2, 1), RTG_DW_ROW(2, 2), RTG_DW_ROW(2, 3)}};
+#undef RTG_DW_ROW
+  const int ci = t.cvs == 8 ? 0 : t.cvs == 16 ? 1 : t.cvs == 32 ? 2 : 3;
+  Kern kern = kerns[stride - 1][ac][ci];
+  static bool configured[2][4][4][16] = {};
+  if (!configured[stride - 1][ac][ci][ctx->device & 15]) {
+    RTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured[stride - 1][ac][ci][ctx->device & 15] = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(jobs));
+  cfg.blockDim = dim3(kDwThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  RTG_CUDA(cudaLaunchKernelEx(&cfg, kern, map, out, wt, bias, g, t));
+  ctx->launches++;
+  RTG_CUDA(cudaGetLastError());
+  return RTG_OK;
+}
+
 rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in, const ConvWeights& w,
                         const float* bias, const rtg_tensor* residual_in, int act, float act_lo, float act_hi,
                         const rtg_tensor& out_in) {
@@ -299,6 +373,16 @@ rtg_status conv_forward(Context* ctx, const ConvPlan& p, const rtg_tensor& x_in,
     const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(total, 256), static_cast<int64_t>(ctx->num_sms) * 32));
     const bool k3 = vec4 && p.kh == 3 && p.kw == 3 && p.dil_h == 1 && p.dil_w == 1 && p.stride_h == p.stride_w &&
                     (p.stride_h == 1 || p.stride_h == 2) && cp_in % 4 == 0;
+    static const bool dw_tma = []() {
+      const char* e = getenv("RTG_DW_TMA");  // developer switch: 0 selects the register-window kernel
+      return !e || atoi(e) != 0;
+    }();
+    if (k3 && dw_tma && W + 2 < (1 << 20)) {
+      RTG_TRY(launch_depthwise3x3_tma(ctx, op, xp, w.wmat, bias, g));
+      ctx->last_kernel = p.stride_h == 1 ? "depthwise3x3_tma<s1>" : "depthwise3x3_tma<s2>";
+      if (!out_nhwc) RTG_TRY(from_nhwc(ctx, op, C, C, out, 0));
+      return RTG_OK;
+    }
     if (k3) {
       // rows per thread: as many as still leave ~512 threads per SM to hide the load latency
       constexpr int kTX = 4;
