@@ -20,6 +20,7 @@ import argparse
 import contextlib
 import io
 import json
+import re
 import os
 import subprocess
 import sys
@@ -488,6 +489,106 @@ def gemm_section(torch, R, ops, ctx, stream, modes, peak_tf32):
     return out
 
 
+def hbm_section(torch, R, ops, ctx, stream):
+    """The HBM-bound kernels either side of the contraction (SURVEY.md section 8 a7/a11/a12 and the depthwise branch of a4):
+    algorithmic bytes (every operand read once, the result written once) / time against the measured HBM copy rate.
+    Tensors are larger than L2 (126 MB) wherever the layer shape allows; CUDA events on the launching stream, 10 calls.
+    Softmax and LayerNormalization have no operator-level entry point: one-operator models, replayed from their graph."""
+    import numpy as np
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    dev = torch.device("cuda", ctx.device)
+    hbm = load_peaks()["hbm_gbs"]
+    out = {"unit": "GB/s", "peak": hbm, "cases": {}}
+    gen = torch.Generator(device=dev).manual_seed(99)
+
+    def record(name, us, nbytes, kernel):
+        out["cases"][name] = {"us": round(us, 1), "gbs": round(nbytes / us / 1e3, 1),
+                              "frac": round(nbytes / us / 1e3 / hbm, 3), "mbytes": round(nbytes / 1e6, 1), "kernel": kernel}
+
+    def timed(fn, nbytes, name, kernel, iters=10):
+        try:
+            for _ in range(3):
+                fn()
+            stream.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(iters):
+                fn()
+            e1.record(stream)
+            stream.synchronize()
+            us = e0.elapsed_time(e1) / iters * 1e3
+            record(name, us, nbytes, kernel)
+        except Exception as exc:  # an extra: never a reason to lose the bench line
+            out["cases"][name] = {"error": str(exc)[:160]}
+            torch.cuda.synchronize()
+
+    def nhwc(*shape):
+        return torch.rand(shape, device=dev, generator=gen).contiguous(memory_format=torch.channels_last)
+
+    with torch.cuda.stream(stream):
+        # depthwise 3x3, the two largest MobileNetV2 layers at batch 64 (stride 1 and stride 2)
+        for name, (c, hw, s) in {"depthwise3x3_s1_32ch_112": (32, 112, 1), "depthwise3x3_s2_96ch_112": (96, 112, 2)}.items():
+            x = nhwc(64, c, hw, hw)
+            w = torch.rand((c, 1, 3, 3), device=dev, generator=gen) - 0.5
+            b = torch.rand((c,), device=dev, generator=gen)
+            ohw = (hw + 2 - 3) // s + 1
+            y = torch.empty((64, c, ohw, ohw), device=dev).contiguous(memory_format=torch.channels_last)
+            timed(lambda: ops.conv(x, w, b, padding=(1, 1, 1, 1), groups=c, strides=(s, s), activation="clip",
+                                   clip=(0.0, 6.0), out=y, ctx=ctx), 4.0 * (x.numel() + y.numel() + w.numel()), name,
+                  f"depthwise3x3_tma<s{s}>")
+            del x, y
+        # elementwise: Relu in place / out of place, Add (ResNet's residual form: same shapes)
+        x = torch.rand((64 << 20,), device=dev, generator=gen) - 0.5
+        z = torch.rand((64 << 20,), device=dev, generator=gen)
+        timed(lambda: ops.relu(x, in_place=True, ctx=ctx), 8.0 * x.numel(), "relu_in_place_256MB", "unary_kernel")
+        y = torch.empty_like(x)
+        timed(lambda: ops.add(x, z, out=y, ctx=ctx), 12.0 * x.numel(), "add_256MB", "binary_kernel")
+        del x, y, z
+        # MaxPool 3x3/2 of ResNet-50's stem at batch 32 (NHWC, as Graph::run sees it)
+        x = nhwc(32, 64, 112, 112)
+        y = torch.empty((32, 64, 56, 56), device=dev).contiguous(memory_format=torch.channels_last)
+        timed(lambda: ops.max_pool(x, (3, 3), (2, 2), (1, 1, 1, 1), ctx=ctx, out=y), 4.0 * (x.numel() + y.numel()),
+              "maxpool3x3_s2_64ch_112", "pool2d_nhwc_kernel")
+        del x, y
+        # Softmax over BERT's score rows and LayerNormalization over its hidden rows, scaled past L2
+        for name, op, cols, attrs, extra in (
+                ("softmax_rows128", "Softmax", 128, ("SoftmaxAttrs", [(0, "i32", -1)]), 0),
+                ("layer_norm_rows768", "LayerNormalization", 768,
+                 ("LayerNormalizationAttrs", [(0, "i32", -1), (1, "f32", 1e-12)]), 2)):
+            try:
+                rows = (200 << 20) // (4 * cols)
+                gb = ModelBuilder()
+                xin = gb.add_value("x", [rows, cols])
+                ins = [xin]
+                if extra:
+                    ins += [gb.add_constant("gamma", np.ones(cols, np.float32)), gb.add_constant("beta", np.zeros(cols, np.float32))]
+                yv = gb.op(op, ins, attrs, name="op")
+                gb.inputs, gb.outputs = [xin], [yv]
+                m = R.Model.load(gb.build(), ctx=ctx)
+                xd = torch.rand((rows, cols), device=dev, generator=gen)
+                yd = torch.empty((rows, cols), device=dev)
+                # the operator's own device time (RunOptions timing: events around the operator), not the run's: a
+                # one-operator model also copies its input in and its output out
+                m.set_timing(True)
+                best = None
+                for _ in range(5):
+                    m.run([xd], out=[yd])
+                    hit = re.search(op + r"\s+([0-9.]+)ms", m.timing_report())
+                    if hit:
+                        best = float(hit.group(1)) if best is None else min(best, float(hit.group(1)))
+                if best is None:
+                    raise RuntimeError("no timing row for " + op)
+                record(name, best * 1e3, 8.0 * rows * cols, "softmax_rows_kernel" if op == "Softmax" else "layer_norm_rows_kernel")
+                out["cases"][name]["timed"] = "operator time from the model's timing report, best of 5"
+                m.close()
+                del xd, yd
+            except Exception as exc:
+                out["cases"][name] = {"error": str(exc)[:160]}
+                torch.cuda.synchronize()
+    return out
+
+
 def nsplit_section(torch, dist, R, ctx, stream, math_name, world, rank):
     """BASELINE.json configs[4] at N GPUs: square GEMM, B column-split over the ranks, result on every rank.  local = this
     rank's block alone, nccl = block + one NCCL all-gather + strided copy, fused = tiles TMA-stored into every rank's
@@ -669,6 +770,7 @@ def run_ours(args):
             extras["nsplit"] = nsplit_section(torch, dist, R, ctx, stream, args.math, world, rank)
         else:
             extras["gemm"] = gemm_section(torch, R, ops, ctx, stream, modes, load_peaks()["tf32_sustained"])
+            extras["hbm_kernels"] = hbm_section(torch, R, ops, ctx, stream)
             ctx.set_math(math)
             # small batches, where the per-launch host cost weighs most (one GPU)
             small = {}

@@ -16,11 +16,12 @@ class Context:
     """Owns one ``rtg_ctx``.  Mirrors what a run of the reference owns implicitly: a TensorPool
     (src/tensor_pool.rs:103-199) plus, new here, the CUDA stream and device weight cache."""
 
-    def __init__(self, device: int = 0, math: int = N.MATH_3XTF32):
+    def __init__(self, device: int = 0, math: int | None = None):
         self._h = C.c_void_p()
         N.check(N.lib().rtg_ctx_create(C.c_int32(device), C.byref(self._h)))
         self.device = device
-        self.set_math(math)
+        if math is not None:  # None: the library's default (3xTF32, or what RTEN_GPU_MATH names)
+            self.set_math(math)
 
     # -- lifecycle
     def close(self):

@@ -37,6 +37,43 @@ void rtg::Model::release_captured() {
 
 namespace {
 
+// RTEN_TIMING (src/model.rs:124-147, :587-590): when set, every Model::run records per-operator times and prints the
+// table; the value is a space-separated list of key=value options.  sort=name | time is honoured; by-shape is accepted
+// but shapes are not recorded here.
+struct TimingEnv {
+  bool on = false, by_name = false;
+};
+const TimingEnv& timing_env() {
+  static const TimingEnv env = []() {
+    TimingEnv t;
+    const char* e = getenv("RTEN_TIMING");
+    if (!e) return t;
+    t.on = true;
+    std::string cfg(e);
+    size_t pos = 0;
+    while (pos < cfg.size()) {
+      size_t end = cfg.find_first_of(" \t\n", pos);
+      if (end == std::string::npos) end = cfg.size();
+      const std::string tok = cfg.substr(pos, end - pos);
+      pos = end + 1;
+      const size_t eq = tok.find('=');
+      if (tok.empty() || eq == std::string::npos) continue;
+      const std::string key = tok.substr(0, eq), val = tok.substr(eq + 1);
+      if (key == "sort") {
+        if (val == "name") t.by_name = true;
+        else if (val == "time") t.by_name = false;
+        else fprintf(stderr, "Unrecognized sort order \"%s\"\n", val.c_str());
+      } else if (key == "by-shape") {
+        // accepted: the table is per operator type either way
+      } else {
+        fprintf(stderr, "Unrecognized timing option \"%s\"\n", key.c_str());
+      }
+    }
+    return t;
+  }();
+  return env;
+}
+
 bool graph_capture_default() {
   static const bool on = []() {
     const char* e = getenv("RTEN_GPU_GRAPH");
@@ -85,7 +122,8 @@ rtg_status run_captured(Model* m, const rtg_tensor* inputs, int32_t n_inputs, co
                         const std::vector<int32_t>& outs_req, Run* run, bool* handled) {
   *handled = false;
   Context* ctx = m->ctx;
-  if (!m->graph_capture || !graph_capture_default() || m->timing || ctx->ktiming) return RTG_OK;
+  if (!m->graph_capture || !graph_capture_default() || m->timing || timing_env().on || ctx->ktiming || !ctx->pool.use_pool)
+    return RTG_OK;
   std::lock_guard<std::mutex> lock(m->cap_mu);
   CapturedPlan* cp = nullptr;
   for (auto& c : m->captured) {
@@ -184,7 +222,7 @@ rtg_status node_info(const Model* m, int32_t id, const char** name, int64_t* sha
 }
 
 // Per-operator timing table, sorted by time, in the layout of the reference's report (src/timing.rs:146-385).
-std::string format_timing(const std::vector<TimingRecord>& recs, const DevPool& pool) {
+std::string format_timing(const std::vector<TimingRecord>& recs, const DevPool& pool, bool by_name = false) {
   std::map<std::string, std::pair<double, int>> by_op;
   double total = 0;
   for (const TimingRecord& r : recs) {
@@ -193,7 +231,8 @@ std::string format_timing(const std::vector<TimingRecord>& recs, const DevPool& 
     total += r.ms;
   }
   std::vector<std::pair<std::string, std::pair<double, int>>> rows(by_op.begin(), by_op.end());
-  std::sort(rows.begin(), rows.end(), [](auto& a, auto& b) { return a.second.first > b.second.first; });
+  if (by_name) std::sort(rows.begin(), rows.end(), [](auto& a, auto& b) { return a.first < b.first; });
+  else std::sort(rows.begin(), rows.end(), [](auto& a, auto& b) { return a.second.first > b.second.first; });
   char line[256];
   snprintf(line, sizeof(line), "Graph run of %zu ops finished in %.3fms (device time)\n\n", recs.size(), total);
   std::string s = line;
@@ -313,10 +352,12 @@ rtg_status run_inputs(Model* m, const rtg_tensor* inputs, int32_t n_inputs, cons
     *out = run.release();
     return RTG_OK;
   }
-  rtg_status st = g.run(ctx, in, outs_req, &run->outputs, m->timing ? &recs : nullptr);
+  const bool timing = m->timing || timing_env().on;
+  rtg_status st = g.run(ctx, in, outs_req, &run->outputs, timing ? &recs : nullptr);
   if (st != RTG_OK) return st;  // Graph::run released the inputs
   run->node_ids = outs_req;
-  if (m->timing) m->timing_report = format_timing(recs, ctx->pool);
+  if (timing) m->timing_report = format_timing(recs, ctx->pool, timing_env().by_name);
+  if (timing_env().on) fputs(m->timing_report.c_str(), stdout);  // the reference prints the table after the run
   *out = run.release();
   return RTG_OK;
 }

@@ -605,7 +605,10 @@ rtg_status conv_gemm_device(Context* ctx, const float* x, const ConvGeom& g, con
 
   CUtensorMap ma, mb;
   {
-    cuuint64_t dims[4] = {static_cast<cuuint64_t>(g.c_total), static_cast<cuuint64_t>(g.w),
+    // The channel extent ends with this group's slice: the 32-channel box of the last block would otherwise read the
+    // next group's channels, and 0 (padded weight) x Inf / NaN there would poison outputs the reference leaves finite.
+    // Past the extent TMA fills zeros.
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(std::min(g.c_total, g.c_off + g.cg)), static_cast<cuuint64_t>(g.w),
                           static_cast<cuuint64_t>(g.h), static_cast<cuuint64_t>(g.n)};
     cuuint64_t strides[3] = {static_cast<cuuint64_t>(g.c_total) * 4, static_cast<cuuint64_t>(g.c_total) * g.w * 4,
                              static_cast<cuuint64_t>(g.c_total) * g.w * g.h * 4};

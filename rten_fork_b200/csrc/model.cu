@@ -41,7 +41,9 @@ rtg_status read_header(const uint8_t* p, size_t n, Header* h) {
 rtg_status make_constant(Context* ctx, int dtype, const std::vector<int64_t>& shape, const void* host, Node* node) {
   Value v;
   int64_t n = 1;
-  for (int64_t d : shape) n *= d;
+  for (int64_t d : shape)
+    if (d < 0 || __builtin_mul_overflow(n, d, &n) || n > (INT64_MAX >> 2))
+      return set_error(RTG_ERR_FORMAT, "graph error: constant data length does not match shape");
   if (shape.size() > RTG_MAX_DIMS) return set_error(RTG_ERR_FORMAT, "constant has too many dimensions");
   RTG_TRY(alloc_value(ctx, dtype, static_cast<int>(shape.size()), shape.data(), false, &v));
   if (n > 0) RTG_CUDA(cudaMemcpyAsync(v.t.data, host, static_cast<size_t>(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -65,6 +67,15 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
   std::unique_ptr<Model> model(new Model());
   model->ctx = ctx;
   const OpRegistry& registry = OpRegistry::with_all_ops();
+  // every error return below hands the constants already uploaded (and whatever the operators prepared) back to the pool
+  struct GraphGuard {
+    Context* ctx;
+    Graph* g;
+    bool armed = true;
+    ~GraphGuard() {
+      if (armed) g->release(ctx);
+    }
+  } guard{ctx, &model->graph};
   try {
     if (model_len < 8) throw fb::Error("file too short");
     fb::Table root = fb::root(model_data, model_len);
@@ -93,7 +104,6 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
         rtg_status st = registry.read_op(view, &node.op);
         if (st != RTG_OK) {
           std::string msg = rtg_last_error();
-          for (Node& nd : g.nodes) if (nd.kind == NodeKind::Constant) release_value(ctx, &nd.constant);
           return set_errorf(st, "operator error: in node \"%s\": %s", node.name.c_str(), msg.c_str());
         }
         fb::Vec<int32_t> ins = d.vec<int32_t>(3), outs = d.vec<int32_t>(4);
@@ -111,13 +121,17 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
         int64_t n = 1;
         for (uint32_t k = 0; k < shp.size(); ++k) {
           shape.push_back(shp[k]);
-          n *= shp[k];
+          // a product that leaves int64 (or whose byte count does) cannot match any data length
+          if (__builtin_mul_overflow(n, static_cast<int64_t>(shp[k]), &n) || n > (INT64_MAX >> 2))
+            return set_error(RTG_ERR_FORMAT, "graph error: constant data length does not match shape");
         }
         const uint8_t data_kind = d.scalar<uint8_t>(1, Data_NONE);
         if (d.has(4)) {
           // tensor data stored after the model buffer (V2 only)
           if (!hdr.present) return set_error(RTG_ERR_FORMAT, "graph error: tensor data section missing");
-          const uint64_t off = hdr.tensor_data_offset + d.scalar<uint64_t>(4, 0);
+          uint64_t off = 0;
+          if (__builtin_add_overflow(static_cast<uint64_t>(hdr.tensor_data_offset), d.scalar<uint64_t>(4, 0), &off))
+            return set_error(RTG_ERR_FORMAT, "graph error: invalid tensor data offset");
           if (!d.has(3)) return set_error(RTG_ERR_FORMAT, "graph error: constant with data offset has no dtype");
           const uint16_t dt = d.scalar<uint16_t>(3, 0);
           if (dt > 1) return set_error(RTG_ERR_FORMAT, "graph error: unsupported data type for external constant");
@@ -157,7 +171,6 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
     for (int32_t id : g.output_ids)
       if (id < 0 || id >= static_cast<int32_t>(g.nodes.size())) return set_error(RTG_ERR_FORMAT, "graph error: output id out of range");
   } catch (const fb::Error& e) {
-    model->graph.release(ctx);
     return set_errorf(RTG_ERR_FORMAT, "parse error: %s", e.what());
   }
   RTG_CUDA(cudaStreamSynchronize(ctx->stream));  // constants are uploaded from the caller's buffer
@@ -168,7 +181,6 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
     rtg_status st = propagate_constants(ctx, &model->graph, &replaced);
     if (st != RTG_OK) {
       std::string msg = rtg_last_error();
-      model->graph.release(ctx);
       return set_errorf(st, "optimization failed: %s", msg.c_str());  // ModelLoadError::OptimizeError
     }
     optimize_graph(&model->graph);
@@ -181,12 +193,9 @@ rtg_status load_model(Context* ctx, const uint8_t* data, size_t len, bool optimi
     OpInputs consts;
     for (int32_t id : node.inputs)
       consts.v.push_back(id >= 0 && g.nodes[id].kind == NodeKind::Constant ? &g.nodes[id].constant : nullptr);
-    rtg_status st = node.op->prepare(ctx, consts);
-    if (st != RTG_OK) {
-      g.release(ctx);
-      return st;
-    }
+    RTG_TRY(node.op->prepare(ctx, consts));
   }
+  guard.armed = false;
   *out = model.release();
   return RTG_OK;
 }

@@ -40,11 +40,12 @@ rtg_status ConvOp::partial_plan(const rtg_tensor& w, ConvPlan* p) const {
   p->dil_h = one_d ? 1 : (attrs.n_dilations > 0 ? attrs.dilations[0] : 1);
   p->dil_w = one_d ? (attrs.n_dilations > 0 ? attrs.dilations[0] : 1) : (attrs.n_dilations > 1 ? attrs.dilations[1] : 1);
   bool unit = true, nopad = attrs.pad_mode == RTG_PAD_SAME;
-  for (int i = 0; i < attrs.n_strides; ++i) unit = unit && attrs.strides[i] == 1;
-  for (int i = 0; i < attrs.n_dilations; ++i) unit = unit && attrs.dilations[i] == 1;
+  // the counts come from the file: more entries than the arrays hold are reported when the plan is made (conv_plan)
+  for (int i = 0; i < std::min(attrs.n_strides, 2); ++i) unit = unit && attrs.strides[i] == 1;
+  for (int i = 0; i < std::min(attrs.n_dilations, 2); ++i) unit = unit && attrs.dilations[i] == 1;
   if (attrs.pad_mode == RTG_PAD_FIXED) {
     nopad = true;
-    for (int i = 0; i < attrs.n_pads; ++i) nopad = nopad && attrs.pads[i] == 0;
+    for (int i = 0; i < std::min(attrs.n_pads, 4); ++i) nopad = nopad && attrs.pads[i] == 0;
   }
   p->pointwise = p->kh == 1 && p->kw == 1 && nopad && attrs.groups == 1 && unit;
   p->depthwise = !p->pointwise && attrs.groups > 0 && p->c == p->o && attrs.groups == p->c;

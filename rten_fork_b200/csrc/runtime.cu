@@ -1,5 +1,7 @@
 // Context, device TensorPool, error strings, host<->device staging.
 #include "runtime.h"
+#include <string>
+#include <algorithm>
 
 #include <stdarg.h>
 #include <stdio.h>
@@ -76,6 +78,12 @@ rtg_status DevPool::free(void* p) {
   auto it = capacity_.find(p);
   if (it == capacity_.end()) return set_error(RTG_ERR_INVALID_VALUE, "pointer was not allocated from this pool");
   if (it->second.pooled) return set_error(RTG_ERR_INVALID_VALUE, "pointer was already returned to the pool (double free)");
+  if (!use_pool && pinned_addresses == 0) {
+    bytes_reserved -= it->second.cap;
+    capacity_.erase(it);
+    RTG_CUDA(cudaFree(p));  // waits for the device: kernels still reading the buffer finish first
+    return RTG_OK;
+  }
   it->second.pooled = true;
   free_.emplace(it->second.cap, p);
   return RTG_OK;
@@ -117,6 +125,33 @@ rtg_status rtg_ctx_create(int32_t device, rtg_ctx** out) {
   Context* c = new Context();
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
+  // Environment, read once per context like the reference reads its own (src/threading.rs:34-60, src/graph.rs:871):
+  //   RTEN_GPU_SMS    n  the share of the machine kernels size their grids for -- the counterpart of RTEN_NUM_THREADS
+  //                      (the reference's thread pool size); persistent kernels launch at most n CTAs
+  //   RTEN_GPU_MATH   tf32 | 3xtf32 | tf32_bf16x2   initial math mode of the context (rtg_ctx_set_math overrides it)
+  //   RTEN_USE_POOL   0  no buffer reuse (see DevPool::use_pool)
+  if (const char* e = getenv("RTEN_GPU_SMS")) {
+    const int n = atoi(e);
+    if (n <= 0) {
+      delete c;
+      return set_errorf(RTG_ERR_INVALID_VALUE, "RTEN_GPU_SMS must be a positive number, got \"%s\"", e);
+    }
+    c->num_sms = std::min(c->num_sms, n);
+  }
+  if (const char* e = getenv("RTEN_GPU_MATH")) {
+    const std::string v(e);
+    if (v == "tf32") c->math = RTG_MATH_TF32;
+    else if (v == "3xtf32") c->math = RTG_MATH_3XTF32;
+    else if (v == "tf32_bf16x2") c->math = RTG_MATH_TF32_BF16X2;
+    else {
+      delete c;
+      return set_errorf(RTG_ERR_INVALID_VALUE, "RTEN_GPU_MATH must be tf32, 3xtf32 or tf32_bf16x2, got \"%s\"", e);
+    }
+  }
+  if (const char* e = getenv("RTEN_USE_POOL")) {
+    const std::string v(e);
+    c->pool.use_pool = !(v == "0" || v == "false" || v == "no" || v == "off");  // str_as_bool, src/env.rs
+  }
   RTG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   c->own_stream = true;
   cudaDriverGetVersion(&c->driver_version);

@@ -46,6 +46,9 @@ class DevPool {
   // > 0 while captured CUDA graphs reference addresses of this pool (Model graph capture): pooled buffers are then
   // never given back to the driver, their addresses are baked into the graphs
   int pinned_addresses = 0;
+  // RTEN_USE_POOL=0 (src/graph.rs:871 env_flag("RTEN_USE_POOL", true)): released buffers go back to the driver instead
+  // of the pool, every allocation is a cudaMalloc.  A debugging aid, as in the reference; it also turns graph capture off.
+  bool use_pool = true;
 
  private:
   struct Slot {

@@ -355,13 +355,16 @@ def _pool_attrs(kernel_size, strides, padding, count_include_pad=False):
     return a
 
 
-def _pool(kind, x, kernel_size, strides, padding, count_include_pad=False, ctx=None):
+def _pool(kind, x, kernel_size, strides, padding, count_include_pad=False, ctx=None, out=None):
     ctx = ctx or context_for(x)
     a = _pool_attrs(kernel_size, strides, padding, count_include_pad)
     ti = as_tensor(x)
     shape = (C.c_int64 * 4)()
     N.check(N.lib().rtg_pool2d_out_shape(C.byref(ti), C.byref(a), shape))
-    out = _empty_like_kind(x, shape[:4])
+    if out is None:
+        out = _empty_like_kind(x, shape[:4])
+    elif tuple(out.shape) != tuple(shape[:4]):
+        raise N.RtgError(3, "output has the wrong shape")
     to = as_tensor(out)
     N.check(N.lib().rtg_pool2d(ctx.handle, C.c_int32(kind), C.byref(ti), C.byref(a), C.byref(to)))
     return out

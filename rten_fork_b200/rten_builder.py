@@ -225,14 +225,16 @@ class ModelBuilder:
                 data_h, kind_id = fb.table([(0, "offset", shape_h)]), 3
             elif nd["kind"] == "const":
                 arr = nd["data"]
-                shape_h = fb.vector("u32", [int(s) for s in arr.shape])
+                # "shape_override" / "offset_override": malformed files for the loader's own error tests
+                shape_h = fb.vector("u32", [int(s) for s in nd.get("shape_override", arr.shape)])
                 is_f = arr.dtype == np.float32
                 if version == 2 and arr.size > inline_limit:
                     pad = (-len(tensor_data)) % 64
                     tensor_data += b"\0" * pad
                     off = len(tensor_data)
                     tensor_data += arr.tobytes()
-                    data_h = fb.table([(0, "offset", shape_h), (3, "u16", 1 if is_f else 0), (4, "u64", off)])
+                    data_h = fb.table([(0, "offset", shape_h), (3, "u16", 1 if is_f else 0),
+                                       (4, "u64", nd.get("offset_override", off))])
                 else:
                     payload = fb.table([(0, "offset", fb.vector("f32" if is_f else "i32", arr.reshape(-1)))])
                     data_h = fb.table([(0, "offset", shape_h), (1, "u8", 1 if is_f else 2), (2, "offset", payload),

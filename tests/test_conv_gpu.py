@@ -96,6 +96,24 @@ def test_conv_grouped(rtg, ctx, oracle, math_mode):  # :963-981 test_conv_not_de
     check_conv(rtg, oracle, math_mode["rtol"], x, w, b, (1, 1, 1, 1), 4, (1, 1), (1, 1))
 
 
+def test_conv_grouped_does_not_leak_non_finite_values_across_groups(rtg, ctx, oracle, math_mode):
+    """The shared-NHWC grouped path reads 32-channel boxes; a group of 8 channels must not see its neighbour's
+    channels (0-weight x Inf would give NaN where the reference's per-group im2col gives finite values)."""
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(77)
+    w, x, b = rng.fill((16, 8, 3, 3)) - 0.5, rng.fill((2, 32, 9, 11)), rng.fill((16,))
+    x[:, 8:16] = np.inf    # group 1 only
+    x[0, 24:32, 3, 4] = np.nan  # group 3 only
+    got = ops.conv(x, w, b, padding=(1, 1, 1, 1), groups=4, ctx=ctx)
+    want = oracle.conv2d(np.where(np.isfinite(x), x, 0).astype(np.float32), w, b, (1, 1, 1, 1), 4, (1, 1), (1, 1))
+    for grp in (0, 2):      # groups whose own inputs are finite
+        sl = slice(4 * grp, 4 * grp + 4)
+        assert np.isfinite(got[:, sl]).all(), "non-finite values leaked from a neighbouring group"
+        np.testing.assert_allclose(got[:, sl], want[:, sl], rtol=math_mode["rtol"] * 4, atol=math_mode["rtol"] * 4 * np.abs(want).max())
+    assert not np.isfinite(got[:, 4:8]).all()   # group 1 really is poisoned, as in the reference
+
+
 @pytest.mark.parametrize("strides", [(2, 2), (3, 3), (1, 3)])
 @pytest.mark.parametrize("pad", [0, 1])
 def test_conv_strided(rtg, ctx, oracle, math_mode, strides, pad):  # :983-1005

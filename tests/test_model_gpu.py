@@ -412,3 +412,43 @@ def test_graph_with_host_round_trip_stays_eager(rtg, oracle):
     assert m.graph_replays == 0
     m.close()
     c.close()
+
+
+def test_loader_rejects_overflowing_constants_and_releases_the_pool(rtg, ctx):
+    """Untrusted files: a shape whose element count leaves int64, a tensor-data offset that wraps u64, and an error
+    after constants were uploaded (they must go back to the pool).  Reference errors: src/model.rs:468-522
+    ("invalid tensor data offset", "length does not match shape")."""
+    from rten_fork_b200.model import Model
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    def small(n_const=1):
+        b = ModelBuilder()
+        x = b.add_value("x", [1, 100])
+        b.inputs = [x]
+        ids = [b.add_constant(f"c{i}", np.ones((1, 100 + 7 * i), np.float32)) for i in range(n_const)]
+        return b, x, ids
+
+    b, x, (c,) = small()
+    b.nodes[c]["shape_override"] = [0xFFFFFFFF, 0xFFFFFFFF, 4]      # 2^66 elements: n * 4 would wrap to a small count
+    b.outputs = [b.op("Add", [x, c])]
+    for version in (1, 2):
+        with pytest.raises(rtg.RtgError, match="does not match shape|invalid tensor data offset") as e:
+            Model.load(b.build(version=version), ctx=ctx)
+        assert e.value.kind == "Format"
+    b, x, (c,) = small()
+    b.nodes[c]["offset_override"] = (1 << 64) - 8                    # tensor_data_offset + offset wraps around
+    b.outputs = [b.op("Add", [x, c])]
+    with pytest.raises(rtg.RtgError, match="invalid tensor data offset"):
+        Model.load(b.build(version=2), ctx=ctx)
+    # two constants are uploaded, then an operator this registry does not have fails the load: both buffers return
+    b, x, ids = small(2)
+    y = b.op("Add", [x, ids[0]])
+    b.outputs = [b.op("Cos", [y])]
+    data = b.build(version=2)
+    with pytest.raises(rtg.RtgError, match="not available"):
+        Model.load(data, ctx=ctx)
+    s0 = ctx.pool_stats()
+    with pytest.raises(rtg.RtgError, match="not available"):
+        Model.load(data, ctx=ctx)
+    s1 = ctx.pool_stats()
+    assert s1["hit_count"] - s0["hit_count"] >= 2 and s1["len"] == s0["len"], "the failed load leaked its constants"
