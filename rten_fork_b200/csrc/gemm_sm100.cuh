@@ -334,22 +334,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (args.flags & kFlagStagedD) ptx::prefetch_tmap(&tmD);
     if (args.flags & kFlagStagedR) ptx::prefetch_tmap(&tmR);
   }
-  if (warp == 0 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) {
+  if (warp == 0) {
+    // one barrier per lane and pass (a single thread needed ~1000 cycles for the ~35 of them, on every launch's critical
+    // path in front of the first TMA load)
+    for (int s = lane; s < kStages; s += 32) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
       // one arrival per split warp (MODE 2: the four A warps only; its B' tile arrives by TMA)
       ptx::mbar_init(xf_bar(s), MODE == 2 ? 4 : 6);  // A-split warps of the four lane quarters (+ 2 B-lo warps)
     }
-    for (int a = 0; a < 2; ++a) {
-      ptx::mbar_init(tfull_bar(a), 1);
-      ptx::mbar_init(tempty_bar(a), Cfg::kEpiWarps);  // one arrival per epilogue warp
+    if (lane >= 8 && lane < 10) {
+      ptx::mbar_init(tfull_bar(lane - 8), 1);
+      ptx::mbar_init(tempty_bar(lane - 8), Cfg::kEpiWarps);  // one arrival per epilogue warp
     }
-    for (int w = 0; w < Cfg::kEpiWarps; ++w)
-      for (int b = 0; b < Cfg::kEpiBufs; ++b) ptx::mbar_init(rbar(w, b), 1);
-    for (int i = 0; i < kAStages; ++i) {
-      ptx::mbar_init(afull_bar(i), 1);
-      ptx::mbar_init(aempty_bar(i), 4);  // one arrival per A-split warp
+    for (int i = lane; i < Cfg::kEpiWarps * Cfg::kEpiBufs; i += 32) ptx::mbar_init(rbar(i / Cfg::kEpiBufs, i % Cfg::kEpiBufs), 1);
+    if (lane >= 16 && lane < 16 + kAStages) {
+      ptx::mbar_init(afull_bar(lane - 16), 1);
+      ptx::mbar_init(aempty_bar(lane - 16), 4);  // one arrival per A-split warp
     }
     ptx::fence_mbar_init();
   }

@@ -131,7 +131,7 @@ rtg_status gemm_op_out_shape(const rtg_tensor* a, const rtg_tensor* b, bool ta, 
 }
 
 rtg_status gemm_op_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& b, const rtg_tensor* c, float alpha,
-                           float beta, bool ta, bool tb, const rtg_tensor& out) {
+                           float beta, bool ta, bool tb, const rtg_tensor& out, const BPack* b_pack) {
   int64_t os[2];
   RTG_TRY(gemm_op_out_shape(&a, &b, ta, tb, os));
   const int64_t M = os[0], N = os[1];
@@ -154,7 +154,15 @@ rtg_status gemm_op_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& 
   float* D = static_cast<float*>(out.data);
   Epilogue ep;
   ep.alpha = alpha;
-  if (use_c) {
+  if (b_pack && b_pack->p) ep.b_pack = *b_pack, ep.b_pack_const = true;  // packed at load time (GemmOp::prepare)
+  // c that is one value per output column (the bias of a linear layer) with beta = 1: alpha * acc + 1.0 * c[n] is the
+  // epilogue's per-column bias term exactly, without first expanding c into the output and reading it back
+  const bool c_is_row = use_c && beta == 1.f && c->device != RTG_HOST && c->shape[c->ndim > 0 ? c->ndim - 1 : 0] == N &&
+                        (c->ndim == 1 || (c->ndim == 2 && c->shape[0] == 1)) && c->strides[c->ndim - 1] == 1;
+  if (c_is_row) {
+    ep.bias = static_cast<const float*>(c->data);
+    ep.bias_mode = BIAS_COL;
+  } else if (use_c) {
     // expand c into the output, then accumulate with beta (src/ops/matmul.rs:46-64)
     rtg_tensor cb = {};
     cb.data = c->data, cb.dtype = RTG_F32, cb.ndim = 2, cb.device = c->device;

@@ -465,13 +465,36 @@ rtg_status GemmOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out
   RTG_TRY(gemm_op_out_shape(&a->t, &b->t, trans_a, trans_b, shape));
   Value y;
   RTG_TRY(alloc_value(ctx, RTG_F32, 2, shape, false, &y));
-  rtg_status st = gemm_op_forward(ctx, a->t, b->t, c ? &c->t : nullptr, alpha, beta, trans_a, trans_b, y.t);
+  rtg_status st = gemm_op_forward(ctx, a->t, b->t, c ? &c->t : nullptr, alpha, beta, trans_a, trans_b, y.t,
+                                  b_pack.p && b_pack_from == b->t.data ? &b_pack : nullptr);
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;
   }
   out->push_back(y);
   return RTG_OK;
+}
+
+rtg_status GemmOp::prepare(Context* ctx, const OpInputs& consts) {
+  release(ctx);
+  const Value* b = consts.get(1);
+  if (!b || b->t.ndim != 2 || b->t.dtype != RTG_F32 || b->t.device == RTG_HOST) return RTG_OK;
+  // the operand as the contraction sees it: [K, N] after the optional transposition (a view change)
+  const int64_t K = trans_b ? b->t.shape[1] : b->t.shape[0], N = trans_b ? b->t.shape[0] : b->t.shape[1];
+  const int64_t rs = trans_b ? b->t.strides[1] : b->t.strides[0], cs = trans_b ? b->t.strides[0] : b->t.strides[1];
+  if (K == 0 || N == 0 || rs < 0 || cs < 0) return RTG_OK;
+  void* d = nullptr;
+  const int64_t ld = b_pack_ld(K);
+  RTG_TRY(ctx->pool.alloc(static_cast<size_t>(N) * ld * 4 * 2, &d));
+  b_pack = BPack{static_cast<const float*>(d), ld, N * ld};
+  b_pack_from = b->t.data;
+  return make_b_pack(ctx, MatView{static_cast<const float*>(b->t.data), K, N, rs, cs}, static_cast<float*>(d), N * ld);
+}
+
+void GemmOp::release(Context* ctx) {
+  if (b_pack.p) ctx->pool.free(const_cast<float*>(b_pack.p));
+  b_pack = BPack{};
+  b_pack_from = nullptr;
 }
 
 rtg_status MatMulOp::prepare(Context* ctx, const OpInputs& consts) {

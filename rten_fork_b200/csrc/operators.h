@@ -99,6 +99,13 @@ class GemmOp : public Operator {
   bool trans_a = false, trans_b = false;
   const char* name() const override { return "Gemm"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
+  // constant weights (the classifier head): packed once at load, like MatMulOp
+  rtg_status prepare(Context* ctx, const OpInputs& consts) override;
+  void release(Context* ctx) override;
+
+ private:
+  BPack b_pack;
+  const void* b_pack_from = nullptr;
 };
 
 // MatMul  src/ops/matmul.rs:241-254 ; FusedTranspose(MatMul) is expressed by a TransposeOp whose result is a view

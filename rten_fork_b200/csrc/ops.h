@@ -130,7 +130,8 @@ rtg_status matmul_out_shape(const rtg_tensor* a, const rtg_tensor* b, int64_t* s
 rtg_status matmul_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& b, const rtg_tensor& out,
                           const Epilogue* fused = nullptr);
 rtg_status gemm_op_forward(Context* ctx, const rtg_tensor& a, const rtg_tensor& b, const rtg_tensor* c, float alpha,
-                           float beta, bool trans_a, bool trans_b, const rtg_tensor& out);
+                           float beta, bool trans_a, bool trans_b, const rtg_tensor& out,
+                           const BPack* b_pack = nullptr);  // b_pack: packed copy of constant weights (GemmOp::prepare)
 rtg_status gemm_op_out_shape(const rtg_tensor* a, const rtg_tensor* b, bool trans_a, bool trans_b, int64_t* shape);
 
 // ------------------------------------------------------------------ pooling
