@@ -94,6 +94,43 @@ __global__ void pool2d_nhwc4_kernel(float* __restrict__ out, const float* __rest
   }
 }
 
+// MaxPool over NHWC with a compile-time window: the window loops of pool2d_nhwc4_kernel are data-dependent (`continue`
+// on padding), so its loads leave one after the other; here all KH x KW loads of a thread are in flight together
+// (out-of-image taps are replaced by -inf, which a max ignores exactly like skipping them).
+template <int KH, int KW>
+__global__ void __launch_bounds__(256) maxpool_nhwc4_kernel(float* __restrict__ out, const float* __restrict__ in, PoolGeom g) {
+  const int c4 = g.c >> 2;
+  const int total = g.n * g.oh * g.ow * c4;  // host guarantees < 2^31
+  const float ninf = __int_as_float(0xff800000);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int r = i;
+    const int cq = r % c4;
+    r /= c4;
+    const int ox = r % g.ow;
+    r /= g.ow;
+    const int oy = r % g.oh;
+    const int n = r / g.oh;
+    const float4* ip = reinterpret_cast<const float4*>(in + static_cast<int64_t>(n) * g.h * g.w * g.c) + cq;
+    const int iy0 = oy * g.stride_h - g.pad_t, ix0 = ox * g.stride_w - g.pad_l;
+    float4 v[KH * KW];
+#pragma unroll
+    for (int ky = 0; ky < KH; ++ky) {
+#pragma unroll
+      for (int kx = 0; kx < KW; ++kx) {
+        const int iy = iy0 + ky, ix = ix0 + kx;
+        const bool ok = iy >= 0 && iy < g.h && ix >= 0 && ix < g.w;
+        v[ky * KW + kx] = ok ? __ldg(ip + (iy * g.w + ix) * c4) : make_float4(ninf, ninf, ninf, ninf);
+      }
+    }
+    float4 acc = make_float4(ninf, ninf, ninf, ninf);
+#pragma unroll
+    for (int k = 0; k < KH * KW; ++k) {  // same fold order as pool2d_kernel: (ky, kx)
+      acc.x = fmaxf(acc.x, v[k].x), acc.y = fmaxf(acc.y, v[k].y), acc.z = fmaxf(acc.z, v[k].z), acc.w = fmaxf(acc.w, v[k].w);
+    }
+    reinterpret_cast<float4*>(out)[i] = acc;
+  }
+}
+
 // One warp per (n, c) for NCHW (contiguous plane, shuffle reduction); for NHWC one thread per (n, c) column walks the
 // pixels so that a warp reads 32 consecutive channels per pixel (coalesced).
 __global__ void gap_nchw_kernel(float* __restrict__ out, const float* __restrict__ in, int64_t nc, int hw, int c,
@@ -178,8 +215,11 @@ rtg_status pool2d_forward(Context* ctx, int kind, const rtg_tensor& in, const rt
   if (is_nhwc_dense(in) && is_nhwc_dense(out) && g.c % 4 == 0 && total < (1ll << 31) &&
       (reinterpret_cast<uintptr_t>(in.data) & 15) == 0 && (reinterpret_cast<uintptr_t>(out.data) & 15) == 0) {
     const int blocks4 = static_cast<int>(std::min<int64_t>(div_ceil(total / 4, 256), static_cast<int64_t>(ctx->num_sms) * 32));
-    pool2d_nhwc4_kernel<<<blocks4, 256, 0, ctx->stream>>>(static_cast<float*>(out.data),
-                                                         static_cast<const float*>(in.data), g);
+    float* op = static_cast<float*>(out.data);
+    const float* ip = static_cast<const float*>(in.data);
+    if (kind == RTG_POOL_MAX && g.kh == 3 && g.kw == 3) maxpool_nhwc4_kernel<3, 3><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+    else if (kind == RTG_POOL_MAX && g.kh == 2 && g.kw == 2) maxpool_nhwc4_kernel<2, 2><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+    else pool2d_nhwc4_kernel<<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
     ctx->launches++;
     RTG_CUDA(cudaGetLastError());
     return RTG_OK;
