@@ -719,6 +719,7 @@ def run_ours(args):
     barrier()
     l0 = ctx.launch_count
     ms_total = timed_device_steps(torch, model, stream, x_dev, out_dev, flush, args.steps)
+    headline_out = out_dev.cpu().numpy().copy()   # out_dev is reused by the other math modes below
     launches = ctx.launch_count - l0
     barrier()
     ms_total = max_over_ranks(ms_total)
@@ -805,8 +806,7 @@ def run_ours(args):
                 dt = (time.perf_counter() - t0) / reps
                 extras["strong"] = {"gpus": world, "batch": args.batch, "ms_per_call": dt * 1e3,
                                     "images_per_s": args.batch / dt,
-                                    "matches_one_gpu": bool(np.abs(os_h - out_dev.cpu().numpy()).max()
-                                                            <= 2e-4 * np.abs(os_h).max()),
+                                    "matches_one_gpu": bool(np.abs(os_h - headline_out).max() <= 2e-4 * np.abs(os_h).max()),
                                     "api": "rtg_sharded_model_run: pageable host input -> dim-0 chunks on N GPUs of one "
                                            "process -> host output; wall clock, copies inside"}
                 sm.close()

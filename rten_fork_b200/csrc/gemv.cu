@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(256) gemv_kmajor_kernel(const GemvArgs g) {
 #pragma unroll
       for (int c = 0; c < NC; ++c) acc[m][c] = 0.f;
     if (VEC) {  // a rows and B columns 16-byte aligned, unit stride along k
+#pragma unroll 2
       for (int k = lane * 4; k < g.K; k += 128) {
         float4 bv[NC];
 #pragma unroll
@@ -200,18 +201,21 @@ rtg_status gemv_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
     g.b_ld = b.cs;
     const bool vec = a.cs == 1 && g.K % 4 == 0 && (a.rows == 1 || a.rs % 4 == 0) && b.cs % 4 == 0 &&
                      (reinterpret_cast<uintptr_t>(a.p) & 15) == 0 && (reinterpret_cast<uintptr_t>(b.p) & 15) == 0;
-    const int nc = g.M <= 1 ? 1 : 4;
+    // Four columns per warp only when that still leaves ~16 warps per SM: the loop is a chain of dependent loads, and a
+    // 1000-column classifier head with 250 busy warps ran at 45 us (batch 8) against 18 us with a warp per column.
+    const int nc = (g.M > 1 && div_ceil(g.N, 4) >= static_cast<int64_t>(ctx->num_sms) * 16) ? 4 : 1;
     const int blocks = static_cast<int>(std::min<int64_t>(div_ceil(div_ceil(g.N, nc), 8), static_cast<int64_t>(ctx->num_sms) * 8));
-    if (g.M <= 1) {
-      if (vec) gemv_kmajor_kernel<1, 1, true><<<blocks, 256, 0, ctx->stream>>>(g);
-      else gemv_kmajor_kernel<1, 1, false><<<blocks, 256, 0, ctx->stream>>>(g);
-    } else if (g.M <= 4) {
-      if (vec) gemv_kmajor_kernel<4, 4, true><<<blocks, 256, 0, ctx->stream>>>(g);
-      else gemv_kmajor_kernel<4, 4, false><<<blocks, 256, 0, ctx->stream>>>(g);
-    } else {
-      if (vec) gemv_kmajor_kernel<8, 4, true><<<blocks, 256, 0, ctx->stream>>>(g);
-      else gemv_kmajor_kernel<8, 4, false><<<blocks, 256, 0, ctx->stream>>>(g);
-    }
+#define RTG_GEMV_K(MR, NC)                                                                  \
+  do {                                                                                      \
+    if (vec) gemv_kmajor_kernel<MR, NC, true><<<blocks, 256, 0, ctx->stream>>>(g);          \
+    else gemv_kmajor_kernel<MR, NC, false><<<blocks, 256, 0, ctx->stream>>>(g);             \
+  } while (0)
+    if (g.M <= 1) RTG_GEMV_K(1, 1);
+    else if (g.M <= 4 && nc == 4) RTG_GEMV_K(4, 4);
+    else if (g.M <= 4) RTG_GEMV_K(4, 1);
+    else if (nc == 4) RTG_GEMV_K(8, 4);
+    else RTG_GEMV_K(8, 1);
+#undef RTG_GEMV_K
     ctx->last_kernel = vec ? "gemv<B=K,float4>" : "gemv<B=K>";
   } else {
     g.b_ld = b.rs;
