@@ -70,7 +70,12 @@ rtg_status rtg_ctx_set_stream(rtg_ctx* ctx, void* cuda_stream);
 /* RTG_MATH_3XTF32 (default): results within rtol 1e-5 of the reference.  RTG_MATH_TF32: rtol 2e-3.
  * RTG_MATH_TF32_BF16X2: the same split as 3xTF32 (a = hi + lo) with hi*hi on the TF32 pipe and the two correction
  * products lo(A)*hi(B) + hi(A)*lo(B) as ONE bf16 MMA of doubled depth: 2 tensor-core passes per product instead of 3.
- * Worst-case error per product 2^-17 (bf16 rounding of the correction operands); also held to rtol 1e-5. */
+ * hi is the operand ROUNDED to nearest TF32 (|lo| <= 2^-12 |a|), so the error per product a*b is at most
+ * 2^-18 + 2^-19 (about 5.7e-6) of |a*b|: lo(A)*lo(B) is dropped (2^-24) and the correction operands are rounded to bf16
+ * (2 x 2^-12 x 2^-8 = 2^-19 ... 2^-18 with the hi parts' bf16 rounding); held to rtol 1e-5 like 3xTF32
+ * (tests/test_fullsize_gpu.py asserts the bound on adversarial operands).
+ * Environment: RTEN_GPU_MATH = tf32 | 3xtf32 | tf32_bf16x2 sets the initial mode of every new context; RTEN_GPU_SMS,
+ * RTEN_USE_POOL, RTEN_TIMING and RTEN_GPU_GRAPH are described in DESIGN.md section 8. */
 rtg_status rtg_ctx_set_math(rtg_ctx* ctx, int32_t mode);
 rtg_status rtg_ctx_get_math(rtg_ctx* ctx, int32_t* mode);
 rtg_status rtg_ctx_sync(rtg_ctx* ctx);
@@ -250,7 +255,10 @@ rtg_status rtg_model_output_info(const rtg_model* model, int32_t i, const char**
                                  int32_t* dtype);
 rtg_status rtg_model_num_ops(const rtg_model* model, int32_t* n);
 
-/* Run handle: the outputs of one Model::run.  Shapes are known after the run; copy out with rtg_run_output_copy. */
+/* Run handle: the outputs of one Model::run.  Shapes are known after the run; copy out with rtg_run_output_copy.
+ * Lifetime of HOST inputs: rtg_model_run* enqueue the uploads on the context's stream and return without waiting (with
+ * pinned memory the copy really is asynchronous), so the caller must leave the input buffers unchanged until it has
+ * copied an output to the host (rtg_run_output_copy synchronises) or called rtg_ctx_sync. */
 typedef struct rtg_run rtg_run;
 rtg_status rtg_model_run(rtg_model* model, const rtg_tensor* inputs, int32_t n_inputs, rtg_run** out);
 rtg_status rtg_run_num_outputs(const rtg_run* run, int32_t* n);
