@@ -1,0 +1,97 @@
+"""Rewrites BASELINE.md section 5 (round-2 results) from the raw bench lines in profiles/r02_bench_n{1,2,4,8}.json.
+Usage: python scripts/baseline_r02.py"""
+import json
+import os
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MARK = "\n\n## 5. Results, round 2 end"
+
+
+def line(n):
+    return json.loads(open(os.path.join(ROOT, "profiles", f"r02_bench_n{n}.json")).read().strip().splitlines()[-1])
+
+
+def main():
+    p = os.path.join(ROOT, "BASELINE.md")
+    s = open(p).read()
+    if MARK in s:
+        s = s[: s.index(MARK)]
+    d = {n: line(n) for n in (1, 2, 4, 8)}
+    b = d[1]
+    g = b["gemm"]["sweep"]
+
+    def sw(n, m, k="tflops"):
+        return g[str(n)][m].get(k)
+
+    rows = [f"| {n} | {x['value']:,.0f} | {x['ms_per_step']:.3f} | {x['e2e']['value']:,.0f} | {x['value'] / b['value']:.2f} |"
+            for n, x in d.items()]
+    ns = []
+    for n in (2, 4, 8):
+        for sz, v in d[n]["nsplit"]["sizes"].items():
+            ns.append(f"| {n} | {sz} | {v['local_ms']:.3f} | {v['nccl_ms']:.3f} ({v['nccl_tflops']:.0f}) | "
+                      f"**{v['fused_ms']:.3f} ({v['fused_tflops']:.0f})** | {v['fused_equals_nccl_bitwise']} |")
+    st = [f"| {n} | {d[n]['strong']['ms_per_call']:.3f} | {d[n]['strong']['images_per_s']:,.0f} | "
+          f"{d[n]['strong']['matches_one_gpu']} |" for n in (2, 4, 8)]
+    hbrows = "\n".join(f"| {k} | {v['mbytes']} | {v['us']} | {v['gbs']:.0f} | {v['frac']:.2f} | `{v['kernel']}` |"
+                       for k, v in b["hbm_kernels"]["cases"].items())
+    gvrows = "\n".join(f"| {k} | {v['us']} | {v['gbs']:.0f} | {v['frac']:.2f} | `{v['kernel']}` |"
+                       for k, v in b["gemm"]["gemv"]["cases"].items())
+    om, cpu, e2e, rf = b["other_modes"], b["cpu_baseline"], b["e2e"], b["roofline"]
+    nl = "\n"
+    sec = f"""
+
+## 5. Results, round 2 end (B200, SM clock {b['clocks']['sm_mhz']:.0f} MHz under load, no throttle reasons; raw lines: `profiles/r02_bench_n{{1,2,4,8}}.json`)
+
+Peaks of this pool (MEASURED_PEAKS.json): HBM 6550.1 GB/s, bf16 1401.3 TF/s sustained => TF32 roof 700.65 TF/s.
+
+| Config | CPU restatement ({cpu['cores']} threads = physical cores, AVX2 6x16) | 1xB200 TF32+BF16x2 (headline) | 1xB200 3xTF32 | 1xB200 TF32 | roofline fraction (contraction kernel) |
+|---|---|---|---|---|---|
+| C2 ResNet-50 b32, device-resident | {cpu['value']:.1f} img/s ({cpu['gflops']:.0f} GFLOP/s = {cpu['fraction_of_avx2_fma_peak']:.2f} of the cores' AVX2 FMA peak; 1 thread {cpu['one_thread_images_per_s']:.2f}; torch/oneDNN on the same cores {cpu['torch_cpu_context_images_per_s']:.0f}) | **{b['value']:,.0f} img/s** ({b['ms_per_step']:.3f} ms/step, {b['gpu_launches'] // b['steps']} launches/step replayed from one CUDA graph) | {om['3xtf32']['value']:,.0f} img/s ({om['3xtf32']['ms_per_step']:.2f} ms) | {om['tf32']['value']:,.0f} img/s ({om['tf32']['ms_per_step']:.2f} ms) | {rf['frac']:.3f} ({rf['achieved']:.0f} TF/s over the summed launch durations; {rf['achieved_in_stream']:.0f} TF/s in stream) / {om['3xtf32']['kernel_frac']:.3f} / {om['tf32']['kernel_frac']:.3f} |
+| C2 end to end (pinned host in/out, {e2e['h2d_bytes_per_step'] / 1e6:.1f} MB H2D + {e2e['d2h_bytes_per_step'] / 1e3:.0f} KB D2H per step) | {cpu['value']:.1f} img/s | **{e2e['value']:,.0f} img/s** ({e2e['ms_per_step']:.2f} ms/step, `Model.run_async`, two submits in flight); {e2e['one_call_at_a_time']['value']:,.0f} img/s ({e2e['one_call_at_a_time']['ms_per_step']:.2f} ms) one `Model.run` call at a time | - | - | - |
+| C2 small batches (device-resident, graph replay) | - | batch 1: {b['small_batch']['1']['ms_per_step']:.3f} ms; batch 4: {b['small_batch']['4']['ms_per_step']:.3f} ms | - | - | launch-latency-bound |
+| C1 GEMM 1024^3 (`bench_gemm` rule, 125 back-to-back calls; in brackets: replayed from a CUDA graph) | - | {sw(1024, 'tf32_bf16x2', 'us')} us, {sw(1024, 'tf32_bf16x2')} TF/s ({sw(1024, 'tf32_bf16x2', 'graph_tflops')}) | {sw(1024, '3xtf32', 'us')} us, {sw(1024, '3xtf32')} TF/s ({sw(1024, '3xtf32', 'graph_tflops')}) | {sw(1024, 'tf32', 'us')} us, {sw(1024, 'tf32')} TF/s ({sw(1024, 'tf32', 'graph_tflops')}) | {g['1024']['tf32_bf16x2']['frac']:.2f} / {g['1024']['3xtf32']['frac']:.2f} / {g['1024']['tf32']['frac']:.2f} (64 tiles: launch-bound) |
+| C5 GEMM 512 / 2048 / 4096 / 8192 / 16384 cubed (one GPU, TF/s) | - | {sw(512, 'tf32_bf16x2')} / {sw(2048, 'tf32_bf16x2')} / {sw(4096, 'tf32_bf16x2')} / {sw(8192, 'tf32_bf16x2')} / {sw(16384, 'tf32_bf16x2')} | {sw(512, '3xtf32')} / {sw(2048, '3xtf32')} / {sw(4096, '3xtf32')} / {sw(8192, '3xtf32')} / {sw(16384, '3xtf32')} | {sw(512, 'tf32')} / {sw(2048, 'tf32')} / {sw(4096, 'tf32')} / {sw(8192, 'tf32')} / {sw(16384, 'tf32')} | 8192^3: {g['8192']['tf32_bf16x2']['frac']:.2f} / {g['8192']['3xtf32']['frac']:.2f} / {g['8192']['tf32']['frac']:.2f}; the fp32-accurate modes' ceiling is 0.5 / 0.33 (2 / 3 tensor passes per product); 16384^3 is power-limited |
+| C3 BERT-base encoder b64 s128 (`profiles/r02_configs.txt`) | - | **10.03 ms/step, 6 382 seq/s** (143 TF/s algorithmic; 187 launches; round 1: 10.5 ms) | - | - | - |
+| C4 MobileNetV2 b64 (`profiles/r02_configs.txt`) | - | **1.72 ms/step, 37 120 img/s** (59 launches; round 1: 2.03 ms) | - | - | depthwise 3x3: 3.85 TB/s stride 1, 5.38 TB/s stride 2 (0.59 / 0.82 of HBM) |
+
+Speed-up of the headline over the CPU restatement on the same box: {e2e['value']:,.0f} / {cpu['value']:.1f} = **{e2e['value'] / cpu['value']:.0f}x end to end**
+({b['value'] / cpu['value']:.0f}x device-resident).  The CPU figure is higher than round 1's 31 img/s because the restatement now runs
+as the reference does: physical-core thread count, pooled buffers, in-place Relu / Add; it is still a port
+(`cpu_baseline.kind = "port"`), not the reference binary, and the ratio says nothing about kernel quality: the roofline
+fraction does, and it did not move this round (DESIGN.md section 3.1 has the measurements).
+
+**HBM-bound kernels (`bench.py` key `hbm_kernels`; algorithmic bytes / time against 6550.1 GB/s; ncu: `profiles/r02_hbm_kernels_summary.txt`):**
+
+| case | MB moved | us | GB/s | fraction | kernel |
+|---|---|---|---|---|---|
+{hbrows}
+
+**gemv (M <= 8) cases (`gemm.gemv`; 200 calls replayed from one CUDA graph; small operands stay in L2):**
+
+| case | us | GB/s | fraction of HBM | kernel |
+|---|---|---|---|---|
+{gvrows}
+
+**Weak scaling (C2, batch 32 per GPU, batch-sharded `Graph::run`, no collective; max over ranks):**
+
+| GPUs | images/s (device-resident) | ms/step | images/s end to end | vs 1 GPU |
+|---|---|---|---|---|
+{nl.join(rows)}
+
+**Strong scaling of ONE call (batch 32 from pageable host memory through `rtg_sharded_model_run`; 1 GPU through `Model.run`: {e2e['one_call_at_a_time']['ms_per_step']:.2f} ms):**
+
+| GPUs | ms per call | images/s | equals the 1-GPU result (2e-4 of the logits' scale) |
+|---|---|---|---|
+{nl.join(st)}
+
+**C5 N-split GEMM (n cubed, B column-split, result on every GPU; TF32+BF16x2; `bench.py` key `nsplit`):**
+
+| GPUs | n | local ms | nccl ms (TF/s) | **fused ms (TF/s)** | bitwise equal |
+|---|---|---|---|---|---|
+{nl.join(ns)}
+"""
+    open(p, "w").write(s.rstrip("\n") + sec)
+
+
+if __name__ == "__main__":
+    main()
