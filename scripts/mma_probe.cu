@@ -418,15 +418,20 @@ __global__ void __launch_bounds__(320, 1) probe_st(int mask, int reps, int mma, 
     const long long t2 = clock64();
     if (lane == 0) out[warp * 2] = t1 - t0, out[warp * 2 + 1] = t2 - t0;
   } else if (warp == 8 && mma) {
-    const uint32_t id_tf32 = ptx::make_idesc_tf32(128, 128, 0, 0);
+    // mma > 0: N = 128 TS-form chain, mma < 0: N = 64; its own duration goes to out[20] (does TMEM store / load traffic
+    // of the other warps lengthen the tensor pipe's time per instruction?)
+    const int n_mma = mma > 0 ? mma : -mma;
+    const uint32_t id_tf32 = mma > 0 ? ptx::make_idesc_tf32(128, 128, 0, 0) : ptx::make_idesc_tf32(128, 64, 0, 0);
     const uint64_t bdesc = ptx::make_smem_desc(base + 32 * 1024, 16, 1024);
+    const long long t0 = clock64();
     if (ptx::elect_one()) {
-      for (int i = 0; i < mma; ++i)
+      for (int i = 0; i < n_mma; ++i)
         ptx::mma_tf32_ts_w(tm, tm + 448 + (i & 3) * 8, static_cast<uint32_t>(bdesc) + (i & 3) * 2, static_cast<uint32_t>(bdesc >> 32), id_tf32, 1);
       ptx::mma_commit(bars);
     }
     __syncwarp();
     ptx::mbar_wait(bars, 0);
+    if (lane == 0) out[20] = clock64() - t0;
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -441,8 +446,9 @@ static void run_st(long long* dout, int mask, int reps, int mma) {
   CK(cudaMemset(dout, 0, 80 * 8));
   probe_st<<<1, 320, kSmem>>>(mask, reps, mma, dout);
   CK(cudaDeviceSynchronize());
-  long long h[16];
+  long long h[24];
   CK(cudaMemcpy(h, dout, sizeof(h), cudaMemcpyDeviceToHost));
+  if (mma) printf("[MMA chain N=%d: %.1f cycles / MMA] ", mma > 0 ? 128 : 64, double(h[20]) / (mma > 0 ? mma : -mma));
   printf("tcgen05.st.32x32b.x16 warps 0x%02x%s:", mask, mma ? " + MMA chain" : "");
   for (int w = 0; w < 8; ++w)
     if ((mask >> w) & 1) printf("  w%d %.1f issue / %.1f done", w, double(h[2 * w]) / reps, double(h[2 * w + 1]) / reps);
@@ -487,6 +493,9 @@ int main(int argc, char** argv) {
   if (argc > 1 && !strcmp(argv[1], "st")) {
     for (int mma : {0, 4096})
       for (int mask : {0x01, 0x11, 0x03, 0x0f, 0xff}) run_st(dout, mask, 256, mma);
+    // the other direction: a long store stream (8 warps x 16384 stores) under a chain of 2048 MMAs
+    for (int mma : {2048, -2048})
+      for (int mask : {0x00, 0x0f, 0xff}) run_st(dout, mask, 16384, mma);
     printf("probe done\n");
     return 0;
   }
