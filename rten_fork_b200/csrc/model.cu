@@ -532,9 +532,39 @@ int optimize_graph(Graph* g) {
         }
       }
     }
+    // --- MatMul [+ bias] -> Add(activation): the residual connection of a transformer block rides in the epilogue
+    //     ((acc + bias) + residual, the order of the unfused chain).  The operand must not depend on this product.
+    next = single_consumer(cur_out);
+    if (mm && !mm->has_residual && mm->act == ACT_NONE && next >= 0 && !dead[next]) {
+      Node& add = g->nodes[next];
+      BinaryOp* b = dynamic_cast<BinaryOp*>(add.op.get());
+      if (b && b->op == RTG_BIN_ADD && add.inputs.size() == 2 && add.outputs.size() == 1) {
+        const int32_t other = add.inputs[0] == cur_out ? add.inputs[1] : add.inputs[0];
+        bool ok = other >= 0 && other != cur_out && g->nodes[other].kind != NodeKind::Constant &&
+                  nd.inputs.size() <= 3;
+        std::vector<int32_t> stack = {other};
+        std::set<int32_t> seen;
+        while (ok && !stack.empty()) {
+          const int32_t v = stack.back();
+          stack.pop_back();
+          if (v == cur_out) ok = false;
+          if (v < 0 || !seen.insert(v).second || producer[v] < 0) continue;
+          for (int32_t in : g->nodes[producer[v]].inputs) stack.push_back(in);
+        }
+        if (ok) {
+          while (nd.inputs.size() < 3) nd.inputs.push_back(-1);
+          nd.inputs.push_back(other);
+          mm->has_residual = true;
+          dead[next] = 1;
+          nd.outputs[0] = add.outputs[0];
+          cur_out = add.outputs[0];
+          ++fused;
+        }
+      }
+    }
     // --- optional activation
     next = single_consumer(cur_out);
-    if (next >= 0 && !dead[next] && (conv || mm->has_bias)) {
+    if (next >= 0 && !dead[next] && (conv || mm->has_bias || mm->has_residual)) {
       Node& an = g->nodes[next];
       int act;
       float lo, hi;

@@ -555,12 +555,29 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
   }
   const bool bias_tail = bias && !(bias->t.dtype == RTG_F32 && numel(bias->t) == shape[nd - 1] && is_contiguous(bias->t));
+  // fused residual: rides in the epilogue when it is a dense f32 tensor of the output's shape and the product is the
+  // collapsed [.., M, K] x [K, N] form (one GEMM over all rows); otherwise it is added after the product, as unfused
+  const Value* res = has_residual ? in.get(3) : nullptr;
+  if (has_residual && !res) {
+    release_value(ctx, &y);
+    return set_error(RTG_ERR_MISSING_INPUTS, "Required inputs were missing");
+  }
+  bool res_fused = res && !bias_tail && res->t.dtype == RTG_F32 && res->t.ndim == nd && is_contiguous(res->t) && tb.ndim == 2 &&
+                   (reinterpret_cast<uintptr_t>(res->t.data) & 15) == 0;
+  for (int i = 0; res_fused && i < nd; ++i) res_fused = res->t.shape[i] == shape[i];
+  const bool res_tail = res && !res_fused;
+  const bool act_fused = !bias_tail && !res_tail;  // the activation comes last: fused only if everything before it is
   if (bias && !bias_tail) {
     ep.bias = static_cast<const float*>(bias->t.data);
     ep.bias_mode = BIAS_COL;
   }
-  if ((bias && !bias_tail) || (!bias_tail && act != ACT_NONE) || scale != 1.f) {
-    ep.act = bias_tail ? ACT_NONE : act;
+  if (res_fused) {
+    ep.R = static_cast<const float*>(res->t.data);
+    ep.beta = 1.f;
+    ep.rmap = OutMap{shape[nd - 1], 0, 0, 0};
+  }
+  if ((bias && !bias_tail) || res_fused || (act_fused && act != ACT_NONE) || scale != 1.f) {
+    ep.act = act_fused ? act : ACT_NONE;
     ep.alpha = scale;
     ep.alpha_div = scale_div;
     epp = &ep;
@@ -571,18 +588,22 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     epp = &ep;
   }
   rtg_status st = matmul_forward(ctx, ta, tb, y.t, epp);
-  if (st == RTG_OK && bias_tail) {
+  // unfused tails, in the order of the original chain: + bias, + residual, activation
+  auto add_tail = [&](const Value* operand) {
     BinaryOp add(RTG_BIN_ADD, "Add");
     OpInputs ain;
-    ain.v = {&y, bias};
+    ain.v = {&y, operand};
     std::vector<Value> sum;
-    st = add.run(ctx, ain, &sum);
-    if (st == RTG_OK) {
+    rtg_status s2 = add.run(ctx, ain, &sum);
+    if (s2 == RTG_OK) {
       release_value(ctx, &y);
       y = sum[0];
-      if (act != ACT_NONE) st = unary_forward(ctx, act, y.t, 0.f, 0.f, y.t);
     }
-  }
+    return s2;
+  };
+  if (st == RTG_OK && bias_tail) st = add_tail(bias);
+  if (st == RTG_OK && res_tail) st = add_tail(res);
+  if (st == RTG_OK && !act_fused && act != ACT_NONE) st = unary_forward(ctx, act, y.t, 0.f, 0.f, y.t);
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;

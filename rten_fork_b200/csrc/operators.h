@@ -112,6 +112,9 @@ class GemmOp : public Operator {
 class MatMulOp : public Operator {
  public:
   bool has_bias = false;  // fused `+ bias[N]` (input 2) and activation, set by optimize_graph
+  // fused `(MatMul [+ bias]) -> Add(residual)` (input 3: an activation of the output's shape; the residual connections of
+  // a transformer block).  Same order as the unfused chain: (acc + bias) + residual, then the activation
+  bool has_residual = false;
   int act = ACT_NONE;
   // fused `MatMul -> Mul(scalar)` / `MatMul -> Div(scalar)` (attention score scaling)
   float scale = 1.f;
@@ -121,7 +124,7 @@ class MatMulOp : public Operator {
   bool has_perm[2] = {false, false};
   bool perm_reverse[2] = {false, false};  // Transpose without `perm`: reverse the dims
   std::vector<int64_t> perm[2];
-  bool fused() const { return has_bias || act != ACT_NONE || scale != 1.f || has_perm[0] || has_perm[1]; }
+  bool fused() const { return has_bias || has_residual || act != ACT_NONE || scale != 1.f || has_perm[0] || has_perm[1]; }
   const char* name() const override { return fused() ? "FusedMatMul" : "MatMul"; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;
   // a constant 2-D right operand (linear-layer weights) gets its packed copy (BPack) once at load (make_b_pack),

@@ -291,3 +291,37 @@ def test_epilogue_fusion_falls_back_when_not_an_epilogue(rtg, ctx, oracle, case)
     assert got.shape == want.shape
     expect_equal(got, want, rtol=1e-5, atol=2e-6)
     expect_equal(_load(ctx, b, optimize=False).run(ins)[0], want, rtol=1e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("res_shape", ["same", "broadcast"])
+@pytest.mark.parametrize("with_bias", [True, False])
+def test_matmul_residual_rides_in_the_epilogue(rtg, ctx, res_shape, with_bias):
+    """MatMul [-> Add(bias)] -> Add(activation) [-> Relu]: the residual connection of a transformer block is fused when it
+    has the output's shape ((acc + bias) + residual in the epilogue, the order of the unfused chain, so optimised and
+    unoptimised runs agree bit for bit in every math mode) and is added after the product when it only broadcasts."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = np.random.default_rng(3)
+    b = ModelBuilder()
+    x = b.add_value("x", ["b", 24, 64])
+    r = b.add_value("r", ["b", 24, 96] if res_shape == "same" else [1, 24, 96])
+    b.inputs = [x, r]
+    w_arr = rng.random((64, 96), dtype=np.float32) - 0.5
+    bias_arr = rng.random(96, dtype=np.float32)
+    w = b.add_constant("w", w_arr)
+    y = b.op("MatMul", [x, w], name="dense")
+    if with_bias:
+        y = b.op("Add", [y, b.add_constant("bias", bias_arr)], name="bias_add")
+    y = b.op("Add", [r, y], name="residual_add")
+    y = b.op("Relu", [y], name="act")
+    b.outputs = [y]
+    xin = rng.random((3, 24, 64), dtype=np.float32) - 0.5
+    rin = rng.random((3, 24, 96) if res_shape == "same" else (1, 24, 96), dtype=np.float32) - 0.5
+    fused, plain = _load(ctx, b), _load(ctx, b, optimize=False)
+    assert fused.source_op(fused.output_ids[0]) == ("FusedMatMul", "dense")      # the whole chain is one operator
+    assert fused.num_ops == 1 and plain.num_ops == (4 if with_bias else 3)
+    got, want = fused.run([xin, rin])[0], plain.run([xin, rin])[0]
+    assert got.shape == (3, 24, 96)
+    np.testing.assert_array_equal(got, want)
+    ref = np.maximum(xin.astype(np.float64) @ w_arr.astype(np.float64) + (bias_arr if with_bias else 0) + rin, 0)
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3)
