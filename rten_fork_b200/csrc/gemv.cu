@@ -111,6 +111,49 @@ __global__ void __launch_bounds__(256) gemv_kmajor_kernel(const GemvArgs g) {
   }
 }
 
+// K-major B with several rows of A: the rows (M * K * 4 bytes, at most kGemvSmemBytes) are staged in shared memory once
+// per CTA, so the B columns stream from HBM / L2 while A is read from shared memory instead of L2 once per column.  A warp
+// per column, the CTA's eight warps walk the columns round-robin.  (The classifier head at batch 8: 1000 columns x 64 KB
+// of A through L2 made the plain kernel 18 us; the weights alone are an 8 MB read.)
+constexpr int kGemvSmemBytes = 96 * 1024;
+template <int MR>
+__global__ void __launch_bounds__(256) gemv_kmajor_smem_kernel(const GemvArgs g) {
+  extern __shared__ __align__(16) float gemv_a[];  // [M][K]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int kv = g.K >> 2;
+  for (int i = threadIdx.x; i < g.M * kv; i += blockDim.x) {
+    const int m = i / kv, k4 = i - m * kv;
+    reinterpret_cast<float4*>(gemv_a)[i] = __ldg(reinterpret_cast<const float4*>(g.a + m * g.a_rs) + k4);
+  }
+  __syncthreads();
+  for (int n = blockIdx.x * 8 + warp; n < g.N; n += gridDim.x * 8) {
+    const float4* bcol = reinterpret_cast<const float4*>(g.b + static_cast<int64_t>(n) * g.b_ld);
+    float acc[MR];
+#pragma unroll
+    for (int m = 0; m < MR; ++m) acc[m] = 0.f;
+#pragma unroll 4
+    for (int k4 = lane; k4 < kv; k4 += 32) {
+      const float4 bv = __ldg(bcol + k4);
+#pragma unroll
+      for (int m = 0; m < MR; ++m)
+        if (m < g.M) {
+          const float4 av = reinterpret_cast<const float4*>(gemv_a)[m * kv + k4];
+          acc[m] = fmaf(av.x, bv.x, acc[m]);
+          acc[m] = fmaf(av.y, bv.y, acc[m]);
+          acc[m] = fmaf(av.z, bv.z, acc[m]);
+          acc[m] = fmaf(av.w, bv.w, acc[m]);
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < MR; ++m) {
+      float v = acc[m];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && m < g.M) g.D[static_cast<int64_t>(m) * g.d_ld + n] = gemv_finish(g, v, m, n);
+    }
+  }
+}
+
 // ---------------------------------------------------------------- MN-major B: a thread per 4 columns
 template <int MR>
 __global__ void __launch_bounds__(256) gemv_mnmajor_kernel(const GemvArgs g) {
@@ -210,6 +253,23 @@ rtg_status gemv_device(Context* ctx, MatView a, MatView b, float* D, OutMap dmap
     if (vec) gemv_kmajor_kernel<MR, NC, true><<<blocks, 256, 0, ctx->stream>>>(g);          \
     else gemv_kmajor_kernel<MR, NC, false><<<blocks, 256, 0, ctx->stream>>>(g);             \
   } while (0)
+    const size_t a_bytes = static_cast<size_t>(g.M) * g.K * 4;
+    if (g.M > 1 && vec && nc == 1 && a_bytes <= kGemvSmemBytes) {
+      // same summation order as gemv_kmajor_kernel<MR, 1, true> (lane-strided float4 steps, then the shuffle tree)
+      const int sblocks = static_cast<int>(std::min<int64_t>(div_ceil(g.N, 8), static_cast<int64_t>(ctx->num_sms) * 2));
+      auto kern = g.M <= 4 ? gemv_kmajor_smem_kernel<4> : gemv_kmajor_smem_kernel<8>;
+      static bool configured[2][16] = {};
+      bool& done = configured[g.M <= 4 ? 0 : 1][ctx->device & 15];
+      if (!done) {
+        RTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemvSmemBytes));
+        done = true;
+      }
+      kern<<<sblocks, 256, a_bytes, ctx->stream>>>(g);
+      ctx->last_kernel = "gemv<B=K,float4,A in smem>";
+      ctx->launches++;
+      RTG_CUDA(cudaGetLastError());
+      return RTG_OK;
+    }
     if (g.M <= 1) RTG_GEMV_K(1, 1);
     else if (g.M <= 4 && nc == 4) RTG_GEMV_K(4, 4);
     else if (g.M <= 4) RTG_GEMV_K(4, 1);
