@@ -14,7 +14,7 @@
 //                                 tile's columns.  MODE 1/2: also fold every 4-k-block accumulation chunk into fp32
 //                                 running sums (round-to-nearest adds)
 //   warp 8        TMA producer    the whole warp walks the loop, an elected lane issues.  MODE 0: A and B tiles of a
-//                                 stage; MODE 1: raw A tiles (own 3-slot ring) and raw B tiles; MODE 2: raw A tiles
+//                                 stage; MODE 1: raw A tiles (own ring: 3 slots at BN = 128, 5 at BN <= 64) and raw B tiles; MODE 2: raw A tiles
 //                                 only (tiled, im2col-mode, row-window or batched maps)
 //   warp 9        MMA issuer      whole warp walks the loop, an elected lane issues tcgen05.mma + commits; TMEM
 //                                 allocation; accumulators double-buffered in TMEM
@@ -34,7 +34,7 @@
 //                  lo = rna_tf32(x - trunc19(x));
 //                  acc += lo_A*hi_B + hi_A*lo_B + hi_A*hi_B.
 //   The tensor core adds into the TMEM accumulator with truncation, which for long K drifts past the reference's
-//   1e-5 tolerance (measured 2.3e-5 at K=1024).  MODE 1 therefore accumulates in TMEM only over chunks of
+//   1e-5 tolerance (measured 2.3e-5 at K=1024).  MODE 1 and 2 therefore accumulate in TMEM only over chunks of
 //   kChunkKb k-blocks; the epilogue warps drain each chunk and keep the running sum in registers with
 //   round-to-nearest adds (the same two-level scheme the reference gets from its kc=256 depth blocks, src/gemm.rs:546).
 #pragma once
@@ -148,8 +148,8 @@ struct GemmArgs {
 constexpr int kFlagDebugHi = 1;  // (debug) MODE 1 also overwrites the raw operand tile with its hi part
 constexpr int kFlagStagedD = 2;  // result leaves through shared memory + TMA store (row-major D, 16-byte aligned)
 constexpr int kFlagStagedR = 4;  // residual arrives by TMA load into the same staging buffer (needs kFlagStagedD)
-constexpr int kFlagDebugNoB = 32, kFlagDebugNoA = 64;
-constexpr int kFlagBConst = 512;   // the packed B operand was written at load time: nothing in this stream produces it  // (debug) MODE 2: skip the B / A TMA stream (timing experiments)
+constexpr int kFlagDebugNoB = 32, kFlagDebugNoA = 64;  // (debug, wrong results) MODE 2: skip the B / A TMA stream (timing experiments)
+constexpr int kFlagBConst = 512;   // the packed B operand was written at load time: nothing in this stream produces it
 constexpr int kFlagAlphaDiv = 16;  // alpha is a divisor: D = acc / alpha (8 is the debug "no staging" switch)
 
 constexpr int kBM = 128;
