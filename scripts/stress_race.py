@@ -29,6 +29,17 @@ for (B, C, O, H, k, s) in [(4, 512, 512, 7, 3, 1), (4, 256, 256, 14, 3, 1), (4, 
 for n, kk in [(1024, 1024), (257, 1000), (2048, 512)]:
     a, bm = torch.rand((n, kk), device="cuda") - 0.5, torch.rand((kk, n), device="cuda") - 0.5
     cases.append((f"gemm {n}x{n}x{kk}", lambda a=a, bm=bm: ops.matmul(a, bm, ctx=ctx)))
+# the TMA-staged depthwise kernel (row ring, warp-granular slot release) and the gemv kernels
+for (B, C, H, s) in [(8, 96, 56, 2), (8, 144, 28, 1), (4, 960, 7, 1)]:
+    x = (torch.rand((B, C, H, H), device="cuda") - 0.4).contiguous(memory_format=cl)
+    w = torch.rand((C, 1, 3, 3), device="cuda") - 0.5
+    b = torch.rand((C,), device="cuda")
+    cases.append((f"depthwise {C}ch {H}x{H} s{s}", lambda x=x, w=w, b=b, C=C, s=s: ops.conv(
+        x, w, b, padding=(1, 1, 1, 1), groups=C, strides=(s, s), activation="clip", clip=(0.0, 6.0), out_nhwc=True, ctx=ctx)))
+for (m, n, kk, tb) in [(1, 4096, 512, False), (8, 1000, 2048, True), (3, 1000, 2048, True)]:
+    a = torch.rand((m, kk), device="cuda") - 0.5
+    bm = (torch.rand((n, kk), device="cuda") - 0.5).t() if tb else torch.rand((kk, n), device="cuda") - 0.5
+    cases.append((f"gemv {m}x{n}x{kk}", lambda a=a, bm=bm: ops.matmul(a, bm, ctx=ctx)))
 sa, sb = torch.rand((64, 64), device="cuda"), torch.rand((64, 64), device="cuda")
 bad_total = 0
 for mode in (sys.argv[2].split(",") if len(sys.argv) > 2 else ("3xtf32", "tf32_bf16x2", "tf32")):

@@ -346,3 +346,45 @@ def test_conv_transpose_in_a_model(rtg, ctx, oracle):
     want = graph_oracle.run_graph(b, [xin])
     assert got[0].shape == (2, 5, 12, 12)
     expect_equal(got[0], want[0], rtol=1e-5, atol=1e-5)
+
+
+DW_CASES = [
+    # (N, C, H, W, stride, pads (t, l, b, r), activation, bias)
+    (1, 4, 1, 1, 1, (1, 1, 1, 1), "none", True),
+    (2, 20, 2, 5, 1, (1, 1, 1, 1), "relu", True),
+    (1, 36, 7, 7, 1, (1, 1, 1, 1), "clip", True),
+    (3, 100, 9, 33, 1, (0, 1, 2, 1), "clip", False),      # ragged: last strip partial, asymmetric padding
+    (1, 144, 14, 14, 2, (1, 1, 1, 1), "clip", True),      # five 32-channel blocks, the last one half empty
+    (2, 260, 30, 65, 1, (1, 1, 1, 1), "none", True),      # two column bands, 65 = 64 + 1
+    (1, 32, 57, 130, 2, (0, 0, 1, 1), "relu", True),      # stride 2, odd sizes, no top / left padding
+    (1, 96, 112, 112, 2, (1, 1, 1, 1), "clip", True),     # MobileNetV2's first stride-2 layer (several row bands)
+    (2, 960, 7, 7, 1, (1, 1, 1, 1), "clip", True),        # 256-channel blocks, 8-column band
+    (1, 8, 40, 3, 1, (2, 2, 2, 2), "none", False),        # padding wider than the kernel's reach
+    (1, 64, 5, 300, 2, (1, 0, 0, 2), "clip", True),       # many column bands, stride 2
+]
+
+
+@pytest.mark.parametrize("n,c,h,w,s,pads,act,with_bias", DW_CASES)
+def test_depthwise3x3_tma_is_bit_exact(rtg, ctx, oracle, n, c, h, w, s, pads, act, with_bias):
+    """The TMA-staged depthwise kernel (csrc/depthwise_tma.cuh) keeps the reference's summation order (bias, taps in
+    (ky, kx) order, separate multiply and add, padding taps skipped: src/ops/conv/depthwise.rs:49-120): its results
+    equal the oracle's bit for bit over band / block / row-band edges, asymmetric paddings and both strides."""
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(c * 1000 + h * 10 + w)
+    x = rng.fill((n, c, h, w)) - 0.5
+    wt = rng.fill((c, 1, 3, 3)) - 0.5
+    b = rng.fill((c,)) - 0.5 if with_bias else None
+    oh = (h + pads[0] + pads[2] - 3) // s + 1
+    ow = (w + pads[1] + pads[3] - 3) // s + 1
+    if oh <= 0 or ow <= 0:
+        pytest.skip("empty output")
+    got = ops.conv(x, wt, b, padding=pads, groups=c, strides=(s, s), activation=act, clip=(-0.25, 0.5), ctx=ctx)
+    assert ctx.last_kernel.startswith("depthwise3x3_tma"), ctx.last_kernel
+    want = oracle.conv2d(x, wt, b, pads, c, (s, s), (1, 1))
+    if act == "relu":
+        want = oracle.unary("relu", want)
+    elif act == "clip":
+        want = oracle.unary("clip", want, -0.25, 0.5)
+    assert got.shape == want.shape == (n, c, oh, ow)
+    np.testing.assert_array_equal(got, want)
