@@ -154,7 +154,10 @@ static rtg_status b_pack_map(Context* ctx, const Epilogue& ep, MatView b, int bn
   }
   cuuint64_t dims[3] = {static_cast<cuuint64_t>(bp.ld), static_cast<cuuint64_t>(b.cols), 2};
   cuuint64_t strides[2] = {static_cast<cuuint64_t>(bp.ld) * 4, static_cast<cuuint64_t>(bp.plane) * 4};
-  cuuint32_t box[3] = {kBK, static_cast<cuuint32_t>(bn), 2};
+  // (debug flag 128, wrong results, timing only) half the rows per box: what the stage would receive if a CTA pair shared
+  // the B tile (cta_group::2), i.e. half the shared-memory write traffic of the B stream
+  static const bool half_b = []() { const char* e = getenv("RTG_DEBUG_FLAGS"); return e && (atoi(e) & 128); }();
+  cuuint32_t box[3] = {kBK, static_cast<cuuint32_t>(half_b ? bn / 2 : bn), 2};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(bp.p), dims, strides, box,
                                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,

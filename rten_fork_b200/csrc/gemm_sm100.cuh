@@ -838,7 +838,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (args.flags & kFlagDebugNoB) {  // (debug, wrong results) timing without the B stream
             ptx::mbar_arrive(full_bar(s));
           } else {
-            ptx::mbar_expect_tx(full_bar(s), 2 * Cfg::kBBytes);
+            ptx::mbar_expect_tx(full_bar(s), (args.flags & 128) ? Cfg::kBBytes : 2 * Cfg::kBBytes);  // 128: debug half box
             ptx::tma_load_3d(ring_base + s * Cfg::kStageBytes, &tmB2, full_bar(s), kb * kBK, n0, 0);
           }
         }
