@@ -252,16 +252,14 @@ __device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
   } else if (act == ACT_CLIP) {
-    // f32::clamp (NaN stays NaN, -0.0 stays -0.0) as two compares and two selects: the nested ?: compiled to a branch
-    // per element, and the MobileNetV2 pointwise layers (K = 16 ... 32, one k-block per tile) were bound by exactly
-    // that (ncu: the epilogue's stalls were branch_resolving / wait inside this loop)
+    // f32::clamp as max.NaN / min.NaN: NaN stays NaN like the reference's clamp (plain max / min would return the bound);
+    // the one difference is the sign of a zero (-0.0 clamped at lo = +0.0 leaves as +0.0, equal in value).  The nested ?:
+    // compiled to a branch per element, and the MobileNetV2 pointwise layers (K = 16 ... 32, one k-block per tile) were
+    // bound by exactly that (ncu: the epilogue's stalls were branch_resolving / wait inside this loop)
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       float r;
-      asm("{\n\t.reg .pred p, q;\n\tsetp.lt.f32 p, %1, %2;\n\tsetp.gt.f32 q, %1, %3;\n\t"
-          "selp.f32 %0, %3, %1, q;\n\tselp.f32 %0, %2, %0, p;\n\t}"
-          : "=f"(r)
-          : "f"(v[j]), "f"(lo), "f"(hi));
+      asm("{\n\t.reg .f32 t;\n\tmax.NaN.f32 t, %1, %2;\n\tmin.NaN.f32 %0, t, %3;\n\t}" : "=f"(r) : "f"(v[j]), "f"(lo), "f"(hi));
       v[j] = r;
     }
   } else {
