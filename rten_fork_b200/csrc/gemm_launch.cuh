@@ -36,12 +36,12 @@ rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma
 
 #ifdef RTG_GEMM_INSTANTIATE
 // ---------------------------------------------------------------- launch
-template <int BN, int MODE, int A_KIND, int B_MAJOR>
+template <int BN, int MODE, int A_KIND, int B_MAJOR, bool EPI2 = false>
 static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2,
                          const CUtensorMap& md, const CUtensorMap& mr, const GemmArgs& args,
                          const ReduceArgs* red = nullptr) {
-  using Cfg = GemmCfg<BN, MODE>;
-  auto kern = gemm_tcgen05_kernel<BN, MODE, A_KIND, B_MAJOR>;
+  using Cfg = GemmCfg<BN, MODE, EPI2>;
+  auto kern = gemm_tcgen05_kernel<BN, MODE, A_KIND, B_MAJOR, EPI2>;
   static bool configured[16] = {};  // per device
   if (!configured[ctx->device & 15]) {
     RTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -106,7 +106,7 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
     static const char* roles[4] = {"tma", "mma", "epi", "split"};
     static const char* slots[4][4] = {{"wait_empty", "issue", "-", "-"},
                                       {"wait_tempty", "wait_full", "issue", "-"},
-                                      {"wait_tfull", "wait_resid", "wait_stread", "wait_stdone"},
+                                      {"waits(tfull,resid,stread)", "drain(ldtm)", "math(bias,res,act)", "stage+store+setup"},
                                       {"wait_afull", "wait_empty", "st_wait_and_arrive", "lds_and_split"}};
     fprintf(stderr, "[prof] BN=%d mode=%d akind=%d grid=%d M=%d N=%d kb=%d:", BN, MODE, A_KIND, grid, args.M, args.N,
             args.num_kb);
@@ -141,8 +141,9 @@ static rtg_status launch(Context* ctx, const CUtensorMap& ma, const CUtensorMap&
   char name[96];
   char sk[24] = "";
   if (args.splits > 1) snprintf(sk, sizeof(sk), ",splitK=%d", args.splits);
-  snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s%s>", BN, MODE == 2 ? "TF32+BF16x2" : MODE ? "3xTF32" : "TF32",
-           A_KIND == 3 ? "batched" : A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K", sk);
+  snprintf(name, sizeof(name), "gemm_tcgen05<BN=%d,%s,%s,B=%s%s%s>", BN, MODE == 2 ? "TF32+BF16x2" : MODE ? "3xTF32" : "TF32",
+           A_KIND == 3 ? "batched" : A_KIND == 2 ? "window" : A_KIND ? "im2col" : "tiled", B_MAJOR ? "MN" : "K", sk,
+           EPI2 ? ",epi2" : "");
   ctx->last_kernel = name;
   return RTG_OK;
 }
@@ -159,6 +160,16 @@ rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma
   } else if (mode == RTG_MATH_TF32_BF16X2 && A_KIND != 3) {  // batched products keep the three-MMA split
     // this mode reads B through its packed K-major copy: there is no MN-major variant
     if constexpr (B_MAJOR == 0) {
+      // tiles with few k-blocks are paced by their epilogue: two staging buffers per warp (GemmCfg EPI2)
+      static const int epi2_kb = []() {
+        const char* e = getenv("RTG_EPI2_KB");  // developer switch: 0 disables
+        return e ? atoi(e) : 4;  // measured on the ResNet-50 layer table: 4 beats 0, 8 and 16
+      }();
+      const int kb_per_unit = args.splits > 1 ? args.kb_per_split : args.num_kb;
+      if (kb_per_unit <= epi2_kb && (args.flags & kFlagStagedD)) {
+        if (bn == 64) return launch<64, 2, A_KIND, 0, true>(ctx, ma, mb, mb2, md, mr, args, redp);
+        if (bn == 128) return launch<128, 2, A_KIND, 0, true>(ctx, ma, mb, mb2, md, mr, args, redp);
+      }
       if (bn == 64) return launch<64, 2, A_KIND, 0>(ctx, ma, mb, mb2, md, mr, args, redp);
       if (bn == 128) return launch<128, 2, A_KIND, 0>(ctx, ma, mb, mb2, md, mr, args, redp);
     } else {

@@ -157,7 +157,11 @@ constexpr int kBK = 32;  // floats per k-block (128 bytes)
 constexpr int kABytes = kBM * kBK * 4;
 constexpr int kChunkKb = 4;  // MODE 1: k-blocks accumulated in TMEM before the epilogue folds them (K = 128)
 
-template <int BN, int MODE>
+// EPI2 (fp32-accurate modes only): two epilogue staging buffers per warp instead of one, paid for with pipeline stages
+// (BN = 128: 2 instead of 4).  For launches whose tiles have few k-blocks the epilogue is what a tile waits for: with one
+// buffer the TMA store of chunk i has to finish reading it (~2000 cycles) before the residual of chunk i + 1 can be
+// loaded into it (~1000 more) -- measured 10 K cycles per 128 x 128 tile on ResNet-50's K = 64 residual layers.
+template <int BN, int MODE, bool EPI2 = false>
 struct GemmCfg {
   static_assert(MODE == 0 || BN <= 128, "3xTF32 keeps BN/2 running sums per epilogue thread in registers");
   static constexpr int kBBytes = BN * kBK * 4;
@@ -184,7 +188,7 @@ struct GemmCfg {
   // finished, and the TMA store of chunk i may still read its buffer while chunk i+1 is written.  With one buffer the
   // short-K layers (ResNet layer1/2 pointwise convs, K = 64..128) were bound by this chain, not by HBM.
   // 3xTF32 keeps one buffer: the pipeline stage the extra 32 KB would cost is worth more there.
-  static constexpr int kEpiBufs = MODE != 0 ? 1 : 2;
+  static constexpr int kEpiBufs = (MODE != 0 && !EPI2) ? 1 : 2;
   static constexpr int kEpiBufBytes = 4096;
   // Column bias of the whole launch (zero padded to n_tiles * BN entries), loaded once per CTA; launches with more
   // output columns than this fall back to a per-tile slice per warp at the start of the same region.
@@ -267,12 +271,12 @@ __device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float
   }
 }
 
-template <int BN, int MODE, int A_KIND, int B_MAJOR>
-__global__ void __launch_bounds__(GemmCfg<BN, MODE>::kThreads, 1)
+template <int BN, int MODE, int A_KIND, int B_MAJOR, bool EPI2 = false>
+__global__ void __launch_bounds__(GemmCfg<BN, MODE, EPI2>::kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ CUtensorMap tmD,
                     const __grid_constant__ CUtensorMap tmR, const GemmArgs args) {
-  using Cfg = GemmCfg<BN, MODE>;
+  using Cfg = GemmCfg<BN, MODE, EPI2>;
 #ifdef RTG_PROF
   const long long prof_entry_ = clock64();
   if (threadIdx.x == 0 && args.prof) {
@@ -631,6 +635,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int as = 0;
     uint32_t aph = 0;
     PROF_DECL;
+    PROF_LINE_DECL;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
       const int split = unit / num_tiles, tile = unit - split * num_tiles;
       const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
@@ -681,9 +686,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
           // earlier stores of this warp no longer read the buffer
           if (newer > 0) {
-            PROF_WAIT(2, ptx::bulk_wait_read<1>());
+            ptx::bulk_wait_read<1>();
           } else {
-            PROF_WAIT(2, ptx::bulk_wait_read<0>());
+            ptx::bulk_wait_read<0>();
           }
           ptx::mbar_expect_tx(rbar(warp, b), Cfg::kEpiBufBytes);
           ptx::tma_load_3d(ebuf0 + b * Cfg::kEpiBufBytes, &tmR, rbar(warp, b), n0 + c0, st_r, st_z);
@@ -717,7 +722,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t row = buf + lane * 128;
           const uint32_t sw = lane & 7;
           if (staged_r) {
-            PROF_WAIT(1, ptx::mbar_wait_parked(rbar(warp, eb), (rph >> eb) & 1u));
+            PROF_LINE(2);
+            ptx::mbar_wait_parked(rbar(warp, eb), (rph >> eb) & 1u);
+            PROF_LINE(0);
             rph ^= 1u << eb;
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
@@ -728,22 +735,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               v[4 * j4 + 3] += args.beta * r.w;
             }
           } else {
-            PROF_WAIT(2, if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>(); __syncwarp());
+            PROF_LINE(2);
+            if (lane == 0) ptx::bulk_wait_read<Cfg::kEpiBufs - 1>();
+            __syncwarp();
+            PROF_LINE(0);
             if (args.R != nullptr && row_ok)  // residual that TMA cannot address (unaligned / NCHW): direct loads
               RTG_EPI_COLD(epi_cold_residual(t_, args.R + r_base + static_cast<int64_t>(n0 + c0) * r_cs, r_cs, args.beta, ncols));
           }
           epi_act(v, args.act, args.act_lo, args.act_hi);
+          PROF_LINE(2);
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4)
             ptx::sts_v4(row + ((j4 ^ sw) << 4), make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]));
           ptx::fence_proxy_async_smem();
           __syncwarp();
+#ifdef RTG_PROF_EPI_FINE
+          PROF_LINE(1);
+#endif
           if (lane == 0) {
             ptx::tma_store_3d(&tmD, buf, n0 + c0, st_r, st_z);  // clipped to the tensor bounds by the TMA unit
             for (int p = 0; p < args.n_peers; ++p) ptx::tma_store_3d(args.peer_maps + p, buf, n0 + c0, st_r, st_z);
             ptx::bulk_commit();
           }
           if (Cfg::kEpiBufs > 1) eb ^= 1;
+          PROF_LINE(3);
           return;
         }
         // outputs TMA cannot address (NCHW for a host caller, unaligned rows): strided stores, out of line
@@ -763,7 +778,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (Cfg::kEpiBufs > 1 && staged_r && nch > 1) fetch_residual(col0 + 32, eb ^ 1, 0);
 
       if (!kChunked) {
-        PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
+        PROF_LINE(3);
+          ptx::mbar_wait_parked(tfull_bar(as), aph);
+          PROF_LINE(0);
         ptx::tc_fence_after();
 #pragma unroll 1
         for (int i = 0; i < nch; ++i) {
@@ -786,7 +803,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // running sums in registers, one per output column of this thread's row
         float acc[kCols];
         for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
-          PROF_WAIT(0, ptx::mbar_wait_parked(tfull_bar(as), aph));
+          PROF_LINE(3);
+          ptx::mbar_wait_parked(tfull_bar(as), aph);
+          PROF_LINE(0);
           ptx::tc_fence_after();
 #pragma unroll
           for (int c0 = 0; c0 < kCols; c0 += 32) {
@@ -808,6 +827,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             as = 0;
             aph ^= 1u;
           }
+          PROF_LINE(1);
         }
 #pragma unroll 1
         for (int ci = 0; ci < nch; ++ci) {  // one call site of `finish`: the chunk is selected, not unrolled
@@ -821,7 +841,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     // the stores must have READ their staging buffers before shared memory goes away; their global writes complete with
     // the grid (a dependent launch waits for that in griddepcontrol.wait)
-    PROF_WAIT(3, if (staged_d && lane == 0) ptx::bulk_wait_read<0>());
+    if (staged_d && lane == 0) ptx::bulk_wait_read<0>();
+    PROF_LINE(0);
     if (warp == 0 && lane == 0) {
       PROF_MARK_LAST(2, 5);  // epilogue drained (stores complete)
       PROF_DUMP(2);
