@@ -549,7 +549,7 @@ def hbm_section(torch, R, ops, ctx, stream):
         x = nhwc(32, 64, 112, 112)
         y = torch.empty((32, 64, 56, 56), device=dev).contiguous(memory_format=torch.channels_last)
         timed(lambda: ops.max_pool(x, (3, 3), (2, 2), (1, 1, 1, 1), ctx=ctx, out=y), 4.0 * (x.numel() + y.numel()),
-              "maxpool3x3_s2_64ch_112", "maxpool_nhwc4_kernel<3,3>")
+              "maxpool3x3_s2_64ch_112", "maxpool_nhwc4_rows2_kernel<3,3,2>")
         del x, y
         # Softmax over BERT's score rows and LayerNormalization over its hidden rows, scaled past L2
         for name, op, cols, attrs, extra in (

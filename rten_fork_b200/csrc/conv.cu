@@ -233,9 +233,28 @@ static rtg_status launch_depthwise3x3_tma(Context* ctx, float* out, const float*
   t.ch_blocks = static_cast<int>(div_ceil(g.c, cb));
   t.bands = static_cast<int>(div_ceil(g.ow, t.tw));
   const int64_t columns = static_cast<int64_t>(g.n) * t.ch_blocks * t.bands;
-  // row bands: ~8 jobs per SM, at least 4 output rows each (a band re-reads 2 / STRIDE halo rows, mostly from L2)
-  const int64_t want = std::max<int64_t>(1, div_ceil(static_cast<int64_t>(ctx->num_sms) * 8, columns));
-  t.rows_per_job = static_cast<int>(std::max<int64_t>(std::min<int64_t>(4, g.oh), div_ceil(g.oh, want)));
+  // Row bands.  CTAs share an SM's issue slots and HBM bandwidth, so a launch takes about (jobs an SM is handed) x (rows a
+  // job streams: its output rows x stride, 2 halo rows, ~3 rows' worth of start-up); 4 CTAs fit an SM (126 registers x
+  // 128 threads; the ring is <= 51 KB).  Pick the band count with the smallest estimate, at least 4 output rows per job.
+  const int smem_bytes = kDwRing * t.row_bytes;
+  const int64_t per_sm = std::max<int64_t>(1, std::min<int64_t>(RTG_DW_MINB > 4 ? RTG_DW_MINB : 4, (227 * 1024) / (smem_bytes + 1024)));
+  static const int rows_env = [] { const char* e = std::getenv("RTG_DW_ROWS"); return e ? std::atoi(e) : 0; }();
+  static const int pred_env = [] { const char* e = std::getenv("RTG_DW_PRED"); return e ? std::atoi(e) : 0; }();
+  t.force_pred = pred_env;
+  int best_rows = g.oh;
+  double best_cost = 1e300;
+  for (int64_t rb = 1; rb <= g.oh; ++rb) {
+    const int rows = static_cast<int>(div_ceil(g.oh, rb));  // the most even cut into rb bands
+    if (rows < std::min(4, g.oh)) break;
+    if (div_ceil(g.oh, rows) != rb) continue;  // the same cut as a smaller band count
+    const int64_t jobs_r = columns * rb;
+    const double rounds = static_cast<double>(div_ceil(jobs_r, static_cast<int64_t>(ctx->num_sms)));
+    // fewer resident CTAs than an SM can hold leave the per-row latency exposed
+    const double thin = jobs_r < ctx->num_sms * per_sm ? static_cast<double>(ctx->num_sms * per_sm) / jobs_r : 1.0;
+    const double cost = rounds * (rows * stride + 2 + 3) * std::min(thin, 2.0);
+    if (cost < best_cost - 1e-9) best_cost = cost, best_rows = rows;
+  }
+  t.rows_per_job = rows_env > 0 ? std::min(rows_env, g.oh) : best_rows;
   t.row_bands = static_cast<int>(div_ceil(g.oh, t.rows_per_job));
   const int64_t jobs = columns * t.row_bands;
   if (jobs > INT32_MAX) return set_error(RTG_ERR_UNSUPPORTED_VALUE, "depthwise convolution: too many tiles");
@@ -253,7 +272,7 @@ static rtg_status launch_depthwise3x3_tma(Context* ctx, float* out, const float*
   if (r != CUDA_SUCCESS)
     return set_errorf(RTG_ERR_CUDA, "cuTensorMapEncodeTiled (depthwise input) failed (%d): dims [%d,%d,%d,%d] box [%d,%d]",
                       (int)r, g.c, g.w, g.h, g.n, cb, t.iwb);
-  const int smem = kDwRing * t.row_bytes;
+  const int smem = smem_bytes;
   const int ac = g.act == ACT_NONE ? 0 : g.act == ACT_RELU ? 1 : g.act == ACT_CLIP ? 2 : 3;
   using Kern = void (*)(const CUtensorMap, float*, const float*, const float*, const DwGeom, const DwTile);
 #define RTG_DW_ROW(S, A) {depthwise3x3_tma_kernel<S, A, 8>, depthwise3x3_tma_kernel<S, A, 16>, depthwise3x3_tma_kernel<S, A, 32>, depthwise3x3_tma_kernel<S, A, 64>}

@@ -14,13 +14,14 @@
 // registers with three statically rotated copies of the loop, 170-200 registers and 90 K instructions, and ran at the
 // register-window kernel's speed (ncu: 19 % of the stalls were instruction fetch).
 //
-// Exactness: the reference skips taps that fall into the padding instead of adding zeros.  Every tap is predicated
-// (one setp per tap vector, predicated adds; no branches; an unpredicated copy of the loop for windows inside the image
-// measured slower: the branch and the second copy cost more than the 36 setp it saves).  Multiply and add stay separate
-// instructions.
+// Exactness: the reference skips taps that fall into the padding instead of adding zeros.  Adding the zeros the TMA
+// unit filled in is the same bits whenever the channel's weights are finite and its bias is not -0.0 (see `plain` in the
+// kernel), which a warp checks once; otherwise every tap is predicated (one setp per tap vector, predicated adds; no
+// branches).  Multiply and add stay separate instructions in both forms.
 #pragma once
 #include "conv_kernels.cuh"
 #include "sm100_ptx.cuh"
+#include <type_traits>
 
 namespace rtg {
 
@@ -31,15 +32,29 @@ struct DwTile {
   int row_bytes;     // bytes per ring slot (box bytes rounded up to 128)
   int box_bytes;
   int ch_blocks, bands, row_bands, rows_per_job;
+  int force_pred;    // (RTG_DW_PRED=1) always skip padding taps by predicate
 };
 constexpr int kDwTX = 4;  // dw_taps below is written out for 4
-constexpr int kDwRing = 6;
+#ifndef RTG_DW_RING
+#define RTG_DW_RING 6
+#endif
+#ifndef RTG_DW_MINB
+#define RTG_DW_MINB 1
+#endif
+constexpr int kDwRing = RTG_DW_RING;
 constexpr int kDwThreads = 128;
 
 // four channels of one tap: acc += x * w (separate multiply and add, as the reference), skipped unless bit BIT of `mask`
 // is set (the validity of the input column under this tap, zero for a row outside the image)
-template <int BIT>
+template <int BIT, bool PRED>
 __device__ __forceinline__ void dw_tap(float (&acc)[4], const float4 x, const float4 w, const uint32_t mask) {
+  if (!PRED) {  // padding taps add the TMA unit's zeros: see `plain` in the kernel for when that is the same bits
+    acc[0] = __fadd_rn(acc[0], __fmul_rn(x.x, w.x));
+    acc[1] = __fadd_rn(acc[1], __fmul_rn(x.y, w.y));
+    acc[2] = __fadd_rn(acc[2], __fmul_rn(x.z, w.z));
+    acc[3] = __fadd_rn(acc[3], __fmul_rn(x.w, w.w));
+    return;
+  }
   asm("{\n\t.reg .pred p;\n\t.reg .b32 m;\n\t.reg .f32 t0, t1, t2, t3;\n\t"
       "and.b32 m, %12, %13;\n\tsetp.ne.u32 p, m, 0;\n\t"
       "mul.rn.f32 t0, %4, %8;\n\tmul.rn.f32 t1, %5, %9;\n\tmul.rn.f32 t2, %6, %10;\n\tmul.rn.f32 t3, %7, %11;\n\t"
@@ -50,6 +65,12 @@ __device__ __forceinline__ void dw_tap(float (&acc)[4], const float4 x, const fl
 
 // f32::clamp of the reference (src/ops/unary_elementwise.rs:325-339): NaN stays NaN, -0.0 stays -0.0; two compares and
 // two selects, no branches
+// the same for operands where max / min agree with it bit for bit (v is never -0.0, hi is not -0.0, no NaN bounds)
+__device__ __forceinline__ float dw_clip_fast(float v, float lo, float hi) {
+  float r;
+  asm("{\n\t.reg .f32 t;\n\tmax.NaN.f32 t, %1, %2;\n\tmin.NaN.f32 %0, t, %3;\n\t}" : "=f"(r) : "f"(v), "f"(lo), "f"(hi));
+  return r;
+}
 __device__ __forceinline__ float dw_clip(float v, float lo, float hi) {
   float r;
   asm("{\n\t.reg .pred p, q;\n\tsetp.lt.f32 p, %1, %2;\n\tsetp.gt.f32 q, %1, %3;\n\t"
@@ -60,28 +81,28 @@ __device__ __forceinline__ float dw_clip(float v, float lo, float hi) {
 }
 
 // the 3 taps of one kernel row for the 4 output columns of a strip (compile-time column indices)
-template <int STRIDE, int IW>
+template <int STRIDE, int IW, bool PRED>
 __device__ __forceinline__ void dw_taps(float (&acc)[kDwTX][4], const float4 (&row)[IW], const float4 w0, const float4 w1,
                                         const float4 w2, const uint32_t rmask) {
-  dw_tap<0 * STRIDE + 0>(acc[0], row[0 * STRIDE + 0], w0, rmask);
-  dw_tap<1 * STRIDE + 0>(acc[1], row[1 * STRIDE + 0], w0, rmask);
-  dw_tap<2 * STRIDE + 0>(acc[2], row[2 * STRIDE + 0], w0, rmask);
-  dw_tap<3 * STRIDE + 0>(acc[3], row[3 * STRIDE + 0], w0, rmask);
-  dw_tap<0 * STRIDE + 1>(acc[0], row[0 * STRIDE + 1], w1, rmask);
-  dw_tap<1 * STRIDE + 1>(acc[1], row[1 * STRIDE + 1], w1, rmask);
-  dw_tap<2 * STRIDE + 1>(acc[2], row[2 * STRIDE + 1], w1, rmask);
-  dw_tap<3 * STRIDE + 1>(acc[3], row[3 * STRIDE + 1], w1, rmask);
-  dw_tap<0 * STRIDE + 2>(acc[0], row[0 * STRIDE + 2], w2, rmask);
-  dw_tap<1 * STRIDE + 2>(acc[1], row[1 * STRIDE + 2], w2, rmask);
-  dw_tap<2 * STRIDE + 2>(acc[2], row[2 * STRIDE + 2], w2, rmask);
-  dw_tap<3 * STRIDE + 2>(acc[3], row[3 * STRIDE + 2], w2, rmask);
+  dw_tap<0 * STRIDE + 0, PRED>(acc[0], row[0 * STRIDE + 0], w0, rmask);
+  dw_tap<1 * STRIDE + 0, PRED>(acc[1], row[1 * STRIDE + 0], w0, rmask);
+  dw_tap<2 * STRIDE + 0, PRED>(acc[2], row[2 * STRIDE + 0], w0, rmask);
+  dw_tap<3 * STRIDE + 0, PRED>(acc[3], row[3 * STRIDE + 0], w0, rmask);
+  dw_tap<0 * STRIDE + 1, PRED>(acc[0], row[0 * STRIDE + 1], w1, rmask);
+  dw_tap<1 * STRIDE + 1, PRED>(acc[1], row[1 * STRIDE + 1], w1, rmask);
+  dw_tap<2 * STRIDE + 1, PRED>(acc[2], row[2 * STRIDE + 1], w1, rmask);
+  dw_tap<3 * STRIDE + 1, PRED>(acc[3], row[3 * STRIDE + 1], w1, rmask);
+  dw_tap<0 * STRIDE + 2, PRED>(acc[0], row[0 * STRIDE + 2], w2, rmask);
+  dw_tap<1 * STRIDE + 2, PRED>(acc[1], row[1 * STRIDE + 2], w2, rmask);
+  dw_tap<2 * STRIDE + 2, PRED>(acc[2], row[2 * STRIDE + 2], w2, rmask);
+  dw_tap<3 * STRIDE + 2, PRED>(acc[3], row[3 * STRIDE + 2], w2, rmask);
 }
 
 // ACT: 0 none, 1 Relu, 2 Clip, 3 any other activation (apply_act's switch).  CVS: channel vectors per CTA (DwTile::cvs), a
 // template parameter so that the shared-memory loads of a row use immediate offsets (runtime strides cost ~100 address
 // instructions per output row, a fifth of the loop).
 template <int STRIDE, int ACT, int CVS>
-__global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tmX,
+__global__ void __launch_bounds__(kDwThreads, RTG_DW_MINB) depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tmX,
                                                                        float* __restrict__ out,
                                                                        const float* __restrict__ wt,
                                                                        const float* __restrict__ bias, const DwGeom g,
@@ -140,6 +161,20 @@ __global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __gr
     for (int k = 0; k < 9; ++k) w[k] = __ldg(reinterpret_cast<const float4*>(wt + static_cast<int64_t>(k) * g.c + c0));
     if (bias != nullptr) b = __ldg(reinterpret_cast<const float4*>(bias + c0));
   }
+  // Adding a padding tap's zero-filled input instead of skipping the tap gives the same bits unless the product is not a
+  // zero (non-finite weight) or the accumulator is -0.0 (only possible if the bias is -0.0: x + y = -0.0 needs both);
+  // max / min give f32::clamp's bits unless v is -0.0 (ditto), `hi` is -0.0 or a bound is NaN.  Decided per warp.
+  bool plain_t = true;
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k)
+      plain_t = plain_t && isfinite(w[k].x) && isfinite(w[k].y) && isfinite(w[k].z) && isfinite(w[k].w);
+    plain_t = plain_t && __float_as_uint(b.x) != 0x80000000u && __float_as_uint(b.y) != 0x80000000u &&
+              __float_as_uint(b.z) != 0x80000000u && __float_as_uint(b.w) != 0x80000000u;
+    if (ACT == 2)
+      plain_t = plain_t && __float_as_uint(g.act_hi) != 0x80000000u && g.act_lo == g.act_lo && g.act_hi == g.act_hi;
+  }
+  const bool plain = __all_sync(0xffffffffu, plain_t) && !t.force_pred;
   // validity of the input columns under this strip (global input column = bx_w + strip * TX * STRIDE + j)
   const int ix0 = bx_w + strip * TX * STRIDE;
   uint32_t colmask = 0;
@@ -159,6 +194,40 @@ __global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __gr
   const int64_t op_row = static_cast<int64_t>(g.ow) * g.cp_out;
   constexpr int cstride = CVS;  // float4 elements between neighbouring input columns
   int iy = oy0 * STRIDE - g.pad_t;
+  // one output row of this thread.  PRED: padding taps are skipped by predicate (always exact); otherwise they add the
+  // zeros the TMA unit filled in, and Clip is max / min
+  auto row_body = [&](auto pred_tag) {
+    constexpr bool PRED = decltype(pred_tag)::value;
+    float acc[TX][4];
+#pragma unroll
+    for (int j = 0; j < TX; ++j) acc[j][0] = b.x, acc[j][1] = b.y, acc[j][2] = b.z, acc[j][3] = b.w;
+    int slot = s0;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const float4* sp = sp0 + slot * slot_vecs;
+      if (++slot == kDwRing) slot = 0;
+      float4 row[IW];
+#pragma unroll
+      for (int j = 0; j < IW; ++j) row[j] = sp[j * cstride];
+      const uint32_t rmask = (PRED && iy + ky >= 0 && iy + ky < g.h) ? colmask : 0u;
+      dw_taps<STRIDE, IW, PRED>(acc, row, w[ky * 3], w[ky * 3 + 1], w[ky * 3 + 2], rmask);
+    }
+#pragma unroll
+    for (int j = 0; j < TX; ++j) {
+      if (ACT == 1) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[j][i] = fmaxf(acc[j][i], 0.f);
+      } else if (ACT == 2) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          acc[j][i] = PRED ? dw_clip(acc[j][i], g.act_lo, g.act_hi) : dw_clip_fast(acc[j][i], g.act_lo, g.act_hi);
+      } else if (ACT == 3) {
+        apply_act_array(acc[j], g.act, g.act_lo, g.act_hi);
+      }
+      if (ox0 + j < g.ow)
+        *reinterpret_cast<float4*>(op + static_cast<int64_t>(j) * g.cp_out) = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+    }
+  };
   for (int oy = oy0; oy < oy1; ++oy, iy += STRIDE, op += op_row) {
     const int k0 = (oy - oy0) * STRIDE;  // the output row reads input rows k0, k0 + 1, k0 + 2 of the job
     // thread 0 refills the slots of the rows the previous output row released, once every warp is done with them
@@ -177,33 +246,10 @@ __global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __gr
       if (++w_slot == kDwRing) w_slot = 0, w_ph ^= 1u;
     }
     if (active) {
-      float acc[TX][4];
-#pragma unroll
-      for (int j = 0; j < TX; ++j) acc[j][0] = b.x, acc[j][1] = b.y, acc[j][2] = b.z, acc[j][3] = b.w;
-      int slot = s0;
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const float4* sp = sp0 + slot * slot_vecs;
-        if (++slot == kDwRing) slot = 0;
-        float4 row[IW];
-#pragma unroll
-        for (int j = 0; j < IW; ++j) row[j] = sp[j * cstride];
-        const uint32_t rmask = (iy + ky >= 0 && iy + ky < g.h) ? colmask : 0u;
-        dw_taps<STRIDE>(acc, row, w[ky * 3], w[ky * 3 + 1], w[ky * 3 + 2], rmask);
-      }
-#pragma unroll
-      for (int j = 0; j < TX; ++j) {
-        if (ACT == 1) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) acc[j][i] = fmaxf(acc[j][i], 0.f);
-        } else if (ACT == 2) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) acc[j][i] = dw_clip(acc[j][i], g.act_lo, g.act_hi);
-        } else if (ACT == 3) {
-          apply_act_array(acc[j], g.act, g.act_lo, g.act_hi);
-        }
-        if (ox0 + j < g.ow)
-          *reinterpret_cast<float4*>(op + static_cast<int64_t>(j) * g.cp_out) = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      if (plain) {
+        row_body(std::false_type{});
+      } else {
+        row_body(std::true_type{});
       }
     }
     // the rows the next output row no longer reads go back to the producer

@@ -131,6 +131,54 @@ __global__ void __launch_bounds__(256) maxpool_nhwc4_kernel(float* __restrict__ 
   }
 }
 
+// The same with two output rows (oy, oy + 1) per thread: their windows share KH - SH input rows, so a thread issues
+// (KH + SH) x KW loads for two results instead of 2 x KH x KW, and the rows both windows read cross L1 / L2 once.
+// Each result folds its own window in (ky, kx) order: identical bits.
+template <int KH, int KW, int SH>
+__global__ void __launch_bounds__(256) maxpool_nhwc4_rows2_kernel(float* __restrict__ out, const float* __restrict__ in, PoolGeom g) {
+  constexpr int R = KH + SH;
+  const int c4 = g.c >> 2;
+  const int ohp = (g.oh + 1) >> 1;
+  const int total = g.n * ohp * g.ow * c4;
+  const float ninf = __int_as_float(0xff800000);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int r = i;
+    const int cq = r % c4;
+    r /= c4;
+    const int ox = r % g.ow;
+    r /= g.ow;
+    const int oy = (r % ohp) * 2;
+    const int n = r / ohp;
+    const bool two = oy + 1 < g.oh;
+    const float4* ip = reinterpret_cast<const float4*>(in + static_cast<int64_t>(n) * g.h * g.w * g.c) + cq;
+    const int iy0 = oy * SH - g.pad_t, ix0 = ox * g.stride_w - g.pad_l;
+    float4 v[R][KW];
+#pragma unroll
+    for (int ky = 0; ky < R; ++ky) {
+#pragma unroll
+      for (int kx = 0; kx < KW; ++kx) {
+        const int iy = iy0 + ky, ix = ix0 + kx;
+        const bool ok = iy >= 0 && iy < g.h && ix >= 0 && ix < g.w && (ky < KH || two);
+        v[ky][kx] = ok ? __ldg(ip + (iy * g.w + ix) * c4) : make_float4(ninf, ninf, ninf, ninf);
+      }
+    }
+    float4* op = reinterpret_cast<float4*>(out) + ((static_cast<int64_t>(n) * g.oh + oy) * g.ow + ox) * c4 + cq;
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+      float4 acc = make_float4(ninf, ninf, ninf, ninf);
+#pragma unroll
+      for (int ky = 0; ky < KH; ++ky) {
+#pragma unroll
+        for (int kx = 0; kx < KW; ++kx) {
+          const float4 x = v[o * SH + ky][kx];
+          acc.x = fmaxf(acc.x, x.x), acc.y = fmaxf(acc.y, x.y), acc.z = fmaxf(acc.z, x.z), acc.w = fmaxf(acc.w, x.w);
+        }
+      }
+      if (o == 0 || two) op[static_cast<int64_t>(o) * g.ow * c4] = acc;
+    }
+  }
+}
+
 // One warp per (n, c) for NCHW (contiguous plane, shuffle reduction); for NHWC one thread per (n, c) column walks the
 // pixels so that a warp reads 32 consecutive channels per pixel (coalesced).
 __global__ void gap_nchw_kernel(float* __restrict__ out, const float* __restrict__ in, int64_t nc, int hw, int c,
@@ -217,9 +265,25 @@ rtg_status pool2d_forward(Context* ctx, int kind, const rtg_tensor& in, const rt
     const int blocks4 = static_cast<int>(std::min<int64_t>(div_ceil(total / 4, 256), static_cast<int64_t>(ctx->num_sms) * 32));
     float* op = static_cast<float*>(out.data);
     const float* ip = static_cast<const float*>(in.data);
-    if (kind == RTG_POOL_MAX && g.kh == 3 && g.kw == 3) maxpool_nhwc4_kernel<3, 3><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
-    else if (kind == RTG_POOL_MAX && g.kh == 2 && g.kw == 2) maxpool_nhwc4_kernel<2, 2><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
-    else pool2d_nhwc4_kernel<<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+    static const bool rows2 = [] { const char* e = std::getenv("RTG_POOL_ROWS2"); return !e || std::atoi(e) != 0; }();
+    const int64_t pairs4 = shape[0] * ((shape[2] + 1) / 2) * shape[3] * (shape[1] / 4);
+    const int blocks_r2 = static_cast<int>(std::min<int64_t>(div_ceil(pairs4, 256), static_cast<int64_t>(ctx->num_sms) * 64));
+    if (rows2 && kind == RTG_POOL_MAX && g.kh == 3 && g.kw == 3 && g.stride_h == 2) {
+      maxpool_nhwc4_rows2_kernel<3, 3, 2><<<blocks_r2, 256, 0, ctx->stream>>>(op, ip, g);
+      ctx->last_kernel = "maxpool_nhwc4<3x3,two rows>";
+    } else if (rows2 && kind == RTG_POOL_MAX && g.kh == 3 && g.kw == 3 && g.stride_h == 1) {
+      maxpool_nhwc4_rows2_kernel<3, 3, 1><<<blocks_r2, 256, 0, ctx->stream>>>(op, ip, g);
+      ctx->last_kernel = "maxpool_nhwc4<3x3,two rows>";
+    } else if (kind == RTG_POOL_MAX && g.kh == 3 && g.kw == 3) {
+      maxpool_nhwc4_kernel<3, 3><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+      ctx->last_kernel = "maxpool_nhwc4<3x3>";
+    } else if (kind == RTG_POOL_MAX && g.kh == 2 && g.kw == 2) {
+      maxpool_nhwc4_kernel<2, 2><<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+      ctx->last_kernel = "maxpool_nhwc4<2x2>";
+    } else {
+      pool2d_nhwc4_kernel<<<blocks4, 256, 0, ctx->stream>>>(op, ip, g);
+      ctx->last_kernel = "pool2d_nhwc4";
+    }
     ctx->launches++;
     RTG_CUDA(cudaGetLastError());
     return RTG_OK;

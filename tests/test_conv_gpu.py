@@ -388,3 +388,32 @@ def test_depthwise3x3_tma_is_bit_exact(rtg, ctx, oracle, n, c, h, w, s, pads, ac
         want = oracle.unary("clip", want, -0.25, 0.5)
     assert got.shape == want.shape == (n, c, oh, ow)
     np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("s", [1, 2])
+def test_depthwise3x3_padding_taps_are_skipped_not_added(rtg, ctx, oracle, s):
+    """The kernel may add the zero-filled padding instead of skipping the tap only where that cannot change a bit.  A
+    channel with an infinite weight (inf x 0 would be NaN), one with a -0.0 bias over an all-zero input (-0.0 + 0.0 would
+    be +0.0) and a Clip whose upper bound is -0.0 all take the predicated path: bit for bit the oracle's result
+    (src/ops/conv/depthwise.rs:60-110 skips out-of-image taps)."""
+    from rten_fork_b200 import ops
+
+    n, c, h, w = 2, 40, 9, 21
+    rng = oracle.XorShiftRng(77 + s)
+    x = rng.fill((n, c, h, w)) - 0.5
+    wt = rng.fill((c, 1, 3, 3)) - 0.5
+    b = rng.fill((c,)) - 0.5
+    wt[3, 0, 0, 0] = np.inf          # top-left tap: in the padding for the first row / column only
+    wt[17, 0, 2, 2] = -np.inf
+    b[5] = -0.0
+    x[:, 5] = 0.0                    # every product of channel 5 is +-0.0
+    wt[5] = -np.abs(wt[5])           # ... and -0.0 wherever the input is +0.0
+    b[33] = -0.0
+    for act, clip in (("none", (0.0, 0.0)), ("clip", (-0.25, 0.5)), ("clip", (-1.0, -0.0))):
+        got = ops.conv(x, wt, b, padding=(1, 1, 1, 1), groups=c, strides=(s, s), activation=act, clip=clip, ctx=ctx)
+        assert ctx.last_kernel.startswith("depthwise3x3_tma"), ctx.last_kernel
+        want = oracle.conv2d(x, wt, b, (1, 1, 1, 1), c, (s, s), (1, 1))
+        if act == "clip":
+            want = oracle.unary("clip", want, clip[0], clip[1])
+        assert got.tobytes() == want.tobytes(), (act, clip)
+

@@ -206,6 +206,34 @@ def test_pool2d_bit_exact(rtg, ctx, oracle, kind, shape, k, s, pads):
     assert got.shape == want.shape and got.tobytes() == want.tobytes()
 
 
+@pytest.mark.parametrize("shape,k,s,pads", [
+    ((2, 8, 9, 9), (3, 3), (2, 2), (1, 1, 1, 1)),      # odd output height: the last row pair has one row
+    ((1, 64, 12, 12), (3, 3), (2, 2), (1, 1, 1, 1)),
+    ((3, 4, 7, 5), (3, 3), (1, 1), (1, 1, 1, 1)),      # stride 1: windows of a pair share two rows
+    ((1, 12, 6, 6), (3, 3), (2, 2), (0, 0, 0, 0)),
+    ((2, 16, 8, 8), (2, 2), (2, 2), (0, 0, 0, 0)),
+])
+def test_max_pool_nhwc_kernels_bit_exact(rtg, ctx, oracle, shape, k, s, pads):
+    """The NHWC MaxPool kernels (compile-time window; two output rows per thread for 3x3) against the oracle, on
+    channels-last device tensors as Graph::run hands them over; -inf and NaN inputs included."""
+    import torch
+    from rten_fork_b200 import ops
+
+    rng = oracle.XorShiftRng(4321)
+    x = rng.fill(shape) - 0.5
+    x[0, 0, 0, 0] = -np.inf
+    x[0, 1, 1, 1] = np.nan
+    want = oracle.pool2d("max", x, k, s, pads)
+    xd = torch.from_numpy(x).cuda().contiguous(memory_format=torch.channels_last)
+    yd = torch.empty(want.shape, device="cuda").contiguous(memory_format=torch.channels_last)
+    torch.cuda.synchronize()
+    ops.max_pool(xd, k, s, pads, ctx=ctx, out=yd)
+    ctx.sync()
+    got = yd.cpu().numpy()
+    assert ctx.last_kernel.startswith("maxpool_nhwc4"), ctx.last_kernel
+    assert got.tobytes() == np.ascontiguousarray(want).tobytes()
+
+
 def test_global_average_pool(rtg, ctx, oracle):
     from rten_fork_b200 import ops
 
