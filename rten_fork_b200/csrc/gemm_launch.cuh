@@ -163,7 +163,9 @@ rtg_status launch_variants(Context* ctx, int bn, int mode, const CUtensorMap& ma
       // tiles with few k-blocks are paced by their epilogue: two staging buffers per warp (GemmCfg EPI2)
       static const int epi2_kb = []() {
         const char* e = getenv("RTG_EPI2_KB");  // developer switch: 0 disables
-        return e ? atoi(e) : 4;  // measured on the ResNet-50 layer table: 4 beats 0, 8 and 16
+        // measured on the ResNet-50 layer table: 4 beats 0, 8 and 16; never above kChunkKb (the variant accumulates a
+        // unit in one chunk, which is the fp32-accurate modes' summation only up to that depth)
+        return std::min(e ? atoi(e) : 4, kChunkKb);
       }();
       const int kb_per_unit = args.splits > 1 ? args.kb_per_split : args.num_kb;
       if (kb_per_unit <= epi2_kb && (args.flags & kFlagStagedD)) {

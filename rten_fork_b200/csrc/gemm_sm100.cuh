@@ -286,11 +286,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 #endif
   constexpr int kStages = Cfg::kStages;
-  constexpr bool kChunked = MODE != 0;
+  // EPI2 launches have at most kChunkKb k-blocks per unit (gemm_launch.cuh): one accumulation chunk, so the epilogue
+  // reads it chunk by chunk like MODE 0 instead of carrying BN/2 running sums (same bits: the chunk is the whole sum)
+  constexpr bool kChunked = MODE != 0 && !EPI2;
   constexpr int kTmaWarp = Cfg::kEpiWarps, kMmaWarp = Cfg::kEpiWarps + 1;
   extern __shared__ uint8_t smem_raw[];
   // 128B swizzle atoms need 1024-byte aligned tiles.
-  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  // opaque to the compiler from here on: it otherwise rematerialises the shared-window base (S2R SR_CgaCtaId + 3 ALU)
+  // in front of nearly every shared-memory access of the epilogue, ~60 instructions per tile on its latency-bound path
+  asm volatile("" : "+r"(smem_base));
   const uint32_t ring_base = smem_base + Cfg::kARingBytes;  // MODE 1: the A ring comes first
   const uint32_t epi_base = ring_base + kStages * Cfg::kStageBytes;
   constexpr int kAStages = Cfg::kAStages;
@@ -308,8 +313,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
 
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
+  int warp = threadIdx.x >> 5;
+  int lane = threadIdx.x & 31;
+  asm volatile("" : "+r"(warp), "+r"(lane));  // ditto: keeps S2R SR_TID.X out of the loops
 
   const int m_tiles_1 = (args.M + kBM - 1) / kBM;  // per batch entry (A_KIND 3: args.M is the per-entry row count)
   const int m_tiles = A_KIND == 2 ? args.ic.win_rows * args.ic.win_tpr
