@@ -232,8 +232,20 @@ __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& b
 static __device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
   for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], alpha);
 }
+// Eight elements at a time with the selection outside the element loop: one element's Gelu is a chain of ~60 dependent
+// instructions (division, exponential), and a loop over single elements ran a 32-column chunk in ~10 K cycles, twice the
+// main loop of BERT's 768 -> 3072 layer (329 us against 145 us for the 3072 -> 768 layer of the same flops); eight
+// independent chains interleave.
 static __device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi) {
-  for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], act, lo, hi);
+#pragma unroll 1
+  for (int j0 = 0; j0 < 32; j0 += 8) {
+    float t[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = v[j0 + i];
+    apply_act_array(t, act, lo, hi);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[j0 + i] = t[i];
+  }
 }
 static __device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
   for (int j = 0; j < ncols; ++j) v[j] += beta * r[j * cs];

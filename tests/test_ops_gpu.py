@@ -140,6 +140,27 @@ def test_unary_bit_exact(rtg, ctx, oracle, kind):
     assert y.tobytes() == want.tobytes()
 
 
+@pytest.mark.parametrize("kind", ["erf", "gelu"])
+def test_erf_gelu_bit_exact_dense_sweep(rtg, ctx, oracle, kind):
+    """The device erf divides with a branch-free reciprocal (MUFU.RCP + one Newton step, the correctly rounded fast path);
+    it has to give the bits of the oracle's IEEE division (rten-vecmath/src/erf.rs:28-58) for every operand, not only for
+    a few random ones: every 5th float of both signs from 1e-3 to 20, plus zeros, huge values, infinities and NaN."""
+    from rten_fork_b200 import ops
+
+    lo, hi = np.float32(1e-3).view(np.uint32), np.float32(20.0).view(np.uint32)
+    pos = np.arange(int(lo), int(hi), 5, dtype=np.uint32).view(np.float32)
+    special = np.array([0.0, -0.0, 1e-30, -1e-30, 1e30, -1e30, 3.4e38, -3.4e38, np.inf, -np.inf, 10.19, 10.2, 10.21, 16.0,
+                        np.nextafter(np.float32(16.0), np.float32(17.0))], dtype=np.float32)
+    x = np.concatenate([pos, -pos, special])
+    got = getattr(ops, kind)(x)
+    want = oracle.unary(kind, x)
+    # gelu(-inf) = -inf * 0 is NaN on both sides (sign / payload of a NaN are not part of the contract)
+    bad = np.flatnonzero((got.view(np.uint32) != want.view(np.uint32)) & ~(np.isnan(got) & np.isnan(want)))
+    assert bad.size == 0, f"{kind}: {bad.size} of {x.size} differ, first x = {x[bad[0]]!r}: {got[bad[0]]!r} vs {want[bad[0]]!r}"
+    nan = np.array([np.nan], dtype=np.float32)
+    assert np.isnan(getattr(ops, kind)(nan)).all()
+
+
 def test_clip_bit_exact(rtg, ctx, oracle):
     from rten_fork_b200 import ops
 
