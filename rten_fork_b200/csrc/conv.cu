@@ -241,6 +241,7 @@ static rtg_status launch_depthwise3x3_tma(Context* ctx, float* out, const float*
   static const int rows_env = [] { const char* e = std::getenv("RTG_DW_ROWS"); return e ? std::atoi(e) : 0; }();
   static const int pred_env = [] { const char* e = std::getenv("RTG_DW_PRED"); return e ? std::atoi(e) : 0; }();
   t.force_pred = pred_env;
+  t.one2 = 0x3f8000003f800000ull;
   int best_rows = g.oh;
   double best_cost = 1e300;
   for (int64_t rb = 1; rb <= g.oh; ++rb) {

@@ -33,6 +33,7 @@ struct DwTile {
   int box_bytes;
   int ch_blocks, bands, row_bands, rows_per_job;
   int force_pred;    // (RTG_DW_PRED=1) always skip padding taps by predicate
+  unsigned long long one2;  // (1.0f, 1.0f): see dw_tap
 };
 constexpr int kDwTX = 4;  // dw_taps below is written out for 4
 #ifndef RTG_DW_RING
@@ -44,23 +45,31 @@ constexpr int kDwTX = 4;  // dw_taps below is written out for 4
 constexpr int kDwRing = RTG_DW_RING;
 constexpr int kDwThreads = 128;
 
-// four channels of one tap: acc += x * w (separate multiply and add, as the reference), skipped unless bit BIT of `mask`
-// is set (the validity of the input column under this tap, zero for a row outside the image)
+// Four channels of one tap: acc += x * w with the multiply and the add rounded separately, as the reference does, on
+// sm_100's packed fp32 pipe: FMUL2 for the two channel pairs, then acc = fma(acc, 1.0, product) — exactly RN(acc + product)
+// — as FFMA2.  (A packed add after a packed multiply is contracted into one FFMA2 by ptxas even with .rn, which would
+// round once; `one` is (1.0f, 1.0f) from the launch parameters so that it cannot simplify the fma back into an add.)
+// Half the issue slots of four FMUL + four FADD.  PRED: skipped unless bit BIT of `mask` is set (the validity of the
+// input column under this tap, zero for a row outside the image).
 template <int BIT, bool PRED>
-__device__ __forceinline__ void dw_tap(float (&acc)[4], const float4 x, const float4 w, const uint32_t mask) {
+__device__ __forceinline__ void dw_tap(unsigned long long (&acc)[2], const float4 x, const unsigned long long (&w)[2],
+                                       const uint32_t mask, const unsigned long long one) {
   if (!PRED) {  // padding taps add the TMA unit's zeros: see `plain` in the kernel for when that is the same bits
-    acc[0] = __fadd_rn(acc[0], __fmul_rn(x.x, w.x));
-    acc[1] = __fadd_rn(acc[1], __fmul_rn(x.y, w.y));
-    acc[2] = __fadd_rn(acc[2], __fmul_rn(x.z, w.z));
-    acc[3] = __fadd_rn(acc[3], __fmul_rn(x.w, w.w));
+    asm("{\n\t.reg .b64 x0, x1, m0, m1;\n\t"
+        "mov.b64 x0, {%2, %3};\n\tmov.b64 x1, {%4, %5};\n\t"
+        "mul.rn.f32x2 m0, x0, %6;\n\tmul.rn.f32x2 m1, x1, %7;\n\t"
+        "fma.rn.f32x2 %0, %0, %8, m0;\n\tfma.rn.f32x2 %1, %1, %8, m1;\n\t}"
+        : "+l"(acc[0]), "+l"(acc[1])
+        : "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w), "l"(w[0]), "l"(w[1]), "l"(one));
     return;
   }
-  asm("{\n\t.reg .pred p;\n\t.reg .b32 m;\n\t.reg .f32 t0, t1, t2, t3;\n\t"
-      "and.b32 m, %12, %13;\n\tsetp.ne.u32 p, m, 0;\n\t"
-      "mul.rn.f32 t0, %4, %8;\n\tmul.rn.f32 t1, %5, %9;\n\tmul.rn.f32 t2, %6, %10;\n\tmul.rn.f32 t3, %7, %11;\n\t"
-      "@p add.rn.f32 %0, %0, t0;\n\t@p add.rn.f32 %1, %1, t1;\n\t@p add.rn.f32 %2, %2, t2;\n\t@p add.rn.f32 %3, %3, t3;\n\t}"
-      : "+f"(acc[0]), "+f"(acc[1]), "+f"(acc[2]), "+f"(acc[3])
-      : "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w), "f"(w.x), "f"(w.y), "f"(w.z), "f"(w.w), "r"(mask), "n"(1u << BIT));
+  asm("{\n\t.reg .pred p;\n\t.reg .b32 m;\n\t.reg .b64 x0, x1, m0, m1;\n\t"
+      "and.b32 m, %9, %10;\n\tsetp.ne.u32 p, m, 0;\n\t"
+      "mov.b64 x0, {%2, %3};\n\tmov.b64 x1, {%4, %5};\n\t"
+      "mul.rn.f32x2 m0, x0, %6;\n\tmul.rn.f32x2 m1, x1, %7;\n\t"
+      "@p fma.rn.f32x2 %0, %0, %8, m0;\n\t@p fma.rn.f32x2 %1, %1, %8, m1;\n\t}"
+      : "+l"(acc[0]), "+l"(acc[1])
+      : "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w), "l"(w[0]), "l"(w[1]), "l"(one), "r"(mask), "n"(1u << BIT));
 }
 
 // f32::clamp of the reference (src/ops/unary_elementwise.rs:325-339): NaN stays NaN, -0.0 stays -0.0; two compares and
@@ -82,20 +91,22 @@ __device__ __forceinline__ float dw_clip(float v, float lo, float hi) {
 
 // the 3 taps of one kernel row for the 4 output columns of a strip (compile-time column indices)
 template <int STRIDE, int IW, bool PRED>
-__device__ __forceinline__ void dw_taps(float (&acc)[kDwTX][4], const float4 (&row)[IW], const float4 w0, const float4 w1,
-                                        const float4 w2, const uint32_t rmask) {
-  dw_tap<0 * STRIDE + 0, PRED>(acc[0], row[0 * STRIDE + 0], w0, rmask);
-  dw_tap<1 * STRIDE + 0, PRED>(acc[1], row[1 * STRIDE + 0], w0, rmask);
-  dw_tap<2 * STRIDE + 0, PRED>(acc[2], row[2 * STRIDE + 0], w0, rmask);
-  dw_tap<3 * STRIDE + 0, PRED>(acc[3], row[3 * STRIDE + 0], w0, rmask);
-  dw_tap<0 * STRIDE + 1, PRED>(acc[0], row[0 * STRIDE + 1], w1, rmask);
-  dw_tap<1 * STRIDE + 1, PRED>(acc[1], row[1 * STRIDE + 1], w1, rmask);
-  dw_tap<2 * STRIDE + 1, PRED>(acc[2], row[2 * STRIDE + 1], w1, rmask);
-  dw_tap<3 * STRIDE + 1, PRED>(acc[3], row[3 * STRIDE + 1], w1, rmask);
-  dw_tap<0 * STRIDE + 2, PRED>(acc[0], row[0 * STRIDE + 2], w2, rmask);
-  dw_tap<1 * STRIDE + 2, PRED>(acc[1], row[1 * STRIDE + 2], w2, rmask);
-  dw_tap<2 * STRIDE + 2, PRED>(acc[2], row[2 * STRIDE + 2], w2, rmask);
-  dw_tap<3 * STRIDE + 2, PRED>(acc[3], row[3 * STRIDE + 2], w2, rmask);
+__device__ __forceinline__ void dw_taps(unsigned long long (&acc)[kDwTX][2], const float4 (&row)[IW],
+                                        const unsigned long long (&w0)[2], const unsigned long long (&w1)[2],
+                                        const unsigned long long (&w2)[2], const uint32_t rmask,
+                                        const unsigned long long one) {
+  dw_tap<0 * STRIDE + 0, PRED>(acc[0], row[0 * STRIDE + 0], w0, rmask, one);
+  dw_tap<1 * STRIDE + 0, PRED>(acc[1], row[1 * STRIDE + 0], w0, rmask, one);
+  dw_tap<2 * STRIDE + 0, PRED>(acc[2], row[2 * STRIDE + 0], w0, rmask, one);
+  dw_tap<3 * STRIDE + 0, PRED>(acc[3], row[3 * STRIDE + 0], w0, rmask, one);
+  dw_tap<0 * STRIDE + 1, PRED>(acc[0], row[0 * STRIDE + 1], w1, rmask, one);
+  dw_tap<1 * STRIDE + 1, PRED>(acc[1], row[1 * STRIDE + 1], w1, rmask, one);
+  dw_tap<2 * STRIDE + 1, PRED>(acc[2], row[2 * STRIDE + 1], w1, rmask, one);
+  dw_tap<3 * STRIDE + 1, PRED>(acc[3], row[3 * STRIDE + 1], w1, rmask, one);
+  dw_tap<0 * STRIDE + 2, PRED>(acc[0], row[0 * STRIDE + 2], w2, rmask, one);
+  dw_tap<1 * STRIDE + 2, PRED>(acc[1], row[1 * STRIDE + 2], w2, rmask, one);
+  dw_tap<2 * STRIDE + 2, PRED>(acc[2], row[2 * STRIDE + 2], w2, rmask, one);
+  dw_tap<3 * STRIDE + 2, PRED>(acc[3], row[3 * STRIDE + 2], w2, rmask, one);
 }
 
 // ACT: 0 none, 1 Relu, 2 Clip, 3 any other activation (apply_act's switch).  CVS: channel vectors per CTA (DwTile::cvs), a
@@ -175,6 +186,16 @@ __global__ void __launch_bounds__(kDwThreads, RTG_DW_MINB) depthwise3x3_tma_kern
       plain_t = plain_t && __float_as_uint(g.act_hi) != 0x80000000u && g.act_lo == g.act_lo && g.act_hi == g.act_hi;
   }
   const bool plain = __all_sync(0xffffffffu, plain_t) && !t.force_pred;
+  // packed (f32x2) copies of the weights and the bias, and (1.0f, 1.0f) for dw_tap
+  unsigned long long w2[9][2], b2[2];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    asm("mov.b64 %0, {%1, %2};" : "=l"(w2[k][0]) : "f"(w[k].x), "f"(w[k].y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(w2[k][1]) : "f"(w[k].z), "f"(w[k].w));
+  }
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b2[0]) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b2[1]) : "f"(b.z), "f"(b.w));
+  const unsigned long long one = t.one2;
   // validity of the input columns under this strip (global input column = bx_w + strip * TX * STRIDE + j)
   const int ix0 = bx_w + strip * TX * STRIDE;
   uint32_t colmask = 0;
@@ -198,9 +219,9 @@ __global__ void __launch_bounds__(kDwThreads, RTG_DW_MINB) depthwise3x3_tma_kern
   // zeros the TMA unit filled in, and Clip is max / min
   auto row_body = [&](auto pred_tag) {
     constexpr bool PRED = decltype(pred_tag)::value;
-    float acc[TX][4];
+    unsigned long long acc2[TX][2];
 #pragma unroll
-    for (int j = 0; j < TX; ++j) acc[j][0] = b.x, acc[j][1] = b.y, acc[j][2] = b.z, acc[j][3] = b.w;
+    for (int j = 0; j < TX; ++j) acc2[j][0] = b2[0], acc2[j][1] = b2[1];
     int slot = s0;
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
@@ -210,22 +231,25 @@ __global__ void __launch_bounds__(kDwThreads, RTG_DW_MINB) depthwise3x3_tma_kern
 #pragma unroll
       for (int j = 0; j < IW; ++j) row[j] = sp[j * cstride];
       const uint32_t rmask = (PRED && iy + ky >= 0 && iy + ky < g.h) ? colmask : 0u;
-      dw_taps<STRIDE, IW, PRED>(acc, row, w[ky * 3], w[ky * 3 + 1], w[ky * 3 + 2], rmask);
+      dw_taps<STRIDE, IW, PRED>(acc2, row, w2[ky * 3], w2[ky * 3 + 1], w2[ky * 3 + 2], rmask, one);
     }
 #pragma unroll
     for (int j = 0; j < TX; ++j) {
+      float acc[4];
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[0]), "=f"(acc[1]) : "l"(acc2[j][0]));
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[2]), "=f"(acc[3]) : "l"(acc2[j][1]));
       if (ACT == 1) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) acc[j][i] = fmaxf(acc[j][i], 0.f);
+        for (int i = 0; i < 4; ++i) acc[i] = fmaxf(acc[i], 0.f);
       } else if (ACT == 2) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          acc[j][i] = PRED ? dw_clip(acc[j][i], g.act_lo, g.act_hi) : dw_clip_fast(acc[j][i], g.act_lo, g.act_hi);
+          acc[i] = PRED ? dw_clip(acc[i], g.act_lo, g.act_hi) : dw_clip_fast(acc[i], g.act_lo, g.act_hi);
       } else if (ACT == 3) {
-        apply_act_array(acc[j], g.act, g.act_lo, g.act_hi);
+        apply_act_array(acc, g.act, g.act_lo, g.act_hi);
       }
       if (ox0 + j < g.ow)
-        *reinterpret_cast<float4*>(op + static_cast<int64_t>(j) * g.cp_out) = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+        *reinterpret_cast<float4*>(op + static_cast<int64_t>(j) * g.cp_out) = make_float4(acc[0], acc[1], acc[2], acc[3]);
     }
   };
   for (int oy = oy0; oy < oy1; ++oy, iy += STRIDE, op += op_row) {
