@@ -265,6 +265,7 @@ static rtg_status dispatch(Context* ctx, int bn, int mode, const CUtensorMap& ma
                            GemmArgs args, int plane_rows = 0, int64_t num_planes = 0, const Epilogue* peers = nullptr,
                            const CUtensorMap* mb2p = nullptr) {
   if (mode == RTG_MATH_TF32_BF16X2 && (!mb2p || A_KIND == 3)) mode = RTG_MATH_3XTF32;  // no B' for this launch
+  args.one2 = 0x3f8000003f800000ull;
   const CUtensorMap& mb2 = mb2p ? *mb2p : mb;
   // Row-major, 16-byte aligned outputs (and residuals) move through shared memory with TMA (see GemmCfg).
   CUtensorMap md = ma, mr = ma;

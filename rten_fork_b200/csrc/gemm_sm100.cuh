@@ -96,6 +96,7 @@ struct GemmArgs {
   int32_t n_peers;
   Im2colArgs ic;
   unsigned long long* prof;  // RTG_PROF builds: per-CTA wait / busy cycle counters (see PROF_* below), else unused
+  unsigned long long one2;   // (1.0f, 1.0f) as a run-time value: see vm_gelu_x2 (vecmath.cuh)
 };
 
 // Developer instrumentation (make PROF=1): cycles each role spends waiting on its barriers.
@@ -236,7 +237,20 @@ static __device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
 // instructions (division, exponential), and a loop over single elements ran a 32-column chunk in ~10 K cycles, twice the
 // main loop of BERT's 768 -> 3072 layer (329 us against 145 us for the 3072 -> 768 layer of the same flops); eight
 // independent chains interleave.
-static __device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi) {
+static __device__ __noinline__ void epi_cold_act(float* v, int act, float lo, float hi, unsigned long long one2) {
+  if (act == ACT_GELU) {  // BERT's 768 -> 3072 layers: two elements per instruction (vm_gelu_x2), eight pairs at a time
+#pragma unroll 1
+    for (int j0 = 0; j0 < 32; j0 += 16) {
+      float t[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t[i] = v[j0 + i];
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) vm_gelu_x2(t[i], t[i + 1], one2);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[j0 + i] = t[i];
+    }
+    return;
+  }
 #pragma unroll 1
   for (int j0 = 0; j0 < 32; j0 += 8) {
     float t[8];
@@ -246,6 +260,16 @@ static __device__ __noinline__ void epi_cold_act(float* v, int act, float lo, fl
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[j0 + i] = t[i];
   }
+}
+struct Float8 {
+  float4 a, b;
+};
+static __device__ __noinline__ Float8 epi_cold_gelu8(Float8 x, unsigned long long one2) {
+  vm_gelu_x2(x.a.x, x.a.y, one2);
+  vm_gelu_x2(x.a.z, x.a.w, one2);
+  vm_gelu_x2(x.b.x, x.b.y, one2);
+  vm_gelu_x2(x.b.z, x.b.w, one2);
+  return x;
 }
 static __device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
   for (int j = 0; j < ncols; ++j) v[j] += beta * r[j * cs];
@@ -262,7 +286,7 @@ static __device__ __noinline__ void epi_cold_store(const float* v, float* d, int
   } while (0)
 
 // Relu / Clip inline, everything else out of line
-__device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float hi) {
+__device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float hi, unsigned long long one2) {
   if (act == ACT_NONE) return;
   if (act == ACT_RELU) {
 #pragma unroll
@@ -278,8 +302,21 @@ __device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float
       asm("{\n\t.reg .f32 t;\n\tmax.NaN.f32 t, %1, %2;\n\tmin.NaN.f32 %0, t, %3;\n\t}" : "=f"(r) : "f"(v[j]), "f"(lo), "f"(hi));
       v[j] = r;
     }
+  } else if (act == ACT_GELU) {
+    // Out of line but in registers: eight values per call go and come back in registers.  The array form below goes
+    // through local memory, which this kernel's 227 KB of shared memory leave almost no L1 for (ncu: the round trips were
+    // a third of the Gelu time of BERT's 768 -> 3072 layer; in the fp32-accurate modes the epilogue warps also drain the
+    // accumulator every four k-blocks, so their time is the tile's).  Inlining it (16 pairs x 2 call sites) tripled the
+    // kernel's code and spilled on the common path.
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      const Float8 r = epi_cold_gelu8(Float8{make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]),
+                                             make_float4(v[j + 4], v[j + 5], v[j + 6], v[j + 7])}, one2);
+      v[j] = r.a.x, v[j + 1] = r.a.y, v[j + 2] = r.a.z, v[j + 3] = r.a.w;
+      v[j + 4] = r.b.x, v[j + 5] = r.b.y, v[j + 6] = r.b.z, v[j + 7] = r.b.w;
+    }
   } else {
-    RTG_EPI_COLD(epi_cold_act(t_, act, lo, hi));
+    RTG_EPI_COLD(epi_cold_act(t_, act, lo, hi, one2));
   }
 }
 
@@ -760,7 +797,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (args.R != nullptr && row_ok)  // residual that TMA cannot address (unaligned / NCHW): direct loads
               RTG_EPI_COLD(epi_cold_residual(t_, args.R + r_base + static_cast<int64_t>(n0 + c0) * r_cs, r_cs, args.beta, ncols));
           }
-          epi_act(v, args.act, args.act_lo, args.act_hi);
+          epi_act(v, args.act, args.act_lo, args.act_hi, args.one2);
           PROF_LINE(2);
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4)
@@ -783,7 +820,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (!row_ok) return;
         if (args.R != nullptr)
           RTG_EPI_COLD(epi_cold_residual(t_, args.R + r_base + static_cast<int64_t>(n0 + c0) * r_cs, r_cs, args.beta, ncols));
-        epi_act(v, args.act, args.act_lo, args.act_hi);
+        epi_act(v, args.act, args.act_lo, args.act_hi, args.one2);
         RTG_EPI_COLD(epi_cold_store(t_, args.D + d_base + static_cast<int64_t>(n0 + c0) * d_cs, d_cs, ncols));
       };
 
