@@ -341,14 +341,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int kTmaWarp = Cfg::kEpiWarps, kMmaWarp = Cfg::kEpiWarps + 1;
   extern __shared__ uint8_t smem_raw[];
   // 128B swizzle atoms need 1024-byte aligned tiles.
-  uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  // opaque to the compiler from here on: it otherwise rematerialises the shared-window base (S2R SR_CgaCtaId + 3 ALU)
-  // in front of nearly every shared-memory access of the epilogue, ~60 instructions per tile on its latency-bound path
-  asm volatile("" : "+r"(smem_base));
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring_base = smem_base + Cfg::kARingBytes;  // MODE 1: the A ring comes first
-  const uint32_t epi_base = ring_base + kStages * Cfg::kStageBytes;
+  uint32_t epi_base = ring_base + kStages * Cfg::kStageBytes;  // (not const: see the epilogue role)
   constexpr int kAStages = Cfg::kAStages;
-  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
+  uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto xf_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
@@ -364,7 +361,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   int warp = threadIdx.x >> 5;
   int lane = threadIdx.x & 31;
-  asm volatile("" : "+r"(warp), "+r"(lane));  // ditto: keeps S2R SR_TID.X out of the loops
 
   const int m_tiles_1 = (args.M + kBM - 1) / kBM;  // per batch entry (A_KIND 3: args.M is the per-entry row count)
   const int m_tiles = A_KIND == 2 ? args.ic.win_rows * args.ic.win_tpr
@@ -673,6 +669,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp < Cfg::kEpiWarps) {
     // ===================================================== epilogue
     if (MODE != 0) ptx::reg_alloc<kRegsEpi>();
+    // Opaque to the compiler inside this role: it otherwise rematerialises the shared-window base (S2R SR_CgaCtaId + 3 ALU)
+    // and the thread ids (S2R SR_TID.X) in front of nearly every shared-memory access, ~100 instructions per tile on
+    // this role's latency-bound path.  Only here, where there are registers to keep them in: done for the whole kernel
+    // the values were spilled and re-loaded from local memory inside the split warps' loop.
+    asm volatile("" : "+r"(epi_base), "+r"(bar_base), "+r"(warp), "+r"(lane));
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     constexpr int kCols = Cfg::kColsPerThread;
     const int col0 = (warp >> 2) * kCols;  // first tile column this warp handles

@@ -44,15 +44,21 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
       : "memory");
   return ok;
 }
+// Out of line and marked as not returning: inlined, the printf call sat inside every wait loop and the values live
+// across it (loop-invariant addresses of the operand-split warps' k-block loop among them) were spilled to local memory.
+static __device__ __noinline__ __attribute__((noreturn)) void mbar_timeout(uint32_t bar, uint32_t parity) {
+  printf("rtg: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+  __trap();
+  for (;;) {
+  }
+}
 // Bounded wait: a pipeline bug must surface as a trapped launch (cudaErrorLaunchFailure), never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 4000000000LL) {  // ~2 s at 2 GHz
-      printf("rtg: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar,
-             parity);
-      __trap();
+      mbar_timeout(bar, parity);
     }
   }
 }
@@ -74,9 +80,7 @@ __device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity) 
     if (ok) return;
     if (t0 == 0) t0 = clock64();
     if (clock64() - t0 > 4000000000LL) {
-      printf("rtg: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar,
-             parity);
-      __trap();
+      mbar_timeout(bar, parity);
     }
   }
 }
