@@ -230,9 +230,6 @@ __device__ __forceinline__ void out_row_base(const OutMap& om, int m, int64_t& b
 // epilogue warps' stall samples on the short-K layers to instruction fetch (stall_no_inst).  Everything that is not on
 // the path of a fused Conv / MatMul (+bias, +residual, Relu / Clip) into a row-major tensor now lives in these
 // functions, called through a scratch copy so that the chunk itself stays in registers on the hot path.
-static __device__ __noinline__ void epi_cold_alpha_div(float* v, float alpha) {
-  for (int j = 0; j < 32; ++j) v[j] = __fdiv_rn(v[j], alpha);
-}
 // Eight elements at a time with the selection outside the element loop: one element's Gelu is a chain of ~60 dependent
 // instructions (division, exponential), and a loop over single elements ran a 32-column chunk in ~10 K cycles, twice the
 // main loop of BERT's 768 -> 3072 layer (329 us against 145 us for the 3072 -> 768 layer of the same flops); eight
@@ -269,6 +266,12 @@ static __device__ __noinline__ Float8 epi_cold_gelu8(Float8 x, unsigned long lon
   vm_gelu_x2(x.a.z, x.a.w, one2);
   vm_gelu_x2(x.b.x, x.b.y, one2);
   vm_gelu_x2(x.b.z, x.b.w, one2);
+  return x;
+}
+// fused `MatMul -> Div(scalar)` with a divisor that is not a power of two: IEEE division, eight values per call in registers
+static __device__ __noinline__ Float8 epi_cold_div8(Float8 x, float alpha) {
+  x.a.x = __fdiv_rn(x.a.x, alpha), x.a.y = __fdiv_rn(x.a.y, alpha), x.a.z = __fdiv_rn(x.a.z, alpha), x.a.w = __fdiv_rn(x.a.w, alpha);
+  x.b.x = __fdiv_rn(x.b.x, alpha), x.b.y = __fdiv_rn(x.b.y, alpha), x.b.z = __fdiv_rn(x.b.z, alpha), x.b.w = __fdiv_rn(x.b.w, alpha);
   return x;
 }
 static __device__ __noinline__ void epi_cold_residual(float* v, const float* r, int64_t cs, float beta, int ncols) {
@@ -757,7 +760,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       auto finish = [&](float (&v)[32], int c0) {
         const int ncols = min(32, args.N - (n0 + c0));
         if (args.flags & kFlagAlphaDiv) {  // fused `MatMul -> Div(scalar)`: IEEE division, as the unfused operator
-          RTG_EPI_COLD(epi_cold_alpha_div(t_, args.alpha));
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const Float8 r = epi_cold_div8(Float8{make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]),
+                                                  make_float4(v[j + 4], v[j + 5], v[j + 6], v[j + 7])}, args.alpha);
+            v[j] = r.a.x, v[j + 1] = r.a.y, v[j + 2] = r.a.z, v[j + 3] = r.a.w;
+            v[j + 4] = r.b.x, v[j + 5] = r.b.y, v[j + 6] = r.b.z, v[j + 7] = r.b.w;
+          }
         } else if (args.alpha != 1.f) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] *= args.alpha;

@@ -1,5 +1,6 @@
 // Operator implementations for the graph executor + the OpRegistry readers that build them from `.rten` operator
 // nodes (reference: src/op_registry.rs:385-817 impl_read_op!, src/ops/*.rs Operator impls).
+#include <cstring>
 #include "graph.h"
 #include "operators.h"
 
@@ -580,6 +581,17 @@ rtg_status MatMulOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* o
     ep.act = act_fused ? act : ACT_NONE;
     ep.alpha = scale;
     ep.alpha_div = scale_div;
+    if (scale_div) {
+      // x / 2^k and x * 2^-k are the same real number, hence the same correctly rounded float (BERT's sqrt(64) = 8):
+      // the multiply stays on the epilogue's inline path, the IEEE division is an out-of-line loop
+      uint32_t bits;
+      memcpy(&bits, &scale, 4);
+      const uint32_t expo = (bits >> 23) & 0xffu;
+      if ((bits & 0x007fffffu) == 0 && expo >= 2 && expo <= 252) {
+        ep.alpha = 1.0f / scale;  // exact
+        ep.alpha_div = false;
+      }
+    }
     epp = &ep;
   }
   if (b_pack.p && tb.data == b_pack_from && tb.ndim == 2 && tb.shape[0] == b_pack_dims[0] &&
