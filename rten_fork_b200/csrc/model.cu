@@ -542,6 +542,10 @@ int optimize_graph(Graph* g) {
         const int32_t other = add.inputs[0] == cur_out ? add.inputs[1] : add.inputs[0];
         bool ok = other >= 0 && other != cur_out && g->nodes[other].kind != NodeKind::Constant &&
                   nd.inputs.size() <= 3;
+        // an Add that feeds a Softmax (attention mask) is left to the Add -> Softmax fusion below: the mask only
+        // broadcasts, which the epilogue cannot take, and the Softmax kernel adds it for free
+        const int32_t after = add.outputs[0] >= 0 ? single_consumer(add.outputs[0]) : -1;
+        if (after >= 0 && !dead[after] && dynamic_cast<SoftmaxOp*>(g->nodes[after].op.get())) ok = false;
         std::vector<int32_t> stack = {other};
         std::set<int32_t> seen;
         while (ok && !stack.empty()) {
@@ -579,6 +583,23 @@ int optimize_graph(Graph* g) {
         }
       }
     }
+  }
+  // --- Add -> Softmax (the attention mask of a transformer block): the add happens in the Softmax kernel's registers,
+  //     one pass over the scores instead of two.  Same bits: the kernel performs the same round-to-nearest add.
+  for (int32_t i = 0; i < n; ++i) {
+    Node& nd = g->nodes[i];
+    if (nd.kind != NodeKind::Operator || dead[i] || nd.outputs.size() != 1 || nd.outputs[0] < 0) continue;
+    BinaryOp* b = dynamic_cast<BinaryOp*>(nd.op.get());
+    if (!b || b->op != RTG_BIN_ADD || nd.inputs.size() != 2 || nd.inputs[0] < 0 || nd.inputs[1] < 0) continue;
+    const int32_t next = single_consumer(nd.outputs[0]);
+    if (next < 0 || dead[next]) continue;
+    Node& sn = g->nodes[next];
+    SoftmaxOp* sm = dynamic_cast<SoftmaxOp*>(sn.op.get());
+    if (!sm || sm->has_addend || sn.inputs.size() != 1 || sn.inputs[0] != nd.outputs[0]) continue;
+    sn.inputs = {nd.inputs[0], nd.inputs[1]};
+    sm->has_addend = true;
+    dead[i] = 1;
+    ++fused;
   }
   // dead operators become value-less placeholders (ids of other nodes must not shift)
   for (int32_t i = 0; i < n; ++i)

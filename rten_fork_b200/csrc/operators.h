@@ -142,6 +142,7 @@ class MatMulOp : public Operator {
 class SoftmaxOp : public Operator {
  public:
   int64_t axis = -1;
+  bool has_addend = false;  // GraphOptimizer: `Add -> Softmax` fused, the other Add operand is input 1
   const char* name() const override { return "Softmax"; }
   bool can_run_in_place() const override { return true; }
   rtg_status run(Context* ctx, const OpInputs& in, std::vector<Value>* out) override;

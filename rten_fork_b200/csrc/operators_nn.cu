@@ -74,7 +74,8 @@ __global__ void layer_norm_kernel(float* __restrict__ out, const float* __restri
 // kernels above re-read it two or three times with 4-byte loads and reached 1.1-1.3 TB/s.  MAXV = float4s per lane.
 template <int MAXV>
 __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ out, const float* __restrict__ in,
-                                                            int64_t rows, int len) {
+                                                            int64_t rows, int len, const float* __restrict__ addend,
+                                                            int64_t rows_per_addend) {
   const int lane = threadIdx.x & 31;
   const int nv = len >> 2;
   const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
@@ -82,6 +83,9 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ o
   for (int64_t r = warp; r < rows; r += nwarps) {
     const float4* x = reinterpret_cast<const float4*>(in + r * len);
     float4* y = reinterpret_cast<float4*>(out + r * len);
+    // fused `Add -> Softmax` (BERT's attention mask): row r adds row r / rows_per_addend of the addend, the same
+    // round-to-nearest add the separate operator performs
+    const float4* a = addend ? reinterpret_cast<const float4*>(addend + (r / rows_per_addend) * len) : nullptr;
     float4 v[MAXV];
     float m = __int_as_float(0xff800000);
 #pragma unroll
@@ -89,6 +93,11 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ o
       const int i = lane + 32 * k;
       if (i < nv) {
         v[k] = x[i];
+        if (a) {
+          const float4 t = __ldg(a + i);
+          v[k].x = __fadd_rn(v[k].x, t.x), v[k].y = __fadd_rn(v[k].y, t.y);
+          v[k].z = __fadd_rn(v[k].z, t.z), v[k].w = __fadd_rn(v[k].w, t.w);
+        }
         m = fmaxf(fmaxf(m, fmaxf(v[k].x, v[k].y)), fmaxf(v[k].z, v[k].w));
       }
     }
@@ -218,7 +227,11 @@ rtg_status make_contiguous(Context* ctx, const Value& v, Value* tmp, rtg_tensor*
 }  // namespace
 
 // ---------------------------------------------------------------- Softmax
-static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_attr, const rtg_tensor& y) {
+// `addend` (optional, fused Add -> Softmax): a contiguous f32 tensor of len-long rows, row r of x adds its row
+// r / rows_per_addend.  Only the rows kernel takes it; *fused_ok tells the caller whether it was applied.
+static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_attr, const rtg_tensor& y,
+                               const float* addend = nullptr, int64_t rows_per_addend = 1, bool* fused_ok = nullptr) {
+  if (fused_ok) *fused_ok = false;
   if (x.ndim == 0) return set_error(RTG_ERR_INVALID_VALUE, "Axis is invalid");
   int axis;
   RTG_TRY(resolve_axis(x.ndim, axis_attr, &axis));
@@ -231,13 +244,18 @@ static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_a
   float* yp = static_cast<float*>(y.data);
   const float* xp = static_cast<const float*>(x.data);
   const int grid = blocks_for(ctx, lanes * 32);
-  if (inner == 1 && len % 4 == 0 && len <= 2048 && aligned16(xp) && aligned16(yp)) {
+  if (inner == 1 && len % 4 == 0 && len <= 2048 && aligned16(xp) && aligned16(yp) && (!addend || aligned16(addend))) {
     const int L = static_cast<int>(len);
-    if (len <= 128) softmax_rows_kernel<1><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L);
-    else if (len <= 256) softmax_rows_kernel<2><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L);
-    else if (len <= 512) softmax_rows_kernel<4><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L);
-    else if (len <= 1024) softmax_rows_kernel<8><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L);
-    else softmax_rows_kernel<16><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L);
+    const float* ad = addend;
+    const int64_t rpa = rows_per_addend;
+    if (len <= 128) softmax_rows_kernel<1><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+    else if (len <= 256) softmax_rows_kernel<2><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+    else if (len <= 512) softmax_rows_kernel<4><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+    else if (len <= 1024) softmax_rows_kernel<8><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+    else softmax_rows_kernel<16><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+    if (fused_ok) *fused_ok = true;
+  } else if (addend) {
+    return RTG_OK;  // the caller adds first and comes back without the addend
   } else {
     softmax_kernel<<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, static_cast<int>(len), inner);
   }
@@ -246,16 +264,75 @@ static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_a
   return RTG_OK;
 }
 
+// Fused `Add -> Softmax` (GraphOptimizer, model.cu): which rows of `a` row r of `x` adds.  True when x has the
+// broadcast shape and `a` is contiguous with the shape [x's leading dims..., 1, ..., 1, len] (any number of leading dims,
+// including none): then rows_per_addend = the product of x's dims that a's ones stand for.
+static bool addend_rows(const rtg_tensor& x, const rtg_tensor& a, int axis, int64_t* rows_per_addend) {
+  if (a.dtype != RTG_F32 || x.dtype != RTG_F32 || axis != x.ndim - 1 || a.ndim > x.ndim || !is_contiguous(a)) return false;
+  const int off = x.ndim - a.ndim;
+  if (a.ndim == 0 || a.shape[a.ndim - 1] != x.shape[x.ndim - 1]) return false;
+  int k = 0;  // leading dims of x that `a` matches (dims x has and `a` lacks count as ones of `a`)
+  if (off == 0)
+    while (k < x.ndim - 1 && a.shape[k] == x.shape[k]) ++k;
+  int64_t rpa = 1;
+  for (int i = k; i < x.ndim - 1; ++i) {
+    if (i >= off && a.shape[i - off] != 1) return false;
+    rpa *= x.shape[i];
+  }
+  *rows_per_addend = rpa > 0 ? rpa : 1;
+  return true;
+}
+
 rtg_status SoftmaxOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* out) {
   const Value* x;
   RTG_TRY(in.require(0, &x));
   if (x->t.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
+  const Value* addend = has_addend ? in.get(1) : nullptr;
+  if (has_addend && !addend) return set_error(RTG_ERR_MISSING_INPUTS, "Missing inputs");
+  Value sum;  // the unfused Add, when the operands do not fit the fused kernel
+  if (addend) {
+    int ax = 0;
+    int64_t rpa = 1;
+    bool fits = resolve_axis(x->t.ndim, axis, &ax) == RTG_OK && is_contiguous(x->t);
+    const Value* big = x;
+    if (fits && !addend_rows(x->t, addend->t, ax, &rpa)) {
+      // Add is commutative: the mask may be the first operand
+      fits = resolve_axis(addend->t.ndim, axis, &ax) == RTG_OK && is_contiguous(addend->t) &&
+             addend_rows(addend->t, x->t, ax, &rpa);
+      if (fits) big = addend, addend = x;
+    }
+    if (fits) {
+      Value y;
+      RTG_TRY(alloc_value(ctx, RTG_F32, big->t.ndim, big->t.shape, false, &y));
+      bool fused_ok = false;
+      rtg_status st = softmax_impl(ctx, big->t, axis, y.t, static_cast<const float*>(addend->t.data), rpa, &fused_ok);
+      if (st == RTG_OK && fused_ok) {
+        out->push_back(y);
+        return RTG_OK;
+      }
+      release_value(ctx, &y);
+      if (st != RTG_OK) return st;
+    }
+    // general broadcast, other axes, unaligned rows: the two operators one after the other
+    const Value* other = in.get(1);
+    int64_t shape[RTG_MAX_DIMS];
+    int32_t nd;
+    RTG_TRY(binary_out_shape(&x->t, &other->t, shape, &nd));
+    RTG_TRY(alloc_value(ctx, RTG_F32, nd, shape, false, &sum));
+    rtg_status st = binary_forward(ctx, RTG_BIN_ADD, x->t, other->t, sum.t);
+    if (st != RTG_OK) {
+      release_value(ctx, &sum);
+      return st;
+    }
+    x = &sum;
+  }
   Value tmp, y;
   rtg_tensor xv;
-  RTG_TRY(make_contiguous(ctx, *x, &tmp, &xv));
-  rtg_status st = alloc_value(ctx, RTG_F32, xv.ndim, xv.shape, false, &y);
+  rtg_status st = make_contiguous(ctx, *x, &tmp, &xv);
+  if (st == RTG_OK) st = alloc_value(ctx, RTG_F32, xv.ndim, xv.shape, false, &y);
   if (st == RTG_OK) st = softmax_impl(ctx, xv, axis, y.t);
   release_value(ctx, &tmp);
+  release_value(ctx, &sum);
   if (st != RTG_OK) {
     release_value(ctx, &y);
     return st;
@@ -264,17 +341,31 @@ rtg_status SoftmaxOp::run(Context* ctx, const OpInputs& in, std::vector<Value>* 
   return RTG_OK;
 }
 
-rtg_status SoftmaxOp::run_in_place(Context* ctx, Value* io, const OpInputs&) {
+rtg_status SoftmaxOp::run_in_place(Context* ctx, Value* io, const OpInputs& rest) {
   if (io->t.dtype != RTG_F32) return set_error(RTG_ERR_INCORRECT_INPUT_TYPE, "Incorrect input type");
-  if (!is_contiguous(io->t)) {
+  const Value* addend = has_addend ? rest.get(0) : nullptr;
+  if (has_addend && !addend) return set_error(RTG_ERR_MISSING_INPUTS, "Missing inputs");
+  int ax = 0;
+  int64_t rpa = 1;
+  const bool fused_fits = addend && is_contiguous(io->t) && resolve_axis(io->t.ndim, axis, &ax) == RTG_OK &&
+                          addend_rows(io->t, addend->t, ax, &rpa);
+  if (!is_contiguous(io->t) || (addend && !fused_fits)) {
     OpInputs in;
     in.v = {io};
+    if (addend) in.v.push_back(addend);
     std::vector<Value> outs;
     RTG_TRY(run(ctx, in, &outs));
     release_value(ctx, io);
     *io = outs[0];
     return RTG_OK;
   }
+  io->host_f32.reset();
+  if (!addend) return softmax_impl(ctx, io->t, axis, io->t);
+  bool fused_ok = false;
+  RTG_TRY(softmax_impl(ctx, io->t, axis, io->t, static_cast<const float*>(addend->t.data), rpa, &fused_ok));
+  if (fused_ok) return RTG_OK;
+  // rows the fused kernel does not take (length not a multiple of four, ...): add in place, then the plain form
+  RTG_TRY(binary_forward(ctx, RTG_BIN_ADD, io->t, addend->t, io->t));
   return softmax_impl(ctx, io->t, axis, io->t);
 }
 

@@ -325,3 +325,36 @@ def test_matmul_residual_rides_in_the_epilogue(rtg, ctx, res_shape, with_bias):
     np.testing.assert_array_equal(got, want)
     ref = np.maximum(xin.astype(np.float64) @ w_arr.astype(np.float64) + (bias_arr if with_bias else 0) + rin, 0)
     np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("case", ["mask_b11s", "mask_first", "full_shape", "vector", "general_broadcast", "ragged_len",
+                                  "other_axis"])
+def test_add_softmax_is_one_kernel_with_the_same_bits(rtg, ctx, case):
+    """Add -> Softmax (BERT's attention mask): the add happens inside the Softmax kernel when the addend is [leading dims,
+    1, ..., 1, len] and the axis is the last one; every other form (general broadcast, row length not a multiple of four,
+    another axis) runs the two steps one after the other inside the same operator.  Optimised and unoptimised runs agree
+    bit for bit in every case, and both follow the oracle's Softmax (rten-vecmath/src/softmax.rs)."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+    import graph_oracle
+
+    rng = np.random.default_rng(11)
+    L = 10 if case == "ragged_len" else 16
+    xs = (2, 3, 8, L)
+    ms = {"mask_b11s": (2, 1, 1, L), "mask_first": (2, 1, 1, L), "full_shape": xs, "vector": (L,),
+          "general_broadcast": (3, 1, L), "ragged_len": (2, 1, 1, L), "other_axis": (2, 1, 1, L)}[case]
+    b = ModelBuilder()
+    x = b.add_value("x", list(xs))
+    m = b.add_value("m", list(ms))
+    b.inputs = [x, m]
+    s = b.op("Add", [m, x] if case == "mask_first" else [x, m], name="mask_add")
+    y = b.op("Softmax", [s], ("SoftmaxAttrs", [(0, "i32", 1 if case == "other_axis" else -1)]), name="softmax")
+    b.outputs = [y]
+    xin = (rng.random(xs, dtype=np.float32) - 0.5) * 8
+    min_ = np.where(rng.random(ms) < 0.3, np.float32(-10000.0), np.float32(0.0)).astype(np.float32)
+    fused, plain = _load(ctx, b), _load(ctx, b, optimize=False)
+    assert fused.num_ops == 1 and plain.num_ops == 2
+    got, want = fused.run([xin, min_])[0], plain.run([xin, min_])[0]
+    assert got.shape == xs
+    np.testing.assert_array_equal(got, want)
+    expect_equal(got, graph_oracle.run_graph(b, [xin, min_])[0], rtol=1e-5, atol=1e-7)
+
