@@ -376,7 +376,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // 2 row panels and every column panel (at 16384^3 the plain order re-reads all of B from HBM for every other m-tile).
   const int group_m = args.group_m;
   auto tile_mn = [&](int tile, int& mt, int& nt) {
-    if (group_m <= 0) {
+    if (n_tiles == 1) {  // one column of tiles (N <= BN, every MobileNet / most ResNet layers): no division
+      mt = tile;
+      nt = 0;
+    } else if (group_m <= 0) {
       mt = tile / n_tiles;
       nt = tile - mt * n_tiles;
     } else {
@@ -462,7 +465,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int ic_dil_h = args.ic.dil_h, ic_dil_w = args.ic.dil_w, ic_c_off = args.ic.c_off;
       const int ic_c_blocks = args.ic.c_blocks, ic_kw = args.ic.kw;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const int split = unit / num_tiles, tile = unit - split * num_tiles;
+        const int split = splits > 1 ? unit / num_tiles : 0, tile = unit - split * num_tiles;
         const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
         int tmt, tnt;
         tile_mn(tile, tmt, tnt);
@@ -612,7 +615,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t aph = 0;
       PROF_DECL;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+        const int kb_begin = (splits > 1 ? unit / num_tiles : 0) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
         for (int kb0 = kb_begin; kb0 < kb_end; kb0 += chunk_kb) {
           PROF_WAIT(0, ptx::mbar_wait(tempty_bar(as), aph ^ 1u));
           ptx::tc_fence_after();
@@ -696,7 +699,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     PROF_DECL;
     PROF_LINE_DECL;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-      const int split = unit / num_tiles, tile = unit - split * num_tiles;
+      const int split = splits > 1 ? unit / num_tiles : 0, tile = unit - split * num_tiles;
       const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
       int tmt, tnt;
       tile_mn(tile, tmt, tnt);
@@ -720,9 +723,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         m = st_r + lane;
         row_ok = m < args.M;
       }
-      int64_t d_base, r_base, d_cs, r_cs;
-      out_row_base(args.dmap, m, d_base, d_cs);
-      out_row_base(args.rmap, m, r_base, r_cs);
+      // element offsets of this row for the strided (non-TMA) output / residual paths; not needed when both are staged
+      int64_t d_base = 0, r_base = 0, d_cs = 1, r_cs = 1;
+      if (!staged_d) out_row_base(args.dmap, m, d_base, d_cs);
+      if (args.R != nullptr && !staged_r) out_row_base(args.rmap, m, r_base, r_cs);
       const float row_bias = (args.bias_mode == BIAS_ROW && row_ok) ? args.bias[m] : 0.f;
       const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 
@@ -921,7 +925,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int s = 0;
     uint32_t ph = 0;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-      const int split = unit / num_tiles, tile = unit - split * num_tiles;
+      const int split = splits > 1 ? unit / num_tiles : 0, tile = unit - split * num_tiles;
       const int kb_begin = split * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
       int tmt, tnt;
       tile_mn(tile, tmt, tnt);
@@ -958,7 +962,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       PROF_DECL;
       int total = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const int kb_begin = (unit / num_tiles) * kb_per_split;
+        const int kb_begin = (splits > 1 ? unit / num_tiles : 0) * kb_per_split;
         total += min(num_kb, kb_begin + kb_per_split) - kb_begin;
       }
       const int first = sw >> 2;  // the two warps of a lane quarter take alternate blocks of the CTA's flat k-block stream
@@ -1041,7 +1045,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int s = 0;
       uint32_t ph = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const int kb_begin = (unit / num_tiles) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
+        const int kb_begin = (splits > 1 ? unit / num_tiles : 0) * kb_per_split, kb_end = min(num_kb, kb_begin + kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           const uint32_t stage = ring_base + s * Cfg::kStageBytes;  // [B raw][B lo]
           ptx::mbar_wait_parked(full_bar(s), ph);
