@@ -72,7 +72,7 @@ __global__ void layer_norm_kernel(float* __restrict__ out, const float* __restri
 // Row-in-registers variants for contiguous rows (the BERT shapes: 128-element score rows, 768-element hidden rows): one
 // warp per row, the row is read once with 16-byte loads, kept in registers for the reductions and written once -- the
 // kernels above re-read it two or three times with 4-byte loads and reached 1.1-1.3 TB/s.  MAXV = float4s per lane.
-template <int MAXV>
+template <int MAXV, bool ADD>
 __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ out, const float* __restrict__ in,
                                                             int64_t rows, int len, const float* __restrict__ addend,
                                                             int64_t rows_per_addend) {
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ o
     float4* y = reinterpret_cast<float4*>(out + r * len);
     // fused `Add -> Softmax` (BERT's attention mask): row r adds row r / rows_per_addend of the addend, the same
     // round-to-nearest add the separate operator performs
-    const float4* a = addend ? reinterpret_cast<const float4*>(addend + (r / rows_per_addend) * len) : nullptr;
+    const float4* a = ADD ? reinterpret_cast<const float4*>(addend + (r / rows_per_addend) * len) : nullptr;
     float4 v[MAXV];
     float m = __int_as_float(0xff800000);
 #pragma unroll
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ o
       const int i = lane + 32 * k;
       if (i < nv) {
         v[k] = x[i];
-        if (a) {
+        if (ADD) {
           const float4 t = __ldg(a + i);
           v[k].x = __fadd_rn(v[k].x, t.x), v[k].y = __fadd_rn(v[k].y, t.y);
           v[k].z = __fadd_rn(v[k].z, t.z), v[k].w = __fadd_rn(v[k].w, t.w);
@@ -248,11 +248,17 @@ static rtg_status softmax_impl(Context* ctx, const rtg_tensor& x, int64_t axis_a
     const int L = static_cast<int>(len);
     const float* ad = addend;
     const int64_t rpa = rows_per_addend;
-    if (len <= 128) softmax_rows_kernel<1><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
-    else if (len <= 256) softmax_rows_kernel<2><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
-    else if (len <= 512) softmax_rows_kernel<4><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
-    else if (len <= 1024) softmax_rows_kernel<8><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
-    else softmax_rows_kernel<16><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);
+#define RTG_SOFTMAX_ROWS(V)                                                                      \
+  do {                                                                                           \
+    if (ad) softmax_rows_kernel<V, true><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa); \
+    else softmax_rows_kernel<V, false><<<grid, 256, 0, ctx->stream>>>(yp, xp, lanes, L, ad, rpa);   \
+  } while (0)
+    if (len <= 128) RTG_SOFTMAX_ROWS(1);
+    else if (len <= 256) RTG_SOFTMAX_ROWS(2);
+    else if (len <= 512) RTG_SOFTMAX_ROWS(4);
+    else if (len <= 1024) RTG_SOFTMAX_ROWS(8);
+    else RTG_SOFTMAX_ROWS(16);
+#undef RTG_SOFTMAX_ROWS
     if (fused_ok) *fused_ok = true;
   } else if (addend) {
     return RTG_OK;  // the caller adds first and comes back without the addend

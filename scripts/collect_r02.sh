@@ -12,4 +12,5 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm
 python scripts/ncu_summary.py gpurun_out/r02_gemm_full.ncu-rep 25 > gpurun_out/r02_gemm_full_summary.txt 2>&1
 timeout 900 python scripts/stress_race.py > gpurun_out/r02_stress.txt 2>&1
 cuobjdump -sass rten_fork_b200/librten_gpu.so 2>/dev/null | grep -E "UTCHMMA|UTCQMMA|UTMALDG|UTMASTG|UTCBAR|LDTM|STTM|UBLKCP" | awk '{print $2}' | sed 's/\..*//' | sort | uniq -c > gpurun_out/r02_sass_mnemonics.txt
+rm -f gpurun_out/r02_gemm_full.ncu-rep
 ls -la gpurun_out
