@@ -427,10 +427,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
     ptx::tmem_relinquish();
   }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  // Two setup barriers instead of one __syncthreads: the TMA producers (A stream; MODE 2: also the B stream's warp) need
+  // the mbarriers, not tensor memory, so they only meet warp 0 (named barrier 2) and issue their first loads while the
+  // TMEM allocation (~1 400 cycles after the CTA starts) is still under way; every other warp meets on named barrier 3
+  // as before.  The first loads' latency then overlaps the allocation instead of following it.
+  constexpr int kProducerWarps = MODE == 2 ? 2 : 1;
+  const bool is_producer = warp == kTmaWarp || (MODE == 2 && warp == kMmaWarp + 9);
+  uint32_t tmem_base = 0;
+  if (is_producer) {
+    asm volatile("bar.sync 2, %0;" ::"n"(32 * (1 + kProducerWarps)) : "memory");
+  } else {
+    if (warp == 0) asm volatile("bar.arrive 2, %0;" ::"n"(32 * (1 + kProducerWarps)) : "memory");
+    ptx::tc_fence_before();
+    asm volatile("bar.sync 3, %0;" ::"n"(Cfg::kThreads - 32 * kProducerWarps) : "memory");
+    ptx::tc_fence_after();
+    tmem_base = *tmem_slot_ptr;
+  }
   if (threadIdx.x == 0) PROF_MARK(2, 7);  // setup (barriers, TMEM allocation) done
   // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may run
   // while the previous kernel in the stream drains.  From here on global memory is read and written: wait for the
