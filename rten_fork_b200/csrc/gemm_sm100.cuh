@@ -288,6 +288,19 @@ static __device__ __noinline__ void epi_cold_store(const float* v, float* d, int
     _Pragma("unroll") for (int j_ = 0; j_ < 32; ++j_) v[j_] = t_[j_]; \
   } while (0)
 
+// two fp32 lanes per instruction (sm_100 FADD2 / FFMA2; lane-wise the same IEEE operations)
+__device__ __forceinline__ void epi_add2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 b, {%2, %3};\n\tadd.rn.f32x2 a, a, b;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void epi_fma2(float& a0, float& a1, float r0, float r1, float s) {  // a += r * s (fused)
+  asm("{\n\t.reg .b64 a, r, m;\n\tmov.b64 a, {%0, %1};\n\tmov.b64 r, {%2, %3};\n\tmov.b64 m, {%4, %4};\n\t"
+      "fma.rn.f32x2 a, r, m, a;\n\tmov.b64 {%0, %1}, a;\n\t}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(r0), "f"(r1), "f"(s));
+}
+
 // Relu / Clip inline, everything else out of line
 __device__ __forceinline__ void epi_act(float (&v)[32], int act, float lo, float hi, unsigned long long one2) {
   if (act == ACT_NONE) return;
@@ -795,7 +808,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 b4 = ptx::lds_v4(ebias + (c0 - col0 + 4 * j4) * 4);  // same address in every lane: broadcast
-            v[4 * j4 + 0] += b4.x, v[4 * j4 + 1] += b4.y, v[4 * j4 + 2] += b4.z, v[4 * j4 + 3] += b4.w;
+            epi_add2(v[4 * j4 + 0], v[4 * j4 + 1], b4.x, b4.y);
+            epi_add2(v[4 * j4 + 2], v[4 * j4 + 3], b4.z, b4.w);
           }
         }
         if (staged_d) {
@@ -810,10 +824,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4) {
               const float4 r = ptx::lds_v4(row + ((j4 ^ sw) << 4));
-              v[4 * j4 + 0] += args.beta * r.x;
-              v[4 * j4 + 1] += args.beta * r.y;
-              v[4 * j4 + 2] += args.beta * r.z;
-              v[4 * j4 + 3] += args.beta * r.w;
+              epi_fma2(v[4 * j4 + 0], v[4 * j4 + 1], r.x, r.y, args.beta);
+              epi_fma2(v[4 * j4 + 2], v[4 * j4 + 3], r.z, r.w, args.beta);
             }
           } else {
             PROF_LINE(2);
