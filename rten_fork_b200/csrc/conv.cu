@@ -237,7 +237,7 @@ static rtg_status launch_depthwise3x3_tma(Context* ctx, float* out, const float*
   // job streams: its output rows x stride, 2 halo rows, ~3 rows' worth of start-up); 4 CTAs fit an SM (126 registers x
   // 128 threads; the ring is <= 51 KB).  Pick the band count with the smallest estimate, at least 4 output rows per job.
   const int smem_bytes = kDwRing * t.row_bytes;
-  const int64_t per_sm = std::max<int64_t>(1, std::min<int64_t>(RTG_DW_MINB > 4 ? RTG_DW_MINB : 4, (227 * 1024) / (smem_bytes + 1024)));
+  const int64_t per_sm = std::max<int64_t>(1, std::min<int64_t>(4, (227 * 1024) / (smem_bytes + 1024)));
   static const int rows_env = [] { const char* e = std::getenv("RTG_DW_ROWS"); return e ? std::atoi(e) : 0; }();
   static const int pred_env = [] { const char* e = std::getenv("RTG_DW_PRED"); return e ? std::atoi(e) : 0; }();
   t.force_pred = pred_env;

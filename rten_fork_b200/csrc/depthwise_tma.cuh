@@ -36,13 +36,7 @@ struct DwTile {
   unsigned long long one2;  // (1.0f, 1.0f): see dw_tap
 };
 constexpr int kDwTX = 4;  // dw_taps below is written out for 4
-#ifndef RTG_DW_RING
-#define RTG_DW_RING 6
-#endif
-#ifndef RTG_DW_MINB
-#define RTG_DW_MINB 1
-#endif
-constexpr int kDwRing = RTG_DW_RING;
+constexpr int kDwRing = 6;  // row buffers per CTA (5 / 4 buffers with 5 / 6 CTAs per SM measured slower)
 constexpr int kDwThreads = 128;
 
 // Four channels of one tap: acc += x * w with the multiply and the add rounded separately, as the reference does, on
@@ -113,7 +107,7 @@ __device__ __forceinline__ void dw_taps(unsigned long long (&acc)[kDwTX][2], con
 // template parameter so that the shared-memory loads of a row use immediate offsets (runtime strides cost ~100 address
 // instructions per output row, a fifth of the loop).
 template <int STRIDE, int ACT, int CVS>
-__global__ void __launch_bounds__(kDwThreads, RTG_DW_MINB) depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tmX,
+__global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tmX,
                                                                        float* __restrict__ out,
                                                                        const float* __restrict__ wt,
                                                                        const float* __restrict__ bias, const DwGeom g,
