@@ -91,9 +91,23 @@ rtg_status check_batch_separable(const Graph& g) {
       ok = true;
     } else if (const MatMulOp* mm = dynamic_cast<const MatMulOp*>(op)) {
       if (mm->has_perm[0] || !batch[nd.inputs[0]] || !is_const(nd.inputs[1])) return refuse("is not activation x constant weights");
+      // a fused bias is a constant; a fused residual (input 3) is an activation of the same batch
+      for (size_t i = 2; i < nd.inputs.size(); ++i)
+        if (nd.inputs[i] >= 0 && !is_const(nd.inputs[i]) && !batch[nd.inputs[i]])
+          return refuse("mixes a per-batch value with a batch-free one");
       ok = true;
     } else if (const SoftmaxOp* sm = dynamic_cast<const SoftmaxOp*>(op)) {
       if (sm->axis == 0) return refuse("normalises over the batch dimension");
+      // a fused `Add -> Softmax` keeps the Add's rule for both operands
+      for (int32_t in : nd.inputs) {
+        if (in < 0) continue;
+        if (is_const(in)) {
+          const rtg_tensor& t = g.nodes[in].constant.t;
+          if (t.ndim >= 1 && t.shape[0] != 1 && t.ndim >= 4) return refuse("has a constant operand with a batch extent");
+        } else if (!batch[in]) {
+          return refuse("mixes a per-batch value with a batch-free one");
+        }
+      }
       ok = true;
     } else if (const LayerNormOp* ln = dynamic_cast<const LayerNormOp*>(op)) {
       if (ln->axis == 0) return refuse("normalises over the batch dimension");
