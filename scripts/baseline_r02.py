@@ -51,8 +51,8 @@ Peaks of this pool (MEASURED_PEAKS.json): HBM 6550.1 GB/s, bf16 1401.3 TF/s sust
 | C2 small batches (device-resident, graph replay) | - | batch 1: {b['small_batch']['1']['ms_per_step']:.3f} ms; batch 4: {b['small_batch']['4']['ms_per_step']:.3f} ms | - | - | launch-latency-bound |
 | C1 GEMM 1024^3 (`bench_gemm` rule, 125 back-to-back calls; in brackets: replayed from a CUDA graph) | - | {sw(1024, 'tf32_bf16x2', 'us')} us, {sw(1024, 'tf32_bf16x2')} TF/s ({sw(1024, 'tf32_bf16x2', 'graph_tflops')}) | {sw(1024, '3xtf32', 'us')} us, {sw(1024, '3xtf32')} TF/s ({sw(1024, '3xtf32', 'graph_tflops')}) | {sw(1024, 'tf32', 'us')} us, {sw(1024, 'tf32')} TF/s ({sw(1024, 'tf32', 'graph_tflops')}) | {g['1024']['tf32_bf16x2']['frac']:.2f} / {g['1024']['3xtf32']['frac']:.2f} / {g['1024']['tf32']['frac']:.2f} (64 tiles: launch-bound) |
 | C5 GEMM 512 / 2048 / 4096 / 8192 / 16384 cubed (one GPU, TF/s) | - | {sw(512, 'tf32_bf16x2')} / {sw(2048, 'tf32_bf16x2')} / {sw(4096, 'tf32_bf16x2')} / {sw(8192, 'tf32_bf16x2')} / {sw(16384, 'tf32_bf16x2')} | {sw(512, '3xtf32')} / {sw(2048, '3xtf32')} / {sw(4096, '3xtf32')} / {sw(8192, '3xtf32')} / {sw(16384, '3xtf32')} | {sw(512, 'tf32')} / {sw(2048, 'tf32')} / {sw(4096, 'tf32')} / {sw(8192, 'tf32')} / {sw(16384, 'tf32')} | 8192^3: {g['8192']['tf32_bf16x2']['frac']:.2f} / {g['8192']['3xtf32']['frac']:.2f} / {g['8192']['tf32']['frac']:.2f}; the fp32-accurate modes' ceiling is 0.5 / 0.33 (2 / 3 tensor passes per product); 16384^3 is power-limited |
-| C3 BERT-base encoder b64 s128 (`profiles/r02_configs.txt`) | - | **6.80 ms/step, 9 406 seq/s** (210 TF/s algorithmic; 151 launches; round 1: 10.5 ms; mid-round 9.83: `profiles/r02_configs_c3_after_residual_fusion.txt`) | - | - | - |
-| C4 MobileNetV2 b64 (`profiles/r02_configs.txt`) | - | **1.16 ms/step, 55 165 img/s** (59 launches; round 1: 2.03 ms; mid-round 1.33: `profiles/r02_configs_c4_after_clip.txt`) | - | - | depthwise 3x3: 4.55 TB/s stride 1, 5.82 TB/s stride 2 (0.69 / 0.89 of HBM) |
+| C3 BERT-base encoder b64 s128 (`profiles/r02_configs.txt`, launch list `profiles/r02_c3_launches_summary.txt`) | - | **6.80 ms/step, 9 406 seq/s** (210 TF/s algorithmic; 151 launches; round 1: 10.5 ms; mid-round 9.83: `profiles/r02_configs_c3_after_residual_fusion.txt`) | - | - | - |
+| C4 MobileNetV2 b64 (`profiles/r02_configs.txt`, launch list `profiles/r02_c4_launches_summary.txt`) | - | **1.16 ms/step, 55 165 img/s** (59 launches; round 1: 2.03 ms; mid-round 1.33: `profiles/r02_configs_c4_after_clip.txt`) | - | - | depthwise 3x3: 4.55 TB/s stride 1, 5.82 TB/s stride 2 (0.69 / 0.89 of HBM) |
 
 Speed-up of the headline over the CPU restatement on the same box: {e2e['value']:,.0f} / {cpu['value']:.1f} = **{e2e['value'] / cpu['value']:.0f}x end to end**
 ({b['value'] / cpu['value']:.0f}x device-resident).  The CPU figure is higher than round 1's 31 img/s because the restatement now runs
