@@ -358,3 +358,34 @@ def test_add_softmax_is_one_kernel_with_the_same_bits(rtg, ctx, case):
     np.testing.assert_array_equal(got, want)
     expect_equal(got, graph_oracle.run_graph(b, [xin, min_])[0], rtol=1e-5, atol=1e-7)
 
+
+@pytest.mark.parametrize("scale", [1.0, 12.0])
+def test_gelu_in_the_matmul_epilogue_has_the_standalone_kernels_bits(rtg, ctx, scale):
+    """MatMul -> Add(bias) -> Gelu: fused, the Gelu runs in the contraction kernel's epilogue on packed fp32 pairs
+    (vm_gelu_x2: FFMA2 / FMUL2, branch-free reciprocal); unfused, in the elementwise kernel with the scalar formula.  Same
+    IEEE operations lane by lane, so the two runs agree bit for bit — over pre-activations from tiny to far in both tails
+    (|x| > 10.2, where exp(-x^2) underflows), and both follow rten-vecmath's gelu (rten-vecmath/src/erf.rs:82-91)."""
+    from rten_fork_b200.rten_builder import ModelBuilder
+
+    rng = np.random.default_rng(17)
+    b = ModelBuilder()
+    x = b.add_value("x", ["b", 40, 64])
+    b.inputs = [x]
+    w_arr = ((rng.random((64, 160), dtype=np.float32) - 0.5) * scale).astype(np.float32)
+    bias_arr = ((rng.random(160, dtype=np.float32) - 0.5) * scale).astype(np.float32)
+    y = b.op("MatMul", [x, b.add_constant("w", w_arr)], name="dense")
+    y = b.op("Add", [y, b.add_constant("bias", bias_arr)], name="bias_add")
+    y = b.op("Gelu", [y], name="act")
+    b.outputs = [y]
+    xin = (rng.random((3, 40, 64), dtype=np.float32) - 0.5) * 2
+    fused, plain = _load(ctx, b), _load(ctx, b, optimize=False)
+    assert fused.num_ops == 1 and plain.num_ops == 3
+    got, want = fused.run([xin])[0], plain.run([xin])[0]
+    pre = xin.astype(np.float64) @ w_arr.astype(np.float64) + bias_arr
+    if scale > 1.0:
+        assert np.abs(pre).max() > 10.2 and (pre < -10.2).any()      # both saturated tails are exercised
+    np.testing.assert_array_equal(got, want)
+    from math import erf
+    ref = 0.5 * pre * (1.0 + np.vectorize(erf)(pre / np.sqrt(2.0)))
+    np.testing.assert_allclose(got, ref, rtol=2e-3, atol=2e-3 * max(1.0, scale))
+
