@@ -133,7 +133,8 @@ __global__ void __launch_bounds__(kDwThreads) depthwise3x3_tma_kernel(const __gr
   const int cv = tid % CVS, strip = tid / CVS;
   const int c0 = (cb * CVS + cv) << 2;
   const int ox0 = band * t.tw + strip * TX;
-  const bool active = c0 < g.c && ox0 < g.ow;
+  // (a shape whose strips x channel vectors do not fill the 128 threads leaves the last threads without a strip)
+  const bool active = c0 < g.c && ox0 < g.ow && strip * TX < t.tw;
   const int oy0 = rb * t.rows_per_job, oy1 = min(g.oh, oy0 + t.rows_per_job);
   const int iy0 = oy0 * STRIDE - g.pad_t;         // first input row of the job
   const int n_in = (oy1 - oy0 - 1) * STRIDE + 3;  // input rows the job reads

@@ -361,6 +361,9 @@ DW_CASES = [
     (2, 960, 7, 7, 1, (1, 1, 1, 1), "clip", True),        # 256-channel blocks, 8-column band
     (1, 8, 40, 3, 1, (2, 2, 2, 2), "none", False),        # padding wider than the kernel's reach
     (1, 64, 5, 300, 2, (1, 0, 0, 2), "clip", True),       # many column bands, stride 2
+    (2, 144, 56, 56, 1, (1, 1, 1, 1), "clip", True),      # MobileNetV2's 144-channel layers: 4.5 channel blocks
+    (1, 144, 56, 56, 2, (1, 1, 1, 1), "clip", True),
+    (1, 180, 9, 120, 1, (1, 1, 1, 1), "relu", True),      # two column bands, the last channel block partly empty
 ]
 
 
